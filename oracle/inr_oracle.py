@@ -1,0 +1,480 @@
+"""CPU ORACLE for the INR-fitting hot path -- TEST INFRASTRUCTURE, NOT PRODUCT CODE.
+
+A CPU restatement (torch-CPU fp32 for the floating-point training arithmetic, numpy float64 for the
+transform code) of what senyuanfan/inr-for-audio computes on the path named by BASELINE.json:
+
+    coords -> SIREN / KAN forward -> loss -> backward -> Adam (+ ReduceLROnPlateau)
+
+Only tests/, __graft_entry__.smoke() and bench.py's cpu_baseline / --impl reference legs may import it.
+The product path (inr_for_audio_b200/) never does; it fails loudly when the CUDA library is missing.
+
+Pinning status:
+  * SIREN, KAN, coords, KBD/MDCT/STMDCT/ISTMDCT, calculate_snr, Adam+plateau: PINNED -- checked against
+    outputs of the reference itself (imported unmodified in the build container by
+    tests/golden/make_golden.py) committed under tests/golden/, and against torch.optim for Adam.
+  * auraloss STFTLoss / SNRLoss (third-party, not vendored, no version pinned anywhere in the reference;
+    call sites run.py:126-128,160,165): PARITY UNPINNED -- restated from the published auraloss algorithm.
+  * MDCT-domain *loss* (BASELINE.json config 3): the reference has no such loss (mdct.py is numpy-only);
+    defined here as L1/MSE between STMDCT(model output) and STMDCT(target) using the reference's exact
+    framing/window/transform (mdct.py:51-72), mixed through run.py:163-169's alpha rule.  Its transform is
+    pinned (against mdct.STMDCT); the loss definition is ours.
+
+Every function cites the reference file:line it follows.
+"""
+from __future__ import annotations
+
+import math
+from typing import List, Optional, Sequence
+
+import numpy as np
+import torch
+import torch.nn.functional as F
+
+# --------------------------------------------------------------------------------------------------
+# A1. coordinates                                                             utils.py:99-109
+# --------------------------------------------------------------------------------------------------
+
+def linspace_f32(T: int, scale: float = 1.0) -> np.ndarray:
+    """Bit-exact restatement of torch.linspace(-scale, scale, T) in fp32 on CPU (utils.py:105).
+
+    torch's CPU kernel computes, in fp32, step = (end-start)/(T-1) and then
+        i <  T//2 : start + step*i         (one fused multiply-add)
+        i >= T//2 : end   - step*(T-1-i)   (one fused multiply-add)
+    Evaluated here in float64 and rounded once: the product of two fp32 values is exact in float64 and
+    the single float64 add followed by one rounding to fp32 equals the fp32 FMA except for double
+    rounding, which the golden test (tests/golden/coords.npz, every config's T) shows does not occur.
+    """
+    if T == 1:
+        return np.array([-scale], dtype=np.float32)
+    start = np.float32(-1 * scale)
+    end = np.float32(1 * scale)
+    step = np.float32((end - start) / np.float32(T - 1))
+    i = np.arange(T, dtype=np.int64)
+    half = T // 2
+    lo = np.float64(start) + np.float64(step) * i.astype(np.float32).astype(np.float64)
+    hi = np.float64(end) - np.float64(step) * (T - 1 - i).astype(np.float32).astype(np.float64)
+    return np.where(i < half, lo, hi).astype(np.float32)
+
+
+def get_coord(sidelen: int, dim: int = 2, scale: float = 1) -> torch.Tensor:
+    """utils.py:99-109 -- (sidelen**dim, dim) grid, 'ij' meshgrid, row-major flatten."""
+    axis = torch.from_numpy(linspace_f32(sidelen, scale))
+    tensors = tuple(dim * [axis])
+    coord = torch.stack(torch.meshgrid(*tensors, indexing="ij"), dim=-1)
+    return coord.reshape(-1, dim)
+
+
+def get_coord_2d(height: int, width: int) -> torch.Tensor:
+    """utils.py:382-403 (MDCTFitting): linspace(-1,1,height) x linspace(-1,1,width), 'ij', flattened."""
+    h = torch.from_numpy(linspace_f32(height))
+    w = torch.from_numpy(linspace_f32(width))
+    hg, wg = torch.meshgrid(h, w, indexing="ij")
+    return torch.stack((hg, wg), dim=-1).reshape(height * width, -1)
+
+
+def calculate_snr(original_signal, noisy_signal) -> float:
+    """utils.py:77-97."""
+    original_signal = np.asarray(original_signal)
+    noisy_signal = np.asarray(noisy_signal)
+    noise = noisy_signal - original_signal
+    return float(10 * np.log10(np.mean(original_signal ** 2) / np.mean(noise ** 2)))
+
+
+def normalise_waveform(data: np.ndarray) -> np.ndarray:
+    """utils.py:144-148 (WaveformFitting.__getitem__): amplitude / max|amplitude|, fp32."""
+    data = np.asarray(data, dtype=np.float32)
+    return (data / np.max(np.abs(data))).astype(np.float32)
+
+
+def synth(T: int, sr: int = 44100, seed: int = 0) -> np.ndarray:
+    """SURVEY.md §8(d) synthetic waveform: 32 tremolo'd partials + white noise, peak-normalised fp32."""
+    rng = np.random.default_rng(seed)
+    K = 32
+    t = np.arange(T, dtype=np.float64) / sr
+    f = np.exp(rng.uniform(np.log(55.0), np.log(8000.0), K))
+    amp = rng.uniform(0.5, 1.0, K) / (np.arange(1, K + 1) ** 0.7)
+    ph = rng.uniform(0, 2 * np.pi, K)
+    r = rng.uniform(0.1, 2.0, K)
+    phi = rng.uniform(0, 2 * np.pi, K)
+    x = np.zeros(T, dtype=np.float64)
+    for k in range(K):
+        x += amp[k] * 0.5 * (1 + np.sin(2 * np.pi * r[k] * t + phi[k])) * np.sin(2 * np.pi * f[k] * t + ph[k])
+    x += rng.normal(0.0, 1e-3, T)
+    x /= np.max(np.abs(x))
+    return x.astype(np.float32)
+
+
+# --------------------------------------------------------------------------------------------------
+# A3/A4. SIREN                                               models.py:84-120, 243-275, 306-394
+# --------------------------------------------------------------------------------------------------
+
+class SirenSpec:
+    """Shape of a sine-only SIREN: Siren(in,H,L,out,outermost_linear) == SirenWithSnakeTanh(num_sine=L)."""
+
+    def __init__(self, in_features=1, hidden_features=256, hidden_layers=3, out_features=1,
+                 outermost_linear=True, first_omega_0=30.0, hidden_omega_0=30.0):
+        self.in_features = in_features
+        self.hidden_features = hidden_features
+        self.hidden_layers = hidden_layers
+        self.out_features = out_features
+        self.outermost_linear = outermost_linear
+        self.first_omega_0 = first_omega_0
+        self.hidden_omega_0 = hidden_omega_0
+
+    def layer_dims(self):
+        H = self.hidden_features
+        dims = [(self.in_features, H)] + [(H, H)] * self.hidden_layers + [(H, self.out_features)]
+        return dims
+
+    def num_params(self):
+        return sum(i * o + o for i, o in self.layer_dims())
+
+
+def siren_init(spec: SirenSpec, seed: Optional[int] = None) -> List[torch.Tensor]:
+    """Parameters in state_dict order [W0,b0,W1,b1,...], consuming the CPU RNG exactly as the reference.
+
+    models.py:94-112: each SineLayer builds nn.Linear (default kaiming-uniform W, U(+-1/sqrt(in)) b draws)
+    and THEN overwrites W with U(+-1/in) (first) or U(+-sqrt(6/in)/omega) (hidden).
+    models.py:258-262: the final nn.Linear likewise, W overwritten with U(+-sqrt(6/H)/hidden_omega).
+    The bounds are computed in float64 by numpy exactly as the reference does.
+    """
+    if seed is not None:
+        torch.manual_seed(seed)
+    params: List[torch.Tensor] = []
+    dims = spec.layer_dims()
+    n = len(dims)
+    with torch.no_grad():
+        for li, (fin, fout) in enumerate(dims):
+            lin = torch.nn.Linear(fin, fout)
+            last = li == n - 1
+            if li == 0:
+                lin.weight.uniform_(-1 / fin, 1 / fin)
+            elif (not last) or True:
+                # hidden SineLayer, final nn.Linear (outermost_linear) and final SineLayer share the bound
+                bound = np.sqrt(6 / fin) / spec.hidden_omega_0
+                lin.weight.uniform_(-bound, bound)
+            params += [lin.weight.detach().clone(), lin.bias.detach().clone()]
+    return params
+
+
+def siren_forward(spec: SirenSpec, params: Sequence[torch.Tensor], coords: torch.Tensor) -> torch.Tensor:
+    """models.py:114-115 per layer: sin(omega_0 * linear(x)); final nn.Linear if outermost_linear."""
+    x = coords
+    n = len(params) // 2
+    for li in range(n):
+        W, b = params[2 * li], params[2 * li + 1]
+        z = F.linear(x, W, b)
+        if li == n - 1 and spec.outermost_linear:
+            x = z
+        else:
+            omega = spec.first_omega_0 if li == 0 else spec.hidden_omega_0
+            x = torch.sin(omega * z)
+    return x
+
+
+def time_loss(out: torch.Tensor, gt: torch.Tensor, loss_mode: str) -> torch.Tensor:
+    """run.py:124-125,161-169: nn.L1Loss / nn.MSELoss (mean over all elements) / auraloss SNRLoss."""
+    if loss_mode == "mae":
+        return torch.mean(torch.abs(out - gt))
+    if loss_mode == "snr":
+        return snr_loss(out.reshape(1, 1, -1), gt.reshape(1, 1, -1))
+    return torch.mean((out - gt) ** 2)
+
+
+# --------------------------------------------------------------------------------------------------
+# A7. Adam + ReduceLROnPlateau                         run.py:116-117,186-189; torch/optim/adam.py
+# --------------------------------------------------------------------------------------------------
+
+class AdamState:
+    def __init__(self, params, lr=1e-3, betas=(0.9, 0.999), eps=1e-8):
+        self.lr = lr
+        self.b1, self.b2 = betas
+        self.eps = eps
+        self.t = 0
+        self.m = [torch.zeros_like(p) for p in params]
+        self.v = [torch.zeros_like(p) for p in params]
+
+
+def adam_step(params: List[torch.Tensor], grads: Sequence[torch.Tensor], st: AdamState) -> None:
+    """torch.optim.Adam single-tensor math (torch 2.11 adam.py _single_tensor_adam), fp32 tensors and
+    float64 Python scalars for the bias corrections, in place."""
+    st.t += 1
+    bc1 = 1 - st.b1 ** st.t
+    bc2 = 1 - st.b2 ** st.t
+    step_size = st.lr / bc1
+    bc2_sqrt = bc2 ** 0.5
+    for p, g, m, v in zip(params, grads, st.m, st.v):
+        m.lerp_(g, 1 - st.b1)
+        v.mul_(st.b2).addcmul_(g, g, value=1 - st.b2)
+        denom = (v.sqrt() / bc2_sqrt).add_(st.eps)
+        p.addcdiv_(m, denom, value=-step_size)
+
+
+class PlateauState:
+    """torch.optim.lr_scheduler.ReduceLROnPlateau(mode='min', factor=0.8, patience=200, min_lr) with the
+    defaults threshold=1e-4 (rel), cooldown=0, eps=1e-8 (run.py:117)."""
+
+    def __init__(self, factor=0.8, patience=200, min_lr=1e-6, threshold=1e-4, eps=1e-8):
+        self.factor, self.patience, self.min_lr, self.threshold, self.eps = factor, patience, min_lr, threshold, eps
+        self.best = float("inf")
+        self.num_bad = 0
+
+    def step(self, loss: float, st: AdamState) -> None:
+        if loss < self.best * (1.0 - self.threshold):
+            self.best = loss
+            self.num_bad = 0
+        else:
+            self.num_bad += 1
+        if self.num_bad > self.patience:
+            new_lr = max(st.lr * self.factor, self.min_lr)
+            if st.lr - new_lr > self.eps:
+                st.lr = new_lr
+            self.num_bad = 0
+
+
+def siren_loss_and_grads(spec, params, coords, gt, loss_mode="mse", alpha=0.0, spec_loss=None):
+    """One evaluation of run.py:158-169 + 185: returns (loss, time_loss, grads) with autograd as the
+    restatement of loss.backward()."""
+    ps = [p.detach().clone().requires_grad_(True) for p in params]
+    out = siren_forward(spec, ps, coords)
+    tl = time_loss(out, gt, loss_mode)
+    if alpha != 0.0 and spec_loss is not None:
+        sl = spec_loss(out, gt)
+        loss = (1 - alpha) * tl + alpha * sl
+    else:
+        loss = (1 - alpha) * tl
+    grads = torch.autograd.grad(loss, ps)
+    return loss.detach(), tl.detach(), [g.detach() for g in grads], out.detach()
+
+
+def siren_fit(spec, params, coords, gt, total_steps, lr=1e-3, min_lr=1e-6, loss_mode="mse", alpha=0.0,
+              spec_loss=None, record=None):
+    """Line-for-line restatement of run.py:116-117 (Adam + plateau) and the loop run.py:156-190
+    (device-agnostic; the STFT term is skipped when alpha == 0 where it is numerically a no-op).
+    `params` is updated in place.  Returns the list of per-step losses (python floats)."""
+    st = AdamState(params, lr=lr)
+    sched = PlateauState(min_lr=min_lr)
+    losses = []
+    for step in range(total_steps):
+        loss, _, grads, _ = siren_loss_and_grads(spec, params, coords, gt, loss_mode, alpha, spec_loss)
+        lv = float(loss)
+        losses.append(lv)
+        if record is not None:
+            record(step, lv, params, grads, st)
+        adam_step(params, grads, st)
+        sched.step(lv, st)
+    return losses, st, sched
+
+
+# --------------------------------------------------------------------------------------------------
+# A10-A12. KBD window, MDCT, STMDCT, ISTMDCT          window.py:42-61, mdct.py:16-113
+# --------------------------------------------------------------------------------------------------
+
+def _i0(x):
+    from scipy.special import i0
+    return i0(x)
+
+
+def kbd_window(N: int, alpha: float = 4.0) -> np.ndarray:
+    """window.py:42-61 -- the window itself (float64), note the non-textbook N/2+1 (window.py:52-58)."""
+    n = np.arange(N)
+    n_a = n[0:N // 2 + 1]
+    n_b = n[N // 2:N]
+    KBW = _i0(np.pi * alpha * np.sqrt(1 - (((2 * n_a + 1) / (N / 2 + 1)) - 1) ** 2)) / _i0(np.pi * alpha)
+    KBW_sum = np.sum(KBW)
+    n_a = n[0:N // 2]
+    KBW = _i0(np.pi * alpha * np.sqrt(1 - (((2 * n_a + 1) / (N / 2 + 1)) - 1) ** 2)) / _i0(np.pi * alpha)
+    a = np.sqrt(np.cumsum(KBW) / KBW_sum)
+    b = a[N - n_b - 1]
+    return np.concatenate([a, b])
+
+
+def mdct_direct(x: np.ndarray, a: int, b: int) -> np.ndarray:
+    """mdct.py:16-42 by the definition it implements: X[k] = (2/N) sum_n x[n] cos(2pi/N (n+n0)(k+1/2)),
+    n0=(b+1)/2, k<N/2.  O(N^2), float64."""
+    N = a + b
+    n0 = (b + 1) / 2
+    n = np.arange(N)[None, :]
+    k = np.arange(N // 2)[:, None]
+    return (2.0 / N) * (np.cos(2 * np.pi / N * (n + n0) * (k + 0.5)) @ np.asarray(x, dtype=np.float64))
+
+
+def mdct_fft(x: np.ndarray, a: int, b: int) -> np.ndarray:
+    """mdct.py:25-42 (forward branch), FFT-based exactly as written."""
+    from scipy.fft import fft
+    N = a + b
+    n0 = (b + 1) / 2
+    n = np.arange(N)
+    k = np.arange(N // 2)
+    pre = np.exp(-1j * np.pi * n / N)
+    post = np.exp(-1j * 2 * np.pi * n0 * (k + 0.5) / N)
+    return (2 / N) * (fft(x * pre)[0:N // 2] * post).real
+
+
+def imdct_direct(X: np.ndarray, a: int, b: int) -> np.ndarray:
+    """mdct.py:29-35,46-48 by definition: x[n] = 2 sum_k X[k] cos(2pi/N (n+n0)(k+1/2))."""
+    N = a + b
+    n0 = (b + 1) / 2
+    n = np.arange(N)[:, None]
+    k = np.arange(N // 2)[None, :]
+    return 2.0 * (np.cos(2 * np.pi / N * (n + n0) * (k + 0.5)) @ np.asarray(X, dtype=np.float64))
+
+
+def stmdct_frames(length: int, N: int):
+    """mdct.py:54-58 framing rule: (halfN, pad_length, num_frames).  pad is a full half-frame when
+    length % halfN == 0; frame i covers padded[i*halfN : i*halfN+N]."""
+    halfN = N // 2
+    pad = halfN - (length % halfN)
+    return halfN, pad, length // halfN
+
+
+def stmdct(data: np.ndarray, N: int = 1024) -> np.ndarray:
+    """mdct.py:51-72 -> (N/2, num_frames) float64."""
+    data = np.asarray(data)
+    halfN, pad, F_ = stmdct_frames(len(data), N)
+    padded = np.pad(data, (0, pad), "constant", constant_values=(0, 0))
+    w = kbd_window(N)
+    out = np.zeros((halfN, F_))
+    for i in range(F_):
+        out[:, i] = mdct_fft(w * padded[i * halfN:i * halfN + N], halfN, halfN)
+    return out
+
+
+def istmdct(coefs: np.ndarray, N: int = 1024) -> np.ndarray:
+    """mdct.py:74-113: IMDCT + KBD window + overlap-add, trim the last half frame."""
+    halfN = N // 2
+    F_ = coefs.shape[1]
+    rec = np.zeros(halfN * F_ + halfN)
+    w = kbd_window(N)
+    for i in range(F_):
+        rec[i * halfN:i * halfN + N] += w * imdct_direct(coefs[:, i], halfN, halfN)
+    return rec[:halfN * F_]
+
+
+def mdct_basis(N: int, dtype=torch.float64) -> torch.Tensor:
+    """(N/2, N) matrix  (2/N) * cos(2pi/N (n+n0)(k+1/2)) * KBD[n]  so that coef[:, i] = B @ frame_i."""
+    halfN = N // 2
+    n0 = (halfN + 1) / 2
+    n = np.arange(N)[None, :]
+    k = np.arange(halfN)[:, None]
+    B = (2.0 / N) * np.cos(2 * np.pi / N * (n + n0) * (k + 0.5)) * kbd_window(N)[None, :]
+    return torch.from_numpy(B).to(dtype)
+
+
+def stmdct_torch(x: torch.Tensor, N: int = 2048, basis: Optional[torch.Tensor] = None) -> torch.Tensor:
+    """Differentiable restatement of mdct.STMDCT (mdct.py:51-72) for the MDCT-domain loss: x (T,) ->
+    (N/2, F).  Framing by unfold with hop N/2 on the tail-padded signal."""
+    T = x.shape[0]
+    halfN, pad, F_ = stmdct_frames(T, N)
+    if basis is None:
+        basis = mdct_basis(N, x.dtype)
+    padded = F.pad(x, (0, pad))
+    frames = padded.unfold(0, N, halfN)[:F_]  # (F, N)
+    return basis.to(x.dtype) @ frames.t()
+
+
+def mdct_loss(out: torch.Tensor, gt: torch.Tensor, N: int = 2048, kind: str = "l1") -> torch.Tensor:
+    """MDCT-domain loss (config 3): mean |STMDCT(out) - STMDCT(gt)| (or squared), see module header."""
+    basis = mdct_basis(N, out.dtype)
+    a = stmdct_torch(out.reshape(-1), N, basis)
+    b = stmdct_torch(gt.reshape(-1), N, basis)
+    d = a - b
+    return torch.mean(torch.abs(d)) if kind == "l1" else torch.mean(d * d)
+
+
+# --------------------------------------------------------------------------------------------------
+# A14. auraloss.freq.STFTLoss / auraloss.time.SNRLoss  -- PARITY UNPINNED (third-party, absent)
+# --------------------------------------------------------------------------------------------------
+
+def stft_mag(x: torch.Tensor, fft_size=1024, hop_size=256, win_length=1024, eps=1e-8) -> torch.Tensor:
+    """auraloss STFTLoss.stft: torch.stft(x, fft, hop, win, hann_window, return_complex=True)
+    (center=True, reflect pad), mag = sqrt(clamp(re^2+im^2, min=eps)).  x: (B, T)."""
+    win = torch.hann_window(win_length, dtype=x.dtype, device=x.device)
+    s = torch.stft(x, fft_size, hop_size, win_length, win, return_complex=True)
+    return torch.sqrt(torch.clamp(s.real ** 2 + s.imag ** 2, min=eps))
+
+
+def stft_loss(out: torch.Tensor, gt: torch.Tensor, fft_size=1024, hop_size=256, win_length=1024,
+              eps=1e-8) -> torch.Tensor:
+    """auraloss.freq.STFTLoss() defaults (w_sc=1, w_log_mag=1, w_lin_mag=0, w_phs=0, L1, mean):
+    ||Y-X||_F/||Y||_F + mean|log X - log Y|, X = |STFT(input)|, Y = |STFT(target)|.
+    Call site run.py:160: mrstft(model_output.view(1,1,-1), ground_truth.view(1,1,-1))."""
+    x = stft_mag(out.reshape(1, -1), fft_size, hop_size, win_length, eps)
+    y = stft_mag(gt.reshape(1, -1), fft_size, hop_size, win_length, eps)
+    sc = torch.norm(y - x, p="fro") / torch.norm(y, p="fro")
+    lm = torch.mean(torch.abs(torch.log(x) - torch.log(y)))
+    return sc + lm
+
+
+def snr_loss(out: torch.Tensor, gt: torch.Tensor, eps=1e-8) -> torch.Tensor:
+    """auraloss.time.SNRLoss(zero_mean=True, eps=1e-8, reduction='mean') on (B, C, T)."""
+    out = out - out.mean(dim=-1, keepdim=True)
+    gt = gt - gt.mean(dim=-1, keepdim=True)
+    res = out - gt
+    losses = 10 * torch.log10((gt ** 2).sum(-1) / ((res ** 2).sum(-1) + eps) + eps)
+    return -losses.mean()
+
+
+# --------------------------------------------------------------------------------------------------
+# A8/A9. efficient-kan                                                         kan.py:6-285
+# --------------------------------------------------------------------------------------------------
+
+def kan_grid(in_features: int, grid_size=5, spline_order=3, grid_range=(-1, 1)) -> torch.Tensor:
+    """kan.py:26-35: knots arange(-order, grid+order+1)*h + lo, expanded to (in, grid+2*order+1)."""
+    h = (grid_range[1] - grid_range[0]) / grid_size
+    g = torch.arange(-spline_order, grid_size + spline_order + 1) * h + grid_range[0]
+    return g.expand(in_features, -1).contiguous()
+
+
+def b_splines(x: torch.Tensor, grid: torch.Tensor, spline_order=3) -> torch.Tensor:
+    """kan.py:78-111 Cox-de Boor recursion, (B,in) -> (B,in,grid_size+order); half-open order-0 test."""
+    x = x.unsqueeze(-1)
+    bases = ((x >= grid[:, :-1]) & (x < grid[:, 1:])).to(x.dtype)
+    for k in range(1, spline_order + 1):
+        bases = ((x - grid[:, :-(k + 1)]) / (grid[:, k:-1] - grid[:, :-(k + 1)]) * bases[:, :, :-1]) + (
+            (grid[:, k + 1:] - x) / (grid[:, k + 1:] - grid[:, 1:(-k)]) * bases[:, :, 1:])
+    return bases.contiguous()
+
+
+def kan_curve2coeff(x, y, grid, spline_order=3):
+    """kan.py:113-143: batched least squares on CPU (driver gelsy)."""
+    A = b_splines(x, grid, spline_order).transpose(0, 1)
+    B = y.transpose(0, 1)
+    sol = torch.linalg.lstsq(A, B).solution
+    return sol.permute(2, 0, 1).contiguous()
+
+
+def kan_layer_init(fin, fout, grid_size=5, spline_order=3, scale_noise=0.1, scale_base=1.0, scale_spline=1.0):
+    """kan.py:56-76 reset_parameters, same RNG consumption order: base_weight kaiming, noise rand,
+    spline_scaler kaiming.  Returns dict(base_weight, spline_weight, spline_scaler, grid)."""
+    grid = kan_grid(fin, grid_size, spline_order)
+    base_weight = torch.empty(fout, fin)
+    torch.nn.init.kaiming_uniform_(base_weight, a=math.sqrt(5) * scale_base)
+    noise = (torch.rand(grid_size + 1, fin, fout) - 1 / 2) * scale_noise / grid_size
+    spline_weight = kan_curve2coeff(grid.T[spline_order:-spline_order], noise, grid, spline_order)
+    spline_scaler = torch.empty(fout, fin)
+    torch.nn.init.kaiming_uniform_(spline_scaler, a=math.sqrt(5) * scale_spline)
+    return dict(base_weight=base_weight, spline_weight=spline_weight, spline_scaler=spline_scaler, grid=grid)
+
+
+def kan_init(layers_hidden, seed=None, **kw):
+    if seed is not None:
+        torch.manual_seed(seed)
+    return [kan_layer_init(i, o, **kw) for i, o in zip(layers_hidden, layers_hidden[1:])]
+
+
+def kan_layer_forward(x, layer, spline_order=3):
+    """kan.py:153-166: SiLU(x) @ base_w^T + vec(B(x)) @ (spline_w * scaler[...,None]).view(out,-1)^T."""
+    shp = x.shape
+    x = x.reshape(-1, shp[-1])
+    base = F.linear(F.silu(x), layer["base_weight"])
+    sw = layer["spline_weight"] * layer["spline_scaler"].unsqueeze(-1)
+    spl = F.linear(b_splines(x, layer["grid"], spline_order).view(x.size(0), -1), sw.view(sw.size(0), -1))
+    return (base + spl).view(*shp[:-1], sw.size(0))
+
+
+def kan_forward(x, layers, spline_order=3):
+    """kan.py:274-279 with update_grid=False (the only mode run.py:158 uses)."""
+    for layer in layers:
+        x = kan_layer_forward(x, layer, spline_order)
+    return x
