@@ -1,0 +1,137 @@
+/* inr_b200.h -- C-ABI of the B200-native INR-fitting hot path (libinr_b200.so).
+ *
+ * The reference (senyuanfan/inr-for-audio) has no FFI: its seam is Python classes.
+ * Each entry point below replaces the reference code cited beside it; the Python host layer in
+ * inr_for_audio_b200/ binds them with ctypes (INTEGRATION.md shows the stub a reference maintainer adds).
+ *
+ * Conventions
+ *   - plain C: borrowed raw DEVICE pointers + sizes + a cudaStream_t passed as void*; no torch types.
+ *   - every function returns 0 on success, <0 on error (INR_E_*); inr_last_error() gives the message.
+ *   - the caller owns all buffers and keeps them alive until the stream work completes; all work is
+ *     enqueued on `stream` and is asynchronous; functions are re-entrant per stream.
+ *   - tensors are fp32, row-major, unless stated.  "flat params" is the concatenation of the model's
+ *     parameters in state_dict order (net.0.linear.weight, net.0.linear.bias, ..., models.py:248-269).
+ *   - there is NO CPU fallback: without a CUDA device every compute call returns INR_E_CUDA.
+ */
+#ifndef INR_B200_H
+#define INR_B200_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define INR_OK 0
+#define INR_E_BADARG (-1)
+#define INR_E_UNSUPPORTED (-2)
+#define INR_E_CUDA (-3)
+#define INR_E_WORKSPACE (-4)
+
+/* arithmetic of the hidden HxH contractions */
+#define INR_PREC_FP32 0 /* CUDA-core fp32 FMA (the parity mode: matches the fp32 reference to ~1e-6)   */
+#define INR_PREC_BF16 1 /* tcgen05 kind::f16 bf16 operands, fp32 TMEM accumulation (the fast mode)     */
+
+/* time-domain loss, run.py:124-125,161-169 */
+#define INR_LOSS_MSE 0
+#define INR_LOSS_MAE 1
+
+/* Shape of a sine-only SIREN: models.py:244-269 Siren(in,H,L,out,outermost_linear,first_omega_0,
+ * hidden_omega_0) == models.py:310-394 SirenWithSnakeTanh(num_sine=L, num_snake=0, num_tanh=0). */
+typedef struct {
+  int32_t in_features;     /* 1 (waveform) or 2 (MDCT image)                      */
+  int32_t hidden_features; /* H                                                   */
+  int32_t hidden_layers;   /* L = number of HxH SineLayers                        */
+  int32_t out_features;    /* must be 1                                           */
+  int32_t outermost_linear;/* 1: final nn.Linear; 0: final SineLayer              */
+  float first_omega_0;
+  float hidden_omega_0;
+  int32_t precision;       /* INR_PREC_*                                          */
+} inr_siren_desc;
+
+/* Optimiser + scheduler state, resident in DEVICE memory (no per-step host sync; the reference syncs
+ * 3-4x per step, run.py:171-187).  Initialise with inr_opt_init. */
+typedef struct {
+  float lr;            /* current learning rate                                    */
+  float min_lr;        /* ReduceLROnPlateau min_lr                                 */
+  float factor;        /* 0.8                                                      */
+  float threshold;     /* 1e-4 (rel)                                               */
+  float sched_eps;     /* 1e-8                                                     */
+  float beta1, beta2, adam_eps;
+  int32_t patience;    /* 200                                                      */
+  int32_t num_bad;     /* plateau counter                                          */
+  int32_t step;        /* number of optimiser steps taken (Adam's t)               */
+  int32_t hist_cap;    /* capacity of the loss-history ring (floats)               */
+  float best;          /* best loss seen by the scheduler                          */
+  float last_loss;     /* loss of the most recent step                             */
+  float step_size;     /* lr/(1-beta1^t) for the NEXT step, computed in float64    */
+  float bc2_sqrt;      /* sqrt(1-beta2^t) for the NEXT step, computed in float64   */
+  double loss_acc[4];  /* [0] time-loss numerator sum, [1] spectral loss, [2..3] scratch; zeroed per step */
+} inr_opt_state;
+
+const char* inr_last_error(void);
+int inr_version(void);
+
+/* Launch accounting: number of kernels this library has launched in this process (bench.py gpu_launches),
+ * and an event-based per-kernel timer: between inr_profile_begin and inr_profile_end every launch is bracketed
+ * by CUDA events on its stream; inr_profile_end synchronises the device and writes "tag,launches,total_ms\n"
+ * lines into buf (returns the full length).  Not usable during CUDA-graph capture. */
+int64_t inr_launch_count(void);
+int inr_profile_begin(void);
+int64_t inr_profile_end(char* buf, int64_t cap);
+
+/* number of floats in the flat parameter vector of `d` */
+int64_t inr_siren_num_params(const inr_siren_desc* d);
+
+/* bytes of scratch inr_siren_forward / inr_siren_loss_backward need for n rows (activations live here;
+ * rows are processed in chunks so the result is bounded) */
+int64_t inr_siren_workspace_bytes(const inr_siren_desc* d, int64_t n_rows, int training);
+
+/* utils.py:99-109 get_coord(sidelen, dim=1, scale): out[j] = linspace(-scale, scale, T_total)[i0 + j],
+ * j < n, BIT-EXACT with torch.linspace on CPU. */
+int inr_coords_linspace(float* out, int64_t i0, int64_t n, int64_t T_total, float scale, void* stream);
+
+/* utils.py:382-403 MDCTFitting 2-D grid: out[(r*W + c), :] = (lin(H)[r], lin(W)[c]) for flat index
+ * i0 <= r*W+c < i0+n. */
+int inr_coords_grid2d(float* out, int64_t i0, int64_t n, int64_t height, int64_t width, void* stream);
+
+/* models.py:271-275 / 388-394  Siren.forward:  out[n, 1] = net(coords).
+ * coords == NULL (in_features == 1 only): row j uses linspace(-scale,scale,T_total)[i0 + j] generated in
+ * the kernel (0 HBM bytes).  Otherwise coords is (n, in_features). */
+int inr_siren_forward(const inr_siren_desc* d, const float* params, const float* coords, int64_t n,
+                      int64_t i0, int64_t T_total, float coord_scale, float* out, void* workspace,
+                      int64_t workspace_bytes, void* stream);
+
+/* run.py:158-169 + 185: forward, loss = weight * reduce(out, target), and backward to the flat gradient.
+ *   grads (P floats)  += d loss / d params      (ACCUMULATES: zero it, or let inr_adam_step re-zero it)
+ *   opt->loss_acc[0]  += sum_j (out-target)^2 or |out-target|   (caller divides by count)
+ * grad_scale = weight / count  ( (1-alpha)/T_total for the mean losses of run.py:163-169 ).
+ * out_or_null receives the forward output when non-NULL.
+ * extra_gout_or_null: optional (n) upstream gradient added to d loss/d out (spectral losses). */
+int inr_siren_loss_backward(const inr_siren_desc* d, const float* params, const float* coords,
+                            const float* target, int64_t n, int64_t i0, int64_t T_total, float coord_scale,
+                            int loss_kind, float grad_scale, const float* extra_gout_or_null,
+                            float* grads, inr_opt_state* opt, float* out_or_null, void* workspace,
+                            int64_t workspace_bytes, void* stream);
+
+/* torch.optim.Adam(lr) + ReduceLROnPlateau('min', 0.8, 200, min_lr), run.py:116-117,186-189.
+ * inr_opt_init writes a fresh state to device memory. */
+int inr_opt_init(inr_opt_state* opt_dev, float lr, float min_lr, int32_t hist_cap, void* stream);
+
+/* One optimiser step on P params: Adam update with the state's lr, then the plateau scheduler fed with
+ *   loss = loss_acc[0] * loss_scale + loss_acc[1]
+ * then step += 1, loss_hist[step % hist_cap] = loss, loss_acc zeroed, grads zeroed. */
+int inr_adam_step(float* params, float* grads, float* m, float* v, int64_t P, inr_opt_state* opt,
+                  float loss_scale, float* loss_hist, void* stream);
+
+/* Fused single-GPU step = inr_siren_loss_backward + inr_adam_step (run.py:158-189), graph-capturable. */
+int inr_siren_fit_step(const inr_siren_desc* d, float* params, float* grads, float* m, float* v,
+                       const float* coords, const float* target, int64_t n, int64_t i0, int64_t T_total,
+                       float coord_scale, int loss_kind, float alpha, inr_opt_state* opt, float* loss_hist,
+                       void* workspace, int64_t workspace_bytes, void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* INR_B200_H */

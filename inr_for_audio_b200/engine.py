@@ -1,0 +1,245 @@
+"""Host-side engine of the SIREN fit path: owns the flat device buffers and drives libinr_b200.so.
+
+SirenFitter replaces the reference's hot loop (run.py:156-190): one `step()` = forward + loss + backward +
+Adam + ReduceLROnPlateau, entirely on the device (the loss history is read back on demand, not per step).
+Single-GPU steps are captured once into a CUDA graph and replayed; with torch.distributed initialised and
+`shard=True` the coordinates are sharded by rank and one sum-allreduce of [grads | loss] runs between the
+backward and the optimiser.
+"""
+from __future__ import annotations
+
+import ctypes as C
+import math
+from dataclasses import dataclass
+from typing import Optional
+
+import numpy as np
+import torch
+
+from . import _lib as L
+
+
+@dataclass
+class SirenSpec:
+    """Shape of a sine-only SIREN (models.py:244-269 / 310-394 with num_snake = num_tanh = 0)."""
+    in_features: int = 1
+    hidden_features: int = 256
+    hidden_layers: int = 3
+    out_features: int = 1
+    outermost_linear: bool = True
+    first_omega_0: float = 30.0
+    hidden_omega_0: float = 30.0
+
+    def desc(self, precision="fp32") -> L.SirenDesc:
+        prec = L.PRECISIONS[precision] if isinstance(precision, str) else int(precision)
+        return L.SirenDesc(self.in_features, self.hidden_features, self.hidden_layers, self.out_features,
+                           int(bool(self.outermost_linear)), float(self.first_omega_0), float(self.hidden_omega_0), prec)
+
+    def layer_shapes(self):
+        H = self.hidden_features
+        return [(H, self.in_features)] + [(H, H)] * self.hidden_layers + [(self.out_features, H)]
+
+    def num_params(self) -> int:
+        return sum(o * i + o for o, i in self.layer_shapes())
+
+    def flops_per_coord(self) -> int:
+        """fwd + bwd dense flops per coordinate, SURVEY.md §8(d): 6 L H^2 + 10 H."""
+        return 6 * self.hidden_layers * self.hidden_features ** 2 + 10 * self.hidden_features
+
+
+def _require_cuda(t: torch.Tensor, what: str):
+    if not t.is_cuda:
+        raise L.InrLibraryError("%s must live on a CUDA device: the INR hot path has no CPU fallback" % what)
+
+
+class Workspace:
+    """Grow-only scratch buffer handed to the C ABI."""
+
+    def __init__(self, device):
+        self.device = device
+        self.buf: Optional[torch.Tensor] = None
+
+    def get(self, desc: L.SirenDesc, n_rows: int, training: bool) -> torch.Tensor:
+        need = L.check(L.lib().inr_siren_workspace_bytes(C.byref(desc), n_rows, int(training)))
+        if self.buf is None or self.buf.numel() < need:
+            self.buf = torch.empty(max(int(need), 256), dtype=torch.uint8, device=self.device)
+        return self.buf
+
+
+def siren_forward(desc: L.SirenDesc, params: torch.Tensor, coords: Optional[torch.Tensor], n: int, ws: Workspace,
+                  i0: int = 0, T_total: int = 0, scale: float = 1.0, out: Optional[torch.Tensor] = None) -> torch.Tensor:
+    """models.py:271-275 through inr_siren_forward.  coords None -> generated in-kernel (in_features == 1)."""
+    _require_cuda(params, "params")
+    if out is None:
+        out = torch.empty(n, dtype=torch.float32, device=params.device)
+    buf = ws.get(desc, n, False)
+    L.check(L.lib().inr_siren_forward(C.byref(desc), L.ptr(params), L.ptr(coords), n, i0, T_total, scale, L.ptr(out),
+                                      L.ptr(buf), buf.numel(), L.stream_ptr()))
+    return out
+
+
+class SirenFitter:
+    """Device-resident fit of one SIREN to one target signal.
+
+    params0: flat fp32 parameter vector in state_dict order (CPU or CUDA; copied).
+    target:  (T_local,) fp32 on the device -- this rank's shard when sharded.
+    coords:  None -> linspace(-scale, scale, T_total)[i0 : i0+T_local] generated in the kernels (bit-exact with
+             utils.py:99-109), else (T_local, in_features) on the device.
+    """
+
+    def __init__(self, spec: SirenSpec, params0: torch.Tensor, target: torch.Tensor, coords: Optional[torch.Tensor] = None,
+                 *, i0: int = 0, T_total: Optional[int] = None, coord_scale: float = 1.0, loss_mode: str = "mse",
+                 lr: float = 1e-3, min_lr: float = 1e-6, alpha: float = 0.0, precision: str = "fp32",
+                 hist_cap: int = 65536, process_group=None, use_graph: bool = True):
+        _require_cuda(target, "target")
+        self.spec = spec
+        self.device = target.device
+        self.desc = spec.desc(precision)
+        self.precision = precision
+        self.P = spec.num_params()
+        assert params0.numel() == self.P, (params0.numel(), self.P)
+        self.target = target.reshape(-1).contiguous().float()
+        self.n = self.target.numel()
+        self.i0 = int(i0)
+        self.T_total = int(T_total if T_total is not None else self.n)
+        self.coord_scale = float(coord_scale)
+        self.coords = None if coords is None else coords.reshape(self.n, spec.in_features).contiguous().float()
+        if loss_mode not in ("mse", "mae"):
+            raise ValueError("loss_mode %r: the device path implements 'mse' and 'mae' (run.py:161-169)" % loss_mode)
+        self.loss_kind = L.LOSS_MSE if loss_mode == "mse" else L.LOSS_MAE
+        self.alpha = float(alpha)
+        self.pg = process_group
+        self.world = torch.distributed.get_world_size(process_group) if process_group is not None else 1
+        dev = self.device
+        # one arena: [params | grads | m | v], each padded to 64 floats so every block is 256-byte aligned
+        self.Ppad = (self.P + 63) // 64 * 64
+        self.arena = torch.zeros(4 * self.Ppad, dtype=torch.float32, device=dev)
+        self.params = self.arena[0:self.P]
+        self.grads = self.arena[self.Ppad:self.Ppad + self.P]
+        self.m = self.arena[2 * self.Ppad:2 * self.Ppad + self.P]
+        self.v = self.arena[3 * self.Ppad:3 * self.Ppad + self.P]
+        self.params.copy_(params0.reshape(-1).to(dev, torch.float32))
+        self.hist_cap = int(hist_cap)
+        self.loss_hist = torch.zeros(self.hist_cap, dtype=torch.float32, device=dev)
+        self.opt = torch.zeros((L.OPT_STATE_BYTES + 7) // 8 * 8, dtype=torch.uint8, device=dev)
+        self.loss_acc = self.opt[L.OPT_LOSS_ACC_OFFSET:L.OPT_LOSS_ACC_OFFSET + 32].view(torch.float64)
+        L.check(L.lib().inr_opt_init(L.ptr(self.opt), lr, min_lr, self.hist_cap, L.stream_ptr()))
+        self.ws = Workspace(dev)
+        self.ws.get(self.desc, self.n, True)
+        self.steps_done = 0
+        self.use_graph = bool(use_graph) and self.world == 1
+        self._graph = None
+        self.launches_per_step = None
+
+    # -- one step -------------------------------------------------------------------------------
+    def _w(self):
+        return 1.0 - self.alpha
+
+    def _enqueue_backward(self, extra_gout=None, out=None):
+        buf = self.ws.get(self.desc, self.n, True)
+        L.check(L.lib().inr_siren_loss_backward(
+            C.byref(self.desc), L.ptr(self.params), L.ptr(self.coords), L.ptr(self.target), self.n, self.i0,
+            self.T_total, self.coord_scale, self.loss_kind, self._w() / float(self.T_total), L.ptr(extra_gout),
+            L.ptr(self.grads), L.ptr(self.opt), L.ptr(out), L.ptr(buf), buf.numel(), L.stream_ptr()))
+
+    def _enqueue_adam(self):
+        L.check(L.lib().inr_adam_step(L.ptr(self.params), L.ptr(self.grads), L.ptr(self.m), L.ptr(self.v), self.P,
+                                      L.ptr(self.opt), self._w() / float(self.T_total), L.ptr(self.loss_hist),
+                                      L.stream_ptr()))
+
+    def _enqueue_step(self):
+        self._enqueue_backward()
+        if self.world > 1:
+            torch.distributed.all_reduce(self.grads, group=self.pg)
+            torch.distributed.all_reduce(self.loss_acc, group=self.pg)
+        self._enqueue_adam()
+
+    def step(self, n_steps: int = 1):
+        """run.py:158-189, n_steps times, no host synchronisation."""
+        if self.use_graph and self._graph is None:
+            # warm the allocator / module load outside capture, on a side stream as torch requires
+            s = torch.cuda.Stream(device=self.device)
+            s.wait_stream(torch.cuda.current_stream(self.device))
+            with torch.cuda.stream(s):
+                g = torch.cuda.CUDAGraph()
+                with torch.cuda.graph(g, stream=s):
+                    self._enqueue_step()
+            torch.cuda.current_stream(self.device).wait_stream(s)
+            self._graph = g
+        for _ in range(n_steps):
+            if self._graph is not None:
+                self._graph.replay()
+            else:
+                self._enqueue_step()
+        self.steps_done += n_steps
+
+    # -- state hand-off ---------------------------------------------------------------------------
+    def set_opt(self, **fields):
+        """Overwrite fields of the device optimiser state (lr, step, num_bad, best ...); the bias-correction
+        scalars for the next step are recomputed in float64 exactly as the device does."""
+        st = self.opt_state()
+        for k, v in fields.items():
+            setattr(st, k, v)
+        t = st.step + 1
+        st.step_size = float(st.lr) / (1.0 - float(st.beta1) ** t)
+        st.bc2_sqrt = math.sqrt(1.0 - float(st.beta2) ** t)
+        raw = np.frombuffer(bytes(st), dtype=np.uint8).copy()
+        self.opt[:raw.size].copy_(torch.from_numpy(raw).to(self.device))
+
+    def load_adam_state(self, osd: dict):
+        """Load a torch.optim.Adam.state_dict() (run.py:84-106 resume): exp_avg / exp_avg_sq / step / lr."""
+        o, step = 0, 0
+        shapes = self.spec.layer_shapes()
+        sizes = [s for oi in shapes for s in (oi[0] * oi[1], oi[0])]
+        for i, n in enumerate(sizes):
+            ent = osd["state"].get(i)
+            if ent is not None:
+                self.m[o:o + n].copy_(ent["exp_avg"].reshape(-1).to(self.device, torch.float32))
+                self.v[o:o + n].copy_(ent["exp_avg_sq"].reshape(-1).to(self.device, torch.float32))
+                step = int(ent["step"])
+            o += n
+        lr = float(osd["param_groups"][0]["lr"]) if osd.get("param_groups") else self.last_lr()
+        self.set_opt(step=step, lr=lr)
+
+    # -- read-backs (synchronising) -------------------------------------------------------------
+    def opt_state(self) -> L.OptState:
+        raw = self.opt.cpu().numpy().tobytes()
+        return L.OptState.from_buffer_copy(raw[:L.OPT_STATE_BYTES])
+
+    def losses(self) -> np.ndarray:
+        """Per-step losses of the steps done so far (the last hist_cap of them), as run.py:171 would print."""
+        n = self.steps_done
+        h = self.loss_hist.cpu().numpy()
+        if n <= self.hist_cap:
+            return h[:n].copy()
+        idx = np.arange(n - self.hist_cap, n) % self.hist_cap
+        return h[idx]
+
+    def last_lr(self) -> float:
+        return float(self.opt_state().lr)
+
+    def forward(self, coords: Optional[torch.Tensor] = None, n: Optional[int] = None, i0: Optional[int] = None,
+                T_total: Optional[int] = None) -> torch.Tensor:
+        """Model output at this fitter's own coordinates (default) or at the given ones."""
+        if coords is None and n is None:
+            coords, n, i0, T_total = self.coords, self.n, self.i0, self.T_total
+        elif coords is not None:
+            coords = coords.reshape(-1, self.spec.in_features).contiguous().float()
+            n, i0, T_total = coords.shape[0], 0, coords.shape[0]
+        return siren_forward(self.desc, self.params, coords, int(n), self.ws, int(i0 or 0), int(T_total or n),
+                             self.coord_scale)
+
+    def loss_and_grads(self, extra_gout: Optional[torch.Tensor] = None):
+        """One forward+backward without the optimiser: (loss, flat grads clone, output) -- teacher-forced tests."""
+        self.grads.zero_()
+        self.loss_acc.zero_()
+        out = torch.empty(self.n, dtype=torch.float32, device=self.device)
+        self._enqueue_backward(extra_gout, out)
+        if self.world > 1:
+            torch.distributed.all_reduce(self.grads, group=self.pg)
+            torch.distributed.all_reduce(self.loss_acc, group=self.pg)
+        loss = float(self.loss_acc[0].item()) * self._w() / float(self.T_total)
+        g = self.grads.clone()
+        self.grads.zero_()
+        self.loss_acc.zero_()
+        return loss, g, out

@@ -1,0 +1,161 @@
+"""Drop-in for the reference's run.py fitting entry point: train(...) with the same signature and return value
+(run.py:30-400).  The hot loop (run.py:156-190) runs on the device through engine.SirenFitter -- forward,
+loss, backward, Adam and ReduceLROnPlateau without a per-step host sync -- instead of PyTorch eager ops.
+
+Out of scope here: plots, loss landscapes, librosa-based comparison figures.  The artefacts
+kept are output.wav, saved_ckpt.pt (same keys as the reference: model_state_dict + torch.optim.Adam-format
+optimizer_state_dict) and parameters.json.
+"""
+from __future__ import annotations
+
+import json
+import os
+import time
+
+import numpy as np
+import torch
+from scipy.io import wavfile
+
+from . import mdct
+from .engine import SirenFitter
+from .models import SirenWithSnakeTanh
+from .utils import MDCTFitting, WaveformFitting, calculate_snr, get_coord
+
+
+def save_parameters(experiment_folder, **kwargs):
+    """run.py:25-28."""
+    with open(f"{experiment_folder}/parameters.json", "w") as file:
+        json.dump(kwargs, file, indent=4)
+
+
+def _adam_state_dict(model, fitter: SirenFitter, lr: float):
+    """torch.optim.Adam.state_dict() layout so that checkpoints interchange with the reference (run.py:357-363)."""
+    state, o = {}, 0
+    names = list(model.state_dict().keys())
+    step = float(fitter.opt_state().step)
+    for i, (_, p) in enumerate(model.named_parameters()):
+        n = p.numel()
+        state[i] = {"step": torch.tensor(step), "exp_avg": fitter.m[o:o + n].view(p.shape).clone(),
+                    "exp_avg_sq": fitter.v[o:o + n].view(p.shape).clone()}
+        o += n
+    group = {"lr": fitter.last_lr(), "betas": (0.9, 0.999), "eps": 1e-8, "weight_decay": 0, "amsgrad": False,
+             "maximize": False, "foreach": None, "capturable": False, "differentiable": False, "fused": None,
+             "decoupled_weight_decay": False, "params": list(range(len(names)))}
+    return {"state": state, "param_groups": [group]}
+
+
+def train(experiment_path: str, tag: str, inst: str, duration: int, num_channels=1, method='wave', arch='mlp',
+          loss_mode='mse', mode=None, decimation=1, bwe=False, num_hidden_features=256, num_sine=2, num_snake=2,
+          num_tanh=0, num_freq=None, omega=22000, first_linear=False, last_linear=True, hidden_omega=30,
+          a_initial=0.5, total_steps=20000, learning_rate=1e-3, min_learning_rate=1e-6, alpha=0.0,
+          prev_ckpt_path=None, visualization=False, *, precision='fp32', data_dir='data', seed=None, verbose=True):
+    """run.py:30.  Extra keyword-only arguments: precision ('fp32' CUDA-core parity mode | 'bf16' tcgen05 mode),
+    data_dir (the reference hard-codes 'data/'), seed (torch.manual_seed before model construction)."""
+    filename = f'{data_dir}/{inst}.wav'
+    experiment_folder = f'{experiment_path}/{inst}-{method}-{tag}'
+    while os.path.exists(experiment_folder):
+        tag = tag + '(2)'
+        experiment_folder = f'{experiment_path}/{inst}-{method}-{tag}'
+    os.makedirs(experiment_folder)
+    decimation = int(decimation)
+    takelog = False
+    if arch == 'kan':
+        raise NotImplementedError("arch='kan' goes through inr_for_audio_b200.kan (KAN fit path)")
+    if num_freq is not None:
+        raise NotImplementedError("num_freq (rff Gaussian encoding, run.py:141-144) is SURVEY.md §8(f)-4, not built")
+    if alpha != 0.0:
+        raise NotImplementedError("alpha != 0 needs the spectral-loss path (use SirenFitter with a spectral loss)")
+
+    if method == 'wave':
+        input_data = WaveformFitting(filename, duration=duration, decimation=decimation, verbose=verbose)
+        input_dimension = 1
+        target_np = input_data.normalised()
+        coords = None                                   # generated in-kernel, bit-exact with get_coord(T, 1)
+    elif method == 'mdct':
+        N = 2048
+        takelog = mode == 'log'
+        input_data = MDCTFitting(filename, duration=duration, N=N, takelog=takelog, verbose=verbose)
+        input_dimension = 2
+        target_np = np.ascontiguousarray(input_data.pixels.reshape(-1), dtype=np.float32)
+        coords = input_data.coords
+    else:
+        raise ValueError('specify the correct fitting method as wave or mdct')
+
+    if seed is not None:
+        torch.manual_seed(seed)
+    model = SirenWithSnakeTanh(in_features=input_dimension, out_features=1, hidden_features=num_hidden_features,
+                               num_sine=num_sine, num_snake=num_snake, num_tanh=num_tanh, num_freq=num_freq,
+                               first_linear=first_linear, last_linear=last_linear, first_omega_0=omega,
+                               hidden_omega_0=hidden_omega, a_initial=a_initial)
+    model.precision = precision
+    checkpoint = None
+    if prev_ckpt_path is not None:
+        checkpoint = torch.load(prev_ckpt_path, map_location='cpu')
+        model.load_state_dict(checkpoint['model_state_dict'])
+    model.cuda()
+    dev = model.flat_parameters().device
+
+    target = torch.from_numpy(target_np).to(dev)
+    fitter = SirenFitter(model.spec, model.flat_parameters(), target,
+                         None if coords is None else coords.to(dev), loss_mode=loss_mode, lr=learning_rate,
+                         min_lr=min_learning_rate, alpha=alpha, precision=precision,
+                         hist_cap=max(int(total_steps), 1))
+    if checkpoint is not None and checkpoint.get('optimizer_state_dict'):
+        fitter.load_adam_state(checkpoint['optimizer_state_dict'])
+
+    start_time = time.time()
+    fitter.step(int(total_steps))
+    torch.cuda.synchronize(dev)
+    total_time = (time.time() - start_time) / 60
+    loss_hist = fitter.losses()
+    losses = [float(10 * np.log10(l + 1e-10)) for l in loss_hist]       # run.py:180-182
+    if verbose and len(loss_hist):
+        print("final loss %.6g (best %.6g at step %d), lr %.3g, %.2f min" % (
+            loss_hist[-1], loss_hist.min(), int(loss_hist.argmin()), fitter.last_lr(), total_time))
+
+    # best_model is an alias of model in the reference (run.py:173): the "best" weights are the final ones
+    with torch.no_grad():
+        model.flat_parameters().copy_(fitter.params)
+    param_size = sum(p.nelement() * p.element_size() for p in model.parameters())
+    buffer_size = sum(b.nelement() * b.element_size() for b in model.buffers())
+    model_size = (param_size + buffer_size) / 1024
+
+    if bwe and method == 'wave':
+        n_bwe = input_data.original_sample_rate * duration
+        final = fitter.forward(n=n_bwe, i0=0, T_total=n_bwe)
+        recover_sample_rate = input_data.original_sample_rate
+    else:
+        final = fitter.forward()
+        recover_sample_rate = input_data.sample_rate
+    if takelog:
+        final = torch.exp(final)
+    final_np = final.detach().cpu().numpy().astype(np.float32)
+
+    savename = f'{experiment_folder}/output.wav'
+    if method == 'wave':
+        wavfile.write(savename, int(recover_sample_rate), final_np.reshape(-1))
+        snr_final = float(calculate_snr(target_np, final_np)) if not bwe else float('nan')
+    else:
+        spec = final_np.reshape(input_data.height, input_data.width) * input_data.scale + input_data.mean - input_data.shift
+        if takelog:
+            spec = np.exp(spec)
+        rec = mdct.ISTMDCT(spec, N=N).astype(np.float32)
+        wavfile.write(savename, int(input_data.sample_rate), rec)
+        ref = input_data.data.numpy()
+        n = min(len(ref), len(rec))
+        snr_final = float(calculate_snr(ref[:n], rec[:n]))
+
+    ckpt_path = f'{experiment_folder}/saved_ckpt.pt'
+    torch.save({'model_state_dict': {k: v.detach().cpu().clone() for k, v in model.state_dict().items()},
+                'optimizer_state_dict': _adam_state_dict(model, fitter, learning_rate)}, ckpt_path)
+    save_parameters(experiment_folder, experiment_path=experiment_path, tag=tag, inst=inst, duration=duration,
+                    num_channels=num_channels, method=method, arch=arch, loss_mode=loss_mode, mode=mode,
+                    decimation=decimation, bwe=bwe, num_hidden_features=num_hidden_features, num_sine=num_sine,
+                    num_snake=num_snake, num_tanh=num_tanh, num_freq=num_freq, omega=omega, hidden_omega=hidden_omega,
+                    a_initial=a_initial, total_steps=total_steps, learning_rate=learning_rate,
+                    min_learning_rate=min_learning_rate, alpha=alpha, prev_ckpt_path=prev_ckpt_path,
+                    curr_ckpt_path=ckpt_path, visualization=visualization, precision=precision,
+                    **{'parameter_size(KB)': param_size / 1024, 'total_model_size(KB)': model_size,
+                       'total_trainig_time(min)': total_time, 'SNR': snr_final,
+                       'final_loss_dB': losses[-1] if losses else None})
+    return ckpt_path

@@ -1,0 +1,122 @@
+"""Host-side logic on the CPU: the C-ABI library loads and exports every declared symbol, the drop-in classes
+reproduce the reference's seeded init / state_dict layout, and the data-prep code matches the golden vectors."""
+import ctypes
+import hashlib
+import os
+import re
+
+import numpy as np
+import pytest
+import torch
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+def sha(a):
+    return hashlib.sha256(np.ascontiguousarray(a).tobytes()).hexdigest()
+
+
+@pytest.fixture(scope="module")
+def built():
+    from inr_for_audio_b200 import build
+    return build.build()
+
+
+def test_library_exports_every_declared_symbol(built):
+    hdr = open(os.path.join(ROOT, "include", "inr_b200.h")).read()
+    hdr = re.sub(r"/\*.*?\*/", "", hdr, flags=re.S)
+    names = set(re.findall(r"\b(inr_[a-z0-9_]+)\s*\(", hdr))
+    assert len(names) >= 10
+    lib = ctypes.CDLL(built)
+    for n in sorted(names):
+        assert hasattr(lib, n), "missing export %s" % n
+    from inr_for_audio_b200 import _lib as L
+    assert set(L.SIGNATURES) == names, (set(L.SIGNATURES) ^ names)
+    assert L.lib().inr_version() >= 100
+
+
+def test_opt_state_struct_matches_header(built):
+    from inr_for_audio_b200 import _lib as L
+    assert L.OPT_STATE_BYTES == 96 and L.OPT_LOSS_ACC_OFFSET == 64
+    assert ctypes.sizeof(L.SirenDesc) == 32
+
+
+def test_no_cpu_fallback():
+    import inr_for_audio_b200 as P
+    from inr_for_audio_b200 import _lib as L
+    m = P.Siren(1, 16, 1, 1, True)
+    with pytest.raises(L.InrLibraryError):
+        m(torch.zeros(1, 4, 1))
+    with pytest.raises(L.InrLibraryError):
+        P.SirenFitter(m.spec, m.flat_parameters(), torch.zeros(8))
+
+
+def test_seeded_init_and_state_dict_match_reference(golden):
+    import inr_for_audio_b200 as P
+    g = golden("siren")
+    torch.manual_seed(0)
+    m = P.Siren(1, 256, 3, 1, True)
+    assert list(m.state_dict().keys()) == [str(k) for k in g["sd_keys_256x3"]]
+    h = hashlib.sha256()
+    for k, v in m.state_dict().items():
+        h.update(k.encode()); h.update(np.ascontiguousarray(v.numpy()).tobytes())
+    assert h.hexdigest() == str(g["sd_hash_256x3_seed0"])
+    torch.manual_seed(0)
+    m2 = P.SirenWithSnakeTanh(1, 1, 256, 3, 0, 0)
+    h = hashlib.sha256()
+    for k, v in m2.state_dict().items():
+        h.update(k.encode()); h.update(np.ascontiguousarray(v.numpy()).tobytes())
+    assert h.hexdigest() == str(g["sd_hash_swst_256x3_seed0"])
+    assert m.spec.num_params() == int(g["nparams_256x3"])
+    torch.manual_seed(0)
+    m3 = P.Siren(1, 512, 5, 1, True)
+    assert m3.spec.num_params() == int(g["nparams_512x5"])
+    # flat buffer is the state_dict order concatenation and parameters are live views of it
+    flat = m.flat_parameters()
+    assert torch.equal(flat, torch.cat([v.reshape(-1) for v in m.state_dict().values()]))
+    flat[0] = 123.0
+    assert m.net[0].linear.weight[0, 0].item() == 123.0
+    torch.manual_seed(4)
+    m4 = P.SirenWithSnakeTanh(1, 1, 64, 2, 0, 0, first_omega_0=22000, hidden_omega_0=30)
+    assert np.array_equal(m4.flat_parameters().numpy(), g["m3_p0"])
+    sd = m4.state_dict()
+    m5 = P.SirenWithSnakeTanh(1, 1, 64, 2, 0, 0)
+    m5.load_state_dict(sd)
+    assert torch.equal(m5.flat_parameters(), m4.flat_parameters())
+
+
+def test_utils_and_mdct_host_match_reference(golden):
+    import inr_for_audio_b200 as P
+    from inr_for_audio_b200 import mdct, window
+    gc, gm = golden("coords"), golden("mdct")
+    assert np.array_equal(P.get_coord(5, 2).numpy(), gc["coord2d_5"])
+    assert np.array_equal(P.get_coord(17, 1, 100).numpy(), gc["coord_scale100_17"])
+    np.testing.assert_allclose(window.KBDWindow(np.ones(2048)), gm["kbd_2048"], rtol=0, atol=1e-15)
+    np.testing.assert_allclose(window.KBDWindow(np.ones(256)), gm["kbd_256"], rtol=0, atol=1e-15)
+    np.testing.assert_allclose(mdct.MDCT(gm["frame"], 1024, 1024), gm["mdct_frame"], atol=1e-13)
+    np.testing.assert_allclose(mdct.IMDCT(gm["mdct_frame"], 1024, 1024), gm["imdct_frame"], atol=1e-11)
+    for key, n, N in (("stmdct_2048", 10000, 2048), ("stmdct_256", 5000, 256), ("stmdct_256_div", 5120, 256)):
+        out = mdct.STMDCT(gm["sig"][:n], N)
+        assert out.shape == gm[key].shape
+        np.testing.assert_allclose(out, gm[key], atol=1e-13)
+    np.testing.assert_allclose(mdct.ISTMDCT(gm["stmdct_256"], 256), gm["istmdct_256"], atol=1e-12)
+    for Lh, F in zip(gm["frame_lens"], gm["frame_counts_2048"]):
+        assert mdct.frame_plan(int(Lh), 2048)[2] == int(F)
+    ds = P.MDCTFitting(os.path.join(ROOT, "data", "gt_bach.wav"), duration=2, N=2048, takelog=False, verbose=False)
+    assert [ds.height, ds.width] == list(gm["mf_shape"])
+    assert sha(ds.coords.numpy()) == str(gm["mf_coords_sha"])
+    np.testing.assert_allclose(ds.pixels[:64].ravel(), gm["mf_pixels_head"], atol=2e-6)
+    x = np.sin(np.arange(1000) / 7.0)
+    assert abs(P.calculate_snr(x, x + 0.01) - 10 * np.log10(np.mean(x ** 2) / 1e-4)) < 1e-9
+
+
+def test_waveform_dataset_matches_reference_rule():
+    import inr_for_audio_b200 as P
+    ds = P.WaveformFitting(os.path.join(ROOT, "data", "gt_bach.wav"), duration=6, verbose=False)
+    assert ds.get_num_samples() == 264600 and ds.sample_rate == 44100
+    c, a = ds[0]
+    assert c.shape == (264600, 1) and a.shape == (264600, 1)
+    assert float(a.abs().max()) == 1.0
+    assert np.array_equal(ds.normalised(), a.numpy().ravel())
+    ds2 = P.WaveformFitting(os.path.join(ROOT, "data", "gt_bach.wav"), duration=2, decimation=2, verbose=False)
+    assert ds2.get_num_samples() == 44100 and ds2.sample_rate == 22050
