@@ -131,6 +131,15 @@ int inr_siren_fit_step(const inr_siren_desc* d, float* params, float* grads, flo
                        float coord_scale, int loss_kind, float alpha, inr_opt_state* opt, float* loss_hist,
                        void* workspace, int64_t workspace_bytes, void* stream);
 
+/* ---- test hooks for the tcgen05 kernels (tests/test_tc_gpu.py): one layer GEMM / one dW GEMM on row-major fp32
+ * inputs; `variant` bit 0 / bit 1 swap the LBO/SBO descriptor strides of operand A / B (convention probe). */
+int64_t inr_dbg_tc_scratch_bytes(int H, int64_t rows);
+int inr_dbg_tc_layer(int H, int mode, const float* A, const float* W, const float* bias, float omega,
+                     const float* Cin, float* out0, float* out1, int64_t rows, int variant, void* scratch,
+                     int64_t scratch_bytes, void* stream);
+int inr_dbg_tc_dw(int H, const float* dZ, const float* S, float* gW, int64_t rows, int variant, void* scratch,
+                  int64_t scratch_bytes, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

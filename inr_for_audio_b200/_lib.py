@@ -56,6 +56,9 @@ SIGNATURES = {
     "inr_adam_step": (_i, [_p, _p, _p, _p, _i64, _p, _f, _p, _p]),
     "inr_siren_fit_step": (_i, [C.POINTER(SirenDesc), _p, _p, _p, _p, _p, _p, _i64, _i64, _i64, _f, _i, _f, _p, _p,
                                 _p, _i64, _p]),
+    "inr_dbg_tc_scratch_bytes": (_i64, [_i, _i64]),
+    "inr_dbg_tc_layer": (_i, [_i, _i, _p, _p, _p, _f, _p, _p, _p, _i64, _i, _p, _i64, _p]),
+    "inr_dbg_tc_dw": (_i, [_i, _p, _p, _p, _i64, _i, _p, _i64, _p]),
 }
 
 _lib = None

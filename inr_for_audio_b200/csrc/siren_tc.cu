@@ -1,11 +1,496 @@
-// siren_tc.cu -- bf16 tcgen05 SIREN path (placeholder until the tcgen05 kernels land; returns UNSUPPORTED).
-#include "common.cuh"
+// siren_tc.cu -- the bf16 tensor-core SIREN fit path (INR_PREC_BF16): host orchestration + the streaming kernels
+// around the tcgen05 GEMMs of tc_gemm.cuh.  All activations live in HBM as bf16 "tile images" (tc_common.cuh).
+//
+//   per step and row chunk (DESIGN.md "bf16 path"):
+//     k_tc_pack        fp32 master weights -> bf16 UMMA operand images W_l (fwd) and W_l^T (dX)      once per call
+//     k_tc_first       S_0, C_0 = sincos(omega_0 (W_0 x + b_0))      fp32, accurate sincosf (models.py:114-115)
+//     k_tc_layer<FWD>  S_l, C_l = sincos(omega (S_{l-1} W_l^T + b_l))                               l = 1..L
+//     k_tc_last        out = S_L w + b; loss; g = dloss/dout; dZ_L = g w omega C_L (over C_L); g -> gvec
+//     k_tc_dw          gW_l += dZ_l^T S_{l-1}                                                       l = L..1
+//     k_tc_layer<BWD>  dZ_{l-1} = (dZ_l W_l) omega C_{l-1}  (over C_{l-1})                          l = L..1
+//     k_tc_colsum      gb_l += colsum(dZ_l); gw_out += gvec^T S_L; gW_0 += dZ_0^T x, gb_0 += colsum(dZ_0)
+#include "tc_gemm.cuh"
+
 namespace inr {
-bool siren_tc_supported(const inr_siren_desc*) { return false; }
-int64_t siren_tc_workspace_bytes(const inr_siren_desc*, int64_t, int) { return INR_E_UNSUPPORTED; }
-int siren_tc_forward(const inr_siren_desc*, const float*, const float*, int64_t, int64_t, int64_t, float, float*, void*,
-                     int64_t, cudaStream_t) { set_error("bf16 path not built"); return INR_E_UNSUPPORTED; }
-int siren_tc_loss_backward(const inr_siren_desc*, const float*, const float*, const float*, int64_t, int64_t, int64_t,
-                           float, int, float, const float*, float*, inr_opt_state*, float*, void*, int64_t,
-                           cudaStream_t) { set_error("bf16 path not built"); return INR_E_UNSUPPORTED; }
+using namespace tc;
+
+// ------------------------------------------------------------------------------------------------ pack
+__global__ void __launch_bounds__(256) k_tc_pack(const float* __restrict__ params, SirenLayout lay, int NS,
+                                                 __nv_bfloat16* __restrict__ Wf, __nv_bfloat16* __restrict__ Wb) {
+  const int H = lay.H;
+  const int64_t per = (int64_t)H * H;
+  const int64_t total = per * lay.L;
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
+    const int l = (int)(i / per);
+    const int rem = (int)(i - (int64_t)l * per);
+    const int o = rem / H, in = rem - o * H;
+    const __nv_bfloat16 w = __float2bfloat16_rn(params[lay.w_off(l + 1) + rem]);
+    // forward operand: B[n = out][k = in]
+    Wf[(int64_t)l * per + (int64_t)(o / NS) * ((int64_t)H * NS) + ((int64_t)(in >> 3) * NS + (o % NS)) * 8 + (in & 7)] = w;
+    // dX operand: B[n = in][k = out]
+    Wb[(int64_t)l * per + (int64_t)(in / NS) * ((int64_t)H * NS) + ((int64_t)(o >> 3) * NS + (in % NS)) * 8 + (o & 7)] = w;
+  }
+}
+
+// ------------------------------------------------------------------------------------------------ first layer
+// one thread = one row x one feature group (8 features); consecutive threads = consecutive rows of a tile
+__global__ void __launch_bounds__(256) k_tc_first(const float* __restrict__ W, const float* __restrict__ B,
+                                                  const float* __restrict__ coords, int in, int H, int64_t rows,
+                                                  int64_t rows_pad, int64_t g0, int64_t T_total, float scale,
+                                                  float omega, __nv_bfloat16* __restrict__ S0,
+                                                  __nv_bfloat16* __restrict__ C0) {
+  const int groups = H >> 3;
+  const int64_t total = rows_pad * groups;
+  for (int64_t idx = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; idx < total; idx += (int64_t)gridDim.x * blockDim.x) {
+    const int r = (int)(idx & (TILE_ROWS - 1));
+    const int64_t tg = idx >> 7;
+    const int kg = (int)(tg % groups);
+    const int64_t tile = tg / groups;
+    int64_t row = tile * TILE_ROWS + r;
+    if (row >= rows) row = rows - 1;   // pad rows replicate the last row: finite values, zero gradient later
+    float x0, x1 = 0.f;
+    if (coords) {
+      x0 = coords[row * in];
+      if (in == 2) x1 = coords[row * in + 1];
+    } else {
+      x0 = linspace_at(g0 + row, T_total, scale);
+    }
+    uint32_t so[4], co[4];
+#pragma unroll
+    for (int h = 0; h < 4; ++h) {
+      float s[2], c[2];
+#pragma unroll
+      for (int u = 0; u < 2; ++u) {
+        const int f = kg * 8 + h * 2 + u;
+        const float z = (in == 1) ? __fmaf_rn(x0, W[f], B[f]) : (__fmaf_rn(x1, W[f * 2 + 1], x0 * W[f * 2]) + B[f]);
+        sincosf(omega * z, &s[u], &c[u]);
+      }
+      so[h] = pack_bf16x2(s[0], s[1]);
+      co[h] = pack_bf16x2(c[0], c[1]);
+    }
+    const int64_t off = idx * 8;   // == ((tile*groups + kg)*128 + r)*8
+    *reinterpret_cast<uint4*>(S0 + off) = make_uint4(so[0], so[1], so[2], so[3]);
+    if (C0) *reinterpret_cast<uint4*>(C0 + off) = make_uint4(co[0], co[1], co[2], co[3]);
+  }
+}
+
+// ------------------------------------------------------------------------------------------------ last layer
+// one thread = one row; block = 128 threads = one tile
+__global__ void __launch_bounds__(128) k_tc_last(const __nv_bfloat16* __restrict__ S, __nv_bfloat16* __restrict__ CdZ,
+                                                 const float* __restrict__ w, const float* __restrict__ bptr,
+                                                 const float* __restrict__ target, const float* __restrict__ extra_g,
+                                                 int64_t rows, int num_tiles, int H, float omega_prev, float omega_hidden,
+                                                 int outermost_linear, int loss_kind, float grad_scale,
+                                                 float* __restrict__ gvec, float* __restrict__ gb,
+                                                 double* __restrict__ loss_acc, float* __restrict__ out, int training) {
+  extern __shared__ float s_w[];   // H floats
+  __shared__ double s_red[4];
+  __shared__ float s_gb[4];
+  for (int i = threadIdx.x; i < H; i += blockDim.x) s_w[i] = w[i];
+  __syncthreads();
+  const int groups = H >> 3;
+  const float bias = bptr[0];
+  const int r = threadIdx.x;
+  double loss_local = 0.0;
+  float gb_local = 0.f;
+  for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
+    const int64_t row = (int64_t)tile * TILE_ROWS + r;
+    const size_t tile_off = (size_t)tile * (TILE_ROWS * (size_t)H);
+    float dot = 0.f;
+    for (int kg = 0; kg < groups; ++kg) {
+      const uint4 u = *reinterpret_cast<const uint4*>(S + tile_off + ((size_t)kg * TILE_ROWS + r) * 8);
+      const uint32_t uw[4] = {u.x, u.y, u.z, u.w};
+#pragma unroll
+      for (int h = 0; h < 4; ++h) {
+        const float2 f = unpack_bf16x2(uw[h]);
+        dot = __fmaf_rn(f.x, s_w[kg * 8 + 2 * h], dot);
+        dot = __fmaf_rn(f.y, s_w[kg * 8 + 2 * h + 1], dot);
+      }
+    }
+    const float z = dot + bias;
+    float o = z, dact = 1.f;
+    if (!outermost_linear) {
+      float sn, cs;
+      sincosf(omega_hidden * z, &sn, &cs);
+      o = sn;
+      dact = omega_hidden * cs;
+    }
+    const bool valid = row < rows;
+    if (out && valid) out[row] = o;
+    if (!training) continue;
+    float g = 0.f;
+    if (valid) {
+      if (target) {
+        const float diff = o - target[row];
+        if (loss_kind == INR_LOSS_MAE) {
+          loss_local += (double)fabsf(diff);
+          g = grad_scale * ((diff > 0.f) ? 1.f : ((diff < 0.f) ? -1.f : 0.f));
+        } else {
+          loss_local += (double)diff * (double)diff;
+          g = grad_scale * 2.f * diff;
+        }
+      }
+      if (extra_g) g += extra_g[row];
+      g *= dact;
+    }
+    gb_local += g;
+    gvec[(int64_t)tile * TILE_ROWS + r] = g;
+    const float gw = g * omega_prev;
+    for (int kg = 0; kg < groups; ++kg) {
+      __nv_bfloat16* cp = CdZ + tile_off + ((size_t)kg * TILE_ROWS + r) * 8;
+      const uint4 u = *reinterpret_cast<const uint4*>(cp);
+      const uint32_t uw[4] = {u.x, u.y, u.z, u.w};
+      uint32_t ow[4];
+#pragma unroll
+      for (int h = 0; h < 4; ++h) {
+        const float2 f = unpack_bf16x2(uw[h]);
+        ow[h] = pack_bf16x2(gw * s_w[kg * 8 + 2 * h] * f.x, gw * s_w[kg * 8 + 2 * h + 1] * f.y);
+      }
+      *reinterpret_cast<uint4*>(cp) = make_uint4(ow[0], ow[1], ow[2], ow[3]);
+    }
+  }
+  if (!training) return;
+  loss_local = warp_sum(loss_local);
+  gb_local = warp_sum(gb_local);
+  if ((threadIdx.x & 31) == 0) { s_red[threadIdx.x >> 5] = loss_local; s_gb[threadIdx.x >> 5] = gb_local; }
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    if (target) atomicAdd(loss_acc, s_red[0] + s_red[1] + s_red[2] + s_red[3]);
+    atomicAdd(gb, s_gb[0] + s_gb[1] + s_gb[2] + s_gb[3]);
+  }
+}
+
+// ------------------------------------------------------------------------------------------------ column sums
+// out_plain[f] += sum_r X[r][f]          (bias gradients)
+// out_w[f*wstride + j] += sum_r wrow_j[r] X[r][f]   (last-layer weight: wrow = gvec; first layer: wrow = coordinates)
+// A warp owns one feature group for a span of tiles: lane = row % 32, 16-byte loads (512 B per warp instruction),
+// 8 register accumulators per output, ONE butterfly reduction at the end, then atomics.
+template <int NW>   // number of weighted outputs per feature: 0, 1 or 2
+__global__ void __launch_bounds__(256) k_tc_colsum(const __nv_bfloat16* __restrict__ X, int H, int num_tiles,
+                                                   int tiles_per_task, const float* __restrict__ wrow,
+                                                   const float* __restrict__ coords, int in, int64_t rows, int64_t g0,
+                                                   int64_t T_total, float scale, float* __restrict__ out_plain,
+                                                   float* __restrict__ out_w, int wstride) {
+  const int groups = H >> 3;
+  const int lane = threadIdx.x & 31;
+  const int64_t warp_id = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+  const int64_t nwarps = ((int64_t)gridDim.x * blockDim.x) >> 5;
+  const int tasks_per_group = (num_tiles + tiles_per_task - 1) / tiles_per_task;
+  const int64_t ntasks = (int64_t)groups * tasks_per_group;
+  for (int64_t task = warp_id; task < ntasks; task += nwarps) {
+    const int kg = (int)(task % groups);
+    const int t0 = (int)(task / groups) * tiles_per_task;
+    const int t1 = min(num_tiles, t0 + tiles_per_task);
+    float acc[8], accw[NW > 0 ? NW : 1][8];
+#pragma unroll
+    for (int j = 0; j < 8; ++j) {
+      acc[j] = 0.f;
+#pragma unroll
+      for (int q = 0; q < (NW > 0 ? NW : 1); ++q) accw[q][j] = 0.f;
+    }
+    for (int tile = t0; tile < t1; ++tile) {
+      const __nv_bfloat16* base = X + (size_t)tile * (TILE_ROWS * (size_t)H) + (size_t)kg * TILE_ROWS * 8;
+#pragma unroll
+      for (int rr = 0; rr < TILE_ROWS; rr += 32) {
+        const int r = rr + lane;
+        const int64_t row = (int64_t)tile * TILE_ROWS + r;
+        const uint4 u = *reinterpret_cast<const uint4*>(base + (size_t)r * 8);
+        const uint32_t uw[4] = {u.x, u.y, u.z, u.w};
+        float wv[NW > 0 ? NW : 1];
+        if (NW > 0) {
+          if (wrow) {
+            wv[0] = wrow[row];
+          } else {   // first layer: the weights are the (generated or given) coordinates; pad rows carry dZ = 0
+            const int64_t rc = row < rows ? row : rows - 1;
+            if (coords) {
+              wv[0] = coords[rc * in];
+              if (NW > 1) wv[NW - 1] = coords[rc * in + 1];
+            } else {
+              wv[0] = linspace_at(g0 + rc, T_total, scale);
+            }
+          }
+        }
+#pragma unroll
+        for (int h = 0; h < 4; ++h) {
+          const float2 f = unpack_bf16x2(uw[h]);
+          acc[2 * h] += f.x;
+          acc[2 * h + 1] += f.y;
+#pragma unroll
+          for (int q = 0; q < NW; ++q) {
+            accw[q][2 * h] = __fmaf_rn(wv[q], f.x, accw[q][2 * h]);
+            accw[q][2 * h + 1] = __fmaf_rn(wv[q], f.y, accw[q][2 * h + 1]);
+          }
+        }
+      }
+    }
+#pragma unroll
+    for (int j = 0; j < 8; ++j) {
+      const float s = warp_sum(acc[j]);
+      if (out_plain && lane == j) atomicAdd(&out_plain[kg * 8 + j], s);
+#pragma unroll
+      for (int q = 0; q < NW; ++q) {
+        const float sw = warp_sum(accw[q][j]);
+        if (lane == j) atomicAdd(&out_w[(int64_t)(kg * 8 + j) * wstride + q], sw);
+      }
+    }
+  }
+}
+
+// ------------------------------------------------------------------------------------------------ host side
+bool siren_tc_supported(const inr_siren_desc* d) {
+  const int H = d->hidden_features;
+  return (H == 128 || H == 256 || H == 512) && d->hidden_layers >= 1 && d->out_features == 1;
+}
+
+static int ns_of(int H) { return H >= 512 ? 128 : H; }
+
+struct TcPlan {
+  int64_t pack_bytes, gvec_bytes, img_bytes_per_row, fixed_bytes;
+  int n_images;
+};
+
+static TcPlan plan_of(const inr_siren_desc* d, int training) {
+  TcPlan pl;
+  const int64_t H = d->hidden_features, L = d->hidden_layers;
+  pl.pack_bytes = 2 * L * H * H * 2;
+  pl.n_images = training ? 2 * (int)(L + 1) : 2;
+  pl.img_bytes_per_row = pl.n_images * H * 2 + (training ? 4 : 0);   // + gvec
+  pl.fixed_bytes = round_up(pl.pack_bytes, 1024) + 4096;
+  pl.gvec_bytes = 0;
+  return pl;
+}
+
+int64_t siren_tc_workspace_bytes(const inr_siren_desc* d, int64_t n_rows, int training) {
+  const TcPlan pl = plan_of(d, training);
+  const int64_t cap = (int64_t)48 << 30;   // row chunks beyond this (180 GB parts hold a 60 s clip at 5x512 in one chunk)
+  int64_t rows = round_up(std::max<int64_t>(n_rows, 1), TILE_ROWS);
+  if (rows * pl.img_bytes_per_row > cap) rows = std::max<int64_t>(cap / pl.img_bytes_per_row / TILE_ROWS, 8) * TILE_ROWS;
+  return pl.fixed_bytes + rows * pl.img_bytes_per_row + 1024;
+}
+
+template <int H, int MODE>
+static int launch_layer(const LayerParams& p, cudaStream_t st) {
+  using Cfg = LayerCfg<H>;
+  static bool attr_set = false;
+  if (!attr_set) {
+    INR_CUDA_CHECK(cudaFuncSetAttribute(k_tc_layer<H, MODE>, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg::SMEM_BYTES));
+    attr_set = true;
+  }
+  int grid = num_sms() / Cfg::NQ * Cfg::NQ;
+  const int max_useful = (int)std::min<int64_t>((int64_t)p.num_tiles * Cfg::NQ, 1 << 30);
+  if (grid > max_useful) grid = max_useful;
+  { LaunchScope ls(MODE == MODE_FWD ? "k_tc_layer_fwd" : "k_tc_layer_bwd", st);
+    k_tc_layer<H, MODE><<<grid, Cfg::THREADS, Cfg::SMEM_BYTES, st>>>(p); }
+  INR_LAUNCH_CHECK();
+  return INR_OK;
+}
+
+template <int H>
+static int launch_dw(const DwParams& p, cudaStream_t st) {
+  using Cfg = DwCfg<H>;
+  static bool attr_set = false;
+  if (!attr_set) {
+    INR_CUDA_CHECK(cudaFuncSetAttribute(k_tc_dw<H>, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg::SMEM_BYTES));
+    attr_set = true;
+  }
+  int grid = num_sms() / Cfg::NBLOCKS * Cfg::NBLOCKS;
+  const int max_useful = (int)std::min<int64_t>((int64_t)p.num_tiles * Cfg::NBLOCKS, 1 << 30);
+  if (grid > max_useful) grid = max_useful;
+  { LaunchScope ls("k_tc_dw", st);
+    k_tc_dw<H><<<grid, Cfg::THREADS, Cfg::SMEM_BYTES, st>>>(p); }
+  INR_LAUNCH_CHECK();
+  return INR_OK;
+}
+
+int tc_layer(int H, int mode, const LayerParams& p, cudaStream_t st) {
+  switch (H) {
+    case 128: return mode == MODE_FWD ? launch_layer<128, MODE_FWD>(p, st) : launch_layer<128, MODE_BWD>(p, st);
+    case 256: return mode == MODE_FWD ? launch_layer<256, MODE_FWD>(p, st) : launch_layer<256, MODE_BWD>(p, st);
+    case 512: return mode == MODE_FWD ? launch_layer<512, MODE_FWD>(p, st) : launch_layer<512, MODE_BWD>(p, st);
+  }
+  set_error("tcgen05 layer kernel: unsupported H=%d", H);
+  return INR_E_UNSUPPORTED;
+}
+
+int tc_dw(int H, const DwParams& p, cudaStream_t st) {
+  switch (H) {
+    case 128: return launch_dw<128>(p, st);
+    case 256: return launch_dw<256>(p, st);
+    case 512: return launch_dw<512>(p, st);
+  }
+  set_error("tcgen05 dW kernel: unsupported H=%d", H);
+  return INR_E_UNSUPPORTED;
+}
+
+static LayerParams layer_params(int H, const __nv_bfloat16* A, const __nv_bfloat16* Bp, const float* bias, float omega,
+                                __nv_bfloat16* out0, __nv_bfloat16* out1, const __nv_bfloat16* Cin, int tiles) {
+  LayerParams p;
+  p.A = A; p.Bpack = Bp; p.bias = bias; p.omega = omega; p.out0 = out0; p.out1 = out1; p.Cin = Cin; p.num_tiles = tiles;
+  p.a_lbo = TILE_ROWS * 16; p.a_sbo = 128;            // K-major, no swizzle: LBO = next 8-feature group, SBO = next 8 rows
+  p.b_lbo = (uint32_t)ns_of(H) * 16; p.b_sbo = 128;
+  return p;
+}
+
+static int colsum(const __nv_bfloat16* X, int H, int tiles, const float* wrow, const float* coords, int in, int64_t rows,
+                  int64_t g0, int64_t T_total, float scale, float* out_plain, float* out_w, int wstride, int nw,
+                  cudaStream_t st) {
+  const int groups = H / 8;
+  int tiles_per_task = std::max(1, (int)cdiv((int64_t)tiles * groups, (int64_t)num_sms() * 32));
+  const int64_t ntasks = (int64_t)groups * cdiv(tiles, tiles_per_task);
+  int blocks = (int)std::min<int64_t>(cdiv(ntasks, 8), (int64_t)num_sms() * 8);
+  if (blocks < 1) blocks = 1;
+  { LaunchScope ls(nw == 0 ? "k_tc_colsum" : "k_tc_colsum_w", st);
+    if (nw == 0)
+      k_tc_colsum<0><<<blocks, 256, 0, st>>>(X, H, tiles, tiles_per_task, wrow, coords, in, rows, g0, T_total, scale, out_plain, out_w, wstride);
+    else if (nw == 1)
+      k_tc_colsum<1><<<blocks, 256, 0, st>>>(X, H, tiles, tiles_per_task, wrow, coords, in, rows, g0, T_total, scale, out_plain, out_w, wstride);
+    else
+      k_tc_colsum<2><<<blocks, 256, 0, st>>>(X, H, tiles, tiles_per_task, wrow, coords, in, rows, g0, T_total, scale, out_plain, out_w, wstride); }
+  INR_LAUNCH_CHECK();
+  return INR_OK;
+}
+
+struct TcWorkspace {
+  __nv_bfloat16 *Wf, *Wb;
+  float* gvec;
+  __nv_bfloat16* img;
+  int64_t chunk_rows;   // multiple of 128
+  int64_t img_elems;    // elements per image
+};
+
+static int carve(const inr_siren_desc* d, int training, int64_t n, void* ws, int64_t ws_bytes, TcWorkspace* w) {
+  const TcPlan pl = plan_of(d, training);
+  const int64_t H = d->hidden_features, L = d->hidden_layers;
+  uint8_t* base = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(ws) + 255) & ~(uintptr_t)255);
+  const int64_t usable = ws_bytes - (base - reinterpret_cast<uint8_t*>(ws));
+  w->Wf = reinterpret_cast<__nv_bfloat16*>(base);
+  w->Wb = w->Wf + L * H * H;
+  int64_t avail = usable - pl.fixed_bytes;
+  int64_t rows = avail / pl.img_bytes_per_row / TILE_ROWS * TILE_ROWS;
+  INR_REQUIRE(rows >= TILE_ROWS, INR_E_WORKSPACE, "workspace of %lld bytes is too small for one 128-row tile", (long long)ws_bytes);
+  rows = std::min<int64_t>(rows, round_up(n, TILE_ROWS));
+  w->chunk_rows = rows;
+  w->img_elems = rows * H;
+  uint8_t* p = base + pl.fixed_bytes;
+  w->gvec = reinterpret_cast<float*>(p);
+  if (training) p += rows * 4;
+  p = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(p) + 255) & ~(uintptr_t)255);
+  w->img = reinterpret_cast<__nv_bfloat16*>(p);
+  return INR_OK;
+}
+
+static int pack_weights(const inr_siren_desc* d, const float* params, const TcWorkspace& w, cudaStream_t st) {
+  SirenLayout lay = layout_of(d);
+  const int64_t total = (int64_t)lay.H * lay.H * lay.L;
+  int blocks = (int)std::min<int64_t>(cdiv(total, 256), (int64_t)num_sms() * 8);
+  { LaunchScope ls("k_tc_pack", st);
+    k_tc_pack<<<blocks, 256, 0, st>>>(params, lay, ns_of(lay.H), w.Wf, w.Wb); }
+  INR_LAUNCH_CHECK();
+  return INR_OK;
+}
+
+static int first_layer(const inr_siren_desc* d, const float* params, const float* coords, int64_t rows, int64_t rows_pad,
+                       int64_t g0, int64_t T_total, float scale, __nv_bfloat16* S0, __nv_bfloat16* C0, cudaStream_t st) {
+  SirenLayout lay = layout_of(d);
+  const int64_t total = rows_pad * (lay.H / 8);
+  int blocks = (int)std::min<int64_t>(cdiv(total, 256), (int64_t)num_sms() * 16);
+  { LaunchScope ls("k_tc_first", st);
+    k_tc_first<<<blocks, 256, 0, st>>>(params + lay.w_off(0), params + lay.b_off(0), coords, lay.in, lay.H, rows, rows_pad,
+                                       g0, T_total, scale, d->first_omega_0, S0, C0); }
+  INR_LAUNCH_CHECK();
+  return INR_OK;
+}
+
+static int last_layer(const inr_siren_desc* d, const float* params, const __nv_bfloat16* SL, __nv_bfloat16* CL,
+                      const float* target, const float* extra_g, int64_t rows, int tiles, int loss_kind, float grad_scale,
+                      float* gvec, float* grads, inr_opt_state* opt, float* out, int training, cudaStream_t st) {
+  SirenLayout lay = layout_of(d);
+  const int last = lay.L + 1;
+  int blocks = std::min(tiles, num_sms() * 8);
+  { LaunchScope ls("k_tc_last", st);
+    k_tc_last<<<blocks, 128, lay.H * sizeof(float), st>>>(
+        SL, CL, params + lay.w_off(last), params + lay.b_off(last), target, extra_g, rows, tiles, lay.H,
+        d->hidden_omega_0, d->hidden_omega_0, d->outermost_linear, loss_kind, grad_scale, gvec,
+        grads ? grads + lay.b_off(last) : nullptr, opt ? &opt->loss_acc[0] : nullptr, out, training); }
+  INR_LAUNCH_CHECK();
+  return INR_OK;
+}
+
+int siren_tc_forward(const inr_siren_desc* d, const float* params, const float* coords, int64_t n, int64_t i0,
+                     int64_t T_total, float scale, float* out, void* ws, int64_t ws_bytes, cudaStream_t st) {
+  SirenLayout lay = layout_of(d);
+  const int H = lay.H, L = lay.L;
+  TcWorkspace w;
+  int rc = carve(d, 0, n, ws, ws_bytes, &w);
+  if (rc) return rc;
+  if ((rc = pack_weights(d, params, w, st))) return rc;
+  for (int64_t r0 = 0; r0 < n; r0 += w.chunk_rows) {
+    const int64_t rows = std::min(w.chunk_rows, n - r0);
+    const int64_t rows_pad = round_up(rows, TILE_ROWS);
+    const int tiles = (int)(rows_pad / TILE_ROWS);
+    __nv_bfloat16* S[2] = {w.img, w.img + w.img_elems};
+    if ((rc = first_layer(d, params, coords ? coords + r0 * lay.in : nullptr, rows, rows_pad, i0 + r0, T_total, scale, S[0],
+                          nullptr, st)))
+      return rc;
+    int cur = 0;
+    for (int l = 1; l <= L; ++l) {
+      LayerParams p = layer_params(H, S[cur], w.Wf + (int64_t)(l - 1) * H * H, params + lay.b_off(l), d->hidden_omega_0,
+                                   S[cur ^ 1], nullptr, nullptr, tiles);
+      if ((rc = tc_layer(H, MODE_FWD, p, st))) return rc;
+      cur ^= 1;
+    }
+    if ((rc = last_layer(d, params, S[cur], nullptr, nullptr, nullptr, rows, tiles, 0, 0.f, nullptr, nullptr, nullptr,
+                         out + r0, 0, st)))
+      return rc;
+  }
+  return INR_OK;
+}
+
+int siren_tc_loss_backward(const inr_siren_desc* d, const float* params, const float* coords, const float* target,
+                           int64_t n, int64_t i0, int64_t T_total, float scale, int loss_kind, float grad_scale,
+                           const float* extra_gout, float* grads, inr_opt_state* opt, float* out, void* ws,
+                           int64_t ws_bytes, cudaStream_t st) {
+  SirenLayout lay = layout_of(d);
+  const int H = lay.H, L = lay.L;
+  TcWorkspace w;
+  int rc = carve(d, 1, n, ws, ws_bytes, &w);
+  if (rc) return rc;
+  if ((rc = pack_weights(d, params, w, st))) return rc;
+  for (int64_t r0 = 0; r0 < n; r0 += w.chunk_rows) {
+    const int64_t rows = std::min(w.chunk_rows, n - r0);
+    const int64_t rows_pad = round_up(rows, TILE_ROWS);
+    const int tiles = (int)(rows_pad / TILE_ROWS);
+    auto S = [&](int l) { return w.img + (int64_t)l * w.img_elems; };
+    auto C = [&](int l) { return w.img + (int64_t)(L + 1 + l) * w.img_elems; };
+    const float* xc = coords ? coords + r0 * lay.in : nullptr;
+    if ((rc = first_layer(d, params, xc, rows, rows_pad, i0 + r0, T_total, scale, S(0), C(0), st))) return rc;
+    for (int l = 1; l <= L; ++l) {
+      LayerParams p = layer_params(H, S(l - 1), w.Wf + (int64_t)(l - 1) * H * H, params + lay.b_off(l), d->hidden_omega_0,
+                                   S(l), C(l), nullptr, tiles);
+      if ((rc = tc_layer(H, MODE_FWD, p, st))) return rc;
+    }
+    if ((rc = last_layer(d, params, S(L), C(L), target ? target + r0 : nullptr, extra_gout ? extra_gout + r0 : nullptr, rows,
+                         tiles, loss_kind, grad_scale, w.gvec, grads, opt, out ? out + r0 : nullptr, 1, st)))
+      return rc;
+    // last-layer weight gradient: gw_out[f] += sum_r g[r] S_L[r][f]
+    if ((rc = colsum(S(L), H, tiles, w.gvec, nullptr, 1, rows, 0, 1, 1.f, nullptr, grads + lay.w_off(L + 1), 1, 1, st)))
+      return rc;
+    for (int l = L; l >= 1; --l) {
+      DwParams dp;
+      dp.dZ = C(l); dp.S = S(l - 1); dp.gW = grads + lay.w_off(l); dp.num_tiles = tiles;
+      dp.lbo = 128; dp.sbo = TILE_ROWS * 16;   // MN-major, no swizzle: LBO = next 8 rows (K), SBO = next 8-feature group
+      if ((rc = tc_dw(H, dp, st))) return rc;
+      if ((rc = colsum(C(l), H, tiles, nullptr, nullptr, 1, rows, 0, 1, 1.f, grads + lay.b_off(l), nullptr, 0, 0, st))) return rc;
+      const float om_prev = (l - 1 == 0) ? d->first_omega_0 : d->hidden_omega_0;
+      LayerParams p = layer_params(H, C(l), w.Wb + (int64_t)(l - 1) * H * H, nullptr, om_prev, C(l - 1), nullptr, C(l - 1), tiles);
+      if ((rc = tc_layer(H, MODE_BWD, p, st))) return rc;
+    }
+    // first layer: gW_0[f][i] += sum_r dZ_0[r][f] x[r][i], gb_0 += colsum(dZ_0)
+    if ((rc = colsum(C(0), H, tiles, nullptr, xc, lay.in, rows, i0 + r0, T_total, scale, grads + lay.b_off(0),
+                     grads + lay.w_off(0), lay.in, lay.in, st)))
+      return rc;
+  }
+  return INR_OK;
+}
+
 }  // namespace inr

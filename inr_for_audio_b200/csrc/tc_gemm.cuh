@@ -1,0 +1,327 @@
+// tc_gemm.cuh -- the two tcgen05 GEMM kernels of the bf16 SIREN path (sm_100a).
+//
+//  k_tc_layer<H, MODE>   weight-stationary layer GEMM over 128-row activation tiles
+//      MODE_FWD :  S_l, C_l  = sincos( omega * (S_{l-1} W_l^T + b_l) )          models.py:114-115
+//      MODE_BWD :  dZ_{l-1}  = (dZ_l W_l) * omega_{l-1} * C_{l-1}               (autograd of the above)
+//    Each CTA keeps its N-slice of the (pre-packed, bf16) weight matrix resident in shared memory for the whole
+//    kernel, streams A tiles (tile images, tc_common.cuh) through a 4-stage cp.async.bulk ring, accumulates in
+//    TMEM (two accumulator buffers) and drains them with 8 epilogue warps that apply the activation math in
+//    fp32 and write the next tile images with coalesced 16-byte stores.
+//    warp 0 = bulk-copy producer, warp 1 = MMA issuer (+ TMEM owner), warps 2..9 = epilogue.
+//
+//  k_tc_dw<H>            dW_l += dZ_l^T S_{l-1}, both operands MN-major views of the SAME tile images, split over
+//    row tiles across CTAs (split-K), accumulated in TMEM across all of a CTA's tiles, reduced into the fp32
+//    gradient with red.global.add.v4.f32 once at the end.
+#pragma once
+#include "common.cuh"
+#include "tc_common.cuh"
+
+namespace inr {
+namespace tc {
+
+enum { MODE_FWD = 0, MODE_BWD = 1 };
+
+template <int H>
+struct LayerCfg {
+  static constexpr int NS = (H >= 512) ? 128 : H;   // output features per CTA (B slice resident in smem)
+  static constexpr int NQ = H / NS;                 // N slices
+  static constexpr int KC = 64;                     // K columns per ring stage
+  static constexpr int NCHUNK = H / KC;
+  static constexpr int STAGES = 4;
+  static constexpr int A_STAGE_BYTES = (KC / 8) * TILE_ROWS * 16;  // 16 KB
+  static constexpr int B_BYTES = H * NS * 2;
+  static constexpr int TMEM_COLS = 2 * NS;          // two accumulator buffers (256 or 512: powers of two)
+  static constexpr int OFF_A = B_BYTES;
+  static constexpr int OFF_BIAS = OFF_A + STAGES * A_STAGE_BYTES;
+  static constexpr int OFF_BAR = OFF_BIAS + NS * 4;
+  static constexpr int SMEM_BYTES = OFF_BAR + 128;
+  static constexpr int THREADS = 320;
+  static_assert(H == 128 || H == 256 || H == 512, "hidden width");
+};
+
+struct LayerParams {
+  const __nv_bfloat16* A;      // input tile images: S_{l-1} (fwd) or dZ_l (bwd)
+  const __nv_bfloat16* Bpack;  // packed weights [NQ][H/8][NS][8]: W_l (fwd) or W_l^T (bwd)
+  const float* bias;           // fwd: b_l (H floats)
+  float omega;                 // fwd: omega_l;  bwd: omega_{l-1}
+  __nv_bfloat16* out0;         // fwd: S_l;  bwd: dZ_{l-1}
+  __nv_bfloat16* out1;         // fwd: C_l or NULL (inference)
+  const __nv_bfloat16* Cin;    // bwd: C_{l-1} (may alias out0: read before written, same thread)
+  int num_tiles;
+  uint32_t a_lbo, a_sbo, b_lbo, b_sbo;  // descriptor strides (bytes); passed in so a test can probe the convention
+};
+
+template <int H, int MODE>
+__global__ void __launch_bounds__(LayerCfg<H>::THREADS, 1) k_tc_layer(const LayerParams p) {
+  using Cfg = LayerCfg<H>;
+  constexpr int NS = Cfg::NS;
+  extern __shared__ __align__(128) uint8_t smem[];
+  const uint32_t smem_base = smem_u32(smem);
+  const uint32_t sB = smem_base;
+  const uint32_t sA = smem_base + Cfg::OFF_A;
+  float* s_bias = reinterpret_cast<float*>(smem + Cfg::OFF_BIAS);
+  const uint32_t bar0 = smem_base + Cfg::OFF_BAR;
+  // barriers (8 bytes each): full[4] empty[4] tfull[2] tempty[2] bfull ; then the TMEM base slot
+  auto bar_full = [&](int s) { return bar0 + 8u * s; };
+  auto bar_empty = [&](int s) { return bar0 + 8u * (Cfg::STAGES + s); };
+  auto bar_tfull = [&](int b) { return bar0 + 8u * (2 * Cfg::STAGES + b); };
+  auto bar_tempty = [&](int b) { return bar0 + 8u * (2 * Cfg::STAGES + 2 + b); };
+  const uint32_t bar_bfull = bar0 + 8u * (2 * Cfg::STAGES + 4);
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(smem + Cfg::OFF_BAR + 8 * (2 * Cfg::STAGES + 5));
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int q = blockIdx.x % Cfg::NQ;                 // N slice of this CTA
+  const int tile0 = blockIdx.x / Cfg::NQ;
+  const int tile_stride = gridDim.x / Cfg::NQ;
+
+  if (threadIdx.x == 0) {
+    for (int s = 0; s < Cfg::STAGES; ++s) { mbar_init(bar_full(s), 1); mbar_init(bar_empty(s), 1); }
+    for (int b = 0; b < 2; ++b) { mbar_init(bar_tfull(b), 1); mbar_init(bar_tempty(b), 8); }
+    mbar_init(bar_bfull, 1);
+    mbar_fence_init();
+  }
+  if (warp == 1) {
+    tmem_alloc(smem_u32(tmem_slot), Cfg::TMEM_COLS);
+    tmem_relinquish();
+  }
+  if (MODE == MODE_FWD) {
+    for (int i = threadIdx.x; i < NS; i += blockDim.x) s_bias[i] = p.omega * p.bias[q * NS + i];
+  }
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot;
+
+  if (warp == 0) {
+    // ===================== producer: weights once, then A chunks through the ring =====================
+    if (lane == 0) {
+      mbar_arrive_expect_tx(bar_bfull, Cfg::B_BYTES);
+      const uint8_t* bsrc = reinterpret_cast<const uint8_t*>(p.Bpack) + (size_t)q * Cfg::B_BYTES;
+      for (int off = 0; off < Cfg::B_BYTES; off += 32768) bulk_g2s(sB + off, bsrc + off, 32768, bar_bfull);
+      int s = 0;
+      uint32_t phase = 0;
+      for (int tile = tile0; tile < p.num_tiles; tile += tile_stride) {
+        const uint8_t* asrc = reinterpret_cast<const uint8_t*>(p.A) + (size_t)tile * (TILE_ROWS * H * 2);
+        for (int c = 0; c < Cfg::NCHUNK; ++c) {
+          mbar_wait(bar_empty(s), phase ^ 1);
+          mbar_arrive_expect_tx(bar_full(s), Cfg::A_STAGE_BYTES);
+          bulk_g2s(sA + s * Cfg::A_STAGE_BYTES, asrc + (size_t)c * Cfg::A_STAGE_BYTES, Cfg::A_STAGE_BYTES, bar_full(s));
+          if (++s == Cfg::STAGES) { s = 0; phase ^= 1; }
+        }
+      }
+    }
+  } else if (warp == 1) {
+    // ===================== MMA issuer (one thread) =====================
+    if (lane == 0) {
+      constexpr uint32_t idesc = make_idesc_bf16(128, NS, 0, 0);
+      mbar_wait(bar_bfull, 0);
+      int s = 0;
+      uint32_t phase = 0;
+      int it = 0;
+      for (int tile = tile0; tile < p.num_tiles; tile += tile_stride, ++it) {
+        const int buf = it & 1;
+        mbar_wait(bar_tempty(buf), ((it >> 1) & 1) ^ 1);   // epilogue drained this accumulator (2 tiles ago)
+        tc_fence_after();
+        const uint32_t d_tmem = tmem_base + buf * NS;
+        for (int c = 0; c < Cfg::NCHUNK; ++c) {
+          mbar_wait(bar_full(s), phase);
+          tc_fence_after();
+#pragma unroll
+          for (int kk = 0; kk < Cfg::KC / 16; ++kk) {
+            const uint64_t ad = make_smem_desc(sA + s * Cfg::A_STAGE_BYTES + kk * 2 * (TILE_ROWS * 16), p.a_lbo, p.a_sbo);
+            const uint64_t bd = make_smem_desc(sB + (c * (Cfg::KC / 8) + kk * 2) * (NS * 16), p.b_lbo, p.b_sbo);
+            umma_bf16(d_tmem, ad, bd, idesc, (c | kk) != 0 ? 1u : 0u);
+          }
+          umma_commit(bar_empty(s));                         // stage reusable once these MMAs have read it
+          if (++s == Cfg::STAGES) { s = 0; phase ^= 1; }
+        }
+        umma_commit(bar_tfull(buf));                         // accumulator complete -> epilogue
+      }
+    }
+  } else {
+    // ===================== epilogue: 8 warps, warp%4 = TMEM lane quadrant, two column-chunk parities =====
+    const int e = warp - 2;
+    const int quad = warp & 3;
+    const int half = e >> 2;
+    const int row = quad * 32 + lane;
+    int it = 0;
+    for (int tile = tile0; tile < p.num_tiles; tile += tile_stride, ++it) {
+      const int buf = it & 1;
+      mbar_wait(bar_tfull(buf), (it >> 1) & 1);
+      tc_fence_after();
+      const size_t tile_off = (size_t)tile * (TILE_ROWS * H);
+      for (int c = half; c < NS / 32; c += 2) {
+        const int g0 = (q * NS + c * 32) >> 3;                // first feature group of this 32-column chunk
+        uint4 cin[4];
+        if (MODE == MODE_BWD) {
+#pragma unroll
+          for (int j = 0; j < 4; ++j)
+            cin[j] = *reinterpret_cast<const uint4*>(p.Cin + tile_off + ((size_t)(g0 + j) * TILE_ROWS + row) * 8);
+        }
+        float v[32];
+        tmem_ld32(tmem_base + buf * NS + c * 32 + ((uint32_t)(quad * 32) << 16), v);
+        tmem_ld_wait();
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+          uint32_t o0[4], o1[4];
+          if (MODE == MODE_FWD) {
+#pragma unroll
+            for (int h = 0; h < 4; ++h) {
+              const int cc = j * 8 + h * 2;
+              const float t0 = __fmaf_rn(v[cc], p.omega, s_bias[c * 32 + cc]);
+              const float t1 = __fmaf_rn(v[cc + 1], p.omega, s_bias[c * 32 + cc + 1]);
+              float s0, c0, s1, c1;
+              __sincosf(t0, &s0, &c0);
+              __sincosf(t1, &s1, &c1);
+              o0[h] = pack_bf16x2(s0, s1);
+              o1[h] = pack_bf16x2(c0, c1);
+            }
+            const size_t off = tile_off + ((size_t)(g0 + j) * TILE_ROWS + row) * 8;
+            *reinterpret_cast<uint4*>(p.out0 + off) = make_uint4(o0[0], o0[1], o0[2], o0[3]);
+            if (p.out1) *reinterpret_cast<uint4*>(p.out1 + off) = make_uint4(o1[0], o1[1], o1[2], o1[3]);
+          } else {
+            const uint32_t cw[4] = {cin[j].x, cin[j].y, cin[j].z, cin[j].w};
+#pragma unroll
+            for (int h = 0; h < 4; ++h) {
+              const int cc = j * 8 + h * 2;
+              const float2 cf = unpack_bf16x2(cw[h]);
+              o0[h] = pack_bf16x2(v[cc] * p.omega * cf.x, v[cc + 1] * p.omega * cf.y);
+            }
+            const size_t off = tile_off + ((size_t)(g0 + j) * TILE_ROWS + row) * 8;
+            *reinterpret_cast<uint4*>(p.out0 + off) = make_uint4(o0[0], o0[1], o0[2], o0[3]);
+          }
+        }
+      }
+      tc_fence_before();
+      __syncwarp();
+      if (lane == 0) mbar_arrive(bar_tempty(buf));
+    }
+  }
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 1) {
+    tc_fence_after();
+    tmem_dealloc(tmem_base, Cfg::TMEM_COLS);
+  }
+}
+
+// ------------------------------------------------------------------------------------------------------------
+template <int H>
+struct DwCfg {
+  static constexpr int NB = (H >= 256) ? 256 : 128;   // in-feature block (MMA N)
+  static constexpr int MBLK = H / 128;                // out-feature blocks (MMA M = 128)
+  static constexpr int NBLK = H / NB;
+  static constexpr int NBLOCKS = MBLK * NBLK;
+  static constexpr int A_BYTES = 128 * TILE_ROWS * 2;  // 16 feature groups of dZ: 32 KB
+  static constexpr int B_BYTES = NB * TILE_ROWS * 2;   // 64 KB / 32 KB of S
+  static constexpr int STAGE_BYTES = A_BYTES + B_BYTES;
+  static constexpr int STAGES = 2;
+  static constexpr int TMEM_COLS = NB;
+  static constexpr int OFF_BAR = STAGES * STAGE_BYTES;
+  static constexpr int SMEM_BYTES = OFF_BAR + 64;
+  static constexpr int THREADS = 192;                  // producer, MMA, 4 epilogue warps
+};
+
+struct DwParams {
+  const __nv_bfloat16* dZ;   // tile images of dZ_l   (M operand: out features)
+  const __nv_bfloat16* S;    // tile images of S_{l-1} (N operand: in features)
+  float* gW;                 // fp32 gradient of W_l, row-major [H out][H in], accumulated with atomics
+  int num_tiles;
+  uint32_t lbo, sbo;         // MN-major strides: LBO = 128 (8-row k groups), SBO = 2048 (feature groups)
+};
+
+template <int H>
+__global__ void __launch_bounds__(DwCfg<H>::THREADS, 1) k_tc_dw(const DwParams p) {
+  using Cfg = DwCfg<H>;
+  extern __shared__ __align__(128) uint8_t smem[];
+  const uint32_t smem_base = smem_u32(smem);
+  const uint32_t bar0 = smem_base + Cfg::OFF_BAR;
+  auto bar_full = [&](int s) { return bar0 + 8u * s; };
+  auto bar_empty = [&](int s) { return bar0 + 8u * (Cfg::STAGES + s); };
+  const uint32_t bar_tfull = bar0 + 8u * (2 * Cfg::STAGES);
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(smem + Cfg::OFF_BAR + 8 * (2 * Cfg::STAGES + 1));
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int blk = blockIdx.x % Cfg::NBLOCKS;
+  const int mb = blk / Cfg::NBLK, nb = blk % Cfg::NBLK;
+  const int tile0 = blockIdx.x / Cfg::NBLOCKS;
+  const int tile_stride = gridDim.x / Cfg::NBLOCKS;
+  const bool has_work = tile0 < p.num_tiles;
+
+  if (threadIdx.x == 0) {
+    for (int s = 0; s < Cfg::STAGES; ++s) { mbar_init(bar_full(s), 1); mbar_init(bar_empty(s), 1); }
+    mbar_init(bar_tfull, 1);
+    mbar_fence_init();
+  }
+  if (warp == 1) {
+    tmem_alloc(smem_u32(tmem_slot), Cfg::TMEM_COLS);
+    tmem_relinquish();
+  }
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot;
+
+  if (warp == 0) {
+    if (lane == 0) {
+      int s = 0;
+      uint32_t phase = 0;
+      for (int tile = tile0; tile < p.num_tiles; tile += tile_stride) {
+        const size_t tile_bytes = (size_t)tile * (TILE_ROWS * H * 2);
+        const uint8_t* a_src = reinterpret_cast<const uint8_t*>(p.dZ) + tile_bytes + (size_t)(mb * 16) * (TILE_ROWS * 16);
+        const uint8_t* b_src = reinterpret_cast<const uint8_t*>(p.S) + tile_bytes + (size_t)(nb * (Cfg::NB / 8)) * (TILE_ROWS * 16);
+        mbar_wait(bar_empty(s), phase ^ 1);
+        mbar_arrive_expect_tx(bar_full(s), Cfg::STAGE_BYTES);
+        const uint32_t dst = smem_base + s * Cfg::STAGE_BYTES;
+        bulk_g2s(dst, a_src, Cfg::A_BYTES, bar_full(s));
+        for (int off = 0; off < Cfg::B_BYTES; off += 32768)
+          bulk_g2s(dst + Cfg::A_BYTES + off, b_src + off, 32768, bar_full(s));
+        if (++s == Cfg::STAGES) { s = 0; phase ^= 1; }
+      }
+    }
+  } else if (warp == 1) {
+    if (lane == 0 && has_work) {
+      constexpr uint32_t idesc = make_idesc_bf16(128, Cfg::NB, 1, 1);   // both operands MN-major
+      int s = 0;
+      uint32_t phase = 0;
+      int it = 0;
+      for (int tile = tile0; tile < p.num_tiles; tile += tile_stride, ++it) {
+        mbar_wait(bar_full(s), phase);
+        tc_fence_after();
+        const uint32_t a0 = smem_base + s * Cfg::STAGE_BYTES;
+        const uint32_t b0 = a0 + Cfg::A_BYTES;
+#pragma unroll
+        for (int kk = 0; kk < TILE_ROWS / 16; ++kk) {   // K = 16 rows per MMA: 16 rows x 16 B inside each feature group
+          const uint64_t ad = make_smem_desc(a0 + kk * 256, p.lbo, p.sbo);
+          const uint64_t bd = make_smem_desc(b0 + kk * 256, p.lbo, p.sbo);
+          umma_bf16(tmem_base, ad, bd, idesc, (it | kk) != 0 ? 1u : 0u);
+        }
+        umma_commit(bar_empty(s));
+        if (++s == Cfg::STAGES) { s = 0; phase ^= 1; }
+      }
+      umma_commit(bar_tfull);
+    }
+  } else if (has_work) {
+    const int quad = warp & 3;
+    const int row = quad * 32 + lane;                 // out-feature index inside the M block
+    mbar_wait(bar_tfull, 0);
+    tc_fence_after();
+    float* grow = p.gW + (size_t)(mb * 128 + row) * H + nb * Cfg::NB;
+    for (int c = 0; c < Cfg::NB / 32; ++c) {
+      float v[32];
+      tmem_ld32(tmem_base + c * 32 + ((uint32_t)(quad * 32) << 16), v);
+      tmem_ld_wait();
+#pragma unroll
+      for (int j = 0; j < 8; ++j) red_add_v4(grow + c * 32 + j * 4, v[4 * j], v[4 * j + 1], v[4 * j + 2], v[4 * j + 3]);
+    }
+  }
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 1) {
+    tc_fence_after();
+    tmem_dealloc(tmem_base, Cfg::TMEM_COLS);
+  }
+}
+
+}  // namespace tc
+}  // namespace inr

@@ -233,3 +233,70 @@ def test_ragged_and_tiny_sizes(pkg, golden):
         np.testing.assert_allclose(out.cpu().numpy(), out_o.numpy().ravel(), atol=5e-6)
         go = torch.cat([x.reshape(-1) for x in grads_o]).numpy().astype(np.float64)
         assert np.linalg.norm(grads.cpu().numpy() - go) <= 3e-5 * np.linalg.norm(go) + 1e-12
+
+
+# ------------------------------------------------------------------------------------------------ bf16 tcgen05 mode
+@pytest.mark.parametrize("H,Lh,n", [(128, 2, 4099), (256, 3, 20000), (512, 2, 3000), (128, 1, 1)])
+def test_bf16_mode_against_oracle(pkg, H, Lh, n):
+    """bf16 operands / fp32 accumulation on the tensor cores: loss within 1e-3 relative (north star), gradients
+    within bf16 rounding noise of the fp32 oracle."""
+    from oracle import inr_oracle as O
+    spec = pkg.SirenSpec(1, H, Lh, 1, True)
+    ospec = O.SirenSpec(1, H, Lh, 1, True)
+    ps = O.siren_init(ospec, seed=H + Lh)
+    flat = torch.cat([p.reshape(-1) for p in ps])
+    gt = torch.from_numpy(pkg.utils.synth_waveform(max(n, 2), seed=3)[:n].copy())
+    coords = O.get_coord(n, 1).view(-1, 1)
+    loss_o, _, grads_o, out_o = O.siren_loss_and_grads(ospec, ps, coords, gt.view(-1, 1))
+    f = pkg.SirenFitter(spec, flat, gt.to(dev()), precision="bf16", use_graph=False)
+    loss, grads, out = f.loss_and_grads()
+    assert abs(loss - float(loss_o)) <= 1e-3 * abs(float(loss_o)) + 1e-9, (loss, float(loss_o))
+    assert float(np.abs(out.cpu().numpy() - out_o.numpy().ravel()).max()) <= 2e-2
+    go = torch.cat([x.reshape(-1) for x in grads_o]).numpy().astype(np.float64)
+    gerr = np.linalg.norm(grads.cpu().numpy() - go) / np.linalg.norm(go)
+    print("bf16 H=%d L=%d n=%d: loss rel err %.2e, grad rel err %.2e" % (H, Lh, n, abs(loss - float(loss_o)) / float(loss_o), gerr))
+    assert gerr <= (5e-2 if n > 1 else 0.2)
+    assert torch.equal(f.forward(), f.forward())
+    np.testing.assert_allclose(f.forward().cpu().numpy(), out.cpu().numpy(), atol=1e-6)
+
+
+def test_bf16_c1_first_steps(pkg, golden):
+    g = golden("siren")
+    ds = pkg.WaveformFitting(os.path.join(ROOT, "data", "gt_bach.wav"), duration=6, verbose=False)
+    torch.manual_seed(0)
+    model = pkg.Siren(1, 256, 3, 1, True)
+    tgt = torch.from_numpy(ds.normalised()).to(dev())
+    f = pkg.SirenFitter(model.spec, model.flat_parameters(), tgt, precision="bf16", use_graph=False)
+    loss, grads, out = f.loss_and_grads()
+    assert abs(loss - g["c1_losses"][0]) <= 1e-3 * g["c1_losses"][0]
+    gn = float(np.linalg.norm(grads.cpu().numpy().astype(np.float64)))
+    assert abs(gn - float(g["c1_g0_norm"])) <= 3e-2 * float(g["c1_g0_norm"])
+    f2 = pkg.SirenFitter(model.spec, model.flat_parameters(), tgt, precision="bf16")
+    f2.step(3)
+    np.testing.assert_allclose(f2.losses(), g["c1_losses"], rtol=5e-3)
+
+
+def test_bf16_convergence_envelope(pkg, golden):
+    """Same protocol as the fp32 envelope test, for the tensor-core mode (H=128 is the smallest width it takes)."""
+    g = golden("converge")
+    from scipy.io import wavfile
+    sr, data = wavfile.read(os.path.join(ROOT, "data", "gt_bach.wav"))
+    data = data.astype(np.float32)[44100:44100 + 8192]
+    gtn = data / np.max(np.abs(data))
+    sig = float(np.mean(gtn.astype(np.float64) ** 2))
+    torch.manual_seed(0)
+    model = pkg.Siren(1, 128, 2, 1, True)
+    f = pkg.SirenFitter(model.spec, model.flat_parameters(), torch.from_numpy(gtn).to(dev()), precision="bf16")
+    f.step(int(g["steps"]))
+    losses = f.losses().astype(np.float64)
+    np.testing.assert_allclose(losses[:3], g["all_losses_t1"][:3], rtol=2e-3)
+
+    def env_db(l, i):
+        return 10 * np.log10(sig / np.minimum.accumulate(np.asarray(l, dtype=np.float64))[i])
+    rows = []
+    for i, tol in ((99, 0.3), (299, 1.5), (599, 1.5), (1499, 3.0)):
+        ours = env_db(losses, i)
+        lo = min(env_db(g["all_losses_t1"], i), env_db(g["all_losses_t8"], i))
+        rows.append((i + 1, ours, lo))
+        assert ours >= lo - tol, (i, ours, lo)
+    print("bf16 best-so-far SNR dB at step: " + "; ".join("%d: ours %.2f ref-min %.2f" % r for r in rows))
