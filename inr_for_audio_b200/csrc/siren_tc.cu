@@ -33,19 +33,31 @@ __global__ void __launch_bounds__(256) k_tc_pack(const float* __restrict__ param
 }
 
 // ------------------------------------------------------------------------------------------------ first layer
-// one thread = one row x one feature group (8 features); consecutive threads = consecutive rows of a tile
+// one thread = one row x one feature group (8 features); consecutive threads = consecutive rows of a tile.
+// The argument omega*z is formed in fp32 exactly as the reference does (Linear -> * omega_0 -> sin, models.py:115);
+// it can reach +-4.4e4 rad (run.py's default omega = 22000), so it is reduced with a two-constant Cody-Waite step
+// (k = rint(t/2pi); r = t - k*C1 - k*C2 with FMAs, error < 2e-7 rad for |t| < 1e6) and the reduced angle goes to the
+// SFU (MUFU.SIN/COS, abs error ~5e-7 on [-pi, pi]) -- two orders below the bf16 rounding of the stored result.
+__device__ __forceinline__ void sincos_reduced(float t, float* s, float* c) {
+  const float k = rintf(t * 0.15915494309189535f);
+  float r = __fmaf_rn(-k, 6.2831854820251465f, t);      // C1 = fl32(2 pi)
+  r = __fmaf_rn(-k, -1.7484555e-7f, r);                 // C2 = 2 pi - C1
+  *s = __sinf(r);
+  *c = __cosf(r);
+}
+
 __global__ void __launch_bounds__(256) k_tc_first(const float* __restrict__ W, const float* __restrict__ B,
                                                   const float* __restrict__ coords, int in, int H, int64_t rows,
                                                   int64_t rows_pad, int64_t g0, int64_t T_total, float scale,
                                                   float omega, __nv_bfloat16* __restrict__ S0,
                                                   __nv_bfloat16* __restrict__ C0) {
-  const int groups = H >> 3;
-  const int64_t total = rows_pad * groups;
+  const int lg = 31 - __clz(H >> 3);                      // H/8 feature groups: a power of two on this path
+  const int64_t total = rows_pad << lg;
   for (int64_t idx = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; idx < total; idx += (int64_t)gridDim.x * blockDim.x) {
     const int r = (int)(idx & (TILE_ROWS - 1));
     const int64_t tg = idx >> 7;
-    const int kg = (int)(tg % groups);
-    const int64_t tile = tg / groups;
+    const int kg = (int)(tg & ((1 << lg) - 1));
+    const int64_t tile = tg >> lg;
     int64_t row = tile * TILE_ROWS + r;
     if (row >= rows) row = rows - 1;   // pad rows replicate the last row: finite values, zero gradient later
     float x0, x1 = 0.f;
@@ -63,7 +75,7 @@ __global__ void __launch_bounds__(256) k_tc_first(const float* __restrict__ W, c
       for (int u = 0; u < 2; ++u) {
         const int f = kg * 8 + h * 2 + u;
         const float z = (in == 1) ? __fmaf_rn(x0, W[f], B[f]) : (__fmaf_rn(x1, W[f * 2 + 1], x0 * W[f * 2]) + B[f]);
-        sincosf(omega * z, &s[u], &c[u]);
+        sincos_reduced(omega * z, &s[u], &c[u]);
       }
       so[h] = pack_bf16x2(s[0], s[1]);
       co[h] = pack_bf16x2(c[0], c[1]);
@@ -477,10 +489,9 @@ int siren_tc_loss_backward(const inr_siren_desc* d, const float* params, const f
       return rc;
     for (int l = L; l >= 1; --l) {
       DwParams dp;
-      dp.dZ = C(l); dp.S = S(l - 1); dp.gW = grads + lay.w_off(l); dp.num_tiles = tiles;
+      dp.dZ = C(l); dp.S = S(l - 1); dp.gW = grads + lay.w_off(l); dp.gb = grads + lay.b_off(l); dp.num_tiles = tiles;
       dp.lbo = 128; dp.sbo = TILE_ROWS * 16;   // MN-major, no swizzle: LBO = next 8 rows (K), SBO = next 8-feature group
       if ((rc = tc_dw(H, dp, st))) return rc;
-      if ((rc = colsum(C(l), H, tiles, nullptr, nullptr, 1, rows, 0, 1, 1.f, grads + lay.b_off(l), nullptr, 0, 0, st))) return rc;
       const float om_prev = (l - 1 == 0) ? d->first_omega_0 : d->hidden_omega_0;
       LayerParams p = layer_params(H, C(l), w.Wb + (int64_t)(l - 1) * H * H, nullptr, om_prev, C(l - 1), nullptr, C(l - 1), tiles);
       if ((rc = tc_layer(H, MODE_BWD, p, st))) return rc;

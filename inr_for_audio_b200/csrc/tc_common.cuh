@@ -72,6 +72,11 @@ __device__ __forceinline__ void bulk_g2s(uint32_t dst_smem, const void* src, uin
                "l"(src), "r"(bytes), "r"(bar)
                : "memory");
 }
+// global -> L2 only (no shared-memory destination, no completion): lets a CTA run DRAM reads many tiles ahead of
+// its small shared-memory ring, so the ring's bulk copies see L2-hit latency instead of DRAM latency
+__device__ __forceinline__ void bulk_prefetch_l2(const void* src, uint32_t bytes) {
+  asm volatile("cp.async.bulk.prefetch.L2.global [%0], %1;" ::"l"(src), "r"(bytes) : "memory");
+}
 // generic-proxy writes to shared memory -> visible to the async proxy (UMMA operand reads, bulk stores)
 __device__ __forceinline__ void fence_proxy_async_smem() { asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); }
 

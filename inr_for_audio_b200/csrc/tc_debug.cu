@@ -87,7 +87,7 @@ int inr_dbg_tc_dw(int H, const float* dZ, const float* S, float* gW, int64_t row
   k_img_from_rows<<<592, 256, 0, st>>>(dZ, rows, rp, H, iZ);
   k_img_from_rows<<<592, 256, 0, st>>>(S, rows, rp, H, iS);
   DwParams p;
-  p.dZ = iZ; p.S = iS; p.gW = gW; p.num_tiles = (int)(rp / TILE_ROWS);
+  p.dZ = iZ; p.S = iS; p.gW = gW; p.gb = nullptr; p.num_tiles = (int)(rp / TILE_ROWS);
   p.lbo = 128; p.sbo = TILE_ROWS * 16;
   if (variant & 1) { uint32_t t = p.lbo; p.lbo = p.sbo; p.sbo = t; }
   return tc_dw(H, p, st);

@@ -98,9 +98,24 @@ __global__ void __launch_bounds__(LayerCfg<H>::THREADS, 1) k_tc_layer(const Laye
       mbar_arrive_expect_tx(bar_bfull, Cfg::B_BYTES);
       const uint8_t* bsrc = reinterpret_cast<const uint8_t*>(p.Bpack) + (size_t)q * Cfg::B_BYTES;
       for (int off = 0; off < Cfg::B_BYTES; off += 32768) bulk_g2s(sB + off, bsrc + off, 32768, bar_bfull);
+      // DRAM latency under load (~2 us, profiles/r01) times the ring's 64 KB would cap a CTA at ~35 GB/s, a third of
+      // what the MMA consumes; so every tile is pulled into L2 PF tiles ahead with cp.async.bulk.prefetch.L2 (no
+      // shared memory needed) and the ring's copies then run at L2-hit latency.  The NQ CTAs that share a row tile
+      // split its chunks between them; the BWD epilogue's C_{l-1} slice is prefetched the same way.
+      constexpr int PF = 4;
+      auto prefetch_tile = [&](int tile) {
+        if (tile >= p.num_tiles) return;
+        const uint8_t* asrc = reinterpret_cast<const uint8_t*>(p.A) + (size_t)tile * (TILE_ROWS * H * 2);
+        for (int c = q; c < Cfg::NCHUNK; c += Cfg::NQ) bulk_prefetch_l2(asrc + (size_t)c * Cfg::A_STAGE_BYTES, Cfg::A_STAGE_BYTES);
+        if (MODE == MODE_BWD)
+          bulk_prefetch_l2(reinterpret_cast<const uint8_t*>(p.Cin) + (size_t)tile * (TILE_ROWS * H * 2) +
+                               (size_t)q * (NS / 8) * (TILE_ROWS * 16), (NS / 8) * (TILE_ROWS * 16));
+      };
+      for (int d = 0; d < PF; ++d) prefetch_tile(tile0 + d * tile_stride);
       int s = 0;
       uint32_t phase = 0;
       for (int tile = tile0; tile < p.num_tiles; tile += tile_stride) {
+        prefetch_tile(tile + PF * tile_stride);
         const uint8_t* asrc = reinterpret_cast<const uint8_t*>(p.A) + (size_t)tile * (TILE_ROWS * H * 2);
         for (int c = 0; c < Cfg::NCHUNK; ++c) {
           mbar_wait(bar_empty(s), phase ^ 1);
@@ -145,19 +160,31 @@ __global__ void __launch_bounds__(LayerCfg<H>::THREADS, 1) k_tc_layer(const Laye
     const int half = e >> 2;
     const int row = quad * 32 + lane;
     int it = 0;
+    // BWD: the C_{l-1} operand of the epilogue comes from HBM; it does not depend on the MMA, so the loads for a
+    // tile are issued one whole tile ahead (into the registers the previous tile has just consumed) and their
+    // ~1 us latency hides behind the tile's MMA instead of serialising with it (profiles/r01: 63 % long_sb).
+    constexpr int NCH = NS / 64;                          // 32-column chunks per warp
+    uint4 cin[NCH][4];
+    auto cin_ptr = [&](int tile, int ci, int j) {
+      const int g0 = (q * NS + (half + 2 * ci) * 32) >> 3;
+      return reinterpret_cast<const uint4*>(p.Cin + (size_t)tile * (TILE_ROWS * H) + ((size_t)(g0 + j) * TILE_ROWS + row) * 8);
+    };
+    if (MODE == MODE_BWD && tile0 < p.num_tiles) {
+#pragma unroll
+      for (int ci = 0; ci < NCH; ++ci)
+#pragma unroll
+        for (int j = 0; j < 4; ++j) cin[ci][j] = *cin_ptr(tile0, ci, j);
+    }
     for (int tile = tile0; tile < p.num_tiles; tile += tile_stride, ++it) {
       const int buf = it & 1;
       mbar_wait(bar_tfull(buf), (it >> 1) & 1);
       tc_fence_after();
       const size_t tile_off = (size_t)tile * (TILE_ROWS * H);
-      for (int c = half; c < NS / 32; c += 2) {
-        const int g0 = (q * NS + c * 32) >> 3;                // first feature group of this 32-column chunk
-        uint4 cin[4];
-        if (MODE == MODE_BWD) {
+      const int next_tile = tile + tile_stride;
 #pragma unroll
-          for (int j = 0; j < 4; ++j)
-            cin[j] = *reinterpret_cast<const uint4*>(p.Cin + tile_off + ((size_t)(g0 + j) * TILE_ROWS + row) * 8);
-        }
+      for (int ci = 0; ci < NCH; ++ci) {
+        const int c = half + 2 * ci;
+        const int g0 = (q * NS + c * 32) >> 3;                // first feature group of this 32-column chunk
         float v[32];
         tmem_ld32(tmem_base + buf * NS + c * 32 + ((uint32_t)(quad * 32) << 16), v);
         tmem_ld_wait();
@@ -180,7 +207,7 @@ __global__ void __launch_bounds__(LayerCfg<H>::THREADS, 1) k_tc_layer(const Laye
             *reinterpret_cast<uint4*>(p.out0 + off) = make_uint4(o0[0], o0[1], o0[2], o0[3]);
             if (p.out1) *reinterpret_cast<uint4*>(p.out1 + off) = make_uint4(o1[0], o1[1], o1[2], o1[3]);
           } else {
-            const uint32_t cw[4] = {cin[j].x, cin[j].y, cin[j].z, cin[j].w};
+            const uint32_t cw[4] = {cin[ci][j].x, cin[ci][j].y, cin[ci][j].z, cin[ci][j].w};
 #pragma unroll
             for (int h = 0; h < 4; ++h) {
               const int cc = j * 8 + h * 2;
@@ -189,6 +216,7 @@ __global__ void __launch_bounds__(LayerCfg<H>::THREADS, 1) k_tc_layer(const Laye
             }
             const size_t off = tile_off + ((size_t)(g0 + j) * TILE_ROWS + row) * 8;
             *reinterpret_cast<uint4*>(p.out0 + off) = make_uint4(o0[0], o0[1], o0[2], o0[3]);
+            if (next_tile < p.num_tiles) cin[ci][j] = *cin_ptr(next_tile, ci, j);
           }
         }
       }
@@ -216,8 +244,9 @@ struct DwCfg {
   static constexpr int B_BYTES = NB * TILE_ROWS * 2;   // 64 KB / 32 KB of S
   static constexpr int STAGE_BYTES = A_BYTES + B_BYTES;
   static constexpr int STAGES = 2;
-  static constexpr int TMEM_COLS = NB;
-  static constexpr int OFF_BAR = STAGES * STAGE_BYTES;
+  static constexpr int TMEM_COLS = 2 * NB;             // [0,NB) dW block, [NB,NB+16) bias column sums (power of two)
+  static constexpr int OFF_ONES = STAGES * STAGE_BYTES; // 512 B of bf16 1.0: the B operand of the bias-gradient MMA
+  static constexpr int OFF_BAR = OFF_ONES + 512;
   static constexpr int SMEM_BYTES = OFF_BAR + 64;
   static constexpr int THREADS = 192;                  // producer, MMA, 4 epilogue warps
 };
@@ -226,6 +255,7 @@ struct DwParams {
   const __nv_bfloat16* dZ;   // tile images of dZ_l   (M operand: out features)
   const __nv_bfloat16* S;    // tile images of S_{l-1} (N operand: in features)
   float* gW;                 // fp32 gradient of W_l, row-major [H out][H in], accumulated with atomics
+  float* gb;                 // fp32 gradient of b_l (H), or NULL: gb[o] += sum_r dZ[r][o] = dZ^T 1, an N=16 MMA against ones
   int num_tiles;
   uint32_t lbo, sbo;         // MN-major strides: LBO = 128 (8-row k groups), SBO = 2048 (feature groups)
 };
@@ -247,12 +277,15 @@ __global__ void __launch_bounds__(DwCfg<H>::THREADS, 1) k_tc_dw(const DwParams p
   const int tile0 = blockIdx.x / Cfg::NBLOCKS;
   const int tile_stride = gridDim.x / Cfg::NBLOCKS;
   const bool has_work = tile0 < p.num_tiles;
+  const bool do_bias = (p.gb != nullptr);   // the NBLK CTAs that share an A slice take alternate tiles of the bias sums
 
   if (threadIdx.x == 0) {
     for (int s = 0; s < Cfg::STAGES; ++s) { mbar_init(bar_full(s), 1); mbar_init(bar_empty(s), 1); }
     mbar_init(bar_tfull, 1);
     mbar_fence_init();
   }
+  for (int i = threadIdx.x; i < 128; i += blockDim.x) reinterpret_cast<uint32_t*>(smem + Cfg::OFF_ONES)[i] = 0x3F803F80u;
+  fence_proxy_async_smem();
   if (warp == 1) {
     tmem_alloc(smem_u32(tmem_slot), Cfg::TMEM_COLS);
     tmem_relinquish();
@@ -264,12 +297,26 @@ __global__ void __launch_bounds__(DwCfg<H>::THREADS, 1) k_tc_dw(const DwParams p
 
   if (warp == 0) {
     if (lane == 0) {
+      constexpr int PF = 3;   // tiles pulled into L2 ahead of the 2-stage ring (see k_tc_layer)
+      auto a_of = [&](int tile) {
+        return reinterpret_cast<const uint8_t*>(p.dZ) + (size_t)tile * (TILE_ROWS * H * 2) + (size_t)(mb * 16) * (TILE_ROWS * 16);
+      };
+      auto b_of = [&](int tile) {
+        return reinterpret_cast<const uint8_t*>(p.S) + (size_t)tile * (TILE_ROWS * H * 2) + (size_t)(nb * (Cfg::NB / 8)) * (TILE_ROWS * 16);
+      };
+      // the NBLK CTAs sharing an A slice and the MBLK CTAs sharing a B slice split the prefetch between them
+      auto prefetch_tile = [&](int tile) {
+        if (tile >= p.num_tiles) return;
+        if ((tile / tile_stride) % Cfg::NBLK == nb) bulk_prefetch_l2(a_of(tile), Cfg::A_BYTES);
+        if ((tile / tile_stride) % Cfg::MBLK == mb) bulk_prefetch_l2(b_of(tile), Cfg::B_BYTES);
+      };
+      for (int d = 0; d < PF; ++d) prefetch_tile(tile0 + d * tile_stride);
       int s = 0;
       uint32_t phase = 0;
       for (int tile = tile0; tile < p.num_tiles; tile += tile_stride) {
-        const size_t tile_bytes = (size_t)tile * (TILE_ROWS * H * 2);
-        const uint8_t* a_src = reinterpret_cast<const uint8_t*>(p.dZ) + tile_bytes + (size_t)(mb * 16) * (TILE_ROWS * 16);
-        const uint8_t* b_src = reinterpret_cast<const uint8_t*>(p.S) + tile_bytes + (size_t)(nb * (Cfg::NB / 8)) * (TILE_ROWS * 16);
+        prefetch_tile(tile + PF * tile_stride);
+        const uint8_t* a_src = a_of(tile);
+        const uint8_t* b_src = b_of(tile);
         mbar_wait(bar_empty(s), phase ^ 1);
         mbar_arrive_expect_tx(bar_full(s), Cfg::STAGE_BYTES);
         const uint32_t dst = smem_base + s * Cfg::STAGE_BYTES;
@@ -296,6 +343,13 @@ __global__ void __launch_bounds__(DwCfg<H>::THREADS, 1) k_tc_dw(const DwParams p
           const uint64_t bd = make_smem_desc(b0 + kk * 256, p.lbo, p.sbo);
           umma_bf16(tmem_base, ad, bd, idesc, (it | kk) != 0 ? 1u : 0u);
         }
+        if (do_bias && (it % Cfg::NBLK) == nb) {   // every element of the ones block is 1.0, so its strides only have to stay inside the block
+          constexpr uint32_t idesc1 = make_idesc_bf16(128, 16, 1, 1);
+          const uint64_t od = make_smem_desc(smem_base + Cfg::OFF_ONES, 128, 256);
+#pragma unroll
+          for (int kk = 0; kk < TILE_ROWS / 16; ++kk)
+            umma_bf16(tmem_base + Cfg::NB, make_smem_desc(a0 + kk * 256, p.lbo, p.sbo), od, idesc1, (it >= Cfg::NBLK || kk != 0) ? 1u : 0u);
+        }
         umma_commit(bar_empty(s));
         if (++s == Cfg::STAGES) { s = 0; phase ^= 1; }
       }
@@ -313,6 +367,12 @@ __global__ void __launch_bounds__(DwCfg<H>::THREADS, 1) k_tc_dw(const DwParams p
       tmem_ld_wait();
 #pragma unroll
       for (int j = 0; j < 8; ++j) red_add_v4(grow + c * 32 + j * 4, v[4 * j], v[4 * j + 1], v[4 * j + 2], v[4 * j + 3]);
+    }
+    if (do_bias && (p.num_tiles - tile0 + tile_stride - 1) / tile_stride > nb) {   // this CTA issued at least one bias MMA
+      float v[32];
+      tmem_ld32(tmem_base + Cfg::NB + ((uint32_t)(quad * 32) << 16), v);   // columns 0..15 all hold the column sum
+      tmem_ld_wait();
+      atomicAdd(p.gb + mb * 128 + row, v[0]);
     }
   }
   tc_fence_before();
