@@ -9,7 +9,9 @@
 //     k_tc_dw          gW_l += dZ_l^T S_{l-1}                                                       l = L..1
 //     k_tc_layer<BWD>  dZ_{l-1} = (dZ_l W_l) omega C_{l-1}  (over C_{l-1})                          l = L..1
 //     k_tc_colsum      gb_l += colsum(dZ_l); gw_out += gvec^T S_L; gW_0 += dZ_0^T x, gb_0 += colsum(dZ_0)
-#include "tc_gemm.cuh"
+#include <stdlib.h>
+
+#include "tc_gemm2.cuh"
 
 namespace inr {
 using namespace tc;
@@ -254,7 +256,16 @@ bool siren_tc_supported(const inr_siren_desc* d) {
   return (H == 128 || H == 256 || H == 512) && d->hidden_layers >= 1 && d->out_features == 1;
 }
 
-static int ns_of(int H) { return H >= 512 ? 128 : H; }
+// INR_TC_PAIR=0 selects the single-CTA layer kernel of tc_gemm.cuh (kept as the A/B baseline of profiles/r01_*);
+// the default is the CTA-pair kernel of tc_gemm2.cuh.
+bool tc_pair_mode() {
+  static int v = -1;
+  if (v < 0) { const char* e = getenv("INR_TC_PAIR"); v = (e && e[0] == '0') ? 0 : 1; }
+  return v != 0;
+}
+// columns of the packed weight slices ([slice][K/8][ns][8]): one slice per CTA
+int tc_ns(int H) { return tc_pair_mode() ? (H >= 256 ? 128 : H / 2) : (H >= 512 ? 128 : H); }
+static int ns_of(int H) { return tc_ns(H); }
 
 struct TcPlan {
   int64_t pack_bytes, gvec_bytes, img_bytes_per_row, fixed_bytes;
@@ -314,7 +325,31 @@ static int launch_dw(const DwParams& p, cudaStream_t st) {
   return INR_OK;
 }
 
+template <int H, int MODE>
+static int launch_layer2(const LayerParams& p, cudaStream_t st) {
+  using Cfg = Layer2Cfg<H>;
+  static bool attr_set = false;
+  if (!attr_set) {
+    INR_CUDA_CHECK(cudaFuncSetAttribute(k_tc_layer2<H, MODE>, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg::SMEM_BYTES));
+    attr_set = true;
+  }
+  int pairs = (num_sms() / 2) / Cfg::NQ * Cfg::NQ;
+  const int max_useful = ((p.num_tiles + 1) / 2) * Cfg::NQ;
+  if (pairs > max_useful) pairs = max_useful;
+  { LaunchScope ls(MODE == MODE_FWD ? "k_tc_layer_fwd" : "k_tc_layer_bwd", st);
+    k_tc_layer2<H, MODE><<<2 * pairs, Cfg::THREADS, Cfg::SMEM_BYTES, st>>>(p); }
+  INR_LAUNCH_CHECK();
+  return INR_OK;
+}
+
 int tc_layer(int H, int mode, const LayerParams& p, cudaStream_t st) {
+  if (tc_pair_mode()) {
+    switch (H) {
+      case 128: return mode == MODE_FWD ? launch_layer2<128, MODE_FWD>(p, st) : launch_layer2<128, MODE_BWD>(p, st);
+      case 256: return mode == MODE_FWD ? launch_layer2<256, MODE_FWD>(p, st) : launch_layer2<256, MODE_BWD>(p, st);
+      case 512: return mode == MODE_FWD ? launch_layer2<512, MODE_FWD>(p, st) : launch_layer2<512, MODE_BWD>(p, st);
+    }
+  }
   switch (H) {
     case 128: return mode == MODE_FWD ? launch_layer<128, MODE_FWD>(p, st) : launch_layer<128, MODE_BWD>(p, st);
     case 256: return mode == MODE_FWD ? launch_layer<256, MODE_FWD>(p, st) : launch_layer<256, MODE_BWD>(p, st);

@@ -7,6 +7,7 @@ namespace inr {
 using namespace tc;
 int tc_layer(int H, int mode, const LayerParams& p, cudaStream_t st);
 int tc_dw(int H, const DwParams& p, cudaStream_t st);
+int tc_ns(int H);
 
 __global__ void k_img_from_rows(const float* __restrict__ X, int64_t rows, int64_t rows_pad, int H, __nv_bfloat16* img) {
   const int64_t total = rows_pad * H;
@@ -52,7 +53,7 @@ int inr_dbg_tc_layer(int H, int mode, const float* A, const float* W, const floa
   INR_REQUIRE(H == 128 || H == 256 || H == 512, INR_E_UNSUPPORTED, "H=%d", H);
   INR_REQUIRE(scratch_bytes >= inr_dbg_tc_scratch_bytes(H, rows), INR_E_WORKSPACE, "scratch too small");
   const int64_t rp = round_up(rows, TILE_ROWS);
-  const int NS = H >= 512 ? 128 : H;
+  const int NS = tc_ns(H);
   __nv_bfloat16* iA = (__nv_bfloat16*)scratch;
   __nv_bfloat16* iO0 = iA + rp * H;
   __nv_bfloat16* iO1 = iO0 + rp * H;

@@ -1,0 +1,247 @@
+// tc_gemm2.cuh -- CTA-pair (tcgen05 cta_group::2) version of the weight-stationary layer GEMM of tc_gemm.cuh.
+//
+// Why pairs (profiles/r01_layer_ablation.md): with one CTA per 128x128 output slice the A stream needs 64 B per MMA
+// cycle per SM; the 64 KB ring left beside the 128 KB weight slice sustains ~20 B/cycle at the measured bulk-copy
+// latency, so the tensor pipe idled 68 % of the time and every A tile crossed the L2 fabric four times.  A pair
+// runs ONE 256-row x NP-column MMA per K step: each CTA stages only its own 128 rows of A and HALF of the
+// weight slice (NP/2 columns), and receives its own 128 rows x NP columns of D in its own TMEM.  Per SM that is
+// half the A bytes per MAC, half the fabric traffic, the same shared-memory budget.
+//
+//   k_tc_layer2<H, MODE>   grid = 2 * pairs, __cluster_dims__(2); pair g handles N-slice q = g % NQ of double
+//                          tiles dt = g / NQ, + pairs/NQ, ...; CTA rank r of the pair owns row tile 2*dt + r.
+//   warp 0 = bulk-copy producer (own A rows, own B half), warp 1 = MMA issuer in the leader (rank 0) / barrier
+//   relay in the peer, warps 2..9 = epilogue (as in tc_gemm.cuh, over NP columns).
+//
+// Barriers (s = ring stage, b = accumulator buffer; "both" = same offset in both CTAs):
+//   full[s]    leader: 2 arrivals = own producer (with tx bytes) + peer relay;  peer: 1 = own producer (tx)
+//   empty[s]   both: 1 arrival, multicast by the leader's tcgen05.commit once the MMAs reading stage s are done
+//   tfull[b]   both: 1 arrival, multicast commit once the tile's last MMA is done
+//   tempty[b]  leader: 16 arrivals = 8 local epilogue warps + 8 remote (peer's epilogue warps)
+//   bfull      leader: 2 (own producer tx + peer relay); peer: 1 (own producer tx)
+#pragma once
+#include "tc_gemm.cuh"
+
+namespace inr {
+namespace tc {
+
+template <int H>
+struct Layer2Cfg {
+  static constexpr int NP = (H >= 256) ? 256 : H;   // output features per pair (MMA N)
+  static constexpr int NC = NP / 2;                 // B columns staged by each CTA
+  static constexpr int NQ = H / NP;                 // N slices
+  static constexpr int KC = 64;                     // K columns per ring stage
+  static constexpr int NCHUNK = H / KC;
+  static constexpr int B_BYTES = H * NC * 2;        // 128 KB (H=512), 64 KB (256), 16 KB (128)
+  static constexpr int A_STAGE_BYTES = (KC / 8) * TILE_ROWS * 16;  // 16 KB
+  static constexpr int STAGES = (H >= 512) ? 4 : 8;
+  static constexpr int TMEM_COLS = 2 * NP;          // two accumulator buffers
+  static constexpr int OFF_A = B_BYTES;
+  static constexpr int OFF_BIAS = OFF_A + STAGES * A_STAGE_BYTES;
+  static constexpr int OFF_BAR = OFF_BIAS + NP * 4;
+  static constexpr int SMEM_BYTES = OFF_BAR + 256;
+  static constexpr int THREADS = 320;
+  static_assert(H == 128 || H == 256 || H == 512, "hidden width");
+};
+
+template <int H, int MODE>
+__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(Layer2Cfg<H>::THREADS, 1) k_tc_layer2(const LayerParams p) {
+  using Cfg = Layer2Cfg<H>;
+  constexpr int NP = Cfg::NP;
+  constexpr int NC = Cfg::NC;
+  extern __shared__ __align__(128) uint8_t smem[];
+  const uint32_t smem_base = smem_u32(smem);
+  const uint32_t sB = smem_base;
+  const uint32_t sA = smem_base + Cfg::OFF_A;
+  float* s_bias = reinterpret_cast<float*>(smem + Cfg::OFF_BIAS);
+  const uint32_t bar0 = smem_base + Cfg::OFF_BAR;
+  auto bar_full = [&](int s) { return bar0 + 8u * s; };
+  auto bar_empty = [&](int s) { return bar0 + 8u * (Cfg::STAGES + s); };
+  auto bar_tfull = [&](int b) { return bar0 + 8u * (2 * Cfg::STAGES + b); };
+  auto bar_tempty = [&](int b) { return bar0 + 8u * (2 * Cfg::STAGES + 2 + b); };
+  const uint32_t bar_bfull = bar0 + 8u * (2 * Cfg::STAGES + 4);
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(smem + Cfg::OFF_BAR + 8 * (2 * Cfg::STAGES + 5));
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const uint32_t rank = cluster_ctarank();
+  const bool leader = rank == 0;
+  const int pair = blockIdx.x >> 1;
+  const int npairs = gridDim.x >> 1;
+  const int q = pair % Cfg::NQ;
+  const int dt0 = pair / Cfg::NQ;
+  const int dt_stride = npairs / Cfg::NQ;
+  const int num_dt = (p.num_tiles + 1) >> 1;          // double tiles (the last may have only its rank-0 half)
+
+  if (threadIdx.x == 0) {
+    for (int s = 0; s < Cfg::STAGES; ++s) { mbar_init(bar_full(s), leader ? 2 : 1); mbar_init(bar_empty(s), 1); }
+    for (int b = 0; b < 2; ++b) { mbar_init(bar_tfull(b), 1); mbar_init(bar_tempty(b), 16); }
+    mbar_init(bar_bfull, leader ? 2 : 1);
+    mbar_fence_init();
+  }
+  if (MODE == MODE_FWD) {
+    for (int i = threadIdx.x; i < NP; i += blockDim.x) s_bias[i] = p.omega * p.bias[q * NP + i];
+  }
+  __syncthreads();
+  cluster_sync_all();                                 // both CTAs' barriers exist before anything can signal them
+  if (warp == 1) {
+    tmem_alloc2(smem_u32(tmem_slot), Cfg::TMEM_COLS);
+    tmem_relinquish2();
+  }
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot;
+
+  if (warp == 0) {
+    // ===================== producer: own half of the weight slice once, then own A rows through the ring =========
+    if (lane == 0) {
+      mbar_arrive_expect_tx(bar_bfull, Cfg::B_BYTES);
+      const uint8_t* bsrc = reinterpret_cast<const uint8_t*>(p.Bpack) + (size_t)(q * 2 + rank) * Cfg::B_BYTES;
+      constexpr int BPIECE = Cfg::B_BYTES < 32768 ? Cfg::B_BYTES : 32768;
+      for (int off = 0; off < Cfg::B_BYTES; off += BPIECE) bulk_g2s(sB + off, bsrc + off, BPIECE, bar_bfull);
+      int s = 0;
+      uint32_t phase = 0;
+      for (int dt = dt0; dt < num_dt; dt += dt_stride) {
+        const int tile = 2 * dt + (int)rank;
+        const bool valid = tile < p.num_tiles;
+        const uint8_t* asrc = reinterpret_cast<const uint8_t*>(p.A) + (size_t)tile * (TILE_ROWS * H * 2);
+        for (int c = 0; c < Cfg::NCHUNK; ++c) {
+          mbar_wait(bar_empty(s), phase ^ 1);
+          if (valid) {
+            mbar_arrive_expect_tx(bar_full(s), Cfg::A_STAGE_BYTES);
+            bulk_g2s(sA + s * Cfg::A_STAGE_BYTES, asrc + (size_t)c * Cfg::A_STAGE_BYTES, Cfg::A_STAGE_BYTES, bar_full(s));
+          } else {
+            mbar_arrive(bar_full(s));                 // odd tile count: the MMA multiplies stale rows, nobody stores them
+          }
+          if (++s == Cfg::STAGES) { s = 0; phase ^= 1; }
+        }
+      }
+    }
+  } else if (warp == 1) {
+    if (lane == 0) {
+      if (leader) {
+        // ===================== MMA issuer (one thread of the pair) =====================
+        constexpr uint32_t idesc = make_idesc_bf16(256, NP, 0, 0);
+        mbar_wait(bar_bfull, 0);
+        int s = 0;
+        uint32_t phase = 0;
+        int it = 0;
+        for (int dt = dt0; dt < num_dt; dt += dt_stride, ++it) {
+          const int buf = it & 1;
+          mbar_wait(bar_tempty(buf), ((it >> 1) & 1) ^ 1);
+          tc_fence_after();
+          const uint32_t d_tmem = tmem_base + buf * NP;
+          for (int c = 0; c < Cfg::NCHUNK; ++c) {
+            mbar_wait(bar_full(s), phase);
+            tc_fence_after();
+#pragma unroll
+            for (int kk = 0; kk < Cfg::KC / 16; ++kk) {
+              const uint64_t ad = make_smem_desc(sA + s * Cfg::A_STAGE_BYTES + kk * 2 * (TILE_ROWS * 16), p.a_lbo, p.a_sbo);
+              const uint64_t bd = make_smem_desc(sB + (c * (Cfg::KC / 8) + kk * 2) * (NC * 16), p.b_lbo, p.b_sbo);
+              umma2_bf16(d_tmem, ad, bd, idesc, (c | kk) != 0 ? 1u : 0u);
+            }
+            umma2_commit_mc(bar_empty(s), 3);
+            if (++s == Cfg::STAGES) { s = 0; phase ^= 1; }
+          }
+          umma2_commit_mc(bar_tfull(buf), 3);
+        }
+      } else {
+        // ===================== peer: forward "my operands have landed" to the leader's barriers ==============
+        mbar_wait(bar_bfull, 0);
+        mbar_arrive_remote(bar_bfull, 0);
+        int s = 0;
+        uint32_t phase = 0;
+        for (int dt = dt0; dt < num_dt; dt += dt_stride) {
+          for (int c = 0; c < Cfg::NCHUNK; ++c) {
+            mbar_wait(bar_full(s), phase);
+            mbar_arrive_remote(bar_full(s), 0);
+            if (++s == Cfg::STAGES) { s = 0; phase ^= 1; }
+          }
+        }
+      }
+    }
+  } else {
+    // ===================== epilogue: 8 warps, warp%4 = TMEM lane quadrant, two column-chunk parities =====
+    const int e = warp - 2;
+    const int quad = warp & 3;
+    const int half = e >> 2;
+    const int row = quad * 32 + lane;
+    constexpr int NCH = NP / 64;                          // 32-column chunks per warp
+    uint4 cin[NCH][4];
+    auto cin_ptr = [&](int tile, int ci, int j) {
+      const int g0 = (q * NP + (half + 2 * ci) * 32) >> 3;
+      return reinterpret_cast<const uint4*>(p.Cin + (size_t)tile * (TILE_ROWS * H) + ((size_t)(g0 + j) * TILE_ROWS + row) * 8);
+    };
+    if (MODE == MODE_BWD && 2 * dt0 + (int)rank < p.num_tiles) {
+#pragma unroll
+      for (int ci = 0; ci < NCH; ++ci)
+#pragma unroll
+        for (int j = 0; j < 4; ++j) cin[ci][j] = *cin_ptr(2 * dt0 + (int)rank, ci, j);
+    }
+    int it = 0;
+    for (int dt = dt0; dt < num_dt; dt += dt_stride, ++it) {
+      const int buf = it & 1;
+      const int tile = 2 * dt + (int)rank;
+      const bool valid = tile < p.num_tiles;
+      mbar_wait(bar_tfull(buf), (it >> 1) & 1);
+      tc_fence_after();
+      const size_t tile_off = (size_t)tile * (TILE_ROWS * H);
+      const int next_tile = tile + 2 * dt_stride;
+      if (valid) {
+#pragma unroll
+        for (int ci = 0; ci < NCH; ++ci) {
+          const int c = half + 2 * ci;
+          const int g0 = (q * NP + c * 32) >> 3;
+          float v[32];
+          tmem_ld32(tmem_base + buf * NP + c * 32 + ((uint32_t)(quad * 32) << 16), v);
+          tmem_ld_wait();
+#pragma unroll
+          for (int j = 0; j < 4; ++j) {
+            uint32_t o0[4], o1[4];
+            const size_t off = tile_off + ((size_t)(g0 + j) * TILE_ROWS + row) * 8;
+            if (MODE == MODE_FWD) {
+#pragma unroll
+              for (int h = 0; h < 4; ++h) {
+                const int cc = j * 8 + h * 2;
+                const float t0 = __fmaf_rn(v[cc], p.omega, s_bias[c * 32 + cc]);
+                const float t1 = __fmaf_rn(v[cc + 1], p.omega, s_bias[c * 32 + cc + 1]);
+                float s0, c0, s1, c1;
+                __sincosf(t0, &s0, &c0);
+                __sincosf(t1, &s1, &c1);
+                o0[h] = pack_bf16x2(s0, s1);
+                o1[h] = pack_bf16x2(c0, c1);
+              }
+              *reinterpret_cast<uint4*>(p.out0 + off) = make_uint4(o0[0], o0[1], o0[2], o0[3]);
+              if (p.out1) *reinterpret_cast<uint4*>(p.out1 + off) = make_uint4(o1[0], o1[1], o1[2], o1[3]);
+            } else {
+              const uint32_t cw[4] = {cin[ci][j].x, cin[ci][j].y, cin[ci][j].z, cin[ci][j].w};
+#pragma unroll
+              for (int h = 0; h < 4; ++h) {
+                const int cc = j * 8 + h * 2;
+                const float2 cf = unpack_bf16x2(cw[h]);
+                o0[h] = pack_bf16x2(v[cc] * p.omega * cf.x, v[cc + 1] * p.omega * cf.y);
+              }
+              *reinterpret_cast<uint4*>(p.out0 + off) = make_uint4(o0[0], o0[1], o0[2], o0[3]);
+              if (next_tile < p.num_tiles) cin[ci][j] = *cin_ptr(next_tile, ci, j);
+            }
+          }
+        }
+      }
+      tc_fence_before();
+      __syncwarp();
+      if (lane == 0) {
+        if (leader) mbar_arrive(bar_tempty(buf));
+        else mbar_arrive_remote(bar_tempty(buf), 0);
+      }
+    }
+  }
+  tc_fence_before();
+  __syncthreads();
+  cluster_sync_all();                                 // the peer's TMEM reads and remote arrivals are done
+  if (warp == 1) {
+    tc_fence_after();
+    tmem_dealloc2(tmem_base, Cfg::TMEM_COLS);
+  }
+}
+
+}  // namespace tc
+}  // namespace inr
