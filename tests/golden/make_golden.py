@@ -175,6 +175,32 @@ def make_converge():
     np.savez_compressed(os.path.join(HERE, "converge.npz"), **out)
 
 
+def make_converge_ens():
+    """The reference's own run-to-run distribution of the running-minimum loss envelope: the same seed-0 fit as
+    make_converge, run with 1..8 intra-op threads (each thread count changes only the summation order of the
+    reference's GEMM/reductions, which is enough to decorrelate the trajectories after ~20 steps)."""
+    sr, data = gt_bach(8192, 44100)
+    gtn = data / np.max(np.abs(data))
+    sig = float(np.mean(gtn.astype(np.float64) ** 2))
+    gt = torch.from_numpy(gtn).view(1, -1, 1)
+    coords = ref.utils.get_coord(8192, 1).view(1, -1, 1)
+    steps = 1500
+    marks = np.array([99, 299, 599, 999, 1499])
+    env, final_snr = [], []
+    for nt in range(1, 9):
+        torch.set_num_threads(nt)
+        torch.manual_seed(0)
+        m = ref.models.Siren(1, 128, 2, 1, True)
+        losses, _, _ = ref_fit(m, coords, gt, steps)
+        e = 10 * np.log10(sig / np.minimum.accumulate(np.asarray(losses, dtype=np.float64)))
+        env.append(e[marks])
+        final_snr.append(ref.utils.calculate_snr(gtn, m(coords).detach().numpy().ravel()))
+        print("threads", nt, "envelope dB", np.round(e[marks], 2), "final-step SNR %.2f" % final_snr[-1], flush=True)
+    torch.set_num_threads(8)
+    np.savez_compressed(os.path.join(HERE, "converge_ens.npz"), marks=marks, env_db=np.array(env),
+                        final_snr=np.array(final_snr), threads=np.arange(1, 9), steps=np.array(steps))
+
+
 # ---------------------------------------------------------------- MDCT / window (mdct.py, window.py)
 def make_mdct():
     out = {}

@@ -142,19 +142,10 @@ def test_c1_full_size_first_steps(pkg, golden):
     np.testing.assert_allclose(f.losses(), g["c1_losses"], rtol=1e-3)
 
 
-def test_convergence_envelope_matches_reference_band(pkg, golden):
-    """SNR parity after the same step count (north star: within 0.1 dB).
-
-    Measured fact (tools/converge_probe.py, profiles/r01_convergence.md): full-batch Adam at lr 1e-3 on a SIREN
-    produces loss SPIKES (the reference's own curve has >130 steps more than 10x above its running minimum), and
-    the reference does not reproduce itself: its 1-thread and 8-thread runs end at 44.79 and 42.04 dB, torch
-    eager on the B200 at 31.45 dB (inside a spike), three runs of this code at 0.23 / 41.47 / 44.17 dB.  The SNR
-    of the weights at one fixed step is therefore not a usable statistic.  What IS reproducible is the
-    running-minimum loss envelope; it is compared in dB (10 log10 signal/loss, the SNR the best weights so far
-    would give) at fixed step counts: within 0.1 dB (+ the reference's own band) while the trajectories still
-    coincide (step 100), within the reference's band +- 1 dB at 300/600, and not below the band by more than
-    3 dB at 1500 where runs have fully decorrelated (reference band there: 2.75 dB)."""
-    g = golden("converge")
+def _envelope_vs_ensemble(pkg, golden, precision, first_rtol):
+    """Fit the converge.npz case, return [(step, ours_dB, ens_min, ens_max, ens_std)] of the running-minimum loss
+    envelope against the reference's own 8-run ensemble (tests/golden/converge_ens.npz)."""
+    g, ens = golden("converge"), golden("converge_ens")
     from scipy.io import wavfile
     sr, data = wavfile.read(os.path.join(ROOT, "data", "gt_bach.wav"))
     data = data.astype(np.float32)[44100:44100 + 8192]
@@ -162,30 +153,35 @@ def test_convergence_envelope_matches_reference_band(pkg, golden):
     sig = float(np.mean(gtn.astype(np.float64) ** 2))
     torch.manual_seed(0)
     model = pkg.Siren(1, 128, 2, 1, True)
-    f = pkg.SirenFitter(model.spec, model.flat_parameters(), torch.from_numpy(gtn).to(dev()))
-    steps = int(g["steps"])
-    f.step(steps)
+    f = pkg.SirenFitter(model.spec, model.flat_parameters(), torch.from_numpy(gtn).to(dev()), precision=precision)
+    f.step(int(ens["steps"]))
     losses = f.losses().astype(np.float64)
-    np.testing.assert_allclose(losses[:3], g["all_losses_t1"][:3], rtol=1e-3)
-
-    def env_db(l, i):
-        return 10 * np.log10(sig / np.minimum.accumulate(np.asarray(l, dtype=np.float64))[i])
+    np.testing.assert_allclose(losses[:3], g["all_losses_t1"][:3], rtol=first_rtol)
+    env = 10 * np.log10(sig / np.minimum.accumulate(losses))
     rows = []
-    # upper side: a run that is AHEAD of the reference band is decorrelation, not an error (measured on B200:
-    # 31.81 dB at step 600 against a band of 28.9-29.8 dB), so the upper tolerance is the reference's own late
-    # band width (3 dB) once the trajectories have separated; the lower side is the parity criterion.
-    for i, tol_lo, tol_hi in ((99, 0.1, 0.1), (299, 1.0, 3.0), (599, 1.0, 3.0), (1499, 3.0, None)):
-        ours = env_db(losses, i)
-        r1, r8 = env_db(g["all_losses_t1"], i), env_db(g["all_losses_t8"], i)
-        lo, hi = min(r1, r8), max(r1, r8)
-        rows.append((i + 1, ours, r1, r8))
-        assert ours >= lo - tol_lo, (i, ours, lo)
-        if tol_hi is not None:
-            assert ours <= hi + tol_hi, (i, ours, hi)
+    for j, i in enumerate(ens["marks"]):
+        col = ens["env_db"][:, j]
+        rows.append((int(i) + 1, float(env[int(i)]), float(col.min()), float(col.max()), float(col.std(ddof=1))))
     final_snr = float(pkg.calculate_snr(gtn, f.forward().cpu().numpy()))
-    print("best-so-far SNR dB at step: " + "; ".join("%d: ours %.2f ref(1t) %.2f ref(8t) %.2f" % r for r in rows))
-    print("final-step SNR (spike-dominated, informational): ours %.2f dB, reference %.2f / %.2f dB" % (
-        final_snr, float(g["snr_t1"]), float(g["snr_t8"])))
+    print(precision + " best-so-far SNR dB at step: " + "; ".join(
+        "%d: ours %.2f ref [%.2f, %.2f] sd %.2f" % r for r in rows))
+    print("final-step SNR (spike-dominated, informational): ours %.2f dB, reference runs %s dB" % (
+        final_snr, np.round(ens["final_snr"], 2)))
+    return rows
+
+
+def test_convergence_envelope_matches_reference_band(pkg, golden):
+    """SNR parity after the same step count (north star: within 0.1 dB).
+
+    Measured fact (tests/golden/make_golden.py make_converge_ens): full-batch Adam at lr 1e-3 on a SIREN produces
+    loss SPIKES and the reference does not reproduce itself -- the SAME seed-0 fit run by the unmodified reference
+    with 1..8 intra-op threads (only the summation order changes) ends with final-step SNRs from 8.5 to 44.8 dB,
+    and its best-so-far (running-minimum loss) SNR at step 1500 spans 37.2 .. 44.8 dB (sd 2.8 dB); at step 100,
+    where trajectories still nearly coincide, the ensemble spans 0.18 dB.  "Within 0.1 dB" is therefore tested as:
+    our envelope lies inside the reference ensemble's own [min, max] band widened by 0.1 dB plus one ensemble
+    standard deviation (the band of 8 samples underestimates the support of the distribution)."""
+    for step, ours, lo, hi, sd in _envelope_vs_ensemble(pkg, golden, "fp32", 1e-3):
+        assert lo - 0.1 - sd <= ours <= hi + 0.1 + sd, (step, ours, lo, hi, sd)
 
 
 def test_module_autograd_route_matches_engine(pkg, golden):
@@ -283,28 +279,8 @@ def test_bf16_c1_first_steps(pkg, golden):
 
 
 def test_bf16_convergence_envelope(pkg, golden):
-    """Same protocol as the fp32 envelope test, for the tensor-core mode (H=128 is the smallest width it takes)."""
-    g = golden("converge")
-    from scipy.io import wavfile
-    sr, data = wavfile.read(os.path.join(ROOT, "data", "gt_bach.wav"))
-    data = data.astype(np.float32)[44100:44100 + 8192]
-    gtn = data / np.max(np.abs(data))
-    sig = float(np.mean(gtn.astype(np.float64) ** 2))
-    torch.manual_seed(0)
-    model = pkg.Siren(1, 128, 2, 1, True)
-    f = pkg.SirenFitter(model.spec, model.flat_parameters(), torch.from_numpy(gtn).to(dev()), precision="bf16")
-    f.step(int(g["steps"]))
-    losses = f.losses().astype(np.float64)
-    np.testing.assert_allclose(losses[:3], g["all_losses_t1"][:3], rtol=2e-3)
-
-    def env_db(l, i):
-        return 10 * np.log10(sig / np.minimum.accumulate(np.asarray(l, dtype=np.float64))[i])
-    rows = []
-    # measured on B200 (runs differ: fp32 atomics order + bf16 operands): step 100 -0.44 dB; step 1500 between -6.7 and
-    # +2 dB of the reference's lower curve, whose own two runs are 2.75 dB apart there (fully decorrelated phase)
-    for i, tol in ((99, 1.0), (299, 1.5), (599, 2.0), (1499, 8.0)):
-        ours = env_db(losses, i)
-        lo = min(env_db(g["all_losses_t1"], i), env_db(g["all_losses_t8"], i))
-        rows.append((i + 1, ours, lo))
-        assert ours >= lo - tol, (i, ours, lo)
-    print("bf16 best-so-far SNR dB at step: " + "; ".join("%d: ours %.2f ref-min %.2f" % r for r in rows))
+    """Same protocol as the fp32 envelope test, for the tensor-core mode (H=128 is the smallest width it takes):
+    bf16 operands perturb the first steps by ~1e-3, after which the run is one more member of the ensemble."""
+    for step, ours, lo, hi, sd in _envelope_vs_ensemble(pkg, golden, "bf16", 2e-3):
+        tol = 0.5 if step <= 100 else 0.1   # step 100: bf16 operand rounding measured at -0.44 dB
+        assert lo - tol - sd <= ours <= hi + tol + sd, (step, ours, lo, hi, sd)
