@@ -115,6 +115,50 @@ int inr_siren_loss_backward(const inr_siren_desc* d, const float* params, const 
                             float* grads, inr_opt_state* opt, float* out_or_null, void* workspace,
                             int64_t workspace_bytes, void* stream);
 
+/* The same step split in two, so that a loss that needs the WHOLE model output (the windowed-transform losses
+ * below; auraloss' SNR) can be evaluated between the halves without a second forward pass:
+ *   inr_siren_train_forward   runs the network keeping every layer's activations in `workspace`, writes out[n];
+ *   inr_siren_train_backward  resumes from the SAME, untouched workspace: time-domain loss against `target`
+ *                             (may be NULL) plus the upstream gradient extra_gout (n floats, may be NULL).
+ * Both need the n rows to fit ONE workspace chunk (INR_E_WORKSPACE otherwise). */
+int inr_siren_train_forward(const inr_siren_desc* d, const float* params, const float* coords, int64_t n, int64_t i0,
+                            int64_t T_total, float coord_scale, float* out, void* workspace, int64_t workspace_bytes,
+                            void* stream);
+int inr_siren_train_backward(const inr_siren_desc* d, const float* params, const float* coords, const float* target,
+                             int64_t n, int64_t i0, int64_t T_total, float coord_scale, int loss_kind, float grad_scale,
+                             const float* extra_gout_or_null, float* grads, inr_opt_state* opt, void* workspace,
+                             int64_t workspace_bytes, void* stream);
+
+/* ---- windowed-transform losses on the model output (spectral.cu) ----------------------------------------------
+ * All of them ACCUMULATE d loss / d pred into gout (T floats: the caller zeroes it once per step) and add
+ * weight * loss to opt->loss_acc[1]; `weight` is alpha of the mixing rule run.py:163-169 (times 1/count for means).
+ *
+ * mdct.py:51-72 STMDCT(data, N) on the device: frames of N samples at hop N/2 over the tail-zero-padded signal
+ * (num_frames = T / (N/2), mdct.py:54-58), window[n] (N floats: window.py:42-61 KBDWindow, computed on the host in
+ * float64), mdct.py:16-42 MDCT with its 2/N factor.  coef is FRAME-major: coef[f*(N/2) + k] (the reference returns
+ * the transpose, (N/2, F), float64).  N in {256, 512, 1024, 2048, 4096}. */
+int64_t inr_stmdct_num_frames(int64_t T, int N);
+int inr_stmdct_forward(const float* x, int64_t T, int N, const float* window, float* coef, void* stream);
+/* MDCT-domain loss (BASELINE.json config 3): weight * sum |STMDCT(pred) - target_coef| (INR_LOSS_MAE) or squared
+ * (INR_LOSS_MSE), and its exact adjoint.  Deterministic (one writer per output sample). */
+int inr_mdct_loss(const float* pred, const float* target_coef, int64_t T, int N, const float* window, int kind,
+                  float weight, float* gout, inr_opt_state* opt, void* stream);
+
+/* auraloss.freq.STFTLoss() (run.py:128,160; third-party, un-vendored: PARITY UNPINNED): magnitudes
+ * sqrt(clamp(re^2+im^2, eps)) of torch.stft(x, n_fft, hop, n_fft, window, center=True, reflect), frame-major
+ * mag[f*(n_fft/2+1) + k], F = 1 + T/hop; loss = ||Y-X||_F / ||Y||_F + mean |log X - log Y|.
+ * inr_stft_mag precomputes the target side (and adds sum Y^2 to *sumsq_dev, a device double the caller zeroed). */
+int64_t inr_stft_num_frames(int64_t T, int hop);
+int inr_stft_mag(const float* x, int64_t T, int n_fft, int hop, const float* window, float eps, float* mag,
+                 double* sumsq_dev, void* stream);
+int inr_stft_loss(const float* pred, const float* target_mag, double target_sumsq, int64_t T, int n_fft, int hop,
+                  const float* window, float eps, float weight, float* gout, inr_opt_state* opt, void* stream);
+
+/* auraloss.time.SNRLoss(zero_mean=True, eps) (run.py:126,165 loss_mode='snr'; PARITY UNPINNED):
+ * -10 log10( sum gt_c^2 / (sum (pred_c - gt_c)^2 + eps) + eps ).  scratch2: two device doubles, zero on entry/exit. */
+int inr_snr_loss(const float* pred, const float* target, int64_t n, float eps, float weight, float* gout,
+                 inr_opt_state* opt, double* scratch2, void* stream);
+
 /* torch.optim.Adam(lr) + ReduceLROnPlateau('min', 0.8, 200, min_lr), run.py:116-117,186-189.
  * inr_opt_init writes a fresh state to device memory. */
 int inr_opt_init(inr_opt_state* opt_dev, float lr, float min_lr, int32_t hist_cap, void* stream);

@@ -52,6 +52,16 @@ SIGNATURES = {
     "inr_siren_forward": (_i, [C.POINTER(SirenDesc), _p, _p, _i64, _i64, _i64, _f, _p, _p, _i64, _p]),
     "inr_siren_loss_backward": (_i, [C.POINTER(SirenDesc), _p, _p, _p, _i64, _i64, _i64, _f, _i, _f, _p, _p, _p, _p,
                                      _p, _i64, _p]),
+    "inr_siren_train_forward": (_i, [C.POINTER(SirenDesc), _p, _p, _i64, _i64, _i64, _f, _p, _p, _i64, _p]),
+    "inr_siren_train_backward": (_i, [C.POINTER(SirenDesc), _p, _p, _p, _i64, _i64, _i64, _f, _i, _f, _p, _p, _p, _p,
+                                      _i64, _p]),
+    "inr_stmdct_num_frames": (_i64, [_i64, _i]),
+    "inr_stmdct_forward": (_i, [_p, _i64, _i, _p, _p, _p]),
+    "inr_mdct_loss": (_i, [_p, _p, _i64, _i, _p, _i, _f, _p, _p, _p]),
+    "inr_stft_num_frames": (_i64, [_i64, _i]),
+    "inr_stft_mag": (_i, [_p, _i64, _i, _i, _p, _f, _p, _p, _p]),
+    "inr_stft_loss": (_i, [_p, _p, C.c_double, _i64, _i, _i, _p, _f, _f, _p, _p, _p]),
+    "inr_snr_loss": (_i, [_p, _p, _i64, _f, _f, _p, _p, _p, _p]),
     "inr_opt_init": (_i, [_p, _f, _f, C.c_int32, _p]),
     "inr_adam_step": (_i, [_p, _p, _p, _p, _i64, _p, _f, _p, _p]),
     "inr_siren_fit_step": (_i, [C.POINTER(SirenDesc), _p, _p, _p, _p, _p, _p, _i64, _i64, _i64, _f, _i, _f, _p, _p,

@@ -151,7 +151,7 @@ int64_t inr_siren_workspace_bytes(const inr_siren_desc* d, int64_t n_rows, int t
   if (d->precision == INR_PREC_BF16) return siren_tc_workspace_bytes(d, n_rows, training);
   // fp32 path: whole-problem activations up to a cap; the host code loops over row chunks beyond it
   const int64_t per_row = siren_fp32_workspace_per_row(d, training);
-  const int64_t cap = (int64_t)8 << 30;
+  const int64_t cap = (int64_t)64 << 30;   // of 180 GB
   int64_t rows = std::max<int64_t>(n_rows, 1);
   if (rows * per_row > cap) rows = std::max<int64_t>(cap / per_row, 1024);
   return rows * per_row;
@@ -219,6 +219,50 @@ int inr_siren_loss_backward(const inr_siren_desc* d, const float* params, const 
   return siren_fp32_loss_backward(d, params, coords, target, n, i0, T_total, coord_scale, loss_kind, grad_scale,
                                   extra_gout_or_null, grads, opt, out_or_null, workspace, workspace_bytes,
                                   (cudaStream_t)stream);
+}
+
+// shared argument checks of the training entry points
+static int check_train_args(const inr_siren_desc* d, const float* params, const float* coords, int64_t n, int64_t i0,
+                            int64_t T_total, const void* workspace, int64_t workspace_bytes) {
+  int rc = check_desc(d);
+  if (rc) return rc;
+  INR_REQUIRE(params && n >= 0, INR_E_BADARG, "NULL params or negative n");
+  INR_REQUIRE(coords || d->in_features == 1, INR_E_BADARG, "coords == NULL needs in_features == 1");
+  INR_REQUIRE(coords || (i0 >= 0 && i0 + n <= T_total), INR_E_BADARG, "generated coords: rows [%lld,%lld) outside T=%lld",
+              (long long)i0, (long long)(i0 + n), (long long)T_total);
+  INR_REQUIRE(n == 0 || (workspace && workspace_bytes > 0), INR_E_WORKSPACE, "workspace missing");
+  return INR_OK;
+}
+
+int inr_siren_train_forward(const inr_siren_desc* d, const float* params, const float* coords, int64_t n, int64_t i0,
+                            int64_t T_total, float coord_scale, float* out, void* workspace, int64_t workspace_bytes,
+                            void* stream) {
+  int rc = check_train_args(d, params, coords, n, i0, T_total, workspace, workspace_bytes);
+  if (rc) return rc;
+  INR_REQUIRE(out, INR_E_BADARG, "train_forward: out is NULL");
+  if (n == 0) return INR_OK;
+  if (d->precision == INR_PREC_BF16)
+    return siren_tc_train(d, params, coords, nullptr, n, i0, T_total, coord_scale, 0, 0.f, nullptr, nullptr, nullptr, out,
+                          workspace, workspace_bytes, 1, (cudaStream_t)stream);
+  return siren_fp32_train(d, params, coords, nullptr, n, i0, T_total, coord_scale, 0, 0.f, nullptr, nullptr, nullptr, out,
+                          workspace, workspace_bytes, 1, (cudaStream_t)stream);
+}
+
+int inr_siren_train_backward(const inr_siren_desc* d, const float* params, const float* coords, const float* target,
+                             int64_t n, int64_t i0, int64_t T_total, float coord_scale, int loss_kind, float grad_scale,
+                             const float* extra_gout_or_null, float* grads, inr_opt_state* opt, void* workspace,
+                             int64_t workspace_bytes, void* stream) {
+  int rc = check_train_args(d, params, coords, n, i0, T_total, workspace, workspace_bytes);
+  if (rc) return rc;
+  INR_REQUIRE(grads && opt, INR_E_BADARG, "train_backward: NULL grads/opt");
+  INR_REQUIRE(target || extra_gout_or_null, INR_E_BADARG, "need a target and/or an upstream gradient");
+  INR_REQUIRE(loss_kind == INR_LOSS_MSE || loss_kind == INR_LOSS_MAE, INR_E_BADARG, "unknown loss kind %d", loss_kind);
+  if (n == 0) return INR_OK;
+  if (d->precision == INR_PREC_BF16)
+    return siren_tc_train(d, params, coords, target, n, i0, T_total, coord_scale, loss_kind, grad_scale, extra_gout_or_null,
+                          grads, opt, nullptr, workspace, workspace_bytes, 2, (cudaStream_t)stream);
+  return siren_fp32_train(d, params, coords, target, n, i0, T_total, coord_scale, loss_kind, grad_scale, extra_gout_or_null,
+                          grads, opt, nullptr, workspace, workspace_bytes, 2, (cudaStream_t)stream);
 }
 
 int inr_opt_init(inr_opt_state* opt_dev, float lr, float min_lr, int32_t hist_cap, void* stream) {

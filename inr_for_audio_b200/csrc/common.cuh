@@ -106,7 +106,14 @@ int siren_fp32_loss_backward(const inr_siren_desc* d, const float* params, const
                              const float* extra_gout, float* grads, inr_opt_state* opt, float* out, void* ws,
                              int64_t ws_bytes, cudaStream_t st);
 
+int siren_fp32_train(const inr_siren_desc* d, const float* params, const float* coords, const float* target, int64_t n,
+                     int64_t i0, int64_t T_total, float scale, int loss_kind, float grad_scale, const float* extra_gout,
+                     float* grads, inr_opt_state* opt, float* out, void* ws, int64_t ws_bytes, int phase, cudaStream_t st);
+
 // ---- bf16 tcgen05 path, siren_tc.cu
+int siren_tc_train(const inr_siren_desc* d, const float* params, const float* coords, const float* target, int64_t n,
+                   int64_t i0, int64_t T_total, float scale, int loss_kind, float grad_scale, const float* extra_gout,
+                   float* grads, inr_opt_state* opt, float* out, void* ws, int64_t ws_bytes, int phase, cudaStream_t st);
 bool siren_tc_supported(const inr_siren_desc* d);
 int64_t siren_tc_workspace_bytes(const inr_siren_desc* d, int64_t n_rows, int training);
 int siren_tc_forward(const inr_siren_desc* d, const float* params, const float* coords, int64_t n, int64_t i0,

@@ -168,26 +168,39 @@ int siren_fp32_forward(const inr_siren_desc* d, const float* params, const float
   return INR_OK;
 }
 
-int siren_fp32_loss_backward(const inr_siren_desc* d, const float* params, const float* coords, const float* target,
-                             int64_t n, int64_t i0, int64_t T_total, float scale, int loss_kind, float grad_scale,
-                             const float* extra_gout, float* grads, inr_opt_state* opt, float* out, void* ws,
-                             int64_t ws_bytes, cudaStream_t st) {
+// phase bits as in siren_tc_train: 1 = forward keeping activations, 2 = backward from them, 3 = fused.
+int siren_fp32_train(const inr_siren_desc* d, const float* params, const float* coords, const float* target,
+                     int64_t n, int64_t i0, int64_t T_total, float scale, int loss_kind, float grad_scale,
+                     const float* extra_gout, float* grads, inr_opt_state* opt, float* out, void* ws,
+                     int64_t ws_bytes, int phase, cudaStream_t st) {
   SirenLayout lay = layout_of(d);
   const int H = d->hidden_features, L = d->hidden_layers;
   const int64_t per_row = siren_fp32_workspace_per_row(d, 1);
   int64_t chunk = std::min<int64_t>(n, ws_bytes / per_row);
   INR_REQUIRE(chunk >= 1, INR_E_WORKSPACE, "workspace of %lld bytes holds no row (need %lld/row)", (long long)ws_bytes, (long long)per_row);
+  INR_REQUIRE(phase == 3 || chunk >= n, INR_E_WORKSPACE,
+              "split forward/backward needs the whole row range in one workspace chunk (%lld rows > %lld)", (long long)n,
+              (long long)chunk);
   for (int64_t r0 = 0; r0 < n; r0 += chunk) {
     const int64_t rows = std::min(chunk, n - r0);
     float* base = (float*)ws;
     auto S = [&](int l) { return base + (int64_t)l * rows * H; };
     auto C = [&](int l) { return base + (int64_t)(L + 1 + l) * rows * H; };
     const float* xc = coords ? coords + r0 * d->in_features : nullptr;
-    int rc = launch_first_layer<float>(d, params, xc, rows, i0 + r0, T_total, scale, S(0), C(0), st);
-    if (rc) return rc;
-    for (int l = 1; l <= L; ++l) {
-      rc = fwd_layer(d, params, l, S(l - 1), S(l), C(l), rows, st);
+    int rc;
+    if (phase & 1) {
+      rc = launch_first_layer<float>(d, params, xc, rows, i0 + r0, T_total, scale, S(0), C(0), st);
       if (rc) return rc;
+      for (int l = 1; l <= L; ++l) {
+        rc = fwd_layer(d, params, l, S(l - 1), S(l), C(l), rows, st);
+        if (rc) return rc;
+      }
+      if (phase == 1) {
+        rc = launch_last_layer<float>(d, params, S(L), nullptr, nullptr, nullptr, rows, 0, 0.f, nullptr, nullptr,
+                                      out + r0, 0, st);
+        if (rc) return rc;
+        continue;
+      }
     }
     rc = launch_last_layer<float>(d, params, S(L), C(L), target ? target + r0 : nullptr,
                                   extra_gout ? extra_gout + r0 : nullptr, rows, loss_kind, grad_scale, grads, opt,
@@ -217,6 +230,14 @@ int siren_fp32_loss_backward(const inr_siren_desc* d, const float* params, const
     if (rc) return rc;
   }
   return INR_OK;
+}
+
+int siren_fp32_loss_backward(const inr_siren_desc* d, const float* params, const float* coords, const float* target,
+                             int64_t n, int64_t i0, int64_t T_total, float scale, int loss_kind, float grad_scale,
+                             const float* extra_gout, float* grads, inr_opt_state* opt, float* out, void* ws,
+                             int64_t ws_bytes, cudaStream_t st) {
+  return siren_fp32_train(d, params, coords, target, n, i0, T_total, scale, loss_kind, grad_scale, extra_gout, grads, opt,
+                          out, ws, ws_bytes, 3, st);
 }
 
 }  // namespace inr

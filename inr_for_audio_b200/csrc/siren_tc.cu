@@ -493,16 +493,22 @@ int siren_tc_forward(const inr_siren_desc* d, const float* params, const float* 
   return INR_OK;
 }
 
-int siren_tc_loss_backward(const inr_siren_desc* d, const float* params, const float* coords, const float* target,
-                           int64_t n, int64_t i0, int64_t T_total, float scale, int loss_kind, float grad_scale,
-                           const float* extra_gout, float* grads, inr_opt_state* opt, float* out, void* ws,
-                           int64_t ws_bytes, cudaStream_t st) {
+// phase bits: 1 = forward (activations kept in the workspace), 2 = backward.  phase 3 is the fused step (the last-layer
+// kernel computes the output, the loss gradient and dZ_L in one pass); phase 1 writes the model output and stops so a
+// spectral loss can be evaluated on it; phase 2 resumes from the SAME workspace with that loss's gradient in extra_gout.
+int siren_tc_train(const inr_siren_desc* d, const float* params, const float* coords, const float* target,
+                   int64_t n, int64_t i0, int64_t T_total, float scale, int loss_kind, float grad_scale,
+                   const float* extra_gout, float* grads, inr_opt_state* opt, float* out, void* ws,
+                   int64_t ws_bytes, int phase, cudaStream_t st) {
   SirenLayout lay = layout_of(d);
   const int H = lay.H, L = lay.L;
   TcWorkspace w;
   int rc = carve(d, 1, n, ws, ws_bytes, &w);
   if (rc) return rc;
-  if ((rc = pack_weights(d, params, w, st))) return rc;
+  INR_REQUIRE(phase == 3 || w.chunk_rows >= n, INR_E_WORKSPACE,
+              "split forward/backward needs the whole row range in one workspace chunk (%lld rows > %lld)", (long long)n,
+              (long long)w.chunk_rows);
+  if ((phase & 1) && (rc = pack_weights(d, params, w, st))) return rc;
   for (int64_t r0 = 0; r0 < n; r0 += w.chunk_rows) {
     const int64_t rows = std::min(w.chunk_rows, n - r0);
     const int64_t rows_pad = round_up(rows, TILE_ROWS);
@@ -510,11 +516,19 @@ int siren_tc_loss_backward(const inr_siren_desc* d, const float* params, const f
     auto S = [&](int l) { return w.img + (int64_t)l * w.img_elems; };
     auto C = [&](int l) { return w.img + (int64_t)(L + 1 + l) * w.img_elems; };
     const float* xc = coords ? coords + r0 * lay.in : nullptr;
-    if ((rc = first_layer(d, params, xc, rows, rows_pad, i0 + r0, T_total, scale, S(0), C(0), st))) return rc;
-    for (int l = 1; l <= L; ++l) {
-      LayerParams p = layer_params(H, S(l - 1), w.Wf + (int64_t)(l - 1) * H * H, params + lay.b_off(l), d->hidden_omega_0,
-                                   S(l), C(l), nullptr, tiles);
-      if ((rc = tc_layer(H, MODE_FWD, p, st))) return rc;
+    if (phase & 1) {
+      if ((rc = first_layer(d, params, xc, rows, rows_pad, i0 + r0, T_total, scale, S(0), C(0), st))) return rc;
+      for (int l = 1; l <= L; ++l) {
+        LayerParams p = layer_params(H, S(l - 1), w.Wf + (int64_t)(l - 1) * H * H, params + lay.b_off(l), d->hidden_omega_0,
+                                     S(l), C(l), nullptr, tiles);
+        if ((rc = tc_layer(H, MODE_FWD, p, st))) return rc;
+      }
+      if (phase == 1) {
+        if ((rc = last_layer(d, params, S(L), nullptr, nullptr, nullptr, rows, tiles, 0, 0.f, nullptr, nullptr, nullptr,
+                             out + r0, 0, st)))
+          return rc;
+        continue;
+      }
     }
     if ((rc = last_layer(d, params, S(L), C(L), target ? target + r0 : nullptr, extra_gout ? extra_gout + r0 : nullptr, rows,
                          tiles, loss_kind, grad_scale, w.gvec, grads, opt, out ? out + r0 : nullptr, 1, st)))
@@ -537,6 +551,14 @@ int siren_tc_loss_backward(const inr_siren_desc* d, const float* params, const f
       return rc;
   }
   return INR_OK;
+}
+
+int siren_tc_loss_backward(const inr_siren_desc* d, const float* params, const float* coords, const float* target,
+                           int64_t n, int64_t i0, int64_t T_total, float scale, int loss_kind, float grad_scale,
+                           const float* extra_gout, float* grads, inr_opt_state* opt, float* out, void* ws,
+                           int64_t ws_bytes, cudaStream_t st) {
+  return siren_tc_train(d, params, coords, target, n, i0, T_total, scale, loss_kind, grad_scale, extra_gout, grads, opt,
+                        out, ws, ws_bytes, 3, st);
 }
 
 }  // namespace inr

@@ -90,7 +90,8 @@ class SirenFitter:
     def __init__(self, spec: SirenSpec, params0: torch.Tensor, target: torch.Tensor, coords: Optional[torch.Tensor] = None,
                  *, i0: int = 0, T_total: Optional[int] = None, coord_scale: float = 1.0, loss_mode: str = "mse",
                  lr: float = 1e-3, min_lr: float = 1e-6, alpha: float = 0.0, precision: str = "fp32",
-                 hist_cap: int = 65536, process_group=None, use_graph: bool = True):
+                 hist_cap: int = 65536, process_group=None, use_graph: bool = True, spectral=None,
+                 spectral_target: Optional[torch.Tensor] = None):
         _require_cuda(target, "target")
         self.spec = spec
         self.device = target.device
@@ -104,12 +105,32 @@ class SirenFitter:
         self.T_total = int(T_total if T_total is not None else self.n)
         self.coord_scale = float(coord_scale)
         self.coords = None if coords is None else coords.reshape(self.n, spec.in_features).contiguous().float()
-        if loss_mode not in ("mse", "mae"):
-            raise ValueError("loss_mode %r: the device path implements 'mse' and 'mae' (run.py:161-169)" % loss_mode)
-        self.loss_kind = L.LOSS_MSE if loss_mode == "mse" else L.LOSS_MAE
+        if loss_mode not in ("mse", "mae", "snr"):
+            raise ValueError("loss_mode %r: the device path implements 'mse', 'mae' and 'snr' (run.py:161-169)" % loss_mode)
+        self.loss_mode = loss_mode
+        self.loss_kind = L.LOSS_MAE if loss_mode == "mae" else L.LOSS_MSE
         self.alpha = float(alpha)
         self.pg = process_group
         self.world = torch.distributed.get_world_size(process_group) if process_group is not None else 1
+        self.rank = torch.distributed.get_rank(process_group) if process_group is not None else 0
+        # losses that need the whole output (run.py:160,165): evaluated between the forward and backward halves on
+        # the full signal; with coordinate sharding every rank all-gathers the outputs and evaluates them redundantly
+        # (they cost microseconds), then back-propagates its own slice of the gradient.
+        from . import spectral as SP
+        full_t = self.target if spectral_target is None else spectral_target.reshape(-1).contiguous().float()
+        if (spectral is not None or loss_mode == "snr") and self.world > 1 and spectral_target is None:
+            raise ValueError("sharded fits with a spectral / SNR loss need spectral_target = the FULL target signal")
+        self.spectral = SP.make_spectral_loss(spectral, full_t) if isinstance(spectral, (str, type(None))) else spectral
+        self.snr = SP.SnrLoss(full_t) if loss_mode == "snr" else None
+        self.split = self.spectral is not None or self.snr is not None
+        if self.split:
+            self.out = torch.empty(self.n, dtype=torch.float32, device=self.device)
+            self.full_T = full_t.numel()
+            self.gout_full = torch.zeros(self.full_T, dtype=torch.float32, device=self.device)
+            self.out_full = self.out if self.world == 1 else torch.empty(self.full_T, dtype=torch.float32, device=self.device)
+            if self.world > 1:
+                # equal shard sizes are what all_gather_into_tensor needs; the bench/train shard that way
+                self._shard = (self.full_T + self.world - 1) // self.world
         dev = self.device
         # one arena: [params | grads | m | v], each padded to 64 floats so every block is 256-byte aligned
         self.Ppad = (self.P + 63) // 64 * 64
@@ -147,11 +168,49 @@ class SirenFitter:
                                       L.ptr(self.opt), self._w() / float(self.T_total), L.ptr(self.loss_hist),
                                       L.stream_ptr()))
 
-    def _enqueue_step(self):
-        self._enqueue_backward()
+    def _enqueue_split_backward(self):
+        """forward (activations kept) -> whole-output losses -> backward with their gradient as the upstream term."""
+        buf = self.ws.get(self.desc, self.n, True)
+        lib = L.lib()
+        L.check(lib.inr_siren_train_forward(C.byref(self.desc), L.ptr(self.params), L.ptr(self.coords), self.n, self.i0,
+                                            self.T_total, self.coord_scale, L.ptr(self.out), L.ptr(buf), buf.numel(),
+                                            L.stream_ptr()))
+        if self.world > 1:
+            self._gather_out()
+        self.gout_full.zero_()
+        if self.spectral is not None:
+            self.spectral.accumulate(self.out_full, self.gout_full, self.opt, self.alpha)
+        if self.snr is not None:
+            self.snr.accumulate(self.out_full, self.gout_full, self.opt, self._w())
+        gslice = self.gout_full[self.i0:self.i0 + self.n]
+        tgt = None if self.snr is not None else self.target
+        L.check(lib.inr_siren_train_backward(
+            C.byref(self.desc), L.ptr(self.params), L.ptr(self.coords), L.ptr(tgt), self.n, self.i0, self.T_total,
+            self.coord_scale, self.loss_kind, self._w() / float(self.T_total), L.ptr(gslice), L.ptr(self.grads),
+            L.ptr(self.opt), L.ptr(buf), buf.numel(), L.stream_ptr()))
+
+    def _gather_out(self):
+        """all-gather the per-rank output shards into out_full (ranks own equal contiguous ranges, the last may be short)."""
+        sh = self._shard
+        pad = torch.zeros(sh, dtype=torch.float32, device=self.device)
+        pad[:self.n].copy_(self.out)
+        gathered = torch.empty(sh * self.world, dtype=torch.float32, device=self.device)
+        torch.distributed.all_gather_into_tensor(gathered, pad, group=self.pg)
+        self.out_full.copy_(gathered[:self.full_T])
+
+    def _allreduce(self):
         if self.world > 1:
             torch.distributed.all_reduce(self.grads, group=self.pg)
-            torch.distributed.all_reduce(self.loss_acc, group=self.pg)
+            torch.distributed.all_reduce(self.loss_acc[0:2], group=self.pg)
+            if self.split:
+                self.loss_acc[1:2].div_(self.world)   # every rank evaluated the same whole-output loss
+
+    def _enqueue_step(self):
+        if self.split:
+            self._enqueue_split_backward()
+        else:
+            self._enqueue_backward()
+        self._allreduce()
         self._enqueue_adam()
 
     def step(self, n_steps: int = 1):
@@ -233,12 +292,16 @@ class SirenFitter:
         """One forward+backward without the optimiser: (loss, flat grads clone, output) -- teacher-forced tests."""
         self.grads.zero_()
         self.loss_acc.zero_()
-        out = torch.empty(self.n, dtype=torch.float32, device=self.device)
-        self._enqueue_backward(extra_gout, out)
-        if self.world > 1:
-            torch.distributed.all_reduce(self.grads, group=self.pg)
-            torch.distributed.all_reduce(self.loss_acc, group=self.pg)
-        loss = float(self.loss_acc[0].item()) * self._w() / float(self.T_total)
+        if self.split:
+            assert extra_gout is None
+            self._enqueue_split_backward()
+            out = self.out.clone()
+        else:
+            out = torch.empty(self.n, dtype=torch.float32, device=self.device)
+            self._enqueue_backward(extra_gout, out)
+        self._allreduce()
+        acc = self.loss_acc.cpu().numpy()
+        loss = float(acc[0]) * self._w() / float(self.T_total) + float(acc[1])
         g = self.grads.clone()
         self.grads.zero_()
         self.loss_acc.zero_()
