@@ -175,6 +175,41 @@ int inr_siren_fit_step(const inr_siren_desc* d, float* params, float* grads, flo
                        float coord_scale, int loss_kind, float alpha, inr_opt_state* opt, float* loss_hist,
                        void* workspace, int64_t workspace_bytes, void* stream);
 
+/* ---- efficient-kan KAN (kan.py:6-285) -----------------------------------------------------------------------
+ * KAN(layers_hidden, grid_size=5, spline_order=3, ...) with update_grid=False, the only mode run.py:158 uses.
+ * flat params, state_dict order per KANLinear (kan.py:36-45): base_weight (out,in), spline_weight (out,in,G+K),
+ * spline_scaler (out,in).  `grids` = the layers' `grid` buffers concatenated, (in_l, G+2K+1) floats each (kan.py:26-35),
+ * so grids refined by the reference's host-side update_grid are honoured.  spline_order must be 3. */
+#define INR_KAN_MAX_LAYERS 8
+typedef struct {
+  int32_t num_layers;                       /* len(layers_hidden) - 1                    */
+  int32_t widths[INR_KAN_MAX_LAYERS + 1];   /* layers_hidden                             */
+  int32_t grid_size;                        /* G (5)                                     */
+  int32_t spline_order;                     /* K (3)                                     */
+  int32_t precision;                        /* INR_PREC_FP32 (bf16 mode: see DESIGN.md)  */
+} inr_kan_desc;
+
+int64_t inr_kan_num_params(const inr_kan_desc* d);
+int64_t inr_kan_num_grid_floats(const inr_kan_desc* d);
+int64_t inr_kan_workspace_bytes(const inr_kan_desc* d, int64_t n_rows, int training);
+
+/* kan.py:78-111 b_splines: x (rows, in) -> bases (rows, in, G+K), Cox-de Boor on grid (in, G+2K+1) with the
+ * reference's half-open order-0 test and operation order. */
+int inr_kan_b_splines(const float* x, const float* grid, int64_t rows, int in_features, int grid_size,
+                      int spline_order, float* bases, void* stream);
+
+/* kan.py:274-279 KAN.forward(x): out (n, widths[L]).  coords NULL (widths[0] == 1): generated as in inr_siren_forward. */
+int inr_kan_forward(const inr_kan_desc* d, const float* params, const float* grids, const float* coords, int64_t n,
+                    int64_t i0, int64_t T_total, float coord_scale, float* out, void* workspace, int64_t workspace_bytes,
+                    void* stream);
+
+/* run.py:158-169 + 185 for arch='kan' (run.py:110): forward, loss, backward to the flat gradient (ACCUMULATES);
+ * same conventions as inr_siren_loss_backward; widths[L] must be 1. */
+int inr_kan_loss_backward(const inr_kan_desc* d, const float* params, const float* grids, const float* coords,
+                          const float* target, int64_t n, int64_t i0, int64_t T_total, float coord_scale, int loss_kind,
+                          float grad_scale, const float* extra_gout_or_null, float* grads, inr_opt_state* opt,
+                          float* out_or_null, void* workspace, int64_t workspace_bytes, void* stream);
+
 /* ---- test hooks for the tcgen05 kernels (tests/test_tc_gpu.py): one layer GEMM / one dW GEMM on row-major fp32
  * inputs; `variant` bit 0 / bit 1 swap the LBO/SBO descriptor strides of operand A / B (convention probe). */
 int64_t inr_dbg_tc_scratch_bytes(int H, int64_t rows);

@@ -22,6 +22,14 @@ class SirenDesc(C.Structure):
                 ("hidden_omega_0", C.c_float), ("precision", C.c_int32)]
 
 
+KAN_MAX_LAYERS = 8
+
+
+class KanDesc(C.Structure):
+    _fields_ = [("num_layers", C.c_int32), ("widths", C.c_int32 * (KAN_MAX_LAYERS + 1)), ("grid_size", C.c_int32),
+                ("spline_order", C.c_int32), ("precision", C.c_int32)]
+
+
 class OptState(C.Structure):
     _fields_ = [("lr", C.c_float), ("min_lr", C.c_float), ("factor", C.c_float), ("threshold", C.c_float),
                 ("sched_eps", C.c_float), ("beta1", C.c_float), ("beta2", C.c_float), ("adam_eps", C.c_float),
@@ -66,6 +74,13 @@ SIGNATURES = {
     "inr_adam_step": (_i, [_p, _p, _p, _p, _i64, _p, _f, _p, _p]),
     "inr_siren_fit_step": (_i, [C.POINTER(SirenDesc), _p, _p, _p, _p, _p, _p, _i64, _i64, _i64, _f, _i, _f, _p, _p,
                                 _p, _i64, _p]),
+    "inr_kan_num_params": (_i64, [C.POINTER(KanDesc)]),
+    "inr_kan_num_grid_floats": (_i64, [C.POINTER(KanDesc)]),
+    "inr_kan_workspace_bytes": (_i64, [C.POINTER(KanDesc), _i64, _i]),
+    "inr_kan_b_splines": (_i, [_p, _p, _i64, _i, _i, _i, _p, _p]),
+    "inr_kan_forward": (_i, [C.POINTER(KanDesc), _p, _p, _p, _i64, _i64, _i64, _f, _p, _p, _i64, _p]),
+    "inr_kan_loss_backward": (_i, [C.POINTER(KanDesc), _p, _p, _p, _p, _i64, _i64, _i64, _f, _i, _f, _p, _p, _p, _p, _p,
+                                   _i64, _p]),
     "inr_dbg_tc_scratch_bytes": (_i64, [_i, _i64]),
     "inr_dbg_tc_layer": (_i, [_i, _i, _p, _p, _p, _f, _p, _p, _p, _i64, _i, _p, _i64, _p]),
     "inr_dbg_tc_dw": (_i, [_i, _p, _p, _p, _i64, _i, _p, _i64, _p]),

@@ -7,123 +7,9 @@
 // One generic 128x128x16 register-tiled SGEMM (8x8 per thread, register prefetch) with fused epilogues.
 // This path exists for parity (fp32 FMA everywhere, like the reference) and for shapes the tcgen05 path
 // does not take; the throughput path is siren_tc.cu.
-#include "common.cuh"
+#include "sgemm.cuh"
 
 namespace inr {
-
-enum { EPI_SINCOS = 0, EPI_COSMUL = 1, EPI_ATOMIC = 2 };
-
-constexpr int BM = 128, BN = 128, BK = 16;
-
-template <bool A_KC, bool B_KC, int EPI>
-__global__ void __launch_bounds__(256)
-k_sgemm(const float* __restrict__ A, int64_t sAm, int64_t sAk, const float* __restrict__ B, int64_t sBn, int64_t sBk,
-        int64_t M, int N, int64_t K, int64_t k_chunk, const float* __restrict__ bias, float omega,
-        float* out0, float* out1, int64_t ldo) {
-  __shared__ __align__(16) float As[BK][BM + 4];
-  __shared__ __align__(16) float Bs[BK][BN + 4];
-  const int tid = threadIdx.x;
-  const int64_t m0 = (int64_t)blockIdx.x * BM;
-  const int n0 = blockIdx.y * BN;
-  const int64_t kbeg = (int64_t)blockIdx.z * k_chunk;
-  const int64_t kend = min(K, kbeg + k_chunk);
-  const int ty = tid / 16, tx = tid % 16;
-
-  float acc[8][8];
-#pragma unroll
-  for (int i = 0; i < 8; ++i)
-#pragma unroll
-    for (int j = 0; j < 8; ++j) acc[i][j] = 0.f;
-
-  float ra[8], rb[8];
-  auto gload = [&](int64_t k0) {
-#pragma unroll
-    for (int p = 0; p < 8; ++p) {
-      const int e = tid + p * 256;
-      int mm, kk;
-      if (A_KC) { mm = e / BK; kk = e % BK; } else { kk = e / BM; mm = e % BM; }
-      const int64_t gm = m0 + mm, gk = k0 + kk;
-      ra[p] = (gm < M && gk < kend) ? A[gm * sAm + gk * sAk] : 0.f;
-      int nn;
-      if (B_KC) { nn = e / BK; kk = e % BK; } else { kk = e / BN; nn = e % BN; }
-      const int gn = n0 + nn;
-      const int64_t gk2 = k0 + kk;
-      rb[p] = (gn < N && gk2 < kend) ? B[(int64_t)gn * sBn + gk2 * sBk] : 0.f;
-    }
-  };
-  auto sstore = [&]() {
-#pragma unroll
-    for (int p = 0; p < 8; ++p) {
-      const int e = tid + p * 256;
-      int mm, kk;
-      if (A_KC) { mm = e / BK; kk = e % BK; } else { kk = e / BM; mm = e % BM; }
-      As[kk][mm] = ra[p];
-      int nn;
-      if (B_KC) { nn = e / BK; kk = e % BK; } else { kk = e / BN; nn = e % BN; }
-      Bs[kk][nn] = rb[p];
-    }
-  };
-
-  gload(kbeg);
-  for (int64_t k0 = kbeg; k0 < kend; k0 += BK) {
-    sstore();
-    __syncthreads();
-    if (k0 + BK < kend) gload(k0 + BK);
-#pragma unroll
-    for (int kk = 0; kk < BK; ++kk) {
-      const float4 a0 = *reinterpret_cast<const float4*>(&As[kk][ty * 4]);
-      const float4 a1 = *reinterpret_cast<const float4*>(&As[kk][64 + ty * 4]);
-      const float4 b0 = *reinterpret_cast<const float4*>(&Bs[kk][tx * 4]);
-      const float4 b1 = *reinterpret_cast<const float4*>(&Bs[kk][64 + tx * 4]);
-      const float a[8] = {a0.x, a0.y, a0.z, a0.w, a1.x, a1.y, a1.z, a1.w};
-      const float b[8] = {b0.x, b0.y, b0.z, b0.w, b1.x, b1.y, b1.z, b1.w};
-#pragma unroll
-      for (int i = 0; i < 8; ++i)
-#pragma unroll
-        for (int j = 0; j < 8; ++j) acc[i][j] = __fmaf_rn(a[i], b[j], acc[i][j]);
-    }
-    __syncthreads();
-  }
-
-#pragma unroll
-  for (int i = 0; i < 8; ++i) {
-    const int64_t gm = m0 + (i < 4 ? ty * 4 + i : 64 + ty * 4 + (i - 4));
-    if (gm >= M) continue;
-#pragma unroll
-    for (int jh = 0; jh < 2; ++jh) {
-      const int gn = n0 + (jh == 0 ? tx * 4 : 64 + tx * 4);
-      if (gn >= N) continue;
-      const bool full = (gn + 3 < N) && ((ldo & 3) == 0);
-      float v[4] = {acc[i][jh * 4 + 0], acc[i][jh * 4 + 1], acc[i][jh * 4 + 2], acc[i][jh * 4 + 3]};
-      float* p0 = out0 + gm * ldo + gn;
-      if (EPI == EPI_SINCOS) {
-        float s[4], c[4];
-#pragma unroll
-        for (int q = 0; q < 4; ++q) {
-          const float z = v[q] + ((gn + q < N) ? bias[gn + q] : 0.f);
-          sincosf(omega * z, &s[q], &c[q]);
-        }
-        float* p1 = out1 ? out1 + gm * ldo + gn : nullptr;
-        if (full) {
-          *reinterpret_cast<float4*>(p0) = make_float4(s[0], s[1], s[2], s[3]);
-          if (p1) *reinterpret_cast<float4*>(p1) = make_float4(c[0], c[1], c[2], c[3]);
-        } else {
-          for (int q = 0; q < 4 && gn + q < N; ++q) { p0[q] = s[q]; if (p1) p1[q] = c[q]; }
-        }
-      } else if (EPI == EPI_COSMUL) {
-        if (full) {
-          float4 c = *reinterpret_cast<float4*>(p0);
-          c.x = v[0] * omega * c.x; c.y = v[1] * omega * c.y; c.z = v[2] * omega * c.z; c.w = v[3] * omega * c.w;
-          *reinterpret_cast<float4*>(p0) = c;
-        } else {
-          for (int q = 0; q < 4 && gn + q < N; ++q) p0[q] = v[q] * omega * p0[q];
-        }
-      } else {
-        for (int q = 0; q < 4 && gn + q < N; ++q) atomicAdd(p0 + q, v[q]);
-      }
-    }
-  }
-}
 
 int siren_fp32_workspace_per_row(const inr_siren_desc* d, int training) {
   const int H = d->hidden_features, L = d->hidden_layers;

@@ -42,6 +42,10 @@ class SirenSpec:
     def num_params(self) -> int:
         return sum(o * i + o for o, i in self.layer_shapes())
 
+    def param_sizes(self):
+        """flat sizes in state_dict order (weight, bias per layer)."""
+        return [s for o, i in self.layer_shapes() for s in (o * i, o)]
+
     def flops_per_coord(self) -> int:
         """fwd + bwd dense flops per coordinate, SURVEY.md §8(d): 6 L H^2 + 10 H."""
         return 6 * self.hidden_layers * self.hidden_features ** 2 + 10 * self.hidden_features
@@ -59,8 +63,9 @@ class Workspace:
         self.device = device
         self.buf: Optional[torch.Tensor] = None
 
-    def get(self, desc: L.SirenDesc, n_rows: int, training: bool) -> torch.Tensor:
-        need = L.check(L.lib().inr_siren_workspace_bytes(C.byref(desc), n_rows, int(training)))
+    def get(self, desc, n_rows: int, training: bool) -> torch.Tensor:
+        fn = L.lib().inr_kan_workspace_bytes if isinstance(desc, L.KanDesc) else L.lib().inr_siren_workspace_bytes
+        need = L.check(fn(C.byref(desc), n_rows, int(training)))
         if self.buf is None or self.buf.numel() < need:
             self.buf = torch.empty(max(int(need), 256), dtype=torch.uint8, device=self.device)
         return self.buf
@@ -248,8 +253,7 @@ class SirenFitter:
     def load_adam_state(self, osd: dict):
         """Load a torch.optim.Adam.state_dict() (run.py:84-106 resume): exp_avg / exp_avg_sq / step / lr."""
         o, step = 0, 0
-        shapes = self.spec.layer_shapes()
-        sizes = [s for oi in shapes for s in (oi[0] * oi[1], oi[0])]
+        sizes = self.spec.param_sizes()
         for i, n in enumerate(sizes):
             ent = osd["state"].get(i)
             if ent is not None:
