@@ -25,10 +25,24 @@ if ROOT not in sys.path:
 
 WORKLOADS = {
     # BASELINE.json configs[1]: SIREN 5x512 on a synthetic 60 s 44.1 kHz waveform -- the config the metric is quoted on
-    "c2": dict(T=2646000, H=512, L=5, seed=0, desc="SIREN 5x512, synthetic 60 s @ 44.1 kHz (T=2646000), mse, Adam lr 1e-3"),
+    "c2": dict(kind="siren", T=2646000, H=512, L=5, seed=0,
+               desc="SIREN 5x512, synthetic 60 s @ 44.1 kHz (T=2646000), mse, Adam lr 1e-3"),
     # configs[0] model shape on a synthetic clip of gt_bach's length (parity case; not a bench line by default)
-    "c1": dict(T=264600, H=256, L=3, seed=0, desc="SIREN 3x256, synthetic 6 s @ 44.1 kHz (T=264600), mse, Adam lr 1e-3"),
-    "c5clip": dict(T=88200, H=256, L=3, seed=0, desc="SIREN 3x256, one synthetic 2 s clip (T=88200)"),
+    "c1": dict(kind="siren", T=264600, H=256, L=3, seed=0,
+               desc="SIREN 3x256, synthetic 6 s @ 44.1 kHz (T=264600), mse, Adam lr 1e-3"),
+    # configs[2]: MDCT-domain + waveform loss on a synthetic 30 s clip (alpha = 0.2, a value run.py:456,486 uses)
+    "c3": dict(kind="siren", T=1323000, H=256, L=3, seed=1, spectral="mdct", alpha=0.2,
+               desc="SIREN 3x256, synthetic 30 s (T=1323000), 0.8*mse + 0.2*MDCT-domain L1 (N=2048, KBD), Adam lr 1e-3"),
+    "c3stft": dict(kind="siren", T=1323000, H=256, L=3, seed=1, spectral="stft", alpha=0.2,
+                   desc="SIREN 3x256, synthetic 30 s (T=1323000), 0.8*mse + 0.2*STFT loss (auraloss defaults), Adam lr 1e-3"),
+    # configs[3]: efficient-kan KAN [1,256,256,1] on a synthetic 10 s waveform
+    "c4": dict(kind="kan", T=441000, widths=[1, 256, 256, 1], seed=2,
+               desc="KAN [1,256,256,1] (grid 5, order 3), synthetic 10 s (T=441000), mse, Adam lr 1e-3"),
+    # configs[4]: 1024 independent 2 s clips, each its own SIREN 3x256, clip-parallel
+    "c5": dict(kind="clips", clips=1024, T=88200, H=256, L=3, seed=0,
+               desc="1024 independent synthetic 2 s clips (T=88200 each), one SIREN 3x256 per clip, mse, Adam lr 1e-3"),
+    "c5small": dict(kind="clips", clips=64, T=88200, H=256, L=3, seed=0,
+                    desc="64 independent synthetic 2 s clips (T=88200 each), one SIREN 3x256 per clip"),
 }
 METRIC = "coord-samples/sec (fwd+bwd+Adam) SIREN fit"
 UNIT = "coord-samples/s"
@@ -40,7 +54,8 @@ def parse_args():
     ap.add_argument("--steps", type=int, default=20)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
-    ap.add_argument("--workload", default="c2", choices=sorted(WORKLOADS))
+    ap.add_argument("--workload", default=os.environ.get("INR_BENCH_WORKLOAD", "c2"), choices=sorted(WORKLOADS))
+    ap.add_argument("--streams", type=int, default=4, help="clip-parallel: concurrent streams per GPU")
     ap.add_argument("--precision", default=os.environ.get("INR_BENCH_PRECISION", "auto"))
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--cpu-budget-s", type=float, default=20.0)
@@ -114,23 +129,41 @@ class ClockSampler:
 # ------------------------------------------------------------------------------------------------- reference arm
 def oracle_fit_rate(wl, rows, steps, warmup, threads):
     """The reference's own algorithm for the path on the host cores: oracle/inr_oracle.py (a line-for-line
-    restatement of run.py:116-117,156-190 around models.Siren, pinned against the reference's outputs) on the
-    first `rows` coordinates of the workload.  Returns (coord-samples/s, seconds per step)."""
+    restatement of run.py:116-117,156-190 around models.Siren / kan.KAN, pinned against the reference's outputs) on
+    the first `rows` coordinates of the workload (for the clip-parallel workload: of ONE clip -- clips are
+    independent, so the per-clip rate is the whole-job rate on the same cores).  Returns (coord-samples/s, s/step)."""
     import torch
     from oracle import inr_oracle as O
     from inr_for_audio_b200.utils import synth_waveform
     torch.set_num_threads(threads)
-    spec = O.SirenSpec(1, wl["H"], wl["L"], 1, True)
-    params = O.siren_init(spec, seed=wl["seed"])
     gt_full = synth_waveform(wl["T"], seed=wl["seed"])
     coords = O.get_coord(wl["T"], 1)[:rows].view(1, -1, 1)
     gt = torch.from_numpy(gt_full[:rows]).view(1, -1, 1)
+    if wl["kind"] == "kan":
+        names = ("base_weight", "spline_weight", "spline_scaler")
+        layers = O.kan_init(wl["widths"], seed=wl["seed"])
+        params = [l[k] for l in layers for k in names]
+
+        def loss_and_grads():
+            req = [p.detach().clone().requires_grad_(True) for p in params]
+            ls = [dict(zip(names, req[3 * i:3 * i + 3]), grid=layers[i]["grid"]) for i in range(len(layers))]
+            loss = torch.mean((O.kan_forward(coords, ls) - gt) ** 2)
+            return loss.detach(), torch.autograd.grad(loss, req)
+    else:
+        spec = O.SirenSpec(1, wl["H"], wl["L"], 1, True)
+        params = O.siren_init(spec, seed=wl["seed"])
+        alpha = wl.get("alpha", 0.0)
+        sl = {"mdct": lambda o, g: O.mdct_loss(o, g, 2048, "l1"), "stft": O.stft_loss, None: None}[wl.get("spectral")]
+
+        def loss_and_grads():
+            loss, _, grads, _ = O.siren_loss_and_grads(spec, params, coords, gt, "mse", alpha, sl)
+            return loss, grads
     st = O.AdamState(params, lr=1e-3)
     sched = O.PlateauState()
     times = []
     for i in range(warmup + steps):
         t0 = time.perf_counter()
-        loss, _, grads, _ = O.siren_loss_and_grads(spec, params, coords, gt)
+        loss, grads = loss_and_grads()
         O.adam_step(params, grads, st)
         sched.step(float(loss), st)
         dt = time.perf_counter() - t0
@@ -146,6 +179,8 @@ def pick_rows(wl, budget_s, n_steps, threads):
     _, per = oracle_fit_rate(wl, probe, 1, 1, threads)
     rows = int(probe * budget_s / max(per * n_steps, 1e-9))
     rows = max(4096, min(wl["T"], rows))
+    if wl["kind"] == "kan":
+        rows = min(rows, 32768)      # the reference materialises ~10 (rows, 256, 8..11) fp32 tensors per layer (kan.py:93-104)
     return rows // 1024 * 1024 if rows < wl["T"] else rows
 
 
@@ -168,6 +203,80 @@ def run_reference(args, wl):
 
 
 # ------------------------------------------------------------------------------------------------- our arm
+class Job:
+    """One workload on this rank: the fitter(s), the pinned host copy of its targets, its work accounting."""
+
+    def __init__(self, args, wl, rank, world, dev, pg, prec):
+        import torch
+        import inr_for_audio_b200 as P
+        self.P, self.torch, self.wl, self.kind = P, torch, wl, wl["kind"]
+        self.args, self.rank, self.world, self.dev, self.pg, self.prec = args, rank, world, dev, pg, prec
+        T = wl["T"]
+        if self.kind == "clips":
+            lo, hi = P.ClipBatchFitter.clip_range(wl["clips"], rank, world)
+            self.units_total = wl["clips"] * T
+            self.n_local = (hi - lo) * T
+            gts = np.stack([P.utils.synth_waveform(T, seed=wl["seed"] + c) for c in range(lo, hi)])
+            flats = []
+            for c in range(lo, hi):
+                torch.manual_seed(wl["seed"] + c)
+                m = P.Siren(1, wl["H"], wl["L"], 1, True)
+                flats.append(m.flat_parameters().clone())
+            self.spec = m.spec
+            self.flat0 = torch.stack(flats)
+            self.host_target = torch.from_numpy(gts).pin_memory()
+            self.flops_per_coord = 6.0 * wl["L"] * wl["H"] ** 2
+        else:
+            # contiguous shard per rank, rounded to the 128-row tile (SURVEY.md §8(e))
+            from inr_for_audio_b200.engine import shard_range
+            self.i0, self.n_local, self.shard = shard_range(T, rank, world)
+            self.units_total = T
+            gt_np = P.utils.synth_waveform(T, seed=wl["seed"])
+            self.host_target = torch.from_numpy(gt_np[self.i0:self.i0 + self.n_local]).pin_memory()
+            self.full_target = torch.from_numpy(gt_np).to(dev) if wl.get("spectral") else None
+            torch.manual_seed(wl["seed"])
+            if self.kind == "kan":
+                self.model = P.KAN(wl["widths"])
+                self.spec = self.model.spec
+                self.flops_per_coord = 3566592.0        # SURVEY.md §8(d): dense-equivalent fwd+bwd flops per coordinate
+            else:
+                self.model = P.Siren(1, wl["H"], wl["L"], 1, True)
+                self.spec = self.model.spec
+                self.flops_per_coord = 6.0 * wl["L"] * wl["H"] ** 2
+        self.target = self.host_target.to(dev, non_blocking=True)
+
+    def make(self, use_graph):
+        P, wl = self.P, self.wl
+        if self.kind == "clips":
+            return P.ClipBatchFitter(self.spec, self.flat0, self.target, precision=self.prec, n_streams=self.args.streams,
+                                     use_graph=use_graph, hist_cap=256)
+        kw = dict(i0=self.i0, T_total=wl["T"], process_group=self.pg, use_graph=use_graph, hist_cap=4096)
+        if self.kind == "kan":
+            return P.KanFitter(self.spec, self.model.flat_parameters(), self.model.flat_grids(), self.target, None, **kw)
+        f = P.SirenFitter(self.spec, self.model.flat_parameters(), self.target, None, precision=self.prec,
+                          alpha=wl.get("alpha", 0.0), spectral=wl.get("spectral"), spectral_target=self.full_target, **kw)
+        return f
+
+    def h2d(self, fit):
+        """the step's input: this rank's target samples, from pinned host memory"""
+        if self.kind == "clips":
+            self.target.copy_(self.host_target, non_blocking=True)
+        else:
+            fit.target.copy_(self.host_target, non_blocking=True)
+
+    def d2h_loss(self, fit):
+        if self.kind == "clips":
+            f0 = fit.fitters[0]
+            return f0.loss_hist[(f0.steps_done - 1) % f0.hist_cap].item()
+        return fit.loss_hist[(fit.steps_done - 1) % fit.hist_cap].item()
+
+    def first_last_loss(self, fit):
+        ls = fit.losses()
+        if self.kind == "clips":
+            ls = ls.mean(axis=0)
+        return [float(ls[0]), float(ls[-1])] if len(ls) else None
+
+
 def run_ours(args, wl):
     import torch
     import torch.distributed as dist
@@ -184,32 +293,18 @@ def run_ours(args, wl):
     if world > 1:
         dist.init_process_group("nccl", device_id=dev)
         pg = dist.group.WORLD
-    T, H, Lh = wl["T"], wl["H"], wl["L"]
 
     prec = args.precision
-    if prec == "auto":
+    if wl["kind"] == "kan":
+        prec = "fp32"
+    elif prec == "auto":
         try:
-            L.check(L.lib().inr_siren_workspace_bytes(P.SirenSpec(1, H, Lh, 1, True).desc("bf16"), 1024, 1))
+            L.check(L.lib().inr_siren_workspace_bytes(P.SirenSpec(1, wl["H"], wl["L"], 1, True).desc("bf16"), 1024, 1))
             prec = "bf16"
         except L.InrLibraryError:
             prec = "fp32"
-
-    # data + model: synthetic waveform, reference-seeded init (random-init weights of the named architecture)
-    gt_np = P.utils.synth_waveform(T, seed=wl["seed"])
-    torch.manual_seed(wl["seed"])
-    model = P.Siren(1, H, Lh, 1, True)
-    spec = model.spec
-    # contiguous shard per rank, rounded to the 128-row tile
-    per = (T + world - 1) // world
-    per = (per + 127) // 128 * 128
-    i0 = min(rank * per, T)
-    n = max(0, min(per, T - i0))
-    host_target = torch.from_numpy(gt_np[i0:i0 + n]).pin_memory()
-    target = host_target.to(dev, non_blocking=True)
-
-    def make(use_graph):
-        return P.SirenFitter(spec, model.flat_parameters(), target, None, i0=i0, T_total=T, precision=prec,
-                             process_group=pg, use_graph=use_graph, hist_cap=4096)
+    job = Job(args, wl, rank, world, dev, pg, prec)
+    units = job.units_total                                   # coordinate-samples one whole-job step processes
 
     def barrier():
         if world > 1:
@@ -229,58 +324,22 @@ def run_ours(args, wl):
         return float(ms.item())
 
     # ---- device-resident throughput ("value")
-    fit = make(True)
+    fit = job.make(True)
     fit.step(args.warmup)
-    lc0 = L.lib().inr_launch_count()
     sampler = ClockSampler(local)
     if rank == 0:
         sampler.start()
     ms = timed(fit.step, args.steps)
     clocks = sampler.stop() if rank == 0 else None
-    value = T * args.steps / (ms * 1e-3)
-    losses = fit.losses()
+    value = units * args.steps / (ms * 1e-3)
+    first_last = job.first_last_loss(fit)
 
-    # ---- launches per step (counted on an un-graphed step: graph replays bypass the counter)
-    fit_ng = make(False)
-    fit_ng.step(1)
-    torch.cuda.synchronize(dev)
-    lc0 = L.lib().inr_launch_count()
-    fit_ng.step(1)
-    launches_per_step = int(L.lib().inr_launch_count() - lc0)
-
-    # ---- per-kernel device time with the library's event profiler (separate pass, same steps, no graph)
-    kern = {}
-    prof_steps = max(1, min(args.steps, 5))
-    fit_ng.step(2)
-    barrier()
-    L.profile_begin()
-    fit_ng.step(prof_steps)
-    prof = L.profile_end()
-    for tag, (cnt, tot) in prof.items():
-        kern[tag] = {"launches_per_step": cnt / prof_steps, "ms_per_step": tot / prof_steps}
-    gemm_tags = [t for t in kern if ("sgemm" in t or t.startswith("k_tc_"))]
-    gemm_ms = sum(kern[t]["ms_per_step"] for t in gemm_tags)
-    gemm_launches = sum(kern[t]["launches_per_step"] for t in gemm_tags)
-    pk = peaks()
-    hidden_flops = 6.0 * Lh * H * H * n                   # this rank's rows: fwd + dX + dW of the L hidden layers
-    achieved = hidden_flops / (gemm_ms * 1e-3) / 1e12 if gemm_ms > 0 else 0.0
-    roofline = {"bound": "tensor", "achieved": achieved, "peak": pk["bf16_sus"], "unit": "TFLOP/s",
-                "frac": achieved / pk["bf16_sus"], "traffic": None,
-                "kernel": "+".join(sorted(gemm_tags)), "flops_per_launch": hidden_flops / max(gemm_launches, 1),
-                "avg_launch_ms": gemm_ms / max(gemm_launches, 1), "gemm_share_of_step": gemm_ms / (ms / args.steps),
-                "peak_source": pk["src"] + ", sustained bf16 (kernel timed inside a long step)",
-                "mma_kind": "tcgen05 kind::f16 (bf16)" if prec == "bf16" else "none: fp32 FFMA on CUDA cores (parity mode)"}
-
-    # ---- end to end through the public API with HOST buffers: H2D of the step's target, D2H of its loss
-    fit_e = make(True)
-    fit_e.step(args.warmup)
-    torch.cuda.synchronize(dev)
-
+    # ---- end to end through the public API with HOST buffers: H2D of the step's targets, D2H of its loss
     def e2e_steps(k):
         for _ in range(k):
-            fit_e.target.copy_(host_target, non_blocking=True)
-            fit_e.step(1)
-            _ = fit_e.loss_hist[(fit_e.steps_done - 1) % fit_e.hist_cap].item()
+            job.h2d(fit)
+            fit.step(1)
+            _ = job.d2h_loss(fit)
     e2e_steps(1)
     barrier()
     t0 = time.perf_counter()
@@ -289,8 +348,67 @@ def run_ours(args, wl):
     dt = torch.tensor([time.perf_counter() - t0], device=dev, dtype=torch.float64)
     if world > 1:
         dist.all_reduce(dt, op=dist.ReduceOp.MAX)
-    e2e = {"value": T * args.steps / float(dt.item()), "unit": UNIT, "h2d_bytes_per_step": int(n * 4),
-           "d2h_bytes_per_step": 4}
+    e2e = {"value": units * args.steps / float(dt.item()), "unit": UNIT,
+           "h2d_bytes_per_step": int(job.host_target.numel() * 4), "d2h_bytes_per_step": 4}
+    del fit
+    torch.cuda.empty_cache()
+
+    # ---- launches per step and per-kernel device time (un-graphed pass: graph replays bypass the library's counter
+    #      and its event profiler); clip-parallel profiles a 8-clip subset on one stream and scales the launch count
+    if job.kind == "clips":
+        sub = P.ClipBatchFitter(job.spec, job.flat0[:8], job.target[:8], precision=prec, n_streams=1, use_graph=False, hist_cap=16)
+        scale_launch = job.flat0.shape[0] / 8.0
+        prof_units = 8 * wl["T"]
+    else:
+        sub = job.make(False)
+        scale_launch = 1.0
+        prof_units = job.n_local
+    sub.step(2)
+    torch.cuda.synchronize(dev)
+    lc0 = L.lib().inr_launch_count()
+    sub.step(1)
+    launches_per_step = int(round((L.lib().inr_launch_count() - lc0) * scale_launch))
+    prof_steps = max(1, min(args.steps, 5))
+    barrier()
+    L.profile_begin()
+    sub.step(prof_steps)
+    prof = L.profile_end()
+    kern = {tag: {"launches_per_step": cnt / prof_steps, "ms_per_step": tot / prof_steps} for tag, (cnt, tot) in prof.items()}
+    gemm_tags = [t for t in kern if ("sgemm" in t or t.startswith("k_tc_"))]
+    gemm_ms = sum(kern[t]["ms_per_step"] for t in gemm_tags)
+    gemm_launches = sum(kern[t]["launches_per_step"] for t in gemm_tags)
+    prof_total_ms = sum(v["ms_per_step"] for v in kern.values())
+    pk = peaks()
+    flops = job.flops_per_coord * prof_units              # dense contraction flops of the profiled rows, fwd + bwd
+    achieved = flops / (gemm_ms * 1e-3) / 1e12 if gemm_ms > 0 else 0.0
+    roofline = {"bound": "tensor", "achieved": achieved, "peak": pk["bf16_sus"], "unit": "TFLOP/s",
+                "frac": achieved / pk["bf16_sus"], "traffic": None,
+                "kernel": "+".join(sorted(gemm_tags)), "flops_per_launch": flops / max(gemm_launches, 1),
+                "avg_launch_ms": gemm_ms / max(gemm_launches, 1), "gemm_share_of_step": gemm_ms / max(prof_total_ms, 1e-9),
+                "peak_source": pk["src"] + ", sustained bf16 (kernel timed inside a long step)",
+                "mma_kind": "tcgen05 kind::f16 (bf16)" if prec == "bf16" else "none: fp32 FFMA on CUDA cores (parity mode)"}
+    # HBM-bound stages (north star: elementwise / spline / MDCT stages as achieved GB/s of the measured copy peak)
+    stages = {}
+
+    def stage(tag, nbytes, what):
+        if tag in kern and kern[tag]["ms_per_step"] > 0:
+            gbs = nbytes / (kern[tag]["ms_per_step"] * 1e-3) / 1e9
+            stages[tag] = {"bound": "hbm", "achieved": gbs, "peak": pk["hbm"], "unit": "GB/s", "frac": gbs / pk["hbm"],
+                           "algorithmic_bytes_per_step": int(nbytes), "what": what}
+    nparams = job.spec.num_params() * (8 if job.kind == "clips" else 1)
+    stage("k_adam", 32 * nparams, "28 B/param Adam + 4 B/param gradient re-zero")
+    if job.kind == "siren" and wl.get("spectral") == "mdct":
+        T = wl["T"]
+        stage("k_mdct_loss", 4 * T + 4 * (T // 1024) * 1024 + 8 * T, "read pred + target coefficients, read-modify-write d loss/d pred")
+    if job.kind == "siren" and wl.get("spectral") == "stft":
+        T = wl["T"]
+        nf = 1 + T // 256
+        stage("k_stft_loss_pass1", 4 * T + 4 * nf * 513, "read pred (frames overlap 4x in L2/L1) + target magnitudes")
+        stage("k_stft_loss_pass2", 4 * T + 4 * nf * 513 + 8 * T, "same + overlap-add of d loss/d pred")
+    if job.kind == "kan":
+        n = job.n_local
+        stage("k_kan_expand", 2 * (4 * n * (1 + 256 + 256) + 4 * n * 9 * (1 + 256 + 256)), "read layer inputs, write Phi (fwd + recompute in bwd)")
+        stage("k_kan_dx", 4 * n * 256 * 11, "read x, dPhi (9/feature), write dx")
 
     # ---- CPU baseline beside it (rank 0, N = 1 only)
     cpu = None
@@ -299,19 +417,20 @@ def run_ours(args, wl):
         rows = pick_rows(wl, args.cpu_budget_s, 4, threads)
         rate, per_s = oracle_fit_rate(wl, rows, 3, 1, threads)
         cpu = {"value": rate, "unit": UNIT, "cores": threads, "kind": "port",
-               "sample": "oracle (torch-CPU fp32 restatement of run.py's loop) on the first %d of %d coordinates, "
-                         "3 timed steps after 1 warm-up, %.2f s/step" % (rows, T, per_s)}
+               "sample": "oracle (torch-CPU fp32 restatement of run.py's loop) on the first %d of %d coordinates%s, "
+                         "3 timed steps after 1 warm-up, %.2f s/step" % (rows, wl["T"], " of one clip" if job.kind == "clips" else "", per_s)}
 
     if rank == 0:
+        par = ("clip-parallel x%d (no collective)" % world) if job.kind == "clips" else ("coord-shard x%d" % world)
         line = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps,
                 "warmup": args.warmup, "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": "strong",
                 "vs_baseline": None, "dtype": "bf16" if prec == "bf16" else "f32", "data": "synthetic",
-                "config": {"workload": wl["desc"], "precision": prec, "parallelism": "coord-shard x%d" % world,
-                           "rows_per_rank": n, "l2": "working set (activation workspace, GBs) >> 126 MB L2; no flush needed",
+                "config": {"workload": wl["desc"], "precision": prec, "parallelism": par,
+                           "units_per_rank": job.n_local, "l2": "working set (activation workspace, GBs) >> 126 MB L2; no flush needed",
                            "cuda_graph": True},
                 "clocks": clocks, "e2e": e2e, "gpu_launches": launches_per_step * args.steps,
-                "roofline": roofline, "cpu_baseline": cpu, "kernels": kern,
-                "loss_first_last": [float(losses[0]), float(losses[-1])] if len(losses) else None}
+                "roofline": roofline, "hbm_stages": stages, "cpu_baseline": cpu, "kernels": kern,
+                "loss_first_last": first_last}
         print(json.dumps(line), flush=True)
     if world > 1:
         dist.destroy_process_group()

@@ -6,9 +6,9 @@ fallback: importing the model classes works anywhere, calling them without the b
 """
 from .models import SineLayer, Siren, SirenWithSnakeTanh  # noqa: F401
 from .utils import get_coord, calculate_snr, WaveformFitting, MDCTFitting  # noqa: F401
-from .engine import SirenFitter, SirenSpec  # noqa: F401
+from .engine import ClipBatchFitter, SirenFitter, SirenSpec  # noqa: F401
 from .kan import KAN, KANLinear, KanFitter, KanSpec  # noqa: F401
 from .run import train  # noqa: F401
 
 __all__ = ["SineLayer", "Siren", "SirenWithSnakeTanh", "get_coord", "calculate_snr", "WaveformFitting",
-           "MDCTFitting", "SirenFitter", "SirenSpec", "KAN", "KANLinear", "KanFitter", "KanSpec", "train"]
+           "MDCTFitting", "SirenFitter", "SirenSpec", "ClipBatchFitter", "KAN", "KANLinear", "KanFitter", "KanSpec", "train"]

@@ -51,6 +51,29 @@ class SirenSpec:
         return 6 * self.hidden_layers * self.hidden_features ** 2 + 10 * self.hidden_features
 
 
+def shard_range(T: int, rank: int, world: int, tile: int = 128):
+    """Coordinate sharding of ONE fit over `world` GPUs: rank r owns the contiguous global index range
+    [i0, i0 + n), every shard a multiple of the 128-row tile except the last; coordinates are generated in-kernel from
+    the GLOBAL index and the GLOBAL length, so they are bit-identical to the single-GPU run.  -> (i0, n, shard_size)"""
+    per = (T + world - 1) // world
+    per = (per + tile - 1) // tile * tile
+    i0 = min(rank * per, T)
+    return i0, max(0, min(per, T - i0)), per
+
+
+def allreduce_step_state(grads: torch.Tensor, loss_acc: torch.Tensor, pg, world: int, whole_output_loss: bool):
+    """The one exchange step of a sharded fit: sum-allreduce of the flat gradient and of the loss accumulators
+    [time-loss numerator, spectral loss].  A whole-output loss was evaluated redundantly (identically) on every rank,
+    so its sum is divided by the world size; the division also makes the value bit-identical on all ranks, which keeps
+    the replicated plateau schedulers in lock-step."""
+    if world <= 1:
+        return
+    torch.distributed.all_reduce(grads, group=pg)
+    torch.distributed.all_reduce(loss_acc[0:2], group=pg)
+    if whole_output_loss:
+        loss_acc[1:2].div_(world)
+
+
 def _require_cuda(t: torch.Tensor, what: str):
     if not t.is_cuda:
         raise L.InrLibraryError("%s must live on a CUDA device: the INR hot path has no CPU fallback" % what)
@@ -96,7 +119,7 @@ class SirenFitter:
                  *, i0: int = 0, T_total: Optional[int] = None, coord_scale: float = 1.0, loss_mode: str = "mse",
                  lr: float = 1e-3, min_lr: float = 1e-6, alpha: float = 0.0, precision: str = "fp32",
                  hist_cap: int = 65536, process_group=None, use_graph: bool = True, spectral=None,
-                 spectral_target: Optional[torch.Tensor] = None):
+                 spectral_target: Optional[torch.Tensor] = None, workspace: Optional["Workspace"] = None):
         _require_cuda(target, "target")
         self.spec = spec
         self.device = target.device
@@ -135,7 +158,7 @@ class SirenFitter:
             self.out_full = self.out if self.world == 1 else torch.empty(self.full_T, dtype=torch.float32, device=self.device)
             if self.world > 1:
                 # equal shard sizes are what all_gather_into_tensor needs; the bench/train shard that way
-                self._shard = (self.full_T + self.world - 1) // self.world
+                self._shard = shard_range(self.full_T, 0, self.world)[2]
         dev = self.device
         # one arena: [params | grads | m | v], each padded to 64 floats so every block is 256-byte aligned
         self.Ppad = (self.P + 63) // 64 * 64
@@ -150,7 +173,7 @@ class SirenFitter:
         self.opt = torch.zeros((L.OPT_STATE_BYTES + 7) // 8 * 8, dtype=torch.uint8, device=dev)
         self.loss_acc = self.opt[L.OPT_LOSS_ACC_OFFSET:L.OPT_LOSS_ACC_OFFSET + 32].view(torch.float64)
         L.check(L.lib().inr_opt_init(L.ptr(self.opt), lr, min_lr, self.hist_cap, L.stream_ptr()))
-        self.ws = Workspace(dev)
+        self.ws = workspace if workspace is not None else Workspace(dev)
         self.ws.get(self.desc, self.n, True)
         self.steps_done = 0
         self.use_graph = bool(use_graph) and self.world == 1
@@ -204,11 +227,7 @@ class SirenFitter:
         self.out_full.copy_(gathered[:self.full_T])
 
     def _allreduce(self):
-        if self.world > 1:
-            torch.distributed.all_reduce(self.grads, group=self.pg)
-            torch.distributed.all_reduce(self.loss_acc[0:2], group=self.pg)
-            if self.split:
-                self.loss_acc[1:2].div_(self.world)   # every rank evaluated the same whole-output loss
+        allreduce_step_state(self.grads, self.loss_acc, self.pg, self.world, self.split)
 
     def _enqueue_step(self):
         if self.split:
@@ -310,3 +329,82 @@ class SirenFitter:
         self.grads.zero_()
         self.loss_acc.zero_()
         return loss, g, out
+
+
+class ClipBatchFitter:
+    """Clip-parallel batch fit (BASELINE.json config 5): K independent clips, each with its OWN SIREN,
+    parameters, Adam state and plateau scheduler, fitted concurrently on one GPU with no communication.
+
+    Every clip is a SirenFitter state (3.2 MB of arena at 3x256); the clips are dealt round-robin onto `n_streams`
+    CUDA streams, each stream owning one activation workspace that its clips reuse in turn, and ONE CUDA graph holds
+    a whole batch step (all clips, all streams, fork/join) so a step costs one launch from the host.  Across GPUs the
+    clips are simply partitioned (`clip_range`): there is no collective on this path.
+    """
+
+    def __init__(self, spec: SirenSpec, params0: torch.Tensor, targets: torch.Tensor, *, precision: str = "fp32",
+                 loss_mode: str = "mse", lr: float = 1e-3, min_lr: float = 1e-6, n_streams: int = 4,
+                 hist_cap: int = 4096, use_graph: bool = True):
+        _require_cuda(targets, "targets")
+        assert targets.dim() == 2 and params0.dim() == 2 and params0.shape[0] == targets.shape[0]
+        self.K, self.T = targets.shape
+        self.device = targets.device
+        self.spec = spec
+        self.n_streams = max(1, min(int(n_streams), self.K))
+        self.workspaces = [Workspace(self.device) for _ in range(self.n_streams)]
+        self.fitters = [SirenFitter(spec, params0[k], targets[k], None, loss_mode=loss_mode, lr=lr, min_lr=min_lr,
+                                    precision=precision, hist_cap=hist_cap, use_graph=False,
+                                    workspace=self.workspaces[k % self.n_streams]) for k in range(self.K)]
+        self.streams = [torch.cuda.Stream(device=self.device) for _ in range(self.n_streams)]
+        self.use_graph = bool(use_graph)
+        self._graph = None
+        self.steps_done = 0
+
+    @staticmethod
+    def clip_range(num_clips: int, rank: int, world: int):
+        """Contiguous block partition of the clips over ranks (the first num_clips % world ranks get one more)."""
+        base, rem = divmod(num_clips, world)
+        lo = rank * base + min(rank, rem)
+        return lo, lo + base + (1 if rank < rem else 0)
+
+    def _enqueue_batch_step(self, main: torch.cuda.Stream):
+        for s in self.streams:
+            s.wait_stream(main)
+        for si, s in enumerate(self.streams):
+            with torch.cuda.stream(s):
+                for k in range(si, self.K, self.n_streams):
+                    self.fitters[k]._enqueue_step()
+        for s in self.streams:
+            main.wait_stream(s)
+
+    def step(self, n_steps: int = 1):
+        cur = torch.cuda.current_stream(self.device)
+        if self.use_graph and self._graph is None:
+            cap = torch.cuda.Stream(device=self.device)
+            cap.wait_stream(cur)
+            with torch.cuda.stream(cap):
+                g = torch.cuda.CUDAGraph()
+                with torch.cuda.graph(g, stream=cap):
+                    self._enqueue_batch_step(cap)
+            cur.wait_stream(cap)
+            self._graph = g
+        for _ in range(n_steps):
+            if self._graph is not None:
+                self._graph.replay()
+            else:
+                self._enqueue_batch_step(cur)
+        self.steps_done += n_steps
+        for f in self.fitters:
+            f.steps_done += n_steps
+
+    def losses(self) -> np.ndarray:
+        """(K, steps) per-clip loss histories."""
+        return np.stack([f.losses() for f in self.fitters])
+
+    def snr_db(self, targets: torch.Tensor) -> np.ndarray:
+        """utils.py:77-97 calculate_snr(target, model output) per clip, evaluated on the device."""
+        out = np.empty(self.K)
+        for k, f in enumerate(self.fitters):
+            y = f.forward().double()
+            t = targets[k].double()
+            out[k] = float(10.0 * torch.log10((t * t).mean() / ((y - t) ** 2).mean()))
+        return out

@@ -44,13 +44,54 @@ def _adam_state_dict(model, fitter: SirenFitter, lr: float):
     return {"state": state, "param_groups": [group]}
 
 
+def _train_kan(a):
+    """run.py:109-110 `KAN([1, H, H, 1])` branch of train(): same loop on the device through KanFitter."""
+    from .kan import KAN, KanFitter
+    H = a['num_hidden_features']
+    model = KAN([a['input_dimension'], H, H, 1])
+    if a['prev_ckpt_path'] is not None:
+        ck = torch.load(a['prev_ckpt_path'], map_location='cpu')
+        model.load_state_dict(ck['model_state_dict'])
+    model.cuda()
+    dev = next(model.parameters()).device
+    target_np = a['target_np']
+    fitter = KanFitter(model.spec, model.flat_parameters(), model.flat_grids(), torch.from_numpy(target_np).to(dev), None,
+                       loss_mode=a['loss_mode'], lr=a['learning_rate'], min_lr=a['min_learning_rate'],
+                       hist_cap=max(int(a['total_steps']), 1))
+    if a['prev_ckpt_path'] is not None and ck.get('optimizer_state_dict'):
+        fitter.load_adam_state(ck['optimizer_state_dict'])
+    t0 = time.time()
+    fitter.step(int(a['total_steps']))
+    torch.cuda.synchronize(dev)
+    total_time = (time.time() - t0) / 60
+    model.load_flat(fitter.params)
+    final_np = fitter.forward().cpu().numpy().astype(np.float32)
+    folder = a['experiment_folder']
+    wavfile.write(f'{folder}/output.wav', int(a['input_data'].sample_rate), final_np)
+    snr_final = float(calculate_snr(target_np, final_np))
+    ckpt_path = f'{folder}/saved_ckpt.pt'
+    torch.save({'model_state_dict': {k: v.detach().cpu().clone() for k, v in model.state_dict().items()},
+                'optimizer_state_dict': _adam_state_dict(model, fitter, a['learning_rate'])}, ckpt_path)
+    loss_hist = fitter.losses()
+    save_parameters(folder, experiment_path=a['experiment_path'], tag=a['tag'], inst=a['inst'], duration=a['duration'],
+                    method=a['method'], arch='kan', loss_mode=a['loss_mode'], num_hidden_features=H,
+                    total_steps=a['total_steps'], learning_rate=a['learning_rate'],
+                    min_learning_rate=a['min_learning_rate'], curr_ckpt_path=ckpt_path,
+                    **{'total_trainig_time(min)': total_time, 'SNR': snr_final,
+                       'final_loss_dB': float(10 * np.log10(loss_hist[-1] + 1e-10)) if len(loss_hist) else None})
+    return ckpt_path
+
+
 def train(experiment_path: str, tag: str, inst: str, duration: int, num_channels=1, method='wave', arch='mlp',
           loss_mode='mse', mode=None, decimation=1, bwe=False, num_hidden_features=256, num_sine=2, num_snake=2,
           num_tanh=0, num_freq=None, omega=22000, first_linear=False, last_linear=True, hidden_omega=30,
           a_initial=0.5, total_steps=20000, learning_rate=1e-3, min_learning_rate=1e-6, alpha=0.0,
-          prev_ckpt_path=None, visualization=False, *, precision='fp32', data_dir='data', seed=None, verbose=True):
+          prev_ckpt_path=None, visualization=False, *, precision='fp32', data_dir='data', seed=None, verbose=True,
+          spectral='stft'):
     """run.py:30.  Extra keyword-only arguments: precision ('fp32' CUDA-core parity mode | 'bf16' tcgen05 mode),
-    data_dir (the reference hard-codes 'data/'), seed (torch.manual_seed before model construction)."""
+    data_dir (the reference hard-codes 'data/'), seed (torch.manual_seed before model construction), spectral (which
+    windowed-transform loss `alpha` mixes in: 'stft' = auraloss STFTLoss as run.py:128,160 does, 'mdct' / 'mdct_mse' =
+    the MDCT-domain loss of BASELINE.json config 3)."""
     filename = f'{data_dir}/{inst}.wav'
     experiment_folder = f'{experiment_path}/{inst}-{method}-{tag}'
     while os.path.exists(experiment_folder):
@@ -59,12 +100,12 @@ def train(experiment_path: str, tag: str, inst: str, duration: int, num_channels
     os.makedirs(experiment_folder)
     decimation = int(decimation)
     takelog = False
-    if arch == 'kan':
-        raise NotImplementedError("arch='kan' goes through inr_for_audio_b200.kan (KAN fit path)")
     if num_freq is not None:
         raise NotImplementedError("num_freq (rff Gaussian encoding, run.py:141-144) is SURVEY.md §8(f)-4, not built")
-    if alpha != 0.0:
-        raise NotImplementedError("alpha != 0 needs the spectral-loss path (use SirenFitter with a spectral loss)")
+    if arch == 'kan' and (method != 'wave' or alpha != 0.0 or loss_mode == 'snr'):
+        raise NotImplementedError("arch='kan' is waveform-only (run.py:93,110) with the mse/mae losses on the device path")
+    if alpha != 0.0 and method != 'wave':
+        raise NotImplementedError("spectral losses act on a waveform output (method='wave')")
 
     if method == 'wave':
         input_data = WaveformFitting(filename, duration=duration, decimation=decimation, verbose=verbose)
@@ -83,6 +124,8 @@ def train(experiment_path: str, tag: str, inst: str, duration: int, num_channels
 
     if seed is not None:
         torch.manual_seed(seed)
+    if arch == 'kan':
+        return _train_kan(locals())
     model = SirenWithSnakeTanh(in_features=input_dimension, out_features=1, hidden_features=num_hidden_features,
                                num_sine=num_sine, num_snake=num_snake, num_tanh=num_tanh, num_freq=num_freq,
                                first_linear=first_linear, last_linear=last_linear, first_omega_0=omega,
@@ -99,7 +142,7 @@ def train(experiment_path: str, tag: str, inst: str, duration: int, num_channels
     fitter = SirenFitter(model.spec, model.flat_parameters(), target,
                          None if coords is None else coords.to(dev), loss_mode=loss_mode, lr=learning_rate,
                          min_lr=min_learning_rate, alpha=alpha, precision=precision,
-                         hist_cap=max(int(total_steps), 1))
+                         hist_cap=max(int(total_steps), 1), spectral=(spectral if alpha != 0.0 else None))
     if checkpoint is not None and checkpoint.get('optimizer_state_dict'):
         fitter.load_adam_state(checkpoint['optimizer_state_dict'])
 

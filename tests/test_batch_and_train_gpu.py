@@ -1,0 +1,79 @@
+"""Clip-parallel batch fitting (BASELINE.json config 5) and the train() drop-in (run.py:30) on the device."""
+import json
+import os
+
+import numpy as np
+import pytest
+import torch
+
+pytestmark = pytest.mark.gpu
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+@pytest.fixture(scope="module")
+def pkg():
+    import inr_for_audio_b200 as P
+    assert torch.cuda.is_available()
+    return P
+
+
+def dev():
+    return torch.device("cuda:0")
+
+
+@pytest.mark.parametrize("precision,streams", [("fp32", 3), ("bf16", 2)])
+def test_clip_parallel_equals_serial_per_clip(pkg, precision, streams):
+    """K clips fitted concurrently (streams + one CUDA graph) == each clip fitted alone: the clips share nothing, so
+    in fp32 mode the first steps agree to reduction-order noise, clip by clip; and against the oracle for clip 0."""
+    from oracle import inr_oracle as O
+    K, T, H, Lh, steps = 5, 6000, 128, 2, 4
+    gts = np.stack([pkg.utils.synth_waveform(T, seed=10 + k) for k in range(K)])
+    flats = []
+    for k in range(K):
+        torch.manual_seed(k)
+        flats.append(pkg.Siren(1, H, Lh, 1, True).flat_parameters().clone())
+    spec = pkg.SirenSpec(1, H, Lh, 1, True)
+    tg = torch.from_numpy(gts).to(dev())
+    batch = pkg.ClipBatchFitter(spec, torch.stack(flats), tg, precision=precision, n_streams=streams)
+    batch.step(steps)
+    bl = batch.losses()
+    assert bl.shape == (K, steps)
+    tol = 1e-4 if precision == "fp32" else 2e-2
+    for k in range(K):
+        solo = pkg.SirenFitter(spec, flats[k], tg[k], precision=precision, use_graph=False)
+        solo.step(steps)
+        np.testing.assert_allclose(bl[k], solo.losses(), rtol=tol)
+    if precision == "fp32":
+        ospec = O.SirenSpec(1, H, Lh, 1, True)
+        ps = O.siren_init(ospec, seed=0)
+        ref, _, _ = O.siren_fit(ospec, ps, O.get_coord(T, 1), torch.from_numpy(gts[0]).view(-1, 1), steps)
+        np.testing.assert_allclose(bl[0], ref, rtol=1e-3)
+    snr = batch.snr_db(tg)
+    assert snr.shape == (K,) and np.all(np.isfinite(snr))
+
+
+def test_train_dropin_wave_kan_and_spectral(pkg, tmp_path):
+    """train(...) keeps run.py:30's signature and artefacts (output.wav, saved_ckpt.pt with the reference's keys,
+    parameters.json) for the sine MLP, for arch='kan' (run.py:110) and with alpha != 0 (run.py:163-169)."""
+    common = dict(inst="gt_bach", duration=1, method="wave", num_snake=0, num_tanh=0, omega=30, total_steps=60,
+                  data_dir=os.path.join(ROOT, "data"), seed=0, verbose=False)
+    ck = pkg.train(str(tmp_path), "mlp", num_sine=2, num_hidden_features=64, **common)
+    sd = torch.load(ck, map_location="cpu")
+    assert list(sd["model_state_dict"].keys()) == ["net.0.linear.weight", "net.0.linear.bias", "net.1.linear.weight",
+                                                   "net.1.linear.bias", "net.2.linear.weight", "net.2.linear.bias",
+                                                   "net.3.weight", "net.3.bias"]
+    par = json.load(open(os.path.join(os.path.dirname(ck), "parameters.json")))
+    assert np.isfinite(par["SNR"]) and par["SNR"] > 0
+    # resume from the checkpoint (run.py:84-106) with a spectral term mixed in
+    ck2 = pkg.train(str(tmp_path), "mlp-stft", num_sine=2, num_hidden_features=64, alpha=0.1, prev_ckpt_path=ck, **common)
+    par2 = json.load(open(os.path.join(os.path.dirname(ck2), "parameters.json")))
+    assert np.isfinite(par2["SNR"])
+    ck3 = pkg.train(str(tmp_path), "mlp-mdct", num_sine=2, num_hidden_features=64, alpha=0.2, spectral="mdct", **common)
+    assert os.path.exists(os.path.join(os.path.dirname(ck3), "output.wav"))
+    ck4 = pkg.train(str(tmp_path), "mlp-snr", num_sine=2, num_hidden_features=64, loss_mode="snr", **common)
+    assert np.isfinite(json.load(open(os.path.join(os.path.dirname(ck4), "parameters.json")))["SNR"])
+    ckk = pkg.train(str(tmp_path), "kan", arch="kan", num_hidden_features=32, **common)
+    sdk = torch.load(ckk, map_location="cpu")
+    assert "layers.0.base_weight" in sdk["model_state_dict"] and "layers.2.grid" in sdk["model_state_dict"]
+    assert json.load(open(os.path.join(os.path.dirname(ckk), "parameters.json")))["SNR"] > 0
