@@ -1,0 +1,86 @@
+"""Multi-GPU equivalence check (run under torchrun, one rank per GPU):
+  (1) coordinate-sharded fit == single-GPU fit of the same problem (loss, gradients, first steps), SIREN fp32/bf16,
+      with and without a whole-output (MDCT) loss, and the KAN;
+  (2) all ranks hold bit-identical parameters after the steps (replicas in lock-step without a broadcast);
+  (3) clip-parallel partition: every rank's clips == the same clips fitted in a single process.
+Prints 'MULTI_GPU_OK' on rank 0.  Used by tests/test_multi_gpu.py and by hand through gpurun --gpus 2."""
+import os
+import sys
+
+import numpy as np
+import torch
+import torch.distributed as dist
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+import inr_for_audio_b200 as P  # noqa: E402
+from inr_for_audio_b200.engine import shard_range  # noqa: E402
+
+
+def main():
+    rank, world, local = int(os.environ["RANK"]), int(os.environ["WORLD_SIZE"]), int(os.environ["LOCAL_RANK"])
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    dist.init_process_group("nccl", device_id=dev)
+    pg = dist.group.WORLD
+    T = 50000
+    gt = torch.from_numpy(P.utils.synth_waveform(T, seed=5)).to(dev)
+    i0, n, _ = shard_range(T, rank, world)
+    cases = [("fp32", None, 0.0, 64, 2, 1e-5, 2e-4), ("bf16", None, 0.0, 128, 2, 1e-3, 2e-2), ("fp32", "mdct", 0.2, 64, 2, 1e-5, 2e-4),
+             ("fp32", "stft", 0.1, 64, 1, 1e-5, 5e-4)]
+    for prec, spectral, alpha, H, Lh, ltol, gtol in cases:
+        torch.manual_seed(0)
+        model = P.Siren(1, H, Lh, 1, True)
+        flat = model.flat_parameters()
+        full = P.SirenFitter(model.spec, flat, gt, precision=prec, alpha=alpha, spectral=spectral, use_graph=False)
+        l1, g1, _ = full.loss_and_grads()
+        sh = P.SirenFitter(model.spec, flat, gt[i0:i0 + n], i0=i0, T_total=T, precision=prec, alpha=alpha, spectral=spectral,
+                           spectral_target=gt if spectral else None, process_group=pg, use_graph=False)
+        l2, g2, _ = sh.loss_and_grads()
+        gerr = float((g1 - g2).norm() / g1.norm())
+        assert abs(l1 - l2) <= ltol * abs(l1), (prec, spectral, l1, l2)
+        assert gerr <= gtol, (prec, spectral, gerr)
+        full.step(5)
+        sh.step(5)
+        np.testing.assert_allclose(sh.losses(), full.losses(), rtol=5e-3 if prec == "fp32" else 5e-2)
+        mine = sh.params.clone()
+        ref = mine.clone()
+        dist.broadcast(ref, 0)
+        assert torch.equal(mine, ref), "replicas diverged (%s, %s)" % (prec, spectral)
+        if rank == 0:
+            print("sharded == single: %s spectral=%s loss %.8f / %.8f grad rel err %.2e" % (prec, spectral, l1, l2, gerr), flush=True)
+    # KAN
+    torch.manual_seed(1)
+    kan = P.KAN([1, 32, 32, 1])
+    fk = P.KanFitter(kan.spec, kan.flat_parameters(), kan.flat_grids(), gt, use_graph=False)
+    l1, g1, _ = fk.loss_and_grads()
+    sk = P.KanFitter(kan.spec, kan.flat_parameters(), kan.flat_grids(), gt[i0:i0 + n], i0=i0, T_total=T, process_group=pg, use_graph=False)
+    l2, g2, _ = sk.loss_and_grads()
+    assert abs(l1 - l2) <= 1e-5 * abs(l1) and float((g1 - g2).norm() / g1.norm()) <= 2e-4
+    # clip-parallel
+    K, Tc = 6, 4000
+    lo, hi = P.ClipBatchFitter.clip_range(K, rank, world)
+    gts = torch.from_numpy(np.stack([P.utils.synth_waveform(Tc, seed=20 + k) for k in range(K)])).to(dev)
+    flats = []
+    for k in range(K):
+        torch.manual_seed(k)
+        flats.append(P.Siren(1, 64, 2, 1, True).flat_parameters().clone())
+    flats = torch.stack(flats)
+    spec = P.SirenSpec(1, 64, 2, 1, True)
+    mine = P.ClipBatchFitter(spec, flats[lo:hi], gts[lo:hi], n_streams=2)
+    mine.step(4)
+    allc = P.ClipBatchFitter(spec, flats, gts, n_streams=1, use_graph=False)
+    allc.step(4)
+    np.testing.assert_allclose(mine.losses(), allc.losses()[lo:hi], rtol=1e-4)
+    final = torch.zeros(K, device=dev, dtype=torch.float64)
+    final[lo:hi] = torch.from_numpy(mine.losses()[:, -1]).to(dev)
+    dist.all_reduce(final)                       # the only communication of the mode: gather the per-clip results
+    np.testing.assert_allclose(final.cpu().numpy(), allc.losses()[:, -1], rtol=1e-4)
+    dist.barrier()
+    if rank == 0:
+        print("MULTI_GPU_OK world=%d" % world, flush=True)
+    dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()
