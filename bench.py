@@ -252,7 +252,8 @@ class Job:
                                      use_graph=use_graph, hist_cap=256)
         kw = dict(i0=self.i0, T_total=wl["T"], process_group=self.pg, use_graph=use_graph, hist_cap=4096)
         if self.kind == "kan":
-            return P.KanFitter(self.spec, self.model.flat_parameters(), self.model.flat_grids(), self.target, None, **kw)
+            return P.KanFitter(self.spec, self.model.flat_parameters(), self.model.flat_grids(), self.target, None,
+                               precision=self.prec, **kw)
         f = P.SirenFitter(self.spec, self.model.flat_parameters(), self.target, None, precision=self.prec,
                           alpha=wl.get("alpha", 0.0), spectral=wl.get("spectral"), spectral_target=self.full_target, **kw)
         return f
@@ -296,7 +297,7 @@ def run_ours(args, wl):
 
     prec = args.precision
     if wl["kind"] == "kan":
-        prec = "fp32"
+        prec = "bf16" if prec == "auto" else prec
     elif prec == "auto":
         try:
             L.check(L.lib().inr_siren_workspace_bytes(P.SirenSpec(1, wl["H"], wl["L"], 1, True).desc("bf16"), 1024, 1))
@@ -374,7 +375,7 @@ def run_ours(args, wl):
     sub.step(prof_steps)
     prof = L.profile_end()
     kern = {tag: {"launches_per_step": cnt / prof_steps, "ms_per_step": tot / prof_steps} for tag, (cnt, tot) in prof.items()}
-    gemm_tags = [t for t in kern if ("sgemm" in t or t.startswith("k_tc_"))]
+    gemm_tags = [t for t in kern if ("sgemm" in t or t.startswith("k_tc_") or t.startswith("k_kan_tc_") or t.startswith("k_kan_thin"))]
     gemm_ms = sum(kern[t]["ms_per_step"] for t in gemm_tags)
     gemm_launches = sum(kern[t]["launches_per_step"] for t in gemm_tags)
     prof_total_ms = sum(v["ms_per_step"] for v in kern.values())

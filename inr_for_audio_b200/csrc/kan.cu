@@ -21,6 +21,7 @@ constexpr int KAN_MAX_KNOTS = 24;   // G + 2K + 1 <= 24  (G <= 17)
 struct KanLayout {
   int L, nb;           // layers, bases per input (G + K)
   int w[INR_KAN_MAX_LAYERS + 1];
+  int kind[INR_KAN_MAX_LAYERS];   // kernel family per layer (KL_*), filled by kan_layout_k
   __host__ __device__ int64_t layer_params(int l) const { return (int64_t)w[l + 1] * w[l] * (nb + 2); }
   __host__ __device__ int64_t base_off(int l) const {
     int64_t o = 0;
@@ -42,6 +43,7 @@ static KanLayout kan_layout(const inr_kan_desc* d) {
   k.L = d->num_layers;
   k.nb = d->grid_size + d->spline_order;
   for (int i = 0; i <= INR_KAN_MAX_LAYERS; ++i) k.w[i] = (i <= d->num_layers) ? d->widths[i] : 0;
+  for (int i = 0; i < INR_KAN_MAX_LAYERS; ++i) k.kind[i] = 0;
   return k;
 }
 
@@ -183,8 +185,25 @@ __global__ void __launch_bounds__(256) k_out_loss(const float* __restrict__ out,
 
 }  // namespace inr
 
+#include "kan_tc.cuh"
+
 // ================================================================================================ host side
 namespace inr {
+
+// which kernel family runs layer l in the bf16 mode
+enum { KL_GENERIC = 0, KL_TC = 1, KL_THIN = 2 };
+static int kan_layer_kind(const inr_kan_desc* d, int l) {
+  if (d->precision != INR_PREC_BF16) return KL_GENERIC;
+  const int in = d->widths[l], out = d->widths[l + 1];
+  if (in % KT_SLAB == 0 && out == KanFwdCfg::OUT) return KL_TC;
+  if (out == 1 && in <= 32 * KT_THIN_PER) return KL_THIN;
+  return KL_GENERIC;
+}
+static KanLayout kan_layout_k(const inr_kan_desc* d) {
+  KanLayout k = kan_layout(d);
+  for (int l = 0; l < k.L; ++l) k.kind[l] = kan_layer_kind(d, l);
+  return k;
+}
 
 static int check_kan_desc(const inr_kan_desc* d) {
   INR_REQUIRE(d != nullptr, INR_E_BADARG, "kan desc is NULL");
@@ -195,12 +214,17 @@ static int check_kan_desc(const inr_kan_desc* d) {
               "KAN: grid_size %d unsupported", d->grid_size);
   for (int i = 0; i <= d->num_layers; ++i)
     INR_REQUIRE(d->widths[i] >= 1 && d->widths[i] <= 4096, INR_E_UNSUPPORTED, "KAN: layer width %d unsupported", d->widths[i]);
-  INR_REQUIRE(d->precision == INR_PREC_FP32, INR_E_UNSUPPORTED, "KAN: only INR_PREC_FP32 is built (precision %d)", d->precision);
+  INR_REQUIRE(d->precision == INR_PREC_FP32 || d->precision == INR_PREC_BF16, INR_E_BADARG, "KAN: unknown precision %d", d->precision);
+  if (d->precision == INR_PREC_BF16)
+    INR_REQUIRE(d->grid_size + d->spline_order + 1 == KT_NF, INR_E_UNSUPPORTED,
+                "KAN bf16 mode is built for grid_size 5 / spline_order 3 (9 expanded features per input), got grid_size %d", d->grid_size);
   return INR_OK;
 }
 
 struct KanWs {
   float* wc[INR_KAN_MAX_LAYERS];   // combined weights per layer
+  __nv_bfloat16* wf[INR_KAN_MAX_LAYERS];   // bf16 mode: packed forward / backward operands of the tensor-core layers
+  __nv_bfloat16* wb[INR_KAN_MAX_LAYERS];
   float* gwc;                      // combined-weight gradient scratch (largest layer), zero between uses
   float* act[INR_KAN_MAX_LAYERS + 1];  // act[l] = input of layer l (act[0] unused: coords), act[L] = network output
   float* phi;                      // rows x max_l (nf * in_l)
@@ -212,7 +236,7 @@ static int64_t kan_fixed_floats(const KanLayout& k) {
   int64_t tot = 0, mx = 0;
   for (int l = 0; l < k.L; ++l) {
     const int64_t n = (int64_t)k.w[l + 1] * k.w[l] * (k.nb + 1);
-    tot += round_up(n, 64);
+    tot += round_up(n, 64) * (k.kind[l] == KL_TC ? 2 : 1);   // + WF and WB (2 x bf16 = one float per element)
     mx = std::max(mx, n);
   }
   return tot + round_up(mx, 64);
@@ -220,7 +244,8 @@ static int64_t kan_fixed_floats(const KanLayout& k) {
 static int64_t kan_row_floats(const KanLayout& k, int training) {
   int64_t wmax = 0, kmax = 0, acts = 0;
   for (int l = 0; l <= k.L; ++l) wmax = std::max<int64_t>(wmax, k.w[l]);
-  for (int l = 0; l < k.L; ++l) kmax = std::max<int64_t>(kmax, (int64_t)k.w[l] * (k.nb + 1));
+  for (int l = 0; l < k.L; ++l)
+    if (k.kind[l] == KL_GENERIC) kmax = std::max<int64_t>(kmax, (int64_t)k.w[l] * (k.nb + 1));   // Phi scratch: fp32 layers only
   for (int l = 1; l <= k.L; ++l) acts += k.w[l];
   return training ? acts + kmax + 2 * wmax : 2 * wmax + kmax;
 }
@@ -240,13 +265,20 @@ static int kan_carve(const KanLayout& k, int training, int64_t n, void* ws, int6
     const int64_t nn = (int64_t)k.w[l + 1] * k.w[l] * (k.nb + 1);
     w->wc[l] = p;
     p += round_up(nn, 64);
+    w->wf[l] = w->wb[l] = nullptr;
+    if (k.kind[l] == KL_TC) {
+      w->wf[l] = reinterpret_cast<__nv_bfloat16*>(p);
+      w->wb[l] = w->wf[l] + nn;
+      p += round_up(nn, 64);
+    }
     mx = std::max(mx, nn);
   }
   w->gwc = p;
   p += round_up(mx, 64);
   int64_t wmax = 0, kmax = 0;
   for (int l = 0; l <= k.L; ++l) wmax = std::max<int64_t>(wmax, k.w[l]);
-  for (int l = 0; l < k.L; ++l) kmax = std::max<int64_t>(kmax, (int64_t)k.w[l] * (k.nb + 1));
+  for (int l = 0; l < k.L; ++l)
+    if (k.kind[l] == KL_GENERIC) kmax = std::max<int64_t>(kmax, (int64_t)k.w[l] * (k.nb + 1));
   auto take = [&](int64_t floats) { float* r = p; p += round_up(floats, 64); return r; };
   w->act[0] = nullptr;
   if (training) {
@@ -272,6 +304,22 @@ static int kan_pack_all(const KanLayout& k, const float* params, const KanWs& w,
                                                  n_oi, k.nb, w.wc[l]);
   }
   INR_LAUNCH_CHECK();
+  for (int l = 0; l < k.L; ++l)
+    if (k.kind[l] == KL_TC) {
+      LaunchScope ls("k_kan_tc_pack", st);
+      k_kan_tc_pack<<<blocks_for((int64_t)k.w[l + 1] * k.w[l] * KT_NF), 256, 0, st>>>(w.wc[l], k.w[l], k.w[l + 1], w.wf[l], w.wb[l]);
+    }
+  INR_LAUNCH_CHECK();
+  return INR_OK;
+}
+
+static int kan_tc_attrs() {
+  static bool done = false;
+  if (!done) {
+    INR_CUDA_CHECK(cudaFuncSetAttribute(k_kan_tc_fwd, cudaFuncAttributeMaxDynamicSharedMemorySize, KanFwdCfg::SMEM_BYTES));
+    INR_CUDA_CHECK(cudaFuncSetAttribute(k_kan_tc_bwd, cudaFuncAttributeMaxDynamicSharedMemorySize, KanBwdCfg::SMEM_BYTES));
+    done = true;
+  }
   return INR_OK;
 }
 
@@ -279,6 +327,21 @@ static int kan_pack_all(const KanLayout& k, const float* params, const KanWs& w,
 static int kan_layer_fwd(const KanLayout& k, int l, const float* x, const float* grids, int nk, int64_t rows, int64_t g0,
                          int64_t T_total, float scale, const KanWs& w, float* y, cudaStream_t st) {
   const int in = k.w[l], out = k.w[l + 1], Kf = in * (k.nb + 1);
+  if (k.kind[l] == KL_TC) {
+    int rc = kan_tc_attrs();
+    if (rc) return rc;
+    const int blocks = (int)std::min<int64_t>(cdiv(rows, 2 * TILE_ROWS), num_sms());
+    { LaunchScope ls("k_kan_tc_fwd", st);
+      k_kan_tc_fwd<<<blocks, KanFwdCfg::THREADS, KanFwdCfg::SMEM_BYTES, st>>>(x, grids + k.grid_off(l, nk), nk, w.wf[l], rows, in, y); }
+    INR_LAUNCH_CHECK();
+    return INR_OK;
+  }
+  if (k.kind[l] == KL_THIN) {
+    { LaunchScope ls("k_kan_thin_fwd", st);
+      k_kan_thin_fwd<<<blocks_for(rows * 32), 256, in * KT_NF * sizeof(float), st>>>(x, grids + k.grid_off(l, nk), nk, w.wc[l], rows, in, y); }
+    INR_LAUNCH_CHECK();
+    return INR_OK;
+  }
   { LaunchScope ls("k_kan_expand", st);
     k_kan_expand<<<blocks_for(rows * in), 256, 0, st>>>(x, grids + k.grid_off(l, nk), rows, in, nk, k.nb, g0, T_total, scale, w.phi); }
   INR_LAUNCH_CHECK();
@@ -291,7 +354,7 @@ static int kan_layer_fwd(const KanLayout& k, int l, const float* x, const float*
 
 int kan_forward(const inr_kan_desc* d, const float* params, const float* grids, const float* coords, int64_t n, int64_t i0,
                 int64_t T_total, float scale, float* out, void* ws, int64_t ws_bytes, cudaStream_t st) {
-  const KanLayout k = kan_layout(d);
+  const KanLayout k = kan_layout_k(d);
   const int nk = d->grid_size + 2 * d->spline_order + 1;
   KanWs w;
   int rc = kan_carve(k, 0, n, ws, ws_bytes, &w);
@@ -314,7 +377,7 @@ int kan_loss_backward(const inr_kan_desc* d, const float* params, const float* g
                       int64_t n, int64_t i0, int64_t T_total, float scale, int loss_kind, float grad_scale,
                       const float* extra_gout, float* grads, inr_opt_state* opt, float* out, void* ws, int64_t ws_bytes,
                       cudaStream_t st) {
-  const KanLayout k = kan_layout(d);
+  const KanLayout k = kan_layout_k(d);
   const int nk = d->grid_size + 2 * d->spline_order + 1;
   const int nf = k.nb + 1;
   KanWs w;
@@ -342,6 +405,28 @@ int kan_loss_backward(const inr_kan_desc* d, const float* params, const float* g
       const int in = k.w[l], outw = k.w[l + 1], Kf = in * nf;
       const float* x = input_of(l);
       const float* g = w.g[cur];
+      if (k.kind[l] != KL_GENERIC) {
+        if (k.kind[l] == KL_TC) {
+          if ((rc = kan_tc_attrs())) return rc;
+          const int nslab = in / KT_SLAB;
+          const int Q = (int)std::max<int64_t>(1, std::min<int64_t>(num_sms() / nslab, cdiv(rows, TILE_ROWS)));
+          LaunchScope ls("k_kan_tc_bwd", st);
+          k_kan_tc_bwd<<<nslab * Q, KanBwdCfg::THREADS, KanBwdCfg::SMEM_BYTES, st>>>(x, grids + k.grid_off(l, nk), nk, w.wb[l], g, rows, in,
+                                                                                    l > 0 ? w.g[cur ^ 1] : nullptr, w.gwc);
+        } else {
+          LaunchScope ls("k_kan_thin_bwd", st);
+          k_kan_thin_bwd<<<std::min(blocks_for(rows * 32), num_sms() * 4), 256, 2 * in * KT_NF * sizeof(float), st>>>(
+              x, grids + k.grid_off(l, nk), nk, w.wc[l], g, rows, in, w.g[cur ^ 1], w.gwc);
+        }
+        INR_LAUNCH_CHECK();
+        const int64_t n_oi = (int64_t)outw * in;
+        { LaunchScope ls("k_kan_unpack_grad", st);
+          k_kan_unpack_grad<<<blocks_for(n_oi), 256, 0, st>>>(w.gwc, params + k.spline_off(l), params + k.scaler_off(l), n_oi, k.nb,
+                                                              grads + k.base_off(l), grads + k.spline_off(l), grads + k.scaler_off(l)); }
+        INR_LAUNCH_CHECK();
+        cur ^= 1;
+        continue;
+      }
       { LaunchScope ls("k_kan_expand", st);
         k_kan_expand<<<blocks_for(rows * in), 256, 0, st>>>(x, grids + k.grid_off(l, nk), rows, in, nk, k.nb, i0 + r0, T_total, scale, w.phi); }
       INR_LAUNCH_CHECK();
@@ -388,7 +473,7 @@ extern "C" {
 
 int64_t inr_kan_num_params(const inr_kan_desc* d) {
   if (check_kan_desc(d) != INR_OK) return INR_E_BADARG;
-  return kan_layout(d).total();
+  return kan_layout_k(d).total();
 }
 
 int64_t inr_kan_num_grid_floats(const inr_kan_desc* d) {
@@ -398,7 +483,7 @@ int64_t inr_kan_num_grid_floats(const inr_kan_desc* d) {
 
 int64_t inr_kan_workspace_bytes(const inr_kan_desc* d, int64_t n_rows, int training) {
   if (check_kan_desc(d) != INR_OK || n_rows < 0) return INR_E_BADARG;
-  const KanLayout k = kan_layout(d);
+  const KanLayout k = kan_layout_k(d);
   const int64_t per_row = (kan_row_floats(k, training) + 8) * 4;
   const int64_t cap = (int64_t)48 << 30;
   int64_t rows = std::max<int64_t>(n_rows, 1);

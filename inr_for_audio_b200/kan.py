@@ -245,6 +245,21 @@ class KAN(nn.Module):
             o += n
 
 
+def _require_uniform_grids(spec: KanSpec, grids: torch.Tensor):
+    """The bf16 tensor-core mode evaluates the cubic B-spline in closed form on a uniform knot vector shared by all
+    inputs of a layer (what KANLinear.__init__ builds, kan.py:26-35); grids refined by update_grid need precision='fp32'."""
+    g = grids.detach().reshape(-1).float().cpu()
+    nk = spec.grid_size + 2 * spec.spline_order + 1
+    o = 0
+    for fin in spec.layers_hidden[:-1]:
+        blk = g[o:o + fin * nk].view(fin, nk)
+        o += fin * nk
+        step = (blk[0, -1] - blk[0, 0]) / (nk - 1)
+        ideal = blk[0, 0] + step * torch.arange(nk)
+        if not (torch.allclose(blk, ideal.expand(fin, nk), rtol=0, atol=1e-5 * float(abs(step)) + 1e-7)):
+            raise L.InrLibraryError("KAN precision='bf16' needs uniform, input-independent knot vectors; use precision='fp32'")
+
+
 class KanFitter(SirenFitter):
     """Device-resident fit of a KAN to one waveform: run.py:156-190 with arch='kan' (run.py:110).  Same engine as
     SirenFitter (flat arena, device Adam + plateau scheduler, CUDA graph, sharded allreduce); only the forward /
@@ -254,6 +269,8 @@ class KanFitter(SirenFitter):
                  coords: Optional[torch.Tensor] = None, **kw):
         self.grids = grids.reshape(-1).contiguous().float().to(target.device)
         kw.setdefault("precision", "fp32")
+        if kw["precision"] == "bf16":
+            _require_uniform_grids(spec, grids)
         if kw.get("spectral") is not None or kw.get("loss_mode", "mse") == "snr":
             raise NotImplementedError("KAN fits use the waveform mse/mae losses (run.py:110 is waveform-only)")
         super().__init__(spec, params0, target, coords, **kw)

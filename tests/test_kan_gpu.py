@@ -122,3 +122,58 @@ def test_kan_bad_arguments(pkg):
     with pytest.raises(L.InrLibraryError):
         pkg.KanSpec((1, 8, 1), spline_order=2).desc() and L.check(
             L.lib().inr_kan_num_params(pkg.KanSpec((1, 8, 1), spline_order=2).desc()))
+
+
+@pytest.mark.parametrize("widths,T", [([1, 256, 256, 1], 5000), ([1, 256, 256, 1], 257), ([1, 256, 256, 256, 1], 1000),
+                                      ([1, 32, 256, 1], 300), ([1, 256, 1], 64)])
+def test_bf16_tensor_core_mode_against_oracle(pkg, widths, T):
+    """INR_PREC_BF16: the fused basis + contraction kernels (kan_tc.cuh).  bf16 operands, fp32 accumulation: loss within
+    2e-3 relative, gradient within 3e-2 of its norm (the SIREN bf16 mode's bars), ragged row counts included."""
+    from oracle import inr_oracle as O
+    layers = O.kan_init(widths, seed=5)
+    gt = pkg.utils.synth_waveform(max(T, 2), seed=2)[:T]
+    coords = O.get_coord(T, 1)
+    ps = []
+    for l in layers:
+        for key in ("base_weight", "spline_weight", "spline_scaler"):
+            l[key] = l[key].clone().requires_grad_(True)
+            ps.append(l[key])
+    out_o = O.kan_forward(coords.view(1, -1, 1), layers)
+    lo = torch.mean((out_o.view(-1) - torch.from_numpy(gt)) ** 2)
+    go = torch.cat([x.reshape(-1) for x in torch.autograd.grad(lo, ps)]).numpy().astype(np.float64)
+    spec = pkg.KanSpec(tuple(widths))
+    flat = torch.cat([p.detach().reshape(-1) for p in ps])
+    grids = torch.cat([l["grid"].reshape(-1) for l in layers])
+    f = pkg.KanFitter(spec, flat, grids, torch.from_numpy(gt).to(dev()), precision="bf16", use_graph=False)
+    loss, grads, out = f.loss_and_grads()
+    np.testing.assert_allclose(out.cpu().numpy(), out_o.detach().numpy().ravel(), atol=5e-3)
+    np.testing.assert_allclose(f.forward().cpu().numpy(), out.cpu().numpy(), atol=1e-6)       # inference path == training path
+    assert abs(loss - float(lo)) <= 2e-3 * float(lo), (loss, float(lo))
+    gerr = np.linalg.norm(grads.cpu().numpy() - go) / np.linalg.norm(go)
+    assert gerr <= 3e-2, gerr
+    # per-tensor check so a wrong (small) block cannot hide behind the norm of the big one
+    o = 0
+    for t in ps:
+        n = t.numel()
+        a, b = grads[o:o + n].cpu().numpy(), go[o:o + n]
+        assert np.linalg.norm(a - b) <= 5e-2 * np.linalg.norm(b) + 1e-9, (o, np.linalg.norm(a - b) / np.linalg.norm(b))
+        o += n
+    # the graphed loop tracks the fp32 mode's trajectory over the first steps (before chaos separates them)
+    f2 = pkg.KanFitter(spec, flat, grids, torch.from_numpy(gt).to(dev()), precision="bf16")
+    f3 = pkg.KanFitter(spec, flat, grids, torch.from_numpy(gt).to(dev()), precision="fp32")
+    f2.step(30)
+    f3.step(30)
+    ls = f2.losses()
+    assert np.all(np.isfinite(ls))
+    np.testing.assert_allclose(ls[:4], f3.losses()[:4], rtol=1e-2)
+    assert abs(ls[-1] - f3.losses()[-1]) <= 0.1 * f3.losses()[-1]
+
+
+def test_bf16_needs_uniform_grid(pkg):
+    from inr_for_audio_b200 import _lib as L
+    torch.manual_seed(0)
+    k = pkg.KAN([1, 256, 256, 1])
+    grids = k.flat_grids()
+    grids[5] += 0.05
+    with pytest.raises(L.InrLibraryError):
+        pkg.KanFitter(k.spec, k.flat_parameters(), grids, torch.zeros(100, device=dev()), precision="bf16")
