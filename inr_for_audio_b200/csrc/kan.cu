@@ -191,12 +191,13 @@ __global__ void __launch_bounds__(256) k_out_loss(const float* __restrict__ out,
 namespace inr {
 
 // which kernel family runs layer l in the bf16 mode
-enum { KL_GENERIC = 0, KL_TC = 1, KL_THIN = 2 };
+enum { KL_GENERIC = 0, KL_TC = 1, KL_THIN = 2, KL_IN1 = 3 };
 static int kan_layer_kind(const inr_kan_desc* d, int l) {
   if (d->precision != INR_PREC_BF16) return KL_GENERIC;
   const int in = d->widths[l], out = d->widths[l + 1];
   if (in % KT_SLAB == 0 && out == KanFwdCfg::OUT) return KL_TC;
   if (out == 1 && in <= 32 * KT_THIN_PER) return KL_THIN;
+  if (in == 1 && out % 4 == 0 && out <= 1024) return KL_IN1;
   return KL_GENERIC;
 }
 static KanLayout kan_layout_k(const inr_kan_desc* d) {
@@ -229,6 +230,7 @@ struct KanWs {
   float* act[INR_KAN_MAX_LAYERS + 1];  // act[l] = input of layer l (act[0] unused: coords), act[L] = network output
   float* phi;                      // rows x max_l (nf * in_l)
   float* g[2];                     // rows x max width, ping-pong upstream gradients
+  __nv_bfloat16* gimg;             // bf16 mode: tile image of the upstream gradient of a tensor-core layer
   int64_t chunk_rows;
 };
 
@@ -247,7 +249,10 @@ static int64_t kan_row_floats(const KanLayout& k, int training) {
   for (int l = 0; l < k.L; ++l)
     if (k.kind[l] == KL_GENERIC) kmax = std::max<int64_t>(kmax, (int64_t)k.w[l] * (k.nb + 1));   // Phi scratch: fp32 layers only
   for (int l = 1; l <= k.L; ++l) acts += k.w[l];
-  return training ? acts + kmax + 2 * wmax : 2 * wmax + kmax;
+  int64_t gimg = 0;
+  for (int l = 0; l < k.L; ++l)
+    if (k.kind[l] == KL_TC) gimg = KanBwdCfg::OUT / 2;          // bf16 image of g: OUT/2 floats per row
+  return training ? acts + kmax + 2 * wmax + gimg : 2 * wmax + kmax;
 }
 
 static int kan_carve(const KanLayout& k, int training, int64_t n, void* ws, int64_t ws_bytes, KanWs* w) {
@@ -255,7 +260,7 @@ static int kan_carve(const KanLayout& k, int training, int64_t n, void* ws, int6
   const int64_t usable = (ws_bytes - (reinterpret_cast<uint8_t*>(base) - reinterpret_cast<uint8_t*>(ws))) / 4;
   const int64_t fixed = kan_fixed_floats(k);
   const int64_t per_row = kan_row_floats(k, training) + 8;
-  int64_t rows = (usable - fixed - 1024) / per_row;
+  int64_t rows = (usable - fixed - 1024 - TILE_ROWS * KanBwdCfg::OUT) / per_row;
   INR_REQUIRE(rows >= 1, INR_E_WORKSPACE, "KAN workspace of %lld bytes is too small", (long long)ws_bytes);
   rows = std::min(rows, n);
   w->chunk_rows = rows;
@@ -290,6 +295,10 @@ static int kan_carve(const KanLayout& k, int training, int64_t n, void* ws, int6
   w->phi = take(rows * kmax);
   w->g[0] = take(rows * wmax);
   w->g[1] = take(rows * wmax);
+  w->gimg = nullptr;
+  if (training)
+    for (int l = 0; l < k.L; ++l)
+      if (k.kind[l] == KL_TC && !w->gimg) w->gimg = reinterpret_cast<__nv_bfloat16*>(take(round_up(rows, TILE_ROWS) * (KanBwdCfg::OUT / 2)));
   INR_REQUIRE((p - base) <= usable, INR_E_WORKSPACE, "KAN workspace carve overflow");
   return INR_OK;
 }
@@ -333,6 +342,13 @@ static int kan_layer_fwd(const KanLayout& k, int l, const float* x, const float*
     const int blocks = (int)std::min<int64_t>(cdiv(rows, 2 * TILE_ROWS), num_sms());
     { LaunchScope ls("k_kan_tc_fwd", st);
       k_kan_tc_fwd<<<blocks, KanFwdCfg::THREADS, KanFwdCfg::SMEM_BYTES, st>>>(x, grids + k.grid_off(l, nk), nk, w.wf[l], rows, in, y); }
+    INR_LAUNCH_CHECK();
+    return INR_OK;
+  }
+  if (k.kind[l] == KL_IN1) {
+    { LaunchScope ls("k_kan_in1_fwd", st);
+      k_kan_in1_fwd<<<blocks_for(rows * (out / 4)), 256, out * KT_NF * sizeof(float), st>>>(x, grids + k.grid_off(l, nk), nk, w.wc[l], rows,
+                                                                                           out, g0, T_total, scale, y); }
     INR_LAUNCH_CHECK();
     return INR_OK;
   }
@@ -410,9 +426,17 @@ int kan_loss_backward(const inr_kan_desc* d, const float* params, const float* g
           if ((rc = kan_tc_attrs())) return rc;
           const int nslab = in / KT_SLAB;
           const int Q = (int)std::max<int64_t>(1, std::min<int64_t>(num_sms() / nslab, cdiv(rows, TILE_ROWS)));
+          { LaunchScope ls("k_rows_to_image", st);
+            k_rows_to_image<<<(unsigned)cdiv(rows, TILE_ROWS), 256, 0, st>>>(g, rows, outw, w.gimg); }
+          INR_LAUNCH_CHECK();
           LaunchScope ls("k_kan_tc_bwd", st);
-          k_kan_tc_bwd<<<nslab * Q, KanBwdCfg::THREADS, KanBwdCfg::SMEM_BYTES, st>>>(x, grids + k.grid_off(l, nk), nk, w.wb[l], g, rows, in,
-                                                                                    l > 0 ? w.g[cur ^ 1] : nullptr, w.gwc);
+          k_kan_tc_bwd<<<nslab * Q, KanBwdCfg::THREADS, KanBwdCfg::SMEM_BYTES, st>>>(x, grids + k.grid_off(l, nk), nk, w.wb[l], w.gimg, rows,
+                                                                                    in, l > 0 ? w.g[cur ^ 1] : nullptr, w.gwc);
+        } else if (k.kind[l] == KL_IN1) {
+          const int64_t rpb = std::max<int64_t>(64, cdiv(rows, (int64_t)num_sms() * 8));
+          LaunchScope ls("k_kan_in1_dw", st);
+          k_kan_in1_dw<<<(unsigned)cdiv(rows, rpb), 256, 0, st>>>(x, grids + k.grid_off(l, nk), nk, g, rows, outw, rpb, i0 + r0, T_total,
+                                                                 scale, w.gwc);
         } else {
           LaunchScope ls("k_kan_thin_bwd", st);
           k_kan_thin_bwd<<<std::min(blocks_for(rows * 32), num_sms() * 4), 256, 2 * in * KT_NF * sizeof(float), st>>>(
@@ -488,7 +512,7 @@ int64_t inr_kan_workspace_bytes(const inr_kan_desc* d, int64_t n_rows, int train
   const int64_t cap = (int64_t)48 << 30;
   int64_t rows = std::max<int64_t>(n_rows, 1);
   if (rows * per_row > cap) rows = std::max<int64_t>(cap / per_row, 1024);
-  return (kan_fixed_floats(k) + 2048) * 4 + rows * per_row + 4096;
+  return (kan_fixed_floats(k) + 2048 + TILE_ROWS * KanBwdCfg::OUT) * 4 + rows * per_row + 4096;
 }
 
 int inr_kan_b_splines(const float* x, const float* grid, int64_t rows, int in_features, int grid_size, int spline_order,

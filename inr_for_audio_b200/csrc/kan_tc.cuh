@@ -122,7 +122,10 @@ __global__ void __launch_bounds__(256) k_kan_thin_fwd(const float* __restrict__ 
   }
 }
 
-// backward of the thin layer: dx[r,i] = g[r] * sum_j phi_j'(x) wc[i*9+j];  gwc[i*9+j] += sum_r g[r] phi_j(x[r,i])
+// backward of the thin layer: dx[r,i] = g[r] * sum_j phi_j'(x) wc[i*9+j];  gwc[i*9+j] += sum_r g[r] phi_j(x[r,i]).
+// Only the 5 non-zero features of an input (SiLU + the 4 bases of its knot interval) are touched: their weights are
+// read from, and their gradient sums accumulated into, shared memory by index (lanes own different inputs, so the
+// stride-9 addresses of a warp fall into different banks); one global atomic per weight and block at the end.
 __global__ void __launch_bounds__(256) k_kan_thin_bwd(const float* __restrict__ x, const float* __restrict__ grid, int nk,
                                                       const float* __restrict__ wc, const float* __restrict__ g, int64_t rows,
                                                       int in, float* __restrict__ dx, float* __restrict__ gwc) {
@@ -134,46 +137,119 @@ __global__ void __launch_bounds__(256) k_kan_thin_bwd(const float* __restrict__ 
   const UGrid ug = load_ugrid(grid, nk);
   const int lane = threadIdx.x & 31;
   const int64_t warp0 = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5, nwarps = ((int64_t)gridDim.x * blockDim.x) >> 5;
-  float gacc[KT_THIN_PER][KT_NF];
-#pragma unroll
-  for (int p = 0; p < KT_THIN_PER; ++p)
-#pragma unroll
-    for (int j = 0; j < KT_NF; ++j) gacc[p][j] = 0.f;
   for (int64_t r = warp0; r < rows; r += nwarps) {
     const float gv = g[r];
+    for (int i = lane; i < in; i += 32) {
+      const float xv = x[r * in + i];
+      float w[4], dw[4];
+      const int m = basis4<true>(xv, ug, w, dw);
+      const float* wp = s_wc + i * KT_NF;
+      float* gp = s_gw + i * KT_NF;
+      const float sg = 1.f / (1.f + __expf(-xv));
+      float d = sg * (1.f + xv * (1.f - sg)) * wp[0];
+      atomicAdd(gp, gv * xv * sg);
 #pragma unroll
-    for (int p = 0; p < KT_THIN_PER; ++p) {
-      const int i = lane + 32 * p;
-      if (i < in) {
-        const float xv = x[r * in + i];
-        float w[4], dw[4];
-        const int m = basis4<true>(xv, ug, w, dw);
-        const float* wp = s_wc + i * KT_NF;
-        const float sg = 1.f / (1.f + __expf(-xv));
-        float d = sg * (1.f + xv * (1.f - sg)) * wp[0];
-        gacc[p][0] = __fmaf_rn(gv, xv * sg, gacc[p][0]);
-#pragma unroll
-        for (int b = 0; b < KT_NF - 1; ++b) {
-          const int q = b - (m - 3);
-          float wv = 0.f, dv = 0.f;
-#pragma unroll
-          for (int t = 0; t < 4; ++t) { wv = (q == t) ? w[t] : wv; dv = (q == t) ? dw[t] : dv; }
-          d = __fmaf_rn(dv, wp[1 + b], d);
-          gacc[p][1 + b] = __fmaf_rn(gv, wv, gacc[p][1 + b]);
+      for (int t = 0; t < 4; ++t) {
+        const int b = m - 3 + t;
+        if (b >= 0 && b < KT_NF - 1) {
+          d = __fmaf_rn(dw[t], wp[1 + b], d);
+          atomicAdd(gp + 1 + b, gv * w[t]);
         }
-        dx[r * in + i] = gv * d;
+      }
+      dx[r * in + i] = gv * d;
+    }
+  }
+  __syncthreads();
+  for (int i = threadIdx.x; i < in * KT_NF; i += blockDim.x) atomicAdd(&gwc[i], s_gw[i]);
+}
+
+// ------------------------------------------------------------------------------------------------ thin input layer
+// all 9 expanded features of one input value (closed form on the uniform grid)
+__device__ __forceinline__ void feats9(float xv, const UGrid& ug, float* f) {
+  float w[4];
+  const int m = basis4<false>(xv, ug, w, nullptr);
+  f[0] = xv / (1.f + __expf(-xv));
+#pragma unroll
+  for (int b = 0; b < KT_NF - 1; ++b) {
+    const int q = b - (m - 3);
+    float v = 0.f;
+#pragma unroll
+    for (int t = 0; t < 4; ++t) v = (q == t) ? w[t] : v;
+    f[1 + b] = v;
+  }
+}
+
+// in_features == 1 (the coordinate layer): y[r,o] = sum_j phi_j(x_r) wc[o*9+j];  gwc[o*9+j] += sum_r g[r,o] phi_j(x_r).
+// x == NULL: the coordinate of global row g0 + r is generated (utils.py:99-109).
+__global__ void __launch_bounds__(256) k_kan_in1_fwd(const float* __restrict__ x, const float* __restrict__ grid, int nk,
+                                                     const float* __restrict__ wc, int64_t rows, int out, int64_t g0,
+                                                     int64_t T_total, float scale, float* __restrict__ y) {
+  extern __shared__ float s_wc1[];
+  for (int i = threadIdx.x; i < out * KT_NF; i += blockDim.x) s_wc1[i] = wc[i];
+  __syncthreads();
+  const UGrid ug = load_ugrid(grid, nk);
+  const int og = out >> 2;                                       // out % 4 == 0
+  const int64_t total = rows * og;
+  for (int64_t idx = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; idx < total; idx += (int64_t)gridDim.x * blockDim.x) {
+    const int64_t r = idx / og;
+    const int o0 = (int)(idx - r * og) * 4;
+    const float xv = x ? x[r] : linspace_at(g0 + r, T_total, scale);
+    float f[KT_NF];
+    feats9(xv, ug, f);
+    float acc[4] = {0.f, 0.f, 0.f, 0.f};
+#pragma unroll
+    for (int u = 0; u < 4; ++u)
+#pragma unroll
+      for (int j = 0; j < KT_NF; ++j) acc[u] = __fmaf_rn(f[j], s_wc1[(o0 + u) * KT_NF + j], acc[u]);
+    *reinterpret_cast<float4*>(y + r * out + o0) = make_float4(acc[0], acc[1], acc[2], acc[3]);
+  }
+}
+
+__global__ void __launch_bounds__(256) k_kan_in1_dw(const float* __restrict__ x, const float* __restrict__ grid, int nk,
+                                                    const float* __restrict__ g, int64_t rows, int out, int64_t rows_per_block,
+                                                    int64_t g0, int64_t T_total, float scale, float* __restrict__ gwc) {
+  // the features of a row are shared by every output: the block evaluates them once for 256 rows into shared memory,
+  // then thread o sweeps those rows with coalesced reads of g[r, o] and broadcast reads of the features
+  __shared__ float s_f[256][KT_NF + 1];
+  const UGrid ug = load_ugrid(grid, nk);
+  const int64_t r0 = (int64_t)blockIdx.x * rows_per_block;
+  const int64_t r1 = min(rows, r0 + rows_per_block);
+  float acc[4][KT_NF];                                           // out <= 1024: up to 4 outputs per thread
+#pragma unroll
+  for (int u = 0; u < 4; ++u)
+#pragma unroll
+    for (int j = 0; j < KT_NF; ++j) acc[u][j] = 0.f;
+  for (int64_t rb = r0; rb < r1; rb += 256) {
+    const int nr = (r1 - rb) < 256 ? (int)(r1 - rb) : 256;
+    __syncthreads();
+    if ((int)threadIdx.x < nr) {
+      const int64_t r = rb + threadIdx.x;
+      const float xv = x ? __ldg(x + r) : linspace_at(g0 + r, T_total, scale);
+      float f[KT_NF];
+      feats9(xv, ug, f);
+#pragma unroll
+      for (int j = 0; j < KT_NF; ++j) s_f[threadIdx.x][j] = f[j];
+    }
+    __syncthreads();
+#pragma unroll
+    for (int u = 0; u < 4; ++u) {
+      const int o = threadIdx.x + u * 256;
+      if (o < out) {
+        for (int rr = 0; rr < nr; ++rr) {
+          const float gv = g[(rb + rr) * out + o];
+#pragma unroll
+          for (int j = 0; j < KT_NF; ++j) acc[u][j] = __fmaf_rn(gv, s_f[rr][j], acc[u][j]);
+        }
       }
     }
   }
 #pragma unroll
-  for (int p = 0; p < KT_THIN_PER; ++p) {
-    const int i = lane + 32 * p;
-    if (i < in)
+  for (int u = 0; u < 4; ++u) {
+    const int o = threadIdx.x + u * 256;
+    if (o < out)
 #pragma unroll
-      for (int j = 0; j < KT_NF; ++j) atomicAdd(&s_gw[i * KT_NF + j], gacc[p][j]);
+      for (int j = 0; j < KT_NF; ++j) atomicAdd(&gwc[o * KT_NF + j], acc[u][j]);
   }
-  __syncthreads();
-  for (int i = threadIdx.x; i < in * KT_NF; i += blockDim.x) atomicAdd(&gwc[i], s_gw[i]);
 }
 
 // ------------------------------------------------------------------------------------------------ forward GEMM
@@ -187,8 +263,8 @@ struct KanFwdCfg {
   static constexpr int STAGES = 4;
   static constexpr int OFF_BAR = STAGES * STAGE_BYTES;
   static constexpr int SMEM_BYTES = OFF_BAR + 128;
-  static constexpr int PROD_WARPS = 8;
-  static constexpr int THREADS = 32 * (2 + PROD_WARPS + 4);     // B producer, MMA, 8 Phi producers, 4 epilogue
+  static constexpr int PROD_WARPS = 16;
+  static constexpr int THREADS = 32 * (2 + PROD_WARPS + 4);     // B producer, MMA, 16 Phi producers, 4 epilogue
 };
 
 // x (rows x in) fp32 row-major, WF packed by k_kan_tc_pack, y (rows x 256) fp32 row-major.  in % 16 == 0.
@@ -269,49 +345,56 @@ __global__ void __launch_bounds__(KanFwdCfg::THREADS, 1) k_kan_tc_fwd(const floa
       }
     }
   } else if (warp < 2 + Cfg::PROD_WARPS) {
-    // ===================== Phi producers: thread = one row of the double tile, all 16 inputs of the slab ==========
+    // ===================== Phi producers: thread = (row of the double tile, 8 inputs of the slab) ==================
+    // All 9 expanded features of the thread's 8 inputs are evaluated ONCE per slab and kept packed in registers
+    // (9 x 16 bytes); the slab's three ring stages (feature triples jg) then only wait for their slot and store.
     const UGrid ug = load_ugrid(grid, nk);
-    const int p = threadIdx.x - 64;                             // 0..255
-    const int t = p >> 7, r = p & 127;
+    const int p = threadIdx.x - 64;                             // 0..511
+    const int hf = p >> 8, rr = p & 255;
+    const int t = rr >> 7, r = rr & 127;
     int s = 0;
     uint32_t phase = 0;
     for (int64_t dt = blockIdx.x; dt < num_dt; dt += gridDim.x) {
-      int64_t grow = dt * (2 * TILE_ROWS) + p;
+      int64_t grow = dt * (2 * TILE_ROWS) + rr;
       if (grow >= rows) grow = rows - 1;                        // pad rows replicate the last row; never stored
-      const float* xrow = x + grow * in;
+      const float* xrow = x + grow * in + hf * 8;
+      float4 f0 = *reinterpret_cast<const float4*>(xrow), f1 = *reinterpret_cast<const float4*>(xrow + 4);
       for (int slab = 0; slab < nslab; ++slab) {
-        float xv[KT_SLAB];
-#pragma unroll
-        for (int v4 = 0; v4 < KT_SLAB / 4; ++v4) {
-          const float4 f = *reinterpret_cast<const float4*>(xrow + slab * KT_SLAB + v4 * 4);
-          xv[v4 * 4] = f.x; xv[v4 * 4 + 1] = f.y; xv[v4 * 4 + 2] = f.z; xv[v4 * 4 + 3] = f.w;
+        const float xv[8] = {f0.x, f0.y, f0.z, f0.w, f1.x, f1.y, f1.z, f1.w};
+        if (slab + 1 < nslab) {                                 // next slab's inputs: in flight under this slab's math
+          f0 = *reinterpret_cast<const float4*>(xrow + (slab + 1) * KT_SLAB);
+          f1 = *reinterpret_cast<const float4*>(xrow + (slab + 1) * KT_SLAB + 4);
         }
-#pragma unroll 1
-        for (int jg = 0; jg < 3; ++jg) {
-          uint32_t o[3][2][4];
+        uint32_t o[KT_NF][4];
 #pragma unroll
-          for (int ii = 0; ii < KT_SLAB; ii += 2) {
-            float f[2][3];
+        for (int e = 0; e < 8; e += 2) {
+          float f[2][KT_NF];
 #pragma unroll
-            for (int u = 0; u < 2; ++u) {
-              const float xx = xv[ii + u];
-              float w[4];
-              const int m = basis4<false>(xx, ug, w, nullptr);
-              const float silu = xx / (1.f + __expf(-xx));
+          for (int u = 0; u < 2; ++u) {
+            const float xx = xv[e + u];
+            float w[4];
+            const int m = basis4<false>(xx, ug, w, nullptr);
+            f[u][0] = xx / (1.f + __expf(-xx));
 #pragma unroll
-              for (int jj = 0; jj < 3; ++jj) f[u][jj] = feat_of(3 * jg + jj, silu, m, w);
+            for (int b = 0; b < KT_NF - 1; ++b) {
+              const int q = b - (m - 3);
+              float v = 0.f;
+#pragma unroll
+              for (int tt = 0; tt < 4; ++tt) v = (q == tt) ? w[tt] : v;
+              f[u][1 + b] = v;
             }
-#pragma unroll
-            for (int jj = 0; jj < 3; ++jj) o[jj][ii >> 3][(ii & 7) >> 1] = pack_bf16x2(f[0][jj], f[1][jj]);
           }
+#pragma unroll
+          for (int j = 0; j < KT_NF; ++j) o[j][e >> 1] = pack_bf16x2(f[0][j], f[1][j]);
+        }
+#pragma unroll
+        for (int jg = 0; jg < 3; ++jg) {
           mbar_wait(bar_empty(s), phase ^ 1);
           uint8_t* abase = smem + s * Cfg::STAGE_BYTES + t * Cfg::A_TILE_BYTES;
 #pragma unroll
           for (int jj = 0; jj < 3; ++jj)
-#pragma unroll
-            for (int hf = 0; hf < 2; ++hf)
-              *reinterpret_cast<uint4*>(abase + ((jj * 2 + hf) * TILE_ROWS + r) * 16) =
-                  make_uint4(o[jj][hf][0], o[jj][hf][1], o[jj][hf][2], o[jj][hf][3]);
+            *reinterpret_cast<uint4*>(abase + ((jj * 2 + hf) * TILE_ROWS + r) * 16) =
+                make_uint4(o[3 * jg + jj][0], o[3 * jg + jj][1], o[3 * jg + jj][2], o[3 * jg + jj][3]);
           fence_proxy_async_smem();
           __syncwarp();
           if (lane == 0) mbar_arrive(bar_full(s));
@@ -375,34 +458,68 @@ __device__ __forceinline__ void tmem_ld8(uint32_t taddr, float (&v)[8]) {
                : "memory");
 }
 
+// fp32 row-major (rows x H) -> bf16 tile image (tc_common.cuh), pad rows zero.  One block per 128-row tile; the tile
+// goes through shared memory in 64-feature chunks so that both the global reads (along features) and the image
+// writes (along rows) are coalesced.
+__global__ void __launch_bounds__(256) k_rows_to_image(const float* __restrict__ src, int64_t rows, int H,
+                                                       __nv_bfloat16* __restrict__ img) {
+  __shared__ float s[TILE_ROWS][65];
+  const int64_t tile = blockIdx.x;
+  const int tid = threadIdx.x;
+  for (int c0 = 0; c0 < H; c0 += 64) {
+    for (int e = tid; e < TILE_ROWS * 16; e += 256) {           // 16 float4 per row chunk
+      const int r = e >> 4, v4 = e & 15;
+      const int64_t grow = tile * TILE_ROWS + r;
+      float4 f = make_float4(0.f, 0.f, 0.f, 0.f);
+      if (grow < rows) f = *reinterpret_cast<const float4*>(src + grow * H + c0 + v4 * 4);
+      s[r][v4 * 4] = f.x; s[r][v4 * 4 + 1] = f.y; s[r][v4 * 4 + 2] = f.z; s[r][v4 * 4 + 3] = f.w;
+    }
+    __syncthreads();
+    for (int e = tid; e < TILE_ROWS * 8; e += 256) {            // 8 feature groups per chunk
+      const int r = e & 127, fg = e >> 7;
+      const float* q = &s[r][fg * 8];
+      const uint4 o = make_uint4(pack_bf16x2(q[0], q[1]), pack_bf16x2(q[2], q[3]), pack_bf16x2(q[4], q[5]), pack_bf16x2(q[6], q[7]));
+      *reinterpret_cast<uint4*>(img + tile * (TILE_ROWS * (int64_t)H) + ((int64_t)((c0 >> 3) + fg) * TILE_ROWS + r) * 8) = o;
+    }
+    __syncthreads();
+  }
+}
+
 struct KanBwdCfg {
   static constexpr int OUT = 256;
   static constexpr int WB_BYTES = (OUT / 8) * KT_SLABF * 16;            // 72 KB: Wc[:, slab]^T, K-major (K = out)
-  static constexpr int G_BYTES = (OUT / 8) * TILE_ROWS * 16;            // 64 KB: g tile image
+  static constexpr int G_BYTES = (OUT / 8) * TILE_ROWS * 16;            // 64 KB: g tile image, two halves of 128 features
+  static constexpr int G_HALF = G_BYTES / 2;
   static constexpr int PHI_BYTES = (KT_SLABF / 8) * TILE_ROWS * 16;     // 36 KB: Phi slab tile image
   static constexpr int OFF_G = WB_BYTES;
   static constexpr int OFF_PHI = OFF_G + G_BYTES;
   static constexpr int OFF_BAR = OFF_PHI + PHI_BYTES;
   static constexpr int SMEM_BYTES = OFF_BAR + 128;
   static constexpr int PROD_WARPS = 8;
-  static constexpr int THREADS = 32 * (2 + PROD_WARPS + 4);
+  static constexpr int EPI_WARPS = 8;
+  static constexpr int THREADS = 32 * (2 + PROD_WARPS + EPI_WARPS);
   static constexpr int COL_DW = 0, COL_DPHI = 2 * KT_SLABF;             // TMEM columns: dW mb0 | dW mb1 | dPhi
 };
 
-// x (rows x in), g (rows x 256) fp32 row-major; dx (rows x in) fp32 (may be NULL: first layer); gwc fp32 [256][in*9]
-// (the i-major layout of kan.cu), accumulated with atomics.  grid = nslab * Q CTAs.
+// x (rows x in) fp32 row-major; gimg = the upstream gradient g (rows x 256) as a bf16 tile image (k_rows_to_image);
+// dx (rows x in) fp32 (may be NULL: first layer); gwc fp32 [256][in*9] (the i-major layout of kan.cu), accumulated with
+// atomics.  grid = nslab * Q CTAs.  The g image sits in two half buffers (features 0..127 | 128..255): the MMAs are
+// ordered [dPhi k 0..7, dW mb0 | dPhi k 8..15, dW mb1] so half 0 is refilled by the bulk-copy engine for the next tile
+// while the tensor pipe still works on half 1.
 __global__ void __launch_bounds__(KanBwdCfg::THREADS, 1) k_kan_tc_bwd(const float* __restrict__ x, const float* __restrict__ grid,
                                                                        int nk, const __nv_bfloat16* __restrict__ WB,
-                                                                       const float* __restrict__ g, int64_t rows, int in,
+                                                                       const __nv_bfloat16* __restrict__ gimg, int64_t rows, int in,
                                                                        float* __restrict__ dx, float* __restrict__ gwc) {
   using Cfg = KanBwdCfg;
   extern __shared__ __align__(128) uint8_t smem[];
   const uint32_t smem_base = smem_u32(smem);
   const uint32_t sWB = smem_base, sG = smem_base + Cfg::OFF_G, sPhi = smem_base + Cfg::OFF_PHI;
   const uint32_t bar0 = smem_base + Cfg::OFF_BAR;
-  const uint32_t bar_bfull = bar0, bar_img_full = bar0 + 8, bar_img_empty = bar0 + 16, bar_dphi_full = bar0 + 24,
+  const uint32_t bar_bfull = bar0, bar_phi_full = bar0 + 8, bar_phi_empty = bar0 + 16, bar_dphi_full = bar0 + 24,
                  bar_dphi_empty = bar0 + 32, bar_done = bar0 + 40;
-  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(smem + Cfg::OFF_BAR + 48);
+  auto bar_g_full = [&](int h) { return bar0 + 48u + 8u * h; };
+  auto bar_g_empty = [&](int h) { return bar0 + 64u + 8u * h; };
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(smem + Cfg::OFF_BAR + 80);
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int nslab = in / KT_SLAB;
   const int slab = blockIdx.x % nslab;
@@ -412,11 +529,12 @@ __global__ void __launch_bounds__(KanBwdCfg::THREADS, 1) k_kan_tc_bwd(const floa
 
   if (threadIdx.x == 0) {
     mbar_init(bar_bfull, 1);
-    mbar_init(bar_img_full, Cfg::PROD_WARPS);
-    mbar_init(bar_img_empty, 1);
+    mbar_init(bar_phi_full, Cfg::PROD_WARPS);
+    mbar_init(bar_phi_empty, 1);
     mbar_init(bar_dphi_full, 1);
-    mbar_init(bar_dphi_empty, 4);
+    mbar_init(bar_dphi_empty, Cfg::EPI_WARPS);
     mbar_init(bar_done, 1);
+    for (int h = 0; h < 2; ++h) { mbar_init(bar_g_full(h), 1); mbar_init(bar_g_empty(h), 1); }
     mbar_fence_init();
   }
   if (warp == 1) {
@@ -429,10 +547,20 @@ __global__ void __launch_bounds__(KanBwdCfg::THREADS, 1) k_kan_tc_bwd(const floa
   const uint32_t tmem_base = *tmem_slot;
 
   if (warp == 0) {
+    // ===================== bulk-copy producer: the slab's weights once, then the g image halves per tile ===========
     if (lane == 0 && has_work) {
       mbar_arrive_expect_tx(bar_bfull, Cfg::WB_BYTES);
       const uint8_t* src = reinterpret_cast<const uint8_t*>(WB) + (size_t)slab * Cfg::WB_BYTES;
       for (int off = 0; off < Cfg::WB_BYTES; off += 24576) bulk_g2s(sWB + off, src + off, 24576, bar_bfull);
+      int it = 0;
+      for (int64_t tile = q0; tile < num_tiles; tile += Q, ++it) {
+        const uint8_t* gsrc = reinterpret_cast<const uint8_t*>(gimg) + (size_t)tile * Cfg::G_BYTES;
+        for (int h = 0; h < 2; ++h) {
+          mbar_wait(bar_g_empty(h), (it & 1) ^ 1);
+          mbar_arrive_expect_tx(bar_g_full(h), Cfg::G_HALF);
+          bulk_g2s(sG + h * Cfg::G_HALF, gsrc + h * Cfg::G_HALF, Cfg::G_HALF, bar_g_full(h));
+        }
+      }
     }
   } else if (warp == 1) {
     if (lane == 0 && has_work) {
@@ -441,134 +569,119 @@ __global__ void __launch_bounds__(KanBwdCfg::THREADS, 1) k_kan_tc_bwd(const floa
       mbar_wait(bar_bfull, 0);
       int it = 0;
       for (int64_t tile = q0; tile < num_tiles; tile += Q, ++it) {
-        mbar_wait(bar_img_full, it & 1);
+        mbar_wait(bar_phi_full, it & 1);
         mbar_wait(bar_dphi_empty, (it & 1) ^ 1);
-        tc_fence_after();
-        // dPhi (128 rows x 144) = g (K-major, K = out) x Wc[:, slab]
 #pragma unroll
-        for (int kk = 0; kk < Cfg::OUT / 16; ++kk) {
-          const uint64_t ad = make_smem_desc(sG + kk * 2 * (TILE_ROWS * 16), TILE_ROWS * 16, 128);
-          const uint64_t bd = make_smem_desc(sWB + kk * 2 * (KT_SLABF * 16), KT_SLABF * 16, 128);
-          umma_bf16(tmem_base + Cfg::COL_DPHI, ad, bd, idesc_dphi, kk != 0 ? 1u : 0u);
-        }
-        umma_commit(bar_dphi_full);
-        // dWc[mb*128 .. +128, slab] += g^T Phi  (both MN-major, K = 16 rows per step)
+        for (int h = 0; h < 2; ++h) {
+          mbar_wait(bar_g_full(h), it & 1);
+          tc_fence_after();
+          // dPhi (128 rows x 144) += g[:, 128h .. 128h+128) (K-major) x Wc[128h .. , slab]
 #pragma unroll
-        for (int mb = 0; mb < Cfg::OUT / 128; ++mb)
+          for (int k8 = 0; k8 < 8; ++k8) {
+            const int kk = h * 8 + k8;
+            const uint64_t ad = make_smem_desc(sG + kk * 2 * (TILE_ROWS * 16), TILE_ROWS * 16, 128);
+            const uint64_t bd = make_smem_desc(sWB + kk * 2 * (KT_SLABF * 16), KT_SLABF * 16, 128);
+            umma_bf16(tmem_base + Cfg::COL_DPHI, ad, bd, idesc_dphi, kk != 0 ? 1u : 0u);
+          }
+          if (h == 1) umma_commit(bar_dphi_full);
+          // dWc[128h .. +128, slab] += g[:, 128h ..]^T Phi  (both MN-major, K = 16 rows per step)
 #pragma unroll
           for (int kk = 0; kk < TILE_ROWS / 16; ++kk) {
-            const uint64_t ad = make_smem_desc(sG + mb * 16 * (TILE_ROWS * 16) + kk * 256, 128, TILE_ROWS * 16);
+            const uint64_t ad = make_smem_desc(sG + h * Cfg::G_HALF + kk * 256, 128, TILE_ROWS * 16);
             const uint64_t bd = make_smem_desc(sPhi + kk * 256, 128, TILE_ROWS * 16);
-            umma_bf16(tmem_base + Cfg::COL_DW + mb * KT_SLABF, ad, bd, idesc_dw, (it | kk) != 0 ? 1u : 0u);
+            umma_bf16(tmem_base + Cfg::COL_DW + h * KT_SLABF, ad, bd, idesc_dw, (it | kk) != 0 ? 1u : 0u);
           }
-        umma_commit(bar_img_empty);
+          umma_commit(bar_g_empty(h));
+        }
+        umma_commit(bar_phi_empty);
       }
       umma_commit(bar_done);
     }
   } else if (warp < 2 + Cfg::PROD_WARPS) {
-    // ===================== producers: g tile -> bf16 image, Phi slab tile -> bf16 image =====================
+    // ===================== Phi producers: thread = (row, 8 inputs of the slab) =====================
     const UGrid ug = load_ugrid(grid, nk);
-    const int p = threadIdx.x - 64;
+    const int p = threadIdx.x - 64;                             // 0..255
     const int r = p & 127, hf = p >> 7;
     int it = 0;
     for (int64_t tile = q0; tile < num_tiles; tile += Q, ++it) {
       const int64_t grow = tile * TILE_ROWS + r;
-      const bool valid = grow < rows;
-      const int64_t crow = valid ? grow : rows - 1;
-      // Phi features of this thread's 8 inputs
+      const int64_t crow = grow < rows ? grow : rows - 1;       // pad rows: finite Phi against a zero g row
+      const float4 f0 = *reinterpret_cast<const float4*>(x + crow * in + slab * KT_SLAB + hf * 8);
+      const float4 f1 = *reinterpret_cast<const float4*>(x + crow * in + slab * KT_SLAB + hf * 8 + 4);
+      const float xv[8] = {f0.x, f0.y, f0.z, f0.w, f1.x, f1.y, f1.z, f1.w};
       uint32_t ph[KT_NF][4];
-      {
-        const float4 f0 = *reinterpret_cast<const float4*>(x + crow * in + slab * KT_SLAB + hf * 8);
-        const float4 f1 = *reinterpret_cast<const float4*>(x + crow * in + slab * KT_SLAB + hf * 8 + 4);
-        const float xv[8] = {f0.x, f0.y, f0.z, f0.w, f1.x, f1.y, f1.z, f1.w};
 #pragma unroll
-        for (int e = 0; e < 8; e += 2) {
-          float f[2][KT_NF];
+      for (int e = 0; e < 8; e += 2) {
+        float fa[KT_NF], fb[KT_NF];
+        feats9(xv[e], ug, fa);
+        feats9(xv[e + 1], ug, fb);
 #pragma unroll
-          for (int u = 0; u < 2; ++u) {
-            float w[4];
-            const int m = basis4<false>(xv[e + u], ug, w, nullptr);
-            const float silu = xv[e + u] / (1.f + __expf(-xv[e + u]));
-#pragma unroll
-            for (int j = 0; j < KT_NF; ++j) f[u][j] = feat_of(j, silu, m, w);
-          }
-#pragma unroll
-          for (int j = 0; j < KT_NF; ++j) ph[j][e >> 1] = pack_bf16x2(f[0][j], f[1][j]);
-        }
+        for (int j = 0; j < KT_NF; ++j) ph[j][e >> 1] = pack_bf16x2(fa[j], fb[j]);
       }
-      mbar_wait(bar_img_empty, (it & 1) ^ 1);
+      mbar_wait(bar_phi_empty, (it & 1) ^ 1);
 #pragma unroll
       for (int j = 0; j < KT_NF; ++j)
         *reinterpret_cast<uint4*>(smem + Cfg::OFF_PHI + ((j * 2 + hf) * TILE_ROWS + r) * 16) = make_uint4(ph[j][0], ph[j][1], ph[j][2], ph[j][3]);
-      // g: this thread converts feature groups hf*16 .. hf*16+15 of its row (zeros for pad rows: they must not reach dW)
-      const float* grow_p = g + crow * Cfg::OUT + hf * 128;
-#pragma unroll 4
-      for (int fg = 0; fg < 16; ++fg) {
-        uint4 o = make_uint4(0u, 0u, 0u, 0u);
-        if (valid) {
-          const float4 a = *reinterpret_cast<const float4*>(grow_p + fg * 8);
-          const float4 b = *reinterpret_cast<const float4*>(grow_p + fg * 8 + 4);
-          o = make_uint4(pack_bf16x2(a.x, a.y), pack_bf16x2(a.z, a.w), pack_bf16x2(b.x, b.y), pack_bf16x2(b.z, b.w));
-        }
-        *reinterpret_cast<uint4*>(smem + Cfg::OFF_G + ((hf * 16 + fg) * TILE_ROWS + r) * 16) = o;
-      }
       fence_proxy_async_smem();
       __syncwarp();
-      if (lane == 0) mbar_arrive(bar_img_full);
+      if (lane == 0) mbar_arrive(bar_phi_full);
     }
   } else {
     // ===================== epilogue: dPhi x phi' -> dx ; at the end dW accumulators -> gwc =====================
+    // 8 warps: two per TMEM lane quadrant, one for each half (8 inputs) of the slab / each out-feature block of dW.
     const UGrid ug = load_ugrid(grid, nk);
     const int quad = warp & 3;
+    const int hf = (warp - (2 + Cfg::PROD_WARPS)) >> 2;
     const int row = quad * 32 + lane;
     const uint32_t lane_addr = (uint32_t)(quad * 32) << 16;
     int it = 0;
     for (int64_t tile = q0; tile < num_tiles; tile += Q, ++it) {
       const int64_t grow = tile * TILE_ROWS + row;
       const int64_t crow = grow < rows ? grow : rows - 1;
+      const float4 f0 = *reinterpret_cast<const float4*>(x + crow * in + slab * KT_SLAB + hf * 8);
+      const float4 f1 = *reinterpret_cast<const float4*>(x + crow * in + slab * KT_SLAB + hf * 8 + 4);
+      const float xv[8] = {f0.x, f0.y, f0.z, f0.w, f1.x, f1.y, f1.z, f1.w};
+      float dwq[8][4], acc[8];
+      int mm[8];
+      if (dx) {
+#pragma unroll
+        for (int e = 0; e < 8; ++e) {
+          float w[4];
+          mm[e] = basis4<true>(xv[e], ug, w, dwq[e]);
+          const float sg = 1.f / (1.f + __expf(-xv[e]));
+          acc[e] = sg * (1.f + xv[e] * (1.f - sg));             // SiLU'(x); multiplied by dPhi_0 below
+        }
+      }
       mbar_wait(bar_dphi_full, it & 1);
       tc_fence_after();
       if (dx) {
-#pragma unroll 1
-        for (int hf = 0; hf < 2; ++hf) {
-          const float4 f0 = *reinterpret_cast<const float4*>(x + crow * in + slab * KT_SLAB + hf * 8);
-          const float4 f1 = *reinterpret_cast<const float4*>(x + crow * in + slab * KT_SLAB + hf * 8 + 4);
-          const float xv[8] = {f0.x, f0.y, f0.z, f0.w, f1.x, f1.y, f1.z, f1.w};
-          float dwq[8][4], dsl[8], acc[8];
-          int mm[8];
 #pragma unroll
-          for (int e = 0; e < 8; ++e) {
-            float w[4];
-            mm[e] = basis4<true>(xv[e], ug, w, dwq[e]);
-            const float sg = 1.f / (1.f + __expf(-xv[e]));
-            dsl[e] = sg * (1.f + xv[e] * (1.f - sg));
-          }
-          {
-            float v[8];
-            tmem_ld8(tmem_base + Cfg::COL_DPHI + hf * 8 + lane_addr, v);
-            tmem_ld_wait();
+        for (int grp = 0; grp < 3; ++grp) {                     // features j = 3 grp .. 3 grp + 2: three loads, one wait
+          float v[3][8];
 #pragma unroll
-            for (int e = 0; e < 8; ++e) acc[e] = v[e] * dsl[e];
-          }
+          for (int jj = 0; jj < 3; ++jj) tmem_ld8(tmem_base + Cfg::COL_DPHI + (3 * grp + jj) * KT_SLAB + hf * 8 + lane_addr, v[jj]);
+          tmem_ld_wait();
 #pragma unroll
-          for (int b = 0; b < KT_NF - 1; ++b) {
-            float v[8];
-            tmem_ld8(tmem_base + Cfg::COL_DPHI + (b + 1) * KT_SLAB + hf * 8 + lane_addr, v);
-            tmem_ld_wait();
+          for (int jj = 0; jj < 3; ++jj) {
+            const int j = 3 * grp + jj;
 #pragma unroll
             for (int e = 0; e < 8; ++e) {
-              const int qq = b - (mm[e] - 3);
-              float dv = 0.f;
+              if (j == 0) {
+                acc[e] *= v[jj][e];
+              } else {
+                const int qq = (j - 1) - (mm[e] - 3);
+                float dv = 0.f;
 #pragma unroll
-              for (int t = 0; t < 4; ++t) dv = (qq == t) ? dwq[e][t] : dv;
-              acc[e] = __fmaf_rn(v[e], dv, acc[e]);
+                for (int t = 0; t < 4; ++t) dv = (qq == t) ? dwq[e][t] : dv;
+                acc[e] = __fmaf_rn(v[jj][e], dv, acc[e]);
+              }
             }
           }
-          if (grow < rows) {
-            float4* dst = reinterpret_cast<float4*>(dx + grow * in + slab * KT_SLAB + hf * 8);
-            dst[0] = make_float4(acc[0], acc[1], acc[2], acc[3]);
-            dst[1] = make_float4(acc[4], acc[5], acc[6], acc[7]);
-          }
+        }
+        if (grow < rows) {
+          float4* dst = reinterpret_cast<float4*>(dx + grow * in + slab * KT_SLAB + hf * 8);
+          dst[0] = make_float4(acc[0], acc[1], acc[2], acc[3]);
+          dst[1] = make_float4(acc[4], acc[5], acc[6], acc[7]);
         }
       }
       tc_fence_before();
@@ -579,17 +692,15 @@ __global__ void __launch_bounds__(KanBwdCfg::THREADS, 1) k_kan_tc_bwd(const floa
       mbar_wait(bar_done, 0);
       tc_fence_after();
       const int Kf = in * KT_NF;
+      const int mb = hf;
+      float* gro = gwc + (size_t)(mb * 128 + row) * Kf + (size_t)slab * KT_SLAB * KT_NF;
 #pragma unroll 1
-      for (int mb = 0; mb < Cfg::OUT / 128; ++mb) {
-        float* gro = gwc + (size_t)(mb * 128 + row) * Kf + (size_t)slab * KT_SLAB * KT_NF;
-#pragma unroll 1
-        for (int j = 0; j < KT_NF; ++j) {
-          float v[16];
-          tmem_ld16(tmem_base + Cfg::COL_DW + mb * KT_SLABF + j * KT_SLAB + lane_addr, v);
-          tmem_ld_wait();
+      for (int j = 0; j < KT_NF; ++j) {
+        float v[16];
+        tmem_ld16(tmem_base + Cfg::COL_DW + mb * KT_SLABF + j * KT_SLAB + lane_addr, v);
+        tmem_ld_wait();
 #pragma unroll
-          for (int ii = 0; ii < KT_SLAB; ++ii) atomicAdd(gro + ii * KT_NF + j, v[ii]);
-        }
+        for (int ii = 0; ii < KT_SLAB; ++ii) atomicAdd(gro + ii * KT_NF + j, v[ii]);
       }
     }
   }
