@@ -29,11 +29,13 @@ struct Layer2Cfg {
   static constexpr int NP = (H >= 256) ? 256 : H;   // output features per pair (MMA N)
   static constexpr int NC = NP / 2;                 // B columns staged by each CTA
   static constexpr int NQ = H / NP;                 // N slices
-  static constexpr int KC = 64;                     // K columns per ring stage
+  // One thread sustains ~1 cp.async.bulk per 0.32 us whatever its size (profiles/r01_bulk_probe_*.csv): 16 KB copies
+  // cap a CTA at ~51 GB/s, below the ~60 GB/s the MMA consumes; 32 KB copies (128 K columns) lift the cap to ~100 GB/s.
+  static constexpr int KC = 128;                    // K columns per ring stage
   static constexpr int NCHUNK = H / KC;
   static constexpr int B_BYTES = H * NC * 2;        // 128 KB (H=512), 64 KB (256), 16 KB (128)
-  static constexpr int A_STAGE_BYTES = (KC / 8) * TILE_ROWS * 16;  // 16 KB
-  static constexpr int STAGES = (H >= 512) ? 4 : 8;
+  static constexpr int A_STAGE_BYTES = (KC / 8) * TILE_ROWS * 16;  // 32 KB
+  static constexpr int STAGES = (H >= 512) ? 3 : 4; // 96 KB / 128 KB in flight
   static constexpr int TMEM_COLS = 2 * NP;          // two accumulator buffers
   static constexpr int OFF_A = B_BYTES;
   static constexpr int OFF_BIAS = OFF_A + STAGES * A_STAGE_BYTES;
