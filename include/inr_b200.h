@@ -37,17 +37,28 @@ extern "C" {
 #define INR_LOSS_MSE 0
 #define INR_LOSS_MAE 1
 
-/* Shape of a sine-only SIREN: models.py:244-269 Siren(in,H,L,out,outermost_linear,first_omega_0,
- * hidden_omega_0) == models.py:310-394 SirenWithSnakeTanh(num_sine=L, num_snake=0, num_tanh=0). */
+/* Shape of the MLP: models.py:244-269 Siren(in,H,L,out,outermost_linear,first_omega_0,hidden_omega_0)
+ * == models.py:310-394 SirenWithSnakeTanh(num_sine=L, num_snake=0, num_tanh=0), and the general
+ * SirenWithSnakeTanh stack (models.py:337-385), in this order:
+ *   layer 0            SineLayer(in->H, is_first)           or, first_linear: nn.Linear(in->H) + Snake(H)
+ *   hidden_layers  x   SineLayer(H->H)                      y = sin(omega z)
+ *   num_snake      x   nn.Linear(H->H) + Snake(H)           y = z + sin^2(a z)/a, `a` (H) TRAINABLE (models.py:185-241)
+ *   num_tanh       x   nn.Linear(H->H) + nn.Tanh()
+ *   last               nn.Linear(H->1) (outermost_linear)   or SineLayer(H->1)
+ * flat params = state_dict order: W, b per layer, with a Snake layer's `a` (H floats) right after its bias.
+ * The bf16 tcgen05 mode takes the sine-only stack; Snake/Tanh stacks run in INR_PREC_FP32. */
 typedef struct {
   int32_t in_features;     /* 1 (waveform) or 2 (MDCT image)                      */
   int32_t hidden_features; /* H                                                   */
-  int32_t hidden_layers;   /* L = number of HxH SineLayers                        */
+  int32_t hidden_layers;   /* number of HxH SineLayers (num_sine)                 */
   int32_t out_features;    /* must be 1                                           */
   int32_t outermost_linear;/* 1: final nn.Linear; 0: final SineLayer              */
   float first_omega_0;
   float hidden_omega_0;
   int32_t precision;       /* INR_PREC_*                                          */
+  int32_t num_snake;       /* number of HxH Linear+Snake layers after the sine layers */
+  int32_t num_tanh;        /* number of HxH Linear+Tanh layers after the snake layers  */
+  int32_t first_linear;    /* 1: layer 0 is nn.Linear + Snake instead of a SineLayer   */
 } inr_siren_desc;
 
 /* Optimiser + scheduler state, resident in DEVICE memory (no per-step host sync; the reference syncs

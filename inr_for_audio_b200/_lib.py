@@ -19,7 +19,8 @@ PRECISIONS = {"fp32": PREC_FP32, "bf16": PREC_BF16}
 class SirenDesc(C.Structure):
     _fields_ = [("in_features", C.c_int32), ("hidden_features", C.c_int32), ("hidden_layers", C.c_int32),
                 ("out_features", C.c_int32), ("outermost_linear", C.c_int32), ("first_omega_0", C.c_float),
-                ("hidden_omega_0", C.c_float), ("precision", C.c_int32)]
+                ("hidden_omega_0", C.c_float), ("precision", C.c_int32), ("num_snake", C.c_int32),
+                ("num_tanh", C.c_int32), ("first_linear", C.c_int32)]
 
 
 KAN_MAX_LAYERS = 8

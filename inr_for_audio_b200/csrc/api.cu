@@ -68,12 +68,17 @@ static int check_desc(const inr_siren_desc* d) {
               INR_E_UNSUPPORTED, "hidden_features must be a multiple of 8 in [8,1024], got %d", d->hidden_features);
   INR_REQUIRE(d->hidden_layers >= 0 && d->hidden_layers <= 16, INR_E_UNSUPPORTED,
               "hidden_layers must be in [0,16], got %d", d->hidden_layers);
+  INR_REQUIRE(d->num_snake >= 0 && d->num_tanh >= 0 && d->hidden_layers + d->num_snake + d->num_tanh <= 16,
+              INR_E_UNSUPPORTED, "num_snake/num_tanh must be >= 0 and sine+snake+tanh layers <= 16 (got %d+%d+%d)",
+              d->hidden_layers, d->num_snake, d->num_tanh);
+  INR_REQUIRE(d->first_linear == 0 || d->first_linear == 1, INR_E_BADARG, "first_linear must be 0 or 1");
   INR_REQUIRE(d->precision == INR_PREC_FP32 || d->precision == INR_PREC_BF16, INR_E_BADARG, "unknown precision %d",
               d->precision);
   if (d->precision == INR_PREC_BF16)
     INR_REQUIRE(siren_tc_supported(d), INR_E_UNSUPPORTED,
-                "bf16 tcgen05 path needs hidden_features in {128,256,512} and hidden_layers >= 1 (got H=%d L=%d)",
-                d->hidden_features, d->hidden_layers);
+                "bf16 tcgen05 path needs hidden_features in {128,256,512}, hidden_layers >= 1 and a sine-only stack "
+                "(got H=%d sine=%d snake=%d tanh=%d first_linear=%d); use INR_PREC_FP32",
+                d->hidden_features, d->hidden_layers, d->num_snake, d->num_tanh, d->first_linear);
   return INR_OK;
 }
 

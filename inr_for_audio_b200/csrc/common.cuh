@@ -74,13 +74,30 @@ __device__ __forceinline__ double warp_sum(double v) {
   return v;
 }
 
-// Layout of the flat parameter vector (state_dict order).
+// Layout of the flat parameter vector (state_dict order) and the activation kind of every layer.
+enum { ACT_SINE = 0, ACT_SNAKE = 1, ACT_TANH = 2 };
+
 struct SirenLayout {
-  int in, H, L, out;
+  int in, H, L, out;          // L = total number of HxH layers = ns + nk + nt
+  int ns, nk, nt, first_snake;
+  __host__ __device__ int kind(int layer) const {        // layer 0..L
+    if (layer == 0) return first_snake ? ACT_SNAKE : ACT_SINE;
+    if (layer <= ns) return ACT_SINE;
+    return (layer <= ns + nk) ? ACT_SNAKE : ACT_TANH;
+  }
+  // number of Snake layers with index < layer (each owns an extra H-vector `a` after its bias)
+  __host__ __device__ int snakes_before(int layer) const {
+    if (layer <= 0) return 0;
+    int k = layer - 1 - ns;
+    k = k < 0 ? 0 : (k > nk ? nk : k);
+    return k + (first_snake ? 1 : 0);
+  }
+  __host__ __device__ int num_snake_layers() const { return nk + (first_snake ? 1 : 0); }
   __host__ __device__ int64_t w_off(int layer) const {  // layer 0..L+1
     if (layer == 0) return 0;
     int64_t o = (int64_t)H * in + H;
     o += (int64_t)(layer - 1) * ((int64_t)H * H + H);
+    o += (int64_t)H * snakes_before(layer);
     return o;
   }
   __host__ __device__ int64_t b_off(int layer) const {
@@ -88,12 +105,15 @@ struct SirenLayout {
     if (layer <= L) return w_off(layer) + (int64_t)H * H;
     return w_off(layer) + (int64_t)out * H;
   }
+  __host__ __device__ int64_t a_off(int layer) const { return b_off(layer) + H; }   // Snake layers only
   __host__ __device__ int64_t total() const { return b_off(L + 1) + out; }
 };
 
 static inline SirenLayout layout_of(const inr_siren_desc* d) {
   SirenLayout s;
-  s.in = d->in_features; s.H = d->hidden_features; s.L = d->hidden_layers; s.out = d->out_features;
+  s.in = d->in_features; s.H = d->hidden_features; s.out = d->out_features;
+  s.ns = d->hidden_layers; s.nk = d->num_snake; s.nt = d->num_tanh; s.first_snake = d->first_linear ? 1 : 0;
+  s.L = s.ns + s.nk + s.nt;
   return s;
 }
 
@@ -125,14 +145,16 @@ int siren_tc_loss_backward(const inr_siren_desc* d, const float* params, const f
 
 // ---- shared elementwise / reduction kernels (siren_common.cu)
 // first layer: S0 = sin(w0*(W x + b)), C0 = cos(..), written as fp32 or bf16
+// (first_linear: S0 = snake(W x + b), C0 = d snake/dz, E0 = d snake/da)
 template <typename OutT>
 int launch_first_layer(const inr_siren_desc* d, const float* params, const float* coords, int64_t rows, int64_t g0,
-                       int64_t T_total, float scale, OutT* S0, OutT* C0, cudaStream_t st);
+                       int64_t T_total, float scale, OutT* S0, OutT* C0, OutT* E0, cudaStream_t st);
 // last layer + loss + dZ_L (in place in C_L) + last-layer grads
+// (EL: d y_L / d a image when layer L is a Snake layer, else NULL; its `a` gradient is accumulated here)
 template <typename ActT>
-int launch_last_layer(const inr_siren_desc* d, const float* params, const ActT* SL, ActT* CL_dZ, const float* target,
-                      const float* extra_gout, int64_t rows, int loss_kind, float grad_scale, float* grads,
-                      inr_opt_state* opt, float* out, int training, cudaStream_t st);
+int launch_last_layer(const inr_siren_desc* d, const float* params, const ActT* SL, ActT* CL_dZ, const ActT* EL,
+                      const float* target, const float* extra_gout, int64_t rows, int loss_kind, float grad_scale,
+                      float* grads, inr_opt_state* opt, float* out, int training, cudaStream_t st);
 // column reductions: gW[h*in + i] += sum_r dZ[r,h]*x[r,i] (x NULL -> generated), gb[h] += sum_r dZ[r,h]
 template <typename ActT>
 int launch_first_layer_grad(const inr_siren_desc* d, const ActT* dZ0, const float* coords, int64_t rows, int64_t g0,

@@ -6,7 +6,11 @@
 
 namespace inr {
 
-enum { EPI_SINCOS = 0, EPI_COSMUL = 1, EPI_ATOMIC = 2, EPI_STORE = 3 };
+// EPI_SNAKE / EPI_TANH: forward epilogues of the Linear+Snake / Linear+Tanh layers (models.py:185-241,356-372):
+//   out0 = y, out1 = dy/dz, (Snake) aux1 = dy/da image, aux0 = the layer's `a` vector.
+// EPI_DMUL_GA: backward epilogue towards a Snake layer: v = dY; out0 (holding dy/dz) <- v * dy/dz;
+//   aux1[n] += sum_m v * aux0[m][n]  (aux0 = the dy/da image, aux1 = the gradient of `a`).
+enum { EPI_SINCOS = 0, EPI_COSMUL = 1, EPI_ATOMIC = 2, EPI_STORE = 3, EPI_SNAKE = 4, EPI_TANH = 5, EPI_DMUL_GA = 6 };
 
 constexpr int BM = 128, BN = 128, BK = 16;
 
@@ -14,7 +18,7 @@ template <bool A_KC, bool B_KC, int EPI>
 __global__ void __launch_bounds__(256)
 k_sgemm(const float* __restrict__ A, int64_t sAm, int64_t sAk, const float* __restrict__ B, int64_t sBn, int64_t sBk,
         int64_t M, int N, int64_t K, int64_t k_chunk, const float* __restrict__ bias, float omega,
-        float* out0, float* out1, int64_t ldo) {
+        float* out0, float* out1, int64_t ldo, const float* __restrict__ aux0 = nullptr, float* aux1 = nullptr) {
   __shared__ __align__(16) float As[BK][BM + 4];
   __shared__ __align__(16) float Bs[BK][BN + 4];
   const int tid = threadIdx.x;
@@ -80,6 +84,11 @@ k_sgemm(const float* __restrict__ A, int64_t sAm, int64_t sAk, const float* __re
     __syncthreads();
   }
 
+  float ga_part[8];
+  if (EPI == EPI_DMUL_GA) {
+#pragma unroll
+    for (int j = 0; j < 8; ++j) ga_part[j] = 0.f;
+  }
 #pragma unroll
   for (int i = 0; i < 8; ++i) {
     const int64_t gm = m0 + (i < 4 ? ty * 4 + i : 64 + ty * 4 + (i - 4));
@@ -113,6 +122,41 @@ k_sgemm(const float* __restrict__ A, int64_t sAm, int64_t sAk, const float* __re
         } else {
           for (int q = 0; q < 4 && gn + q < N; ++q) p0[q] = v[q] * omega * p0[q];
         }
+      } else if (EPI == EPI_SNAKE || EPI == EPI_TANH) {
+        float y[4], dz[4], da[4];
+#pragma unroll
+        for (int q = 0; q < 4; ++q) {
+          const bool in = gn + q < N;
+          const float z = v[q] + (in ? bias[gn + q] : 0.f);
+          if (EPI == EPI_SNAKE) {
+            const float a = in ? aux0[gn + q] : 1.f;
+            float sn, cs;
+            sincosf(z * a, &sn, &cs);
+            const float ia = 1.0f / a, s2 = sn * sn, sc2 = 2.f * sn * cs;
+            y[q] = z + ia * s2;
+            dz[q] = 1.f + sc2;
+            da[q] = ia * (z * sc2 - ia * s2);
+          } else {
+            y[q] = tanhf(z);
+            dz[q] = 1.f - y[q] * y[q];
+            da[q] = 0.f;
+          }
+        }
+        float* p1 = out1 ? out1 + gm * ldo + gn : nullptr;
+        float* p2 = (EPI == EPI_SNAKE && aux1) ? aux1 + gm * ldo + gn : nullptr;
+        if (full) {
+          *reinterpret_cast<float4*>(p0) = make_float4(y[0], y[1], y[2], y[3]);
+          if (p1) *reinterpret_cast<float4*>(p1) = make_float4(dz[0], dz[1], dz[2], dz[3]);
+          if (p2) *reinterpret_cast<float4*>(p2) = make_float4(da[0], da[1], da[2], da[3]);
+        } else {
+          for (int q = 0; q < 4 && gn + q < N; ++q) { p0[q] = y[q]; if (p1) p1[q] = dz[q]; if (p2) p2[q] = da[q]; }
+        }
+      } else if (EPI == EPI_DMUL_GA) {
+        const float* pe = aux0 + gm * ldo + gn;
+        for (int q = 0; q < 4 && gn + q < N; ++q) {
+          ga_part[jh * 4 + q] = __fmaf_rn(v[q], pe[q], ga_part[jh * 4 + q]);
+          p0[q] = v[q] * p0[q];
+        }
       } else if (EPI == EPI_STORE) {
         if (full) *reinterpret_cast<float4*>(p0) = make_float4(v[0], v[1], v[2], v[3]);
         else for (int q = 0; q < 4 && gn + q < N; ++q) p0[q] = v[q];
@@ -120,6 +164,16 @@ k_sgemm(const float* __restrict__ A, int64_t sAm, int64_t sAk, const float* __re
         for (int q = 0; q < 4 && gn + q < N; ++q) atomicAdd(p0 + q, v[q]);
       }
     }
+  }
+  if (EPI == EPI_DMUL_GA) {
+    // the main loop ended with __syncthreads(): As is free -> block-level column sums, one global atomic per column
+    float* s_ga = &As[0][0];
+    if (tid < BN) s_ga[tid] = 0.f;
+    __syncthreads();
+#pragma unroll
+    for (int j = 0; j < 8; ++j) atomicAdd(&s_ga[(j < 4 ? tx * 4 + j : 64 + tx * 4 + (j - 4))], ga_part[j]);
+    __syncthreads();
+    if (tid < BN && n0 + tid < N) atomicAdd(&aux1[n0 + tid], s_ga[tid]);
   }
 }
 

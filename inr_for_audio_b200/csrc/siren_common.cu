@@ -34,11 +34,26 @@ __device__ __forceinline__ void from_f(__nv_bfloat16* p, float v) { *p = __float
 // ------------------------------------------------------------------------------------------------
 // first layer
 // ------------------------------------------------------------------------------------------------
+// Snake (models.py:235-241): y = z + (1/a) sin^2(z a);  dy/dz = 1 + 2 sin(za) cos(za);
+// dy/da = (2 z sin(za) cos(za) - sin^2(za)/a) / a.   Evaluated in the reference's operation order.
+__device__ __forceinline__ void snake_eval(float z, float a, float* y, float* dz, float* da) {
+  float sn, cs;
+  sincosf(z * a, &sn, &cs);
+  const float ia = 1.0f / a;
+  const float s2 = sn * sn;
+  const float sc2 = 2.f * sn * cs;
+  *y = z + ia * s2;
+  *dz = 1.f + sc2;
+  *da = ia * (z * sc2 - ia * s2);
+}
+
 template <typename OutT>
 __global__ void __launch_bounds__(256) k_first_layer(const float* __restrict__ W, const float* __restrict__ B,
+                                                     const float* __restrict__ Aparam,
                                                      const float* __restrict__ coords, int in, int H, int64_t rows,
                                                      int64_t g0, int64_t T_total, float scale, float omega,
-                                                     OutT* __restrict__ S0, OutT* __restrict__ C0) {
+                                                     OutT* __restrict__ S0, OutT* __restrict__ C0,
+                                                     OutT* __restrict__ E0) {
   constexpr int V = Vec<OutT>::N;
   const int groups = H / V;
   const int64_t total = rows * groups;
@@ -52,7 +67,7 @@ __global__ void __launch_bounds__(256) k_first_layer(const float* __restrict__ W
     } else {
       x0 = linspace_at(g0 + r, T_total, scale);
     }
-    float s[V], c[V];
+    float s[V], c[V], e[V];
 #pragma unroll
     for (int j = 0; j < V; ++j) {
       const int h = h0 + j;
@@ -62,57 +77,65 @@ __global__ void __launch_bounds__(256) k_first_layer(const float* __restrict__ W
       } else {
         z = __fmaf_rn(x1, W[h * 2 + 1], x0 * W[h * 2]) + B[h];
       }
-      sincosf(omega * z, &s[j], &c[j]);
+      if (Aparam) {                     // first_linear: nn.Linear + Snake (models.py:343-347)
+        snake_eval(z, Aparam[h], &s[j], &c[j], &e[j]);
+      } else {
+        sincosf(omega * z, &s[j], &c[j]);
+      }
     }
     Vec<OutT>::store(S0 + r * H + h0, s);
     if (C0) Vec<OutT>::store(C0 + r * H + h0, c);
+    if (Aparam && E0) Vec<OutT>::store(E0 + r * H + h0, e);
   }
 }
 
 template <typename OutT>
 int launch_first_layer(const inr_siren_desc* d, const float* params, const float* coords, int64_t rows, int64_t g0,
-                       int64_t T_total, float scale, OutT* S0, OutT* C0, cudaStream_t st) {
+                       int64_t T_total, float scale, OutT* S0, OutT* C0, OutT* E0, cudaStream_t st) {
   SirenLayout lay = layout_of(d);
   const int64_t total = rows * (d->hidden_features / Vec<OutT>::N);
   int blocks = (int)std::min<int64_t>(cdiv(total, 256), (int64_t)num_sms() * 16);
   if (blocks < 1) blocks = 1;
   { LaunchScope ls("k_first_layer", st);
-  k_first_layer<OutT><<<blocks, 256, 0, st>>>(params + lay.w_off(0), params + lay.b_off(0), coords, d->in_features,
-                                              d->hidden_features, rows, g0, T_total, scale, d->first_omega_0, S0, C0); }
+  k_first_layer<OutT><<<blocks, 256, 0, st>>>(params + lay.w_off(0), params + lay.b_off(0),
+                                              lay.first_snake ? params + lay.a_off(0) : nullptr, coords, d->in_features,
+                                              d->hidden_features, rows, g0, T_total, scale, d->first_omega_0, S0, C0, E0); }
   INR_LAUNCH_CHECK();
   return INR_OK;
 }
-template int launch_first_layer<float>(const inr_siren_desc*, const float*, const float*, int64_t, int64_t, int64_t, float, float*, float*, cudaStream_t);
-template int launch_first_layer<__nv_bfloat16>(const inr_siren_desc*, const float*, const float*, int64_t, int64_t, int64_t, float, __nv_bfloat16*, __nv_bfloat16*, cudaStream_t);
+template int launch_first_layer<float>(const inr_siren_desc*, const float*, const float*, int64_t, int64_t, int64_t, float, float*, float*, float*, cudaStream_t);
+template int launch_first_layer<__nv_bfloat16>(const inr_siren_desc*, const float*, const float*, int64_t, int64_t, int64_t, float, __nv_bfloat16*, __nv_bfloat16*, __nv_bfloat16*, cudaStream_t);
 
 // ------------------------------------------------------------------------------------------------
 // last layer + loss + first backward step.  One warp per row (grid-stride); lane j owns h = j, j+32, ...
 // ------------------------------------------------------------------------------------------------
 constexpr int kMaxHPerLane = 32;  // H <= 1024
 
-template <typename ActT>
+template <typename ActT, bool SNAKE>
 __global__ void __launch_bounds__(256) k_last_layer(const ActT* __restrict__ S, ActT* __restrict__ CdZ,
+                                                    const ActT* __restrict__ E, float* __restrict__ gA,
                                                     const float* __restrict__ w, const float* __restrict__ bptr,
                                                     const float* __restrict__ target, const float* __restrict__ extra_g,
                                                     int64_t rows, int H, float omega_prev, float omega_hidden, int outermost_linear,
                                                     int loss_kind, float grad_scale, float* __restrict__ gW,
                                                     float* __restrict__ gb, double* __restrict__ loss_acc,
                                                     float* __restrict__ out, int training) {
-  extern __shared__ float s_gw[];  // H floats + 1
+  extern __shared__ float s_gw[];  // H floats + 1 (+ H for the Snake `a` gradient)
   const int lane = threadIdx.x & 31;
   const int warp_in_block = threadIdx.x >> 5;
   const int warps_per_block = blockDim.x >> 5;
   const int nper = (H + 31) / 32;
   if (training) {
-    for (int i = threadIdx.x; i <= H; i += blockDim.x) s_gw[i] = 0.f;
+    for (int i = threadIdx.x; i <= (SNAKE ? 2 * H : H); i += blockDim.x) s_gw[i] = 0.f;
     __syncthreads();
   }
-  float wreg[kMaxHPerLane], gacc[kMaxHPerLane];
+  float wreg[kMaxHPerLane], gacc[kMaxHPerLane], aacc[SNAKE ? kMaxHPerLane : 1];
 #pragma unroll
   for (int j = 0; j < kMaxHPerLane; ++j) {
     const int h = j * 32 + lane;
     wreg[j] = (j < nper && h < H) ? w[h] : 0.f;
     gacc[j] = 0.f;
+    if (SNAKE) aacc[j] = 0.f;
   }
   const float bias = bptr[0];
   double loss_local = 0.0;
@@ -167,6 +190,7 @@ __global__ void __launch_bounds__(256) k_last_layer(const ActT* __restrict__ S, 
         gacc[j] = __fmaf_rn(g, sreg[j], gacc[j]);
         const float c = to_f(crow[h]);
         from_f(crow + h, gw * wreg[j] * c);  // dZ_L = g * w[h] * omega * cos(omega z_L), in place over C_L
+        if (SNAKE) aacc[j] = __fmaf_rn(g * wreg[j], to_f(E[r * H + h]), aacc[j]);   // d loss/d a_L
       }
     }
   }
@@ -174,38 +198,54 @@ __global__ void __launch_bounds__(256) k_last_layer(const ActT* __restrict__ S, 
 #pragma unroll
   for (int j = 0; j < kMaxHPerLane; ++j) {
     const int h = j * 32 + lane;
-    if (j < nper && h < H) atomicAdd(&s_gw[h], gacc[j]);
+    if (j < nper && h < H) {
+      atomicAdd(&s_gw[h], gacc[j]);
+      if (SNAKE) atomicAdd(&s_gw[H + 1 + h], aacc[j]);
+    }
   }
   if (lane == 0) {
     atomicAdd(&s_gw[H], gb_local);
     if (target) atomicAdd(loss_acc, loss_local);
   }
   __syncthreads();
-  for (int i = threadIdx.x; i < H; i += blockDim.x) atomicAdd(&gW[i], s_gw[i]);
+  for (int i = threadIdx.x; i < H; i += blockDim.x) {
+    atomicAdd(&gW[i], s_gw[i]);
+    if (SNAKE) atomicAdd(&gA[i], s_gw[H + 1 + i]);
+  }
   if (threadIdx.x == 0) atomicAdd(gb, s_gw[H]);
 }
 
 template <typename ActT>
-int launch_last_layer(const inr_siren_desc* d, const float* params, const ActT* SL, ActT* CL_dZ, const float* target,
-                      const float* extra_gout, int64_t rows, int loss_kind, float grad_scale, float* grads,
-                      inr_opt_state* opt, float* out, int training, cudaStream_t st) {
+int launch_last_layer(const inr_siren_desc* d, const float* params, const ActT* SL, ActT* CL_dZ, const ActT* EL,
+                      const float* target, const float* extra_gout, int64_t rows, int loss_kind, float grad_scale,
+                      float* grads, inr_opt_state* opt, float* out, int training, cudaStream_t st) {
   SirenLayout lay = layout_of(d);
   const int H = d->hidden_features;
   INR_REQUIRE(H <= 32 * kMaxHPerLane, INR_E_UNSUPPORTED, "hidden_features %d > %d unsupported", H, 32 * kMaxHPerLane);
-  const int last = d->hidden_layers + 1;
+  const int last = lay.L + 1;
+  const int kindL = lay.kind(lay.L);
+  // factor between the stored derivative image and d y_L/d z_L: the sine layers keep cos(omega z) (x omega here),
+  // Snake/Tanh layers keep the full derivative
+  const float dfac = kindL == ACT_SINE ? (lay.L == 0 ? d->first_omega_0 : d->hidden_omega_0) : 1.f;
+  const bool snake = training && kindL == ACT_SNAKE && EL != nullptr;
   int blocks = (int)std::min<int64_t>(cdiv(rows, 8), (int64_t)num_sms() * 4);
   if (blocks < 1) blocks = 1;
   { LaunchScope ls("k_last_layer", st);
-  k_last_layer<ActT><<<blocks, 256, (H + 1) * sizeof(float), st>>>(
-      SL, CL_dZ, params + lay.w_off(last), params + lay.b_off(last), target, extra_gout, rows, H,
-      d->hidden_layers == 0 ? d->first_omega_0 : d->hidden_omega_0, d->hidden_omega_0,
-      d->outermost_linear, loss_kind, grad_scale, grads ? grads + lay.w_off(last) : nullptr,
-      grads ? grads + lay.b_off(last) : nullptr, opt ? &opt->loss_acc[0] : nullptr, out, training); }
+  if (snake)
+    k_last_layer<ActT, true><<<blocks, 256, (2 * H + 1) * sizeof(float), st>>>(
+        SL, CL_dZ, EL, grads + lay.a_off(lay.L), params + lay.w_off(last), params + lay.b_off(last), target, extra_gout,
+        rows, H, dfac, d->hidden_omega_0, d->outermost_linear, loss_kind, grad_scale, grads + lay.w_off(last),
+        grads + lay.b_off(last), opt ? &opt->loss_acc[0] : nullptr, out, training);
+  else
+    k_last_layer<ActT, false><<<blocks, 256, (H + 1) * sizeof(float), st>>>(
+        SL, CL_dZ, nullptr, nullptr, params + lay.w_off(last), params + lay.b_off(last), target, extra_gout, rows, H,
+        dfac, d->hidden_omega_0, d->outermost_linear, loss_kind, grad_scale, grads ? grads + lay.w_off(last) : nullptr,
+        grads ? grads + lay.b_off(last) : nullptr, opt ? &opt->loss_acc[0] : nullptr, out, training); }
   INR_LAUNCH_CHECK();
   return INR_OK;
 }
-template int launch_last_layer<float>(const inr_siren_desc*, const float*, const float*, float*, const float*, const float*, int64_t, int, float, float*, inr_opt_state*, float*, int, cudaStream_t);
-template int launch_last_layer<__nv_bfloat16>(const inr_siren_desc*, const float*, const __nv_bfloat16*, __nv_bfloat16*, const float*, const float*, int64_t, int, float, float*, inr_opt_state*, float*, int, cudaStream_t);
+template int launch_last_layer<float>(const inr_siren_desc*, const float*, const float*, float*, const float*, const float*, const float*, int64_t, int, float, float*, inr_opt_state*, float*, int, cudaStream_t);
+template int launch_last_layer<__nv_bfloat16>(const inr_siren_desc*, const float*, const __nv_bfloat16*, __nv_bfloat16*, const __nv_bfloat16*, const float*, const float*, int64_t, int, float, float*, inr_opt_state*, float*, int, cudaStream_t);
 
 // ------------------------------------------------------------------------------------------------
 // column reductions over coordinates: gb[h] += sum_r dZ[r,h];  gW[h*in+i] += sum_r dZ[r,h] * x[r,i]

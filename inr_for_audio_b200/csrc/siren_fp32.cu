@@ -12,26 +12,45 @@
 namespace inr {
 
 int siren_fp32_workspace_per_row(const inr_siren_desc* d, int training) {
-  const int H = d->hidden_features, L = d->hidden_layers;
-  // training: S_0..S_L and C_0..C_L (C_l is overwritten by dZ_l);  inference: two ping-pong S buffers
-  return training ? 2 * (L + 1) * H * (int)sizeof(float) : 2 * H * (int)sizeof(float);
+  const SirenLayout lay = layout_of(d);
+  const int H = lay.H, L = lay.L;
+  // training: Y_0..Y_L (layer outputs) and D_0..D_L (derivative images, overwritten by dZ_l), + one dy/da image per
+  // Snake layer;  inference: two ping-pong buffers
+  return training ? (2 * (L + 1) + lay.num_snake_layers()) * H * (int)sizeof(float) : 2 * H * (int)sizeof(float);
 }
 
+// forward of hidden layer `layer` (1..L): Sout = act(Sin W^T + b), Cout = derivative image, Eout = dy/da (Snake)
 static int fwd_layer(const inr_siren_desc* d, const float* params, int layer, const float* Sin, float* Sout,
-                     float* Cout, int64_t rows, cudaStream_t st) {
+                     float* Cout, float* Eout, int64_t rows, cudaStream_t st) {
   SirenLayout lay = layout_of(d);
   const int H = d->hidden_features;
   dim3 grid((unsigned)cdiv(rows, BM), (unsigned)cdiv(H, BN), 1);
-  { LaunchScope ls("k_sgemm_fwd_sincos", st);
-  k_sgemm<true, true, EPI_SINCOS><<<grid, 256, 0, st>>>(Sin, H, 1, params + lay.w_off(layer), H, 1, rows, H, H, H,
-                                                        params + lay.b_off(layer), d->hidden_omega_0, Sout, Cout, H); }
+  const float* W = params + lay.w_off(layer);
+  const float* b = params + lay.b_off(layer);
+  switch (lay.kind(layer)) {
+    case ACT_SINE: {
+      LaunchScope ls("k_sgemm_fwd_sincos", st);
+      k_sgemm<true, true, EPI_SINCOS><<<grid, 256, 0, st>>>(Sin, H, 1, W, H, 1, rows, H, H, H, b, d->hidden_omega_0, Sout,
+                                                            Cout, H);
+    } break;
+    case ACT_SNAKE: {
+      LaunchScope ls("k_sgemm_fwd_snake", st);
+      k_sgemm<true, true, EPI_SNAKE><<<grid, 256, 0, st>>>(Sin, H, 1, W, H, 1, rows, H, H, H, b, 1.f, Sout, Cout, H,
+                                                           params + lay.a_off(layer), Eout);
+    } break;
+    default: {
+      LaunchScope ls("k_sgemm_fwd_tanh", st);
+      k_sgemm<true, true, EPI_TANH><<<grid, 256, 0, st>>>(Sin, H, 1, W, H, 1, rows, H, H, H, b, 1.f, Sout, Cout, H);
+    } break;
+  }
   INR_LAUNCH_CHECK();
   return INR_OK;
 }
 
 int siren_fp32_forward(const inr_siren_desc* d, const float* params, const float* coords, int64_t n, int64_t i0,
                        int64_t T_total, float scale, float* out, void* ws, int64_t ws_bytes, cudaStream_t st) {
-  const int H = d->hidden_features, L = d->hidden_layers;
+  const SirenLayout lay = layout_of(d);
+  const int H = lay.H, L = lay.L;
   const int64_t per_row = siren_fp32_workspace_per_row(d, 0);
   int64_t chunk = std::min<int64_t>(n, ws_bytes / per_row);
   INR_REQUIRE(chunk >= 1, INR_E_WORKSPACE, "workspace of %lld bytes holds no row (need %lld/row)", (long long)ws_bytes, (long long)per_row);
@@ -39,15 +58,15 @@ int siren_fp32_forward(const inr_siren_desc* d, const float* params, const float
     const int64_t rows = std::min(chunk, n - r0);
     float* S[2] = {(float*)ws, (float*)ws + rows * H};
     int rc = launch_first_layer<float>(d, params, coords ? coords + r0 * d->in_features : nullptr, rows, i0 + r0,
-                                       T_total, scale, S[0], nullptr, st);
+                                       T_total, scale, S[0], nullptr, nullptr, st);
     if (rc) return rc;
     int cur = 0;
     for (int l = 1; l <= L; ++l) {
-      rc = fwd_layer(d, params, l, S[cur], S[cur ^ 1], nullptr, rows, st);
+      rc = fwd_layer(d, params, l, S[cur], S[cur ^ 1], nullptr, nullptr, rows, st);
       if (rc) return rc;
       cur ^= 1;
     }
-    rc = launch_last_layer<float>(d, params, S[cur], nullptr, nullptr, nullptr, rows, 0, 0.f, nullptr, nullptr,
+    rc = launch_last_layer<float>(d, params, S[cur], nullptr, nullptr, nullptr, nullptr, rows, 0, 0.f, nullptr, nullptr,
                                   out + r0, 0, st);
     if (rc) return rc;
   }
@@ -60,7 +79,7 @@ int siren_fp32_train(const inr_siren_desc* d, const float* params, const float* 
                      const float* extra_gout, float* grads, inr_opt_state* opt, float* out, void* ws,
                      int64_t ws_bytes, int phase, cudaStream_t st) {
   SirenLayout lay = layout_of(d);
-  const int H = d->hidden_features, L = d->hidden_layers;
+  const int H = lay.H, L = lay.L;
   const int64_t per_row = siren_fp32_workspace_per_row(d, 1);
   int64_t chunk = std::min<int64_t>(n, ws_bytes / per_row);
   INR_REQUIRE(chunk >= 1, INR_E_WORKSPACE, "workspace of %lld bytes holds no row (need %lld/row)", (long long)ws_bytes, (long long)per_row);
@@ -72,23 +91,27 @@ int siren_fp32_train(const inr_siren_desc* d, const float* params, const float* 
     float* base = (float*)ws;
     auto S = [&](int l) { return base + (int64_t)l * rows * H; };
     auto C = [&](int l) { return base + (int64_t)(L + 1 + l) * rows * H; };
+    // dy/da image of Snake layer l (NULL for the other kinds)
+    auto E = [&](int l) -> float* {
+      return lay.kind(l) == ACT_SNAKE ? base + (int64_t)(2 * (L + 1) + lay.snakes_before(l)) * rows * H : nullptr;
+    };
     const float* xc = coords ? coords + r0 * d->in_features : nullptr;
     int rc;
     if (phase & 1) {
-      rc = launch_first_layer<float>(d, params, xc, rows, i0 + r0, T_total, scale, S(0), C(0), st);
+      rc = launch_first_layer<float>(d, params, xc, rows, i0 + r0, T_total, scale, S(0), C(0), E(0), st);
       if (rc) return rc;
       for (int l = 1; l <= L; ++l) {
-        rc = fwd_layer(d, params, l, S(l - 1), S(l), C(l), rows, st);
+        rc = fwd_layer(d, params, l, S(l - 1), S(l), C(l), E(l), rows, st);
         if (rc) return rc;
       }
       if (phase == 1) {
-        rc = launch_last_layer<float>(d, params, S(L), nullptr, nullptr, nullptr, rows, 0, 0.f, nullptr, nullptr,
+        rc = launch_last_layer<float>(d, params, S(L), nullptr, nullptr, nullptr, nullptr, rows, 0, 0.f, nullptr, nullptr,
                                       out + r0, 0, st);
         if (rc) return rc;
         continue;
       }
     }
-    rc = launch_last_layer<float>(d, params, S(L), C(L), target ? target + r0 : nullptr,
+    rc = launch_last_layer<float>(d, params, S(L), C(L), E(L), target ? target + r0 : nullptr,
                                   extra_gout ? extra_gout + r0 : nullptr, rows, loss_kind, grad_scale, grads, opt,
                                   out ? out + r0 : nullptr, 1, st);
     if (rc) return rc;
@@ -103,12 +126,22 @@ int siren_fp32_train(const inr_siren_desc* d, const float* params, const float* 
       INR_LAUNCH_CHECK();
       rc = launch_colsum<float>(C(l), rows, H, grads + lay.b_off(l), st);
       if (rc) return rc;
-      // dZ_{l-1} = (dZ_l W_l) * omega_{l-1} * C_{l-1}: A = dZ_l (k contiguous), B(n,k) = W_l[k][n] (n contiguous)
-      const float om = (l - 1 == 0) ? d->first_omega_0 : d->hidden_omega_0;
+      // dZ_{l-1} = (dZ_l W_l) * (d y_{l-1}/d z_{l-1}): A = dZ_l (k contiguous), B(n,k) = W_l[k][n] (n contiguous).
+      // Sine layers keep cos(omega z) in C (times omega here); Snake/Tanh keep the whole derivative; a Snake layer
+      // also takes its `a` gradient from the same product (dY = dZ_l W_l) against its dy/da image.
       dim3 gbw((unsigned)cdiv(rows, BM), (unsigned)cdiv(H, BN), 1);
-      { LaunchScope ls("k_sgemm_bwd_cosmul", st);
-      k_sgemm<true, false, EPI_COSMUL><<<gbw, 256, 0, st>>>(C(l), H, 1, params + lay.w_off(l), 1, H, rows, H, H, H,
-                                                            nullptr, om, C(l - 1), nullptr, H); }
+      const int kprev = lay.kind(l - 1);
+      if (kprev == ACT_SNAKE) {
+        LaunchScope ls("k_sgemm_bwd_snake", st);
+        k_sgemm<true, false, EPI_DMUL_GA><<<gbw, 256, 0, st>>>(C(l), H, 1, params + lay.w_off(l), 1, H, rows, H, H, H,
+                                                               nullptr, 1.f, C(l - 1), nullptr, H, E(l - 1),
+                                                               grads + lay.a_off(l - 1));
+      } else {
+        const float om = kprev == ACT_TANH ? 1.f : ((l - 1 == 0) ? d->first_omega_0 : d->hidden_omega_0);
+        LaunchScope ls("k_sgemm_bwd_cosmul", st);
+        k_sgemm<true, false, EPI_COSMUL><<<gbw, 256, 0, st>>>(C(l), H, 1, params + lay.w_off(l), 1, H, rows, H, H, H,
+                                                              nullptr, om, C(l - 1), nullptr, H);
+      }
       INR_LAUNCH_CHECK();
     }
     rc = launch_first_layer_grad<float>(d, C(0), xc, rows, i0 + r0, T_total, scale, grads + lay.w_off(0),

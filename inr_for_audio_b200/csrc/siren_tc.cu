@@ -253,7 +253,8 @@ __global__ void __launch_bounds__(256) k_tc_colsum(const __nv_bfloat16* __restri
 // ------------------------------------------------------------------------------------------------ host side
 bool siren_tc_supported(const inr_siren_desc* d) {
   const int H = d->hidden_features;
-  return (H == 128 || H == 256 || H == 512) && d->hidden_layers >= 1 && d->out_features == 1;
+  return (H == 128 || H == 256 || H == 512) && d->hidden_layers >= 1 && d->out_features == 1 && d->num_snake == 0 &&
+         d->num_tanh == 0 && d->first_linear == 0;   // sine-only stacks; Snake/Tanh stacks run in the fp32 mode
 }
 
 // INR_TC_PAIR=0 selects the single-CTA layer kernel of tc_gemm.cuh (kept as the A/B baseline of profiles/r01_*);

@@ -21,34 +21,58 @@ from . import _lib as L
 
 @dataclass
 class SirenSpec:
-    """Shape of a sine-only SIREN (models.py:244-269 / 310-394 with num_snake = num_tanh = 0)."""
+    """Shape of the MLP: models.py:244-269 Siren, or the general models.py:310-394 SirenWithSnakeTanh stack
+    (layer 0, `hidden_layers` sine layers, `num_snake` Linear+Snake layers, `num_tanh` Linear+Tanh layers, last)."""
     in_features: int = 1
     hidden_features: int = 256
-    hidden_layers: int = 3
+    hidden_layers: int = 3          # number of HxH SineLayers (num_sine)
     out_features: int = 1
     outermost_linear: bool = True
     first_omega_0: float = 30.0
     hidden_omega_0: float = 30.0
+    num_snake: int = 0
+    num_tanh: int = 0
+    first_linear: bool = False
 
     def desc(self, precision="fp32") -> L.SirenDesc:
         prec = L.PRECISIONS[precision] if isinstance(precision, str) else int(precision)
         return L.SirenDesc(self.in_features, self.hidden_features, self.hidden_layers, self.out_features,
-                           int(bool(self.outermost_linear)), float(self.first_omega_0), float(self.hidden_omega_0), prec)
+                           int(bool(self.outermost_linear)), float(self.first_omega_0), float(self.hidden_omega_0), prec,
+                           int(self.num_snake), int(self.num_tanh), int(bool(self.first_linear)))
+
+    @property
+    def total_hidden(self) -> int:
+        return self.hidden_layers + self.num_snake + self.num_tanh
+
+    def sine_only(self) -> bool:
+        return self.num_snake == 0 and self.num_tanh == 0 and not self.first_linear
+
+    def layer_kinds(self):
+        """activation of layers 0..L: 'sine' | 'snake' | 'tanh'."""
+        return (["snake" if self.first_linear else "sine"] + ["sine"] * self.hidden_layers +
+                ["snake"] * self.num_snake + ["tanh"] * self.num_tanh)
 
     def layer_shapes(self):
         H = self.hidden_features
-        return [(H, self.in_features)] + [(H, H)] * self.hidden_layers + [(self.out_features, H)]
-
-    def num_params(self) -> int:
-        return sum(o * i + o for o, i in self.layer_shapes())
+        return [(H, self.in_features)] + [(H, H)] * self.total_hidden + [(self.out_features, H)]
 
     def param_sizes(self):
-        """flat sizes in state_dict order (weight, bias per layer)."""
-        return [s for o, i in self.layer_shapes() for s in (o * i, o)]
+        """flat sizes in state_dict order: weight, bias per layer, a Snake layer's `a` right after its bias."""
+        H = self.hidden_features
+        kinds = self.layer_kinds() + [None]
+        out = []
+        for (o, i), k in zip(self.layer_shapes(), kinds):
+            out += [o * i, o]
+            if k == "snake":
+                out.append(H)
+        return out
+
+    def num_params(self) -> int:
+        return sum(self.param_sizes())
 
     def flops_per_coord(self) -> int:
         """fwd + bwd dense flops per coordinate, SURVEY.md §8(d): 6 L H^2 + 10 H."""
-        return 6 * self.hidden_layers * self.hidden_features ** 2 + 10 * self.hidden_features
+        return 6 * self.total_hidden * self.hidden_features ** 2 + 10 * self.hidden_features
 
 
 def shard_range(T: int, rank: int, world: int, tile: int = 128):

@@ -1,4 +1,4 @@
-"""Drop-in for the reference's models.py on the sine path: SineLayer, Siren, SirenWithSnakeTanh.
+"""Drop-in for the reference's models.py on the fit path: SineLayer, Snake, Siren, SirenWithSnakeTanh.
 
 Same constructor arguments, module tree, state_dict keys and CPU-RNG consumption as the reference
 (models.py:84-120, 243-275, 306-394), so `torch.manual_seed(s); Siren(...)` yields bit-identical parameters and
@@ -156,20 +156,46 @@ class Siren(_FlatSirenBase):
                                     float(first_omega_0), float(hidden_omega_0)))
 
 
+class Snake(nn.Module):
+    """models.py:185-241: y = x + sin^2(a x)/a with a per-feature `a`, always trainable (the reference sets a
+    misspelt `requiresGrad`, models.py:233, so `a` stays a trainable nn.Parameter).  Holds the parameter only:
+    the activation itself runs inside the fused CUDA path (forward epilogue of the layer GEMM)."""
+
+    def __init__(self, in_features, a=None, trainable=True):
+        super().__init__()
+        self.in_features = in_features if isinstance(in_features, list) else [in_features]
+        if a is not None:
+            self.a = nn.Parameter(torch.ones(self.in_features) * a)
+        else:  # models.py:229-231: random init = mix of frequencies
+            m = torch.distributions.exponential.Exponential(torch.tensor([0.1]))
+            self.a = nn.Parameter((m.rsample(self.in_features)).squeeze())
+        self.a.requiresGrad = trainable
+
+
 class SirenWithSnakeTanh(_FlatSirenBase):
-    """models.py:306-394 -- the class run.py:112 instantiates.  The device path covers the sine-only case
-    (num_snake == num_tanh == 0, first_linear False), which is bit-identical in structure and seeded init to
-    Siren(outermost_linear=last_linear).  Snake/Tanh stacks are SURVEY.md §8(f)-1 ("next")."""
+    """models.py:306-394 -- the class run.py:112 instantiates: layer 0 (SineLayer, or nn.Linear + Snake when
+    first_linear), num_sine SineLayers, num_snake x (nn.Linear + Snake), num_tanh x (nn.Linear + Tanh), then the
+    final nn.Linear (last_linear) or SineLayer.  Same module tree, state_dict keys and RNG consumption as the
+    reference.  Sine-only stacks are identical to Siren(outermost_linear=last_linear) and run in either precision;
+    stacks with Snake/Tanh layers run in the fp32 mode (the bf16 tcgen05 kernels take sine layers only)."""
 
     def __init__(self, in_features, out_features, hidden_features, num_sine, num_snake, num_tanh, first_linear=False,
                  last_linear=True, first_omega_0=30, hidden_omega_0=30., a_initial=50, num_freq=None, scale=2.0):
         super().__init__()
-        if num_snake or num_tanh or first_linear:
-            raise NotImplementedError("Snake/Tanh layers (models.py:185-241,356-372) are not on the B200 path yet; "
-                                      "use num_snake=0, num_tanh=0, first_linear=False")
-        net = [SineLayer(in_features, hidden_features, is_first=True, omega_0=first_omega_0)]
+        net = []
+        if first_linear:
+            net.append(nn.Linear(in_features, hidden_features))
+            net.append(Snake(hidden_features, a=a_initial))
+        else:
+            net.append(SineLayer(in_features, hidden_features, is_first=True, omega_0=first_omega_0))
         for _ in range(num_sine):
             net.append(SineLayer(hidden_features, hidden_features, is_first=False, omega_0=hidden_omega_0))
+        for _ in range(num_snake):
+            net.append(nn.Linear(hidden_features, hidden_features))
+            net.append(Snake(hidden_features, a=a_initial))
+        for _ in range(num_tanh):
+            net.append(nn.Linear(hidden_features, hidden_features))
+            net.append(nn.Tanh())
         if last_linear:
             final_linear = nn.Linear(hidden_features, out_features)
             with torch.no_grad():
@@ -180,4 +206,5 @@ class SirenWithSnakeTanh(_FlatSirenBase):
             net.append(SineLayer(hidden_features, out_features, is_first=False, omega_0=hidden_omega_0))
         self.net = nn.Sequential(*net)
         self._finish_init(SirenSpec(in_features, hidden_features, num_sine, out_features, bool(last_linear),
-                                    float(first_omega_0), float(hidden_omega_0)))
+                                    float(first_omega_0), float(hidden_omega_0), int(num_snake), int(num_tanh),
+                                    bool(first_linear)))

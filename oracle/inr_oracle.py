@@ -109,10 +109,13 @@ def synth(T: int, sr: int = 44100, seed: int = 0) -> np.ndarray:
 # --------------------------------------------------------------------------------------------------
 
 class SirenSpec:
-    """Shape of a sine-only SIREN: Siren(in,H,L,out,outermost_linear) == SirenWithSnakeTanh(num_sine=L)."""
+    """Shape of the MLP: Siren(in,H,L,out,outermost_linear) == SirenWithSnakeTanh(num_sine=L), and the general
+    SirenWithSnakeTanh stack (models.py:337-385): layer 0 (SineLayer, or Linear+Snake when first_linear),
+    hidden_layers x SineLayer, num_snake x (Linear + Snake(a_initial)), num_tanh x (Linear + Tanh), last layer."""
 
     def __init__(self, in_features=1, hidden_features=256, hidden_layers=3, out_features=1,
-                 outermost_linear=True, first_omega_0=30.0, hidden_omega_0=30.0):
+                 outermost_linear=True, first_omega_0=30.0, hidden_omega_0=30.0, num_snake=0, num_tanh=0,
+                 first_linear=False, a_initial=50.0):
         self.in_features = in_features
         self.hidden_features = hidden_features
         self.hidden_layers = hidden_layers
@@ -120,55 +123,81 @@ class SirenSpec:
         self.outermost_linear = outermost_linear
         self.first_omega_0 = first_omega_0
         self.hidden_omega_0 = hidden_omega_0
+        self.num_snake = num_snake
+        self.num_tanh = num_tanh
+        self.first_linear = first_linear
+        self.a_initial = a_initial
 
     def layer_dims(self):
         H = self.hidden_features
-        dims = [(self.in_features, H)] + [(H, H)] * self.hidden_layers + [(H, self.out_features)]
+        n_hidden = self.hidden_layers + self.num_snake + self.num_tanh
+        dims = [(self.in_features, H)] + [(H, H)] * n_hidden + [(H, self.out_features)]
         return dims
 
+    def layer_kinds(self):
+        """'sine' | 'snake' | 'tanh' | 'linear' for layers 0..L+1."""
+        return (["snake" if self.first_linear else "sine"] + ["sine"] * self.hidden_layers +
+                ["snake"] * self.num_snake + ["tanh"] * self.num_tanh +
+                ["linear" if self.outermost_linear else "sine"])
+
     def num_params(self):
-        return sum(i * o + o for i, o in self.layer_dims())
+        H = self.hidden_features
+        return sum(i * o + o for i, o in self.layer_dims()) + H * self.layer_kinds().count("snake")
 
 
 def siren_init(spec: SirenSpec, seed: Optional[int] = None) -> List[torch.Tensor]:
-    """Parameters in state_dict order [W0,b0,W1,b1,...], consuming the CPU RNG exactly as the reference.
+    """Parameters in state_dict order [W0,b0,(a0),W1,b1,(a1),...], consuming the CPU RNG exactly as the reference.
 
     models.py:94-112: each SineLayer builds nn.Linear (default kaiming-uniform W, U(+-1/sqrt(in)) b draws)
     and THEN overwrites W with U(+-1/in) (first) or U(+-sqrt(6/in)/omega) (hidden).
-    models.py:258-262: the final nn.Linear likewise, W overwritten with U(+-sqrt(6/H)/hidden_omega).
+    models.py:258-262 / 375-379: the final nn.Linear likewise, W overwritten with U(+-sqrt(6/H)/hidden_omega).
+    models.py:343-347,356-372: the Linear of a Snake / Tanh layer keeps nn.Linear's default init; Snake's `a` is
+    ones * a_initial (models.py:226-227, no RNG draw).
     The bounds are computed in float64 by numpy exactly as the reference does.
     """
     if seed is not None:
         torch.manual_seed(seed)
     params: List[torch.Tensor] = []
     dims = spec.layer_dims()
-    n = len(dims)
+    kinds = spec.layer_kinds()
     with torch.no_grad():
         for li, (fin, fout) in enumerate(dims):
             lin = torch.nn.Linear(fin, fout)
-            last = li == n - 1
-            if li == 0:
+            kind = kinds[li]
+            if kind == "sine" and li == 0:
                 lin.weight.uniform_(-1 / fin, 1 / fin)
-            elif (not last) or True:
+            elif kind in ("sine", "linear"):
                 # hidden SineLayer, final nn.Linear (outermost_linear) and final SineLayer share the bound
                 bound = np.sqrt(6 / fin) / spec.hidden_omega_0
                 lin.weight.uniform_(-bound, bound)
             params += [lin.weight.detach().clone(), lin.bias.detach().clone()]
+            if kind == "snake":
+                params.append(torch.ones(fout) * spec.a_initial)
     return params
 
 
 def siren_forward(spec: SirenSpec, params: Sequence[torch.Tensor], coords: torch.Tensor) -> torch.Tensor:
-    """models.py:114-115 per layer: sin(omega_0 * linear(x)); final nn.Linear if outermost_linear."""
+    """models.py:114-115 per SineLayer: sin(omega_0 * linear(x)); models.py:235-241 Snake: x + (1/a) sin^2(x a);
+    nn.Tanh; final nn.Linear if outermost_linear."""
     x = coords
-    n = len(params) // 2
-    for li in range(n):
-        W, b = params[2 * li], params[2 * li + 1]
+    kinds = spec.layer_kinds()
+    pi = 0
+    for li, kind in enumerate(kinds):
+        W, b = params[pi], params[pi + 1]
+        pi += 2
         z = F.linear(x, W, b)
-        if li == n - 1 and spec.outermost_linear:
+        if kind == "linear":
             x = z
-        else:
+        elif kind == "sine":
             omega = spec.first_omega_0 if li == 0 else spec.hidden_omega_0
             x = torch.sin(omega * z)
+        elif kind == "snake":
+            a = params[pi]
+            pi += 1
+            x = z + (1.0 / a) * torch.pow(torch.sin(z * a), 2)
+        else:
+            x = torch.tanh(z)
+    assert pi == len(params)
     return x
 
 

@@ -51,6 +51,43 @@ def make_coords():
     np.savez_compressed(os.path.join(HERE, "coords.npz"), **out)
 
 
+
+# ---------------------------------------------------------------- Snake / Tanh stacks (models.py:185-241,306-394)
+def make_snake():
+    """SirenWithSnakeTanh with Snake / Tanh layers -- run.py's actual default architecture (run.py:30: num_sine=2,
+    num_snake=2, a_initial=0.5).  Small widths, full tensors: init, forward, teacher-forced steps, free-run losses."""
+    out = {}
+    sr, data = gt_bach(4096, 44100)
+    gt = torch.from_numpy(data / np.max(np.abs(data))).view(1, -1, 1)
+    coords = ref.utils.get_coord(4096, 1).view(1, -1, 1)
+    out["gt"] = gt.numpy().ravel()
+    cases = {
+        # name: (ctor kwargs, loss_mode)
+        "a": (dict(in_features=1, out_features=1, hidden_features=64, num_sine=1, num_snake=2, num_tanh=1,
+                   first_omega_0=30, hidden_omega_0=30.0, a_initial=0.5), "mse"),
+        # run.py's defaults (run.py:30,112-113) at a small width: omega=22000, two sine + two snake layers
+        "b": (dict(in_features=1, out_features=1, hidden_features=40, num_sine=2, num_snake=2, num_tanh=0,
+                   first_omega_0=22000, hidden_omega_0=30, a_initial=0.5), "mse"),
+        # first_linear (Linear+Snake as layer 0), class-default a_initial=50, final SineLayer, mae loss
+        "c": (dict(in_features=1, out_features=1, hidden_features=32, num_sine=0, num_snake=1, num_tanh=2,
+                   first_linear=True, last_linear=False, hidden_omega_0=30.0), "mae"),
+        # the last hidden layer is a Tanh layer; no sine layer besides the first
+        "d": (dict(in_features=1, out_features=1, hidden_features=24, num_sine=0, num_snake=1, num_tanh=1,
+                   a_initial=2.0), "mse"),
+    }
+    for name, (kw, loss_mode) in cases.items():
+        torch.manual_seed(7)
+        m = ref.models.SirenWithSnakeTanh(**kw)
+        out[name + "_keys"] = np.array(list(m.state_dict().keys()))
+        out[name + "_p0"] = np.concatenate([p.detach().numpy().ravel() for p in m.parameters()])
+        out[name + "_out0"] = m(coords).detach().numpy().ravel()
+        losses, lrs, rec = ref_fit(m, coords, gt, 8, loss_mode=loss_mode, record_steps=(0, 1, 5))
+        out[name + "_losses"] = np.array(losses, dtype=np.float64)
+        for k, v in rec.items():
+            out[name + "_" + k] = v
+    np.savez_compressed(os.path.join(HERE, "snake.npz"), **out)
+
+
 # ---------------------------------------------------------------- SIREN (models.py)
 def gt_bach(n=None, start=0):
     from scipy.io import wavfile
@@ -263,7 +300,7 @@ def make_kan():
 
 
 if __name__ == "__main__":
-    which = sys.argv[1:] or ["coords", "siren", "mdct", "kan", "converge"]
+    which = sys.argv[1:] or ["coords", "siren", "snake", "mdct", "kan", "converge"]
     for w in which:
         print("making", w)
         globals()["make_" + w]()

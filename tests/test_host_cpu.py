@@ -38,7 +38,7 @@ def test_library_exports_every_declared_symbol(built):
 def test_opt_state_struct_matches_header(built):
     from inr_for_audio_b200 import _lib as L
     assert L.OPT_STATE_BYTES == 96 and L.OPT_LOSS_ACC_OFFSET == 64
-    assert ctypes.sizeof(L.SirenDesc) == 32
+    assert ctypes.sizeof(L.SirenDesc) == 44
 
 
 def test_no_cpu_fallback():
@@ -139,3 +139,31 @@ def test_kan_seeded_init_and_state_dict_match_reference(golden):
     big = P.KAN([1, 256, 256, 1])
     assert sum(p.numel() for p in big.parameters()) == int(g["nparams_256"]) == big.spec.num_params()
     assert big.spec.flops_per_coord() == 2 * 2 * 9 * 256 + 3 * 2 * 256 * 9 * 256 + 3 * 2 * 256 * 9
+
+
+SNAKE_CASES = {
+    # name: (ctor kwargs of SirenWithSnakeTanh exactly as tests/golden/make_golden.py make_snake, loss_mode)
+    "a": (dict(in_features=1, out_features=1, hidden_features=64, num_sine=1, num_snake=2, num_tanh=1,
+               first_omega_0=30, hidden_omega_0=30.0, a_initial=0.5), "mse"),
+    "b": (dict(in_features=1, out_features=1, hidden_features=40, num_sine=2, num_snake=2, num_tanh=0,
+               first_omega_0=22000, hidden_omega_0=30, a_initial=0.5), "mse"),
+    "c": (dict(in_features=1, out_features=1, hidden_features=32, num_sine=0, num_snake=1, num_tanh=2,
+               first_linear=True, last_linear=False, hidden_omega_0=30.0), "mae"),
+    "d": (dict(in_features=1, out_features=1, hidden_features=24, num_sine=0, num_snake=1, num_tanh=1,
+               a_initial=2.0), "mse"),
+}
+
+
+@pytest.mark.parametrize("name", sorted(SNAKE_CASES))
+def test_snake_tanh_module_tree_and_seeded_init_match_reference(golden, name):
+    """models.py:306-394 with Snake / Tanh layers: same state_dict keys, same seeded parameters (bit-exact), and the
+    flat layout of SirenSpec / the C header equals the state_dict order."""
+    import inr_for_audio_b200 as P
+    g = golden("snake")
+    kw, _ = SNAKE_CASES[name]
+    torch.manual_seed(7)
+    m = P.SirenWithSnakeTanh(**kw)
+    assert list(m.state_dict().keys()) == [str(k) for k in g[name + "_keys"]]
+    assert np.array_equal(m.flat_parameters().numpy(), g[name + "_p0"])
+    assert m.spec.param_sizes() == [p.numel() for p in m.parameters()]
+    assert m.spec.num_params() == g[name + "_p0"].size

@@ -188,3 +188,45 @@ def test_stft_snr_losses_selfconsistent():
     assert O.stft_mag(x.view(1, -1)).shape == (1, 513, 17)
     s = float(O.snr_loss(y.view(1, 1, -1), x.view(1, 1, -1)))
     assert -25 < s < -15
+
+
+SNAKE_SPECS = {
+    # the oracle's SirenSpec for the cases of tests/golden/make_golden.py make_snake
+    "a": (O.SirenSpec(1, 64, 1, 1, True, 30.0, 30.0, num_snake=2, num_tanh=1, a_initial=0.5), "mse"),
+    "b": (O.SirenSpec(1, 40, 2, 1, True, 22000.0, 30.0, num_snake=2, num_tanh=0, a_initial=0.5), "mse"),
+    "c": (O.SirenSpec(1, 32, 0, 1, False, 30.0, 30.0, num_snake=1, num_tanh=2, first_linear=True, a_initial=50.0), "mae"),
+    "d": (O.SirenSpec(1, 24, 0, 1, True, 30.0, 30.0, num_snake=1, num_tanh=1, a_initial=2.0), "mse"),
+}
+
+
+def _split_sizes(flat, sizes_like):
+    out, o = [], 0
+    for t in sizes_like:
+        n = t.numel()
+        out.append(torch.from_numpy(np.asarray(flat[o:o + n])).view(t.shape).clone())
+        o += n
+    assert o == len(flat)
+    return out
+
+
+@pytest.mark.parametrize("name", sorted(SNAKE_SPECS))
+def test_snake_tanh_stacks_against_reference(golden, name):
+    """models.py:185-241,306-394: seeded init (bit-exact), forward, per-step loss + gradients (teacher-forced from the
+    reference's recorded parameters) and the first free-running losses, against outputs of the reference itself."""
+    g = golden("snake")
+    spec, loss_mode = SNAKE_SPECS[name]
+    ps = O.siren_init(spec, seed=7)
+    assert np.array_equal(_flat(ps), g[name + "_p0"])
+    assert spec.num_params() == g[name + "_p0"].size
+    coords = O.get_coord(4096, 1).view(1, -1, 1)
+    gt = torch.from_numpy(g["gt"]).view(1, -1, 1)
+    tol = 5e-4 if spec.first_omega_0 > 1000 else 2e-5       # omega=22000: sin argument ~4e4 rad, see test_siren_variants
+    np.testing.assert_allclose(O.siren_forward(spec, ps, coords).numpy().ravel(), g[name + "_out0"], atol=tol)
+    for k in (0, 1, 5):
+        pk = _split_sizes(g[f"{name}_p_{k}"], ps)
+        loss, _, grads, out = O.siren_loss_and_grads(spec, pk, coords, gt, loss_mode)
+        assert abs(float(loss) - g[name + "_losses"][k]) <= 1e-5 * g[name + "_losses"][k]
+        gref = g[f"{name}_g_{k}"].astype(np.float64)
+        assert np.linalg.norm(_flat(grads) - gref) <= (1e-3 if loss_mode == "mae" else 1e-4) * np.linalg.norm(gref)
+    losses, _, _ = O.siren_fit(spec, ps, coords, gt, 3, loss_mode=loss_mode)
+    np.testing.assert_allclose(losses, g[name + "_losses"][:3], rtol=1e-4)

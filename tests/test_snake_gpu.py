@@ -1,0 +1,151 @@
+"""SirenWithSnakeTanh stacks with Snake / Tanh layers (models.py:185-241,306-394; SURVEY.md §8(f)-1 -- run.py's actual
+default architecture) on the CUDA path, against golden vectors made by the reference (tests/golden/snake.npz) and
+against the oracle on ragged sizes.  fp32 mode; tolerance: per-step loss within 1e-3 relative (north star), observed
+~1e-6."""
+import numpy as np
+import pytest
+import torch
+
+from test_host_cpu import SNAKE_CASES
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.fixture(scope="module")
+def pkg():
+    import inr_for_audio_b200 as P
+    assert torch.cuda.is_available()
+    return P
+
+
+def dev():
+    return torch.device("cuda:0")
+
+
+def _model(pkg, name):
+    kw, loss_mode = SNAKE_CASES[name]
+    torch.manual_seed(7)
+    return pkg.SirenWithSnakeTanh(**kw), loss_mode
+
+
+def _fitter(pkg, spec, p0, gt, **kw):
+    return pkg.SirenFitter(spec, torch.from_numpy(np.asarray(p0)), torch.from_numpy(np.asarray(gt)).to(dev()), **kw)
+
+
+@pytest.mark.parametrize("name", sorted(SNAKE_CASES))
+def test_forward_matches_reference(pkg, golden, name):
+    g = golden("snake")
+    m, _ = _model(pkg, name)
+    f = _fitter(pkg, m.spec, g[name + "_p0"], g["gt"])
+    tol = 2e-3 if m.spec.first_omega_0 > 1000 else 5e-6      # omega 22000: fp32 sin of ~4e4 rad (see test_siren_gpu)
+    np.testing.assert_allclose(f.forward().cpu().numpy(), g[name + "_out0"], atol=tol)
+    coords = pkg.get_coord(4096, 1, device=dev())
+    assert torch.equal(f.forward(coords), f.forward())
+
+
+@pytest.mark.parametrize("name", sorted(SNAKE_CASES))
+@pytest.mark.parametrize("k", [0, 1, 5])
+def test_teacher_forced_step(pkg, golden, name, k):
+    """reference params (+ Adam state) at step k in -> loss, gradients (incl. the Snake `a` gradients), updated params out."""
+    g = golden("snake")
+    m, loss_mode = _model(pkg, name)
+    big_omega = m.spec.first_omega_0 > 1000
+    f = _fitter(pkg, m.spec, g[f"{name}_p_{k}"], g["gt"], loss_mode=loss_mode, use_graph=False)
+    loss, grads, out = f.loss_and_grads()
+    ref_loss = float(g[name + "_losses"][k])
+    assert abs(loss - ref_loss) <= 1e-3 * ref_loss                      # the north-star tolerance
+    assert abs(loss - ref_loss) <= (2e-4 if big_omega else 1e-5) * ref_loss
+    gref = g[f"{name}_g_{k}"].astype(np.float64)
+    gtol = 2e-2 if (big_omega or loss_mode == "mae") else 5e-5
+    assert np.linalg.norm(grads.cpu().numpy() - gref) <= gtol * np.linalg.norm(gref)
+    # the Snake `a` gradients on their own (they are a small part of the norm above)
+    sizes = m.spec.param_sizes()
+    offs = np.cumsum([0] + sizes)
+    names = [n for n, _ in m.named_parameters()]
+    for i, n in enumerate(names):
+        if n.endswith(".a"):
+            ga, gr = grads[offs[i]:offs[i + 1]].cpu().numpy(), gref[offs[i]:offs[i + 1]]
+            assert np.linalg.norm(ga - gr) <= max(gtol, 2e-4) * np.linalg.norm(gr) + 1e-9, n
+    if k > 0:
+        f.m.copy_(torch.from_numpy(g[f"{name}_m_{k}"]).to(dev()))
+        f.v.copy_(torch.from_numpy(g[f"{name}_v_{k}"]).to(dev()))
+        f.set_opt(step=k)
+    f.step(1)
+    pn = f.params.cpu().numpy()
+    pref = g[f"{name}_pnext_{k}"]
+    upd = np.abs(pref - g[f"{name}_p_{k}"]).max()
+    assert np.abs(pn - pref).max() <= (0.1 if (big_omega or loss_mode == "mae") else 2e-3) * upd + 1e-9
+
+
+@pytest.mark.parametrize("name", ["a", "c", "d"])
+def test_free_run_first_steps(pkg, golden, name):
+    g = golden("snake")
+    m, loss_mode = _model(pkg, name)
+    f = _fitter(pkg, m.spec, g[name + "_p0"], g["gt"], loss_mode=loss_mode)
+    f.step(8)
+    np.testing.assert_allclose(f.losses()[:3], g[name + "_losses"][:3], rtol=1e-3)
+    np.testing.assert_allclose(f.losses(), g[name + "_losses"], rtol=2e-2)
+
+
+def test_module_autograd_route_with_snake(pkg, golden):
+    """model(coords) + loss.backward() + torch.optim.Adam, the reference's own loop (run.py:156-187): the Snake `a`
+    parameters receive gradients and are updated like every other parameter."""
+    g = golden("snake")
+    m, _ = _model(pkg, "a")
+    m.cuda()
+    coords = pkg.get_coord(4096, 1).view(1, -1, 1).cuda()
+    gt = torch.from_numpy(g["gt"]).view(1, -1, 1).cuda()
+    opt = torch.optim.Adam(m.parameters(), lr=1e-3)
+    losses = []
+    for _ in range(3):
+        out = m(coords)
+        loss = torch.nn.functional.mse_loss(out, gt)
+        losses.append(loss.item())
+        opt.zero_grad()
+        loss.backward()
+        opt.step()
+    np.testing.assert_allclose(losses, g["a_losses"][:3], rtol=2e-5)
+    a = dict(m.named_parameters())["net.3.a"]
+    assert a.grad is not None and float(a.grad.abs().max()) > 0 and not torch.equal(a.detach().cpu(), torch.full((64,), 0.5))
+
+
+def test_ragged_sizes_against_oracle(pkg):
+    """rows not a multiple of the GEMM tile, H not a multiple of 128, every layer-kind transition."""
+    from oracle import inr_oracle as O
+    for (H, ns, nk, nt, fl, last_lin, n) in ((40, 1, 1, 1, False, True, 1000), (24, 0, 2, 0, True, True, 333),
+                                            (136, 2, 1, 2, False, False, 4099), (8, 0, 0, 1, False, True, 1)):
+        ospec = O.SirenSpec(1, H, ns, 1, last_lin, 30.0, 30.0, num_snake=nk, num_tanh=nt, first_linear=fl, a_initial=1.5)
+        spec = pkg.SirenSpec(1, H, ns, 1, last_lin, 30.0, 30.0, nk, nt, fl)
+        ps = O.siren_init(ospec, seed=H)
+        flat = torch.cat([p.reshape(-1) for p in ps])
+        assert flat.numel() == spec.num_params()
+        gt = torch.sin(torch.linspace(0, 20, n))
+        coords = O.get_coord(n, 1).view(-1, 1)
+        loss_o, _, grads_o, out_o = O.siren_loss_and_grads(ospec, ps, coords, gt.view(-1, 1))
+        f = pkg.SirenFitter(spec, flat, gt.to(dev()), use_graph=False)
+        loss, grads, out = f.loss_and_grads()
+        assert abs(loss - float(loss_o)) <= 1e-5 * abs(float(loss_o)) + 1e-12
+        np.testing.assert_allclose(out.cpu().numpy(), out_o.numpy().ravel(), atol=1e-5)
+        go = torch.cat([x.reshape(-1) for x in grads_o]).numpy().astype(np.float64)
+        assert np.linalg.norm(grads.cpu().numpy() - go) <= 5e-5 * np.linalg.norm(go) + 1e-12
+
+
+def test_bf16_mode_rejects_snake_stacks(pkg):
+    from inr_for_audio_b200 import _lib as L
+    spec = pkg.SirenSpec(1, 128, 1, 1, True, 30.0, 30.0, 1, 0, False)
+    with pytest.raises(L.InrLibraryError):
+        pkg.SirenFitter(spec, torch.zeros(spec.num_params()), torch.zeros(256, device=dev()), precision="bf16")
+
+
+def test_train_dropin_default_architecture(pkg, tmp_path):
+    """run.train with run.py:30's default stack (num_sine=2, num_snake=2, a_initial=0.5) end to end on gt_bach."""
+    import os
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    ck = pkg.train(str(tmp_path), "t", "gt_bach", 1, num_hidden_features=64, omega=3000, total_steps=60,
+                   data_dir=os.path.join(root, "data"), seed=0, verbose=False)
+    sd = torch.load(ck, map_location="cpu")["model_state_dict"]
+    assert "net.4.a" in sd and "net.6.a" in sd and sd["net.4.a"].shape == (64,)
+    assert not torch.equal(sd["net.4.a"], torch.full((64,), 0.5))          # `a` was trained
+    import json
+    meta = json.load(open(os.path.join(os.path.dirname(ck), "parameters.json")))
+    assert np.isfinite(meta["SNR"]) and meta["SNR"] > 0.0
