@@ -12,6 +12,7 @@
 #include <stdlib.h>
 
 #include "tc_gemm2.cuh"
+#include "tc_fused.cuh"
 
 namespace inr {
 using namespace tc;
@@ -36,18 +37,7 @@ __global__ void __launch_bounds__(256) k_tc_pack(const float* __restrict__ param
 
 // ------------------------------------------------------------------------------------------------ first layer
 // one thread = one row x one feature group (8 features); consecutive threads = consecutive rows of a tile.
-// The argument omega*z is formed in fp32 exactly as the reference does (Linear -> * omega_0 -> sin, models.py:115);
-// it can reach +-4.4e4 rad (run.py's default omega = 22000), so it is reduced with a two-constant Cody-Waite step
-// (k = rint(t/2pi); r = t - k*C1 - k*C2 with FMAs, error < 2e-7 rad for |t| < 1e6) and the reduced angle goes to the
-// SFU (MUFU.SIN/COS, abs error ~5e-7 on [-pi, pi]) -- two orders below the bf16 rounding of the stored result.
-__device__ __forceinline__ void sincos_reduced(float t, float* s, float* c) {
-  const float k = rintf(t * 0.15915494309189535f);
-  float r = __fmaf_rn(-k, 6.2831854820251465f, t);      // C1 = fl32(2 pi)
-  r = __fmaf_rn(-k, -1.7484555e-7f, r);                 // C2 = 2 pi - C1
-  *s = __sinf(r);
-  *c = __cosf(r);
-}
-
+// sincos_reduced (tc_fused.cuh): fp32 argument omega*z as the reference forms it, Cody-Waite reduction, MUFU sincos.
 __global__ void __launch_bounds__(256) k_tc_first(const float* __restrict__ W, const float* __restrict__ B,
                                                   const float* __restrict__ coords, int in, int H, int64_t rows,
                                                   int64_t rows_pad, int64_t g0, int64_t T_total, float scale,
@@ -370,6 +360,52 @@ int tc_dw(int H, const DwParams& p, cudaStream_t st) {
   return INR_E_UNSUPPORTED;
 }
 
+// INR_TC_FUSED=0 selects the layer-major forward (k_tc_first + one k_tc_layer2<FWD> per layer, kept as the A/B
+// baseline); the default for H <= 256 is the fused all-layer forward of tc_fused.cuh.
+bool tc_fused_mode() {
+  static int v = -1;
+  if (v < 0) { const char* e = getenv("INR_TC_FUSED"); v = (e && e[0] == '0') ? 0 : 1; }
+  return v != 0;
+}
+static bool fused_ok(const inr_siren_desc* d) {
+  return tc_fused_mode() && tc_pair_mode() && (d->hidden_features == 128 || d->hidden_features == 256) &&
+         d->hidden_layers >= 1 && d->hidden_layers <= FUSED_MAX_L;
+}
+
+template <int H>
+static int launch_fused(const FusedParams& p, cudaStream_t st) {
+  using Cfg = FusedCfg<H>;
+  static bool attr_set = false;
+  if (!attr_set) {
+    INR_CUDA_CHECK(cudaFuncSetAttribute(k_tc_fused_fwd<H>, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg::SMEM_BYTES));
+    attr_set = true;
+  }
+  int pairs = num_sms() / 2;
+  const int num_dt = (p.num_tiles + 1) / 2;
+  if (pairs > num_dt) pairs = num_dt;
+  { LaunchScope ls("k_tc_fused_fwd", st);
+    k_tc_fused_fwd<H><<<2 * pairs, Cfg::THREADS, Cfg::SMEM_BYTES, st>>>(p); }
+  INR_LAUNCH_CHECK();
+  return INR_OK;
+}
+
+// first layer + all hidden layers of one row chunk in ONE kernel; S[l] / C[l] (l = 0..L) are the stash images to
+// write (NULL entries are skipped: inference keeps only S_L)
+static int fused_forward(const inr_siren_desc* d, const float* params, const __nv_bfloat16* Wf, const float* coords,
+                         int64_t rows, int tiles, int64_t g0, int64_t T_total, float scale, __nv_bfloat16* const* S,
+                         __nv_bfloat16* const* C, cudaStream_t st) {
+  SirenLayout lay = layout_of(d);
+  FusedParams p;
+  p.Wf = Wf; p.W0 = params + lay.w_off(0); p.B0 = params + lay.b_off(0);
+  for (int l = 0; l <= FUSED_MAX_L; ++l) { p.S[l] = nullptr; p.C[l] = nullptr; }
+  for (int l = 1; l <= lay.L; ++l) p.bias[l - 1] = params + lay.b_off(l);
+  for (int l = lay.L; l < FUSED_MAX_L; ++l) p.bias[l] = nullptr;
+  for (int l = 0; l <= lay.L; ++l) { p.S[l] = S[l]; p.C[l] = C ? C[l] : nullptr; }
+  p.coords = coords; p.in = lay.in; p.L = lay.L; p.num_tiles = tiles; p.rows = rows; p.g0 = g0; p.T_total = T_total;
+  p.scale = scale; p.omega0 = d->first_omega_0; p.omega_h = d->hidden_omega_0;
+  return lay.H == 256 ? launch_fused<256>(p, st) : launch_fused<128>(p, st);
+}
+
 static LayerParams layer_params(int H, const __nv_bfloat16* A, const __nv_bfloat16* Bp, const float* bias, float omega,
                                 __nv_bfloat16* out0, __nv_bfloat16* out1, const __nv_bfloat16* Cin, int tiles) {
   LayerParams p;
@@ -477,6 +513,17 @@ int siren_tc_forward(const inr_siren_desc* d, const float* params, const float* 
     const int64_t rows_pad = round_up(rows, TILE_ROWS);
     const int tiles = (int)(rows_pad / TILE_ROWS);
     __nv_bfloat16* S[2] = {w.img, w.img + w.img_elems};
+    if (fused_ok(d)) {   // all layers in one kernel; only S_L goes to HBM, for the output dot below
+      __nv_bfloat16* Sl[FUSED_MAX_L + 1] = {nullptr};
+      Sl[L] = S[0];
+      if ((rc = fused_forward(d, params, w.Wf, coords ? coords + r0 * lay.in : nullptr, rows, tiles, i0 + r0, T_total, scale,
+                              Sl, nullptr, st)))
+        return rc;
+      if ((rc = last_layer(d, params, S[0], nullptr, nullptr, nullptr, rows, tiles, 0, 0.f, nullptr, nullptr, nullptr,
+                           out + r0, 0, st)))
+        return rc;
+      continue;
+    }
     if ((rc = first_layer(d, params, coords ? coords + r0 * lay.in : nullptr, rows, rows_pad, i0 + r0, T_total, scale, S[0],
                           nullptr, st)))
       return rc;
@@ -518,11 +565,17 @@ int siren_tc_train(const inr_siren_desc* d, const float* params, const float* co
     auto C = [&](int l) { return w.img + (int64_t)(L + 1 + l) * w.img_elems; };
     const float* xc = coords ? coords + r0 * lay.in : nullptr;
     if (phase & 1) {
+      if (fused_ok(d)) {   // one kernel: S_l never re-read from HBM, only the stash the backward needs is written
+        __nv_bfloat16 *Sl[FUSED_MAX_L + 1], *Cl[FUSED_MAX_L + 1];
+        for (int l = 0; l <= L; ++l) { Sl[l] = S(l); Cl[l] = C(l); }
+        if ((rc = fused_forward(d, params, w.Wf, xc, rows, tiles, i0 + r0, T_total, scale, Sl, Cl, st))) return rc;
+      } else {
       if ((rc = first_layer(d, params, xc, rows, rows_pad, i0 + r0, T_total, scale, S(0), C(0), st))) return rc;
       for (int l = 1; l <= L; ++l) {
         LayerParams p = layer_params(H, S(l - 1), w.Wf + (int64_t)(l - 1) * H * H, params + lay.b_off(l), d->hidden_omega_0,
                                      S(l), C(l), nullptr, tiles);
         if ((rc = tc_layer(H, MODE_FWD, p, st))) return rc;
+      }
       }
       if (phase == 1) {
         if ((rc = last_layer(d, params, S(L), nullptr, nullptr, nullptr, rows, tiles, 0, 0.f, nullptr, nullptr, nullptr,

@@ -1,0 +1,327 @@
+// tc_fused.cuh -- fused all-layer SIREN forward for H <= 256 (sm_100a, tcgen05 cta_group::2).
+//
+// One kernel runs the FIRST layer and ALL hidden layers of a row tile (models.py:114-115 per layer, 271-275 for the
+// stack) without the activations leaving the SM between layers:
+//
+//   * a CTA pair owns two 256-row "slots" (X, Y), each CTA 128 rows of each; the current layer input of a slot lives
+//     in shared memory as a bf16 tile image (the UMMA K-major operand layout of tc_common.cuh) and is OVERWRITTEN by
+//     the epilogue with the next layer's input -- S_l is never read back from HBM;
+//   * the weights are the streamed operand: every layer's packed bf16 matrix (L2-resident, 128 KB at H = 256) is
+//     pulled through a bulk-copy ring, each CTA staging its half of the N columns (cta_group::2 B split);
+//   * accumulators: one TMEM buffer per slot; while the 8 epilogue warps drain slot X (omega*acc + omega*b -> sincos ->
+//     bf16 -> shared-memory image + the S_l / C_l stash the backward needs), the tensor pipe runs slot Y;
+//   * the first layer (fp32 FMA, Cody-Waite reduction, MUFU sincos) is computed by the epilogue warps straight into the
+//     slot's image, from coordinates generated in-kernel (0 HBM bytes) or given.
+//
+// HBM traffic of the forward: only the stash writes (S_l, C_l: 2 units per layer) -- the layer-major path
+// additionally READS S_{l-1} once per layer.  What the backward needs is written in the same tile-image layout as the
+// layer-major forward, so k_tc_layer2<BWD>, k_tc_dw and k_tc_last run unchanged.
+//
+// Job order of a pair (k-th double tile of the pair -> slot k&1, round r = k>>1):
+//   MMA / weight ring:  for r: for l = 1..L: (X, l), (Y, l)
+//   epilogue:           gen X(0), gen Y(0); for r: for l = 1..L: epi(X, l) [l == L: gen X(r+1)], epi(Y, l) [gen Y(r+1)]
+// Barriers (s = ring stage, b = slot):
+//   wfull[s]   leader: 2 arrivals (own producer with tx bytes + peer relay); peer: 1 (own producer, tx)
+//   wempty[s]  both: 1, multicast tcgen05.commit once the MMAs reading stage s are done
+//   tfull[b]   both: 1, multicast commit after the job's last MMA
+//   aready[b]  leader: 16 arrivals (8 local + 8 remote epilogue warps): the slot's image holds the next layer's input
+//              in BOTH CTAs and its accumulator has been drained
+#pragma once
+#include "tc_gemm.cuh"
+
+namespace inr {
+namespace tc {
+
+// The argument omega*z of the first layer is formed in fp32 exactly as the reference does (Linear -> * omega_0 -> sin,
+// models.py:115); it can reach +-4.4e4 rad (run.py's default omega = 22000), so it is reduced with a two-constant
+// Cody-Waite step (k = rint(t/2pi); r = t - k*C1 - k*C2 with FMAs, error < 2e-7 rad for |t| < 1e6) and the reduced
+// angle goes to the SFU (MUFU.SIN/COS, abs error ~5e-7 on [-pi, pi]) -- two orders below the bf16 rounding of the
+// stored result.
+__device__ __forceinline__ void sincos_reduced(float t, float* s, float* c) {
+  const float k = rintf(t * 0.15915494309189535f);
+  float r = __fmaf_rn(-k, 6.2831854820251465f, t);      // C1 = fl32(2 pi)
+  r = __fmaf_rn(-k, -1.7484555e-7f, r);                 // C2 = 2 pi - C1
+  *s = __sinf(r);
+  *c = __cosf(r);
+}
+
+constexpr int FUSED_MAX_L = 8;
+
+template <int H>
+struct FusedCfg {
+  static constexpr int NP = H;                      // output features per pair (MMA N): the whole layer
+  static constexpr int NC = NP / 2;                 // weight columns staged by each CTA
+  static constexpr int KC = 64;                     // K columns per weight ring stage
+  static constexpr int NCHUNK = H / KC;
+  static constexpr int W_STAGE_BYTES = (KC / 8) * NC * 16;          // 16 KB (H = 256), 8 KB (128)
+  static constexpr int STAGES = 5;
+  static constexpr int A_BYTES = (H / 8) * TILE_ROWS * 16;          // one slot image: 64 KB (H = 256)
+  static constexpr int TMEM_COLS = 2 * NP;          // one accumulator per slot
+  static constexpr int OFF_A = 0;
+  static constexpr int OFF_W = 2 * A_BYTES;
+  static constexpr int OFF_BIAS = OFF_W + STAGES * W_STAGE_BYTES;   // omega * b_l, l = 1..L (FUSED_MAX_L x H floats)
+  static constexpr int OFF_W0 = OFF_BIAS + FUSED_MAX_L * H * 4;     // first-layer weight (H x in, in <= 2)
+  static constexpr int OFF_B0 = OFF_W0 + 2 * H * 4;
+  static constexpr int OFF_BAR = OFF_B0 + H * 4;
+  static constexpr int SMEM_BYTES = OFF_BAR + 256;
+  static constexpr int THREADS = 320;
+  static_assert(H == 128 || H == 256, "fused forward: hidden width 128 or 256");
+  static_assert(SMEM_BYTES <= 232448, "shared-memory budget");
+};
+
+struct FusedParams {
+  const __nv_bfloat16* Wf;     // packed hidden weights, layer l-1 at Wf + (l-1)*H*H: [2 slices][H/8][NC][8]
+  const float* W0;             // first layer weight (H x in), bias (H)
+  const float* B0;
+  const float* bias[FUSED_MAX_L];        // hidden biases b_1..b_L
+  __nv_bfloat16* S[FUSED_MAX_L + 1];     // stash of S_0..S_L (tile images) or NULL
+  __nv_bfloat16* C[FUSED_MAX_L + 1];     // stash of C_0..C_L or NULL
+  const float* coords;         // (rows, in) or NULL: generated from the global index
+  int in, L, num_tiles;
+  int64_t rows, g0, T_total;
+  float scale, omega0, omega_h;
+};
+
+template <int H>
+__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(FusedCfg<H>::THREADS, 1) k_tc_fused_fwd(const FusedParams p) {
+  using Cfg = FusedCfg<H>;
+  constexpr int NP = Cfg::NP;
+  constexpr int NC = Cfg::NC;
+  extern __shared__ __align__(128) uint8_t smem[];
+  const uint32_t smem_base = smem_u32(smem);
+  auto sA = [&](int slot) { return smem_base + Cfg::OFF_A + slot * Cfg::A_BYTES; };
+  const uint32_t sW = smem_base + Cfg::OFF_W;
+  float* s_bias = reinterpret_cast<float*>(smem + Cfg::OFF_BIAS);
+  float* s_w0 = reinterpret_cast<float*>(smem + Cfg::OFF_W0);
+  float* s_b0 = reinterpret_cast<float*>(smem + Cfg::OFF_B0);
+  const uint32_t bar0 = smem_base + Cfg::OFF_BAR;
+  auto bar_wfull = [&](int s) { return bar0 + 8u * s; };
+  auto bar_wempty = [&](int s) { return bar0 + 8u * (Cfg::STAGES + s); };
+  auto bar_tfull = [&](int b) { return bar0 + 8u * (2 * Cfg::STAGES + b); };
+  auto bar_aready = [&](int b) { return bar0 + 8u * (2 * Cfg::STAGES + 2 + b); };
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(smem + Cfg::OFF_BAR + 8 * (2 * Cfg::STAGES + 4));
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const uint32_t rank = cluster_ctarank();
+  const bool leader = rank == 0;
+  const int pair = blockIdx.x >> 1;
+  const int npairs = gridDim.x >> 1;
+  const int num_dt = (p.num_tiles + 1) >> 1;          // double tiles (the last may have only its rank-0 half)
+  const int n_k = pair < num_dt ? (num_dt - pair + npairs - 1) / npairs : 0;   // double tiles of this pair
+  const int L = p.L;
+  auto dt_of = [&](int k) { return pair + k * npairs; };
+
+  if (threadIdx.x == 0) {
+    for (int s = 0; s < Cfg::STAGES; ++s) { mbar_init(bar_wfull(s), leader ? 2 : 1); mbar_init(bar_wempty(s), 1); }
+    for (int b = 0; b < 2; ++b) { mbar_init(bar_tfull(b), 1); mbar_init(bar_aready(b), 16); }
+    mbar_fence_init();
+  }
+  for (int l = 0; l < L; ++l)
+    for (int i = threadIdx.x; i < H; i += blockDim.x) s_bias[l * H + i] = p.omega_h * p.bias[l][i];
+  for (int i = threadIdx.x; i < H * p.in; i += blockDim.x) s_w0[i] = p.W0[i];
+  for (int i = threadIdx.x; i < H; i += blockDim.x) s_b0[i] = p.B0[i];
+  __syncthreads();
+  cluster_sync_all();                                 // both CTAs' barriers exist before anything can signal them
+  if (warp == 1) {
+    tmem_alloc2(smem_u32(tmem_slot), Cfg::TMEM_COLS);
+    tmem_relinquish2();
+  }
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot;
+
+  if (warp == 0) {
+    // ===================== producer: this CTA's half of every job's weight matrix through the ring ===============
+    if (lane == 0) {
+      int s = 0;
+      uint32_t phase = 0;
+      for (int r = 0; 2 * r < n_k; ++r) {
+        const int nslots = (2 * r + 1 < n_k) ? 2 : 1;
+        for (int l = 1; l <= L; ++l) {
+          const uint8_t* wsrc = reinterpret_cast<const uint8_t*>(p.Wf) + (size_t)(l - 1) * H * H * 2 +
+                                (size_t)rank * (H * NC * 2);
+          for (int b = 0; b < nslots; ++b) {
+            for (int c = 0; c < Cfg::NCHUNK; ++c) {
+              mbar_wait(bar_wempty(s), phase ^ 1);
+              mbar_arrive_expect_tx(bar_wfull(s), Cfg::W_STAGE_BYTES);
+              bulk_g2s(sW + s * Cfg::W_STAGE_BYTES, wsrc + (size_t)c * Cfg::W_STAGE_BYTES, Cfg::W_STAGE_BYTES, bar_wfull(s));
+              if (++s == Cfg::STAGES) { s = 0; phase ^= 1; }
+            }
+          }
+        }
+      }
+    }
+  } else if (warp == 1) {
+    if (lane == 0) {
+      if (leader) {
+        // ===================== MMA issuer (one thread of the pair) =====================
+        constexpr uint32_t idesc = make_idesc_bf16(256, NP, 0, 0);
+        int s = 0;
+        uint32_t phase = 0;
+        for (int r = 0; 2 * r < n_k; ++r) {
+          const int nslots = (2 * r + 1 < n_k) ? 2 : 1;
+          for (int l = 1; l <= L; ++l) {
+            const uint32_t par = (uint32_t)(r * L + l - 1) & 1u;
+            for (int b = 0; b < nslots; ++b) {
+              mbar_wait(bar_aready(b), par);          // image written in both CTAs, accumulator drained
+              tc_fence_after();
+              const uint32_t d_tmem = tmem_base + b * NP;
+              for (int c = 0; c < Cfg::NCHUNK; ++c) {
+                mbar_wait(bar_wfull(s), phase);
+                tc_fence_after();
+#pragma unroll
+                for (int kk = 0; kk < Cfg::KC / 16; ++kk) {
+                  const uint64_t ad = make_smem_desc(sA(b) + (c * (Cfg::KC / 8) + kk * 2) * (TILE_ROWS * 16), TILE_ROWS * 16, 128);
+                  const uint64_t bd = make_smem_desc(sW + s * Cfg::W_STAGE_BYTES + kk * 2 * (NC * 16), NC * 16, 128);
+                  umma2_bf16(d_tmem, ad, bd, idesc, (c | kk) != 0 ? 1u : 0u);
+                }
+                umma2_commit_mc(bar_wempty(s), 3);
+                if (++s == Cfg::STAGES) { s = 0; phase ^= 1; }
+              }
+              umma2_commit_mc(bar_tfull(b), 3);
+            }
+          }
+        }
+      } else {
+        // ===================== peer: forward "my weight stage has landed" to the leader's barriers ==============
+        int s = 0;
+        uint32_t phase = 0;
+        for (int r = 0; 2 * r < n_k; ++r) {
+          const int nslots = (2 * r + 1 < n_k) ? 2 : 1;
+          for (int j = 0; j < L * nslots * Cfg::NCHUNK; ++j) {
+            mbar_wait(bar_wfull(s), phase);
+            mbar_arrive_remote(bar_wfull(s), 0);
+            if (++s == Cfg::STAGES) { s = 0; phase ^= 1; }
+          }
+        }
+      }
+    }
+  } else {
+    // ===================== epilogue: 8 warps, warp%4 = TMEM lane quadrant, two column-chunk parities =====
+    const int e = warp - 2;
+    const int quad = warp & 3;
+    const int half = e >> 2;
+    const int row = quad * 32 + lane;
+    constexpr int NCH = NP / 64;                          // 32-column chunks per warp
+    uint8_t* smem_gen = smem;                             // generic-proxy view of the slot images
+
+    auto signal_ready = [&](int b) {
+      fence_proxy_async_smem();                           // generic-proxy image writes -> visible to the UMMA reads
+      tc_fence_before();
+      __syncwarp();
+      if (lane == 0) {
+        if (leader) mbar_arrive(bar_aready(b));
+        else mbar_arrive_remote(bar_aready(b), 0);
+      }
+    };
+    // first layer of double tile k into slot b (this CTA's 128 rows), + the S_0 / C_0 stash
+    auto gen_first = [&](int b, int k) {
+      const int tile = 2 * dt_of(k) + (int)rank;
+      if (tile < p.num_tiles) {
+        int64_t grow = (int64_t)tile * TILE_ROWS + row;
+        if (grow >= p.rows) grow = p.rows - 1;            // pad rows replicate the last row: finite, zero gradient later
+        float x0, x1 = 0.f;
+        if (p.coords) {
+          x0 = p.coords[grow * p.in];
+          if (p.in == 2) x1 = p.coords[grow * p.in + 1];
+        } else {
+          x0 = linspace_at(p.g0 + grow, p.T_total, p.scale);
+        }
+        const size_t tile_off = (size_t)tile * (TILE_ROWS * H);
+        uint8_t* img = smem_gen + Cfg::OFF_A + b * Cfg::A_BYTES;
+#pragma unroll 1
+        for (int ci = 0; ci < NCH; ++ci) {
+          const int g0 = ((half + 2 * ci) * 32) >> 3;
+#pragma unroll
+          for (int j = 0; j < 4; ++j) {
+            uint32_t so[4], co[4];
+#pragma unroll
+            for (int h = 0; h < 4; ++h) {
+              float s[2], c[2];
+#pragma unroll
+              for (int u = 0; u < 2; ++u) {
+                const int f = (g0 + j) * 8 + h * 2 + u;
+                const float z = (p.in == 1) ? __fmaf_rn(x0, s_w0[f], s_b0[f])
+                                            : (__fmaf_rn(x1, s_w0[f * 2 + 1], x0 * s_w0[f * 2]) + s_b0[f]);
+                sincos_reduced(p.omega0 * z, &s[u], &c[u]);
+              }
+              so[h] = pack_bf16x2(s[0], s[1]);
+              co[h] = pack_bf16x2(c[0], c[1]);
+            }
+            const size_t loc = ((size_t)(g0 + j) * TILE_ROWS + row) * 8;   // elements inside the tile image
+            *reinterpret_cast<uint4*>(img + loc * 2) = make_uint4(so[0], so[1], so[2], so[3]);
+            if (p.S[0]) *reinterpret_cast<uint4*>(p.S[0] + tile_off + loc) = make_uint4(so[0], so[1], so[2], so[3]);
+            if (p.C[0]) *reinterpret_cast<uint4*>(p.C[0] + tile_off + loc) = make_uint4(co[0], co[1], co[2], co[3]);
+          }
+        }
+      }
+      signal_ready(b);
+    };
+
+    if (n_k > 0) gen_first(0, 0);
+    if (n_k > 1) gen_first(1, 1);
+    for (int r = 0; 2 * r < n_k; ++r) {
+      const int nslots = (2 * r + 1 < n_k) ? 2 : 1;
+      for (int l = 1; l <= L; ++l) {
+        const uint32_t par = (uint32_t)(r * L + l - 1) & 1u;
+        const float* bias_l = s_bias + (l - 1) * H;
+        for (int b = 0; b < nslots; ++b) {
+          const int k = 2 * r + b;
+          const int tile = 2 * dt_of(k) + (int)rank;
+          const bool valid = tile < p.num_tiles;
+          mbar_wait(bar_tfull(b), par);
+          tc_fence_after();
+          if (valid) {
+            const size_t tile_off = (size_t)tile * (TILE_ROWS * H);
+            uint8_t* img = smem_gen + Cfg::OFF_A + b * Cfg::A_BYTES;
+            __nv_bfloat16* Sl = p.S[l];
+            __nv_bfloat16* Cl = p.C[l];
+#pragma unroll
+            for (int ci = 0; ci < NCH; ++ci) {
+              const int c = half + 2 * ci;
+              const int g0 = (c * 32) >> 3;
+              float v[32];
+              tmem_ld32(tmem_base + b * NP + c * 32 + ((uint32_t)(quad * 32) << 16), v);
+              tmem_ld_wait();
+#pragma unroll
+              for (int j = 0; j < 4; ++j) {
+                uint32_t o0[4], o1[4];
+#pragma unroll
+                for (int h = 0; h < 4; ++h) {
+                  const int cc = j * 8 + h * 2;
+                  const float t0 = __fmaf_rn(v[cc], p.omega_h, bias_l[c * 32 + cc]);
+                  const float t1 = __fmaf_rn(v[cc + 1], p.omega_h, bias_l[c * 32 + cc + 1]);
+                  float s0, c0, s1, c1;
+                  __sincosf(t0, &s0, &c0);
+                  __sincosf(t1, &s1, &c1);
+                  o0[h] = pack_bf16x2(s0, s1);
+                  o1[h] = pack_bf16x2(c0, c1);
+                }
+                const size_t loc = ((size_t)(g0 + j) * TILE_ROWS + row) * 8;
+                if (l < L) *reinterpret_cast<uint4*>(img + loc * 2) = make_uint4(o0[0], o0[1], o0[2], o0[3]);
+                if (Sl) *reinterpret_cast<uint4*>(Sl + tile_off + loc) = make_uint4(o0[0], o0[1], o0[2], o0[3]);
+                if (Cl) *reinterpret_cast<uint4*>(Cl + tile_off + loc) = make_uint4(o1[0], o1[1], o1[2], o1[3]);
+              }
+            }
+          }
+          if (l < L) {
+            signal_ready(b);                              // next layer's input is in place, accumulator drained
+          } else if (k + 2 < n_k) {
+            gen_first(b, k + 2);                          // the slot's next double tile (also releases the accumulator)
+          }
+        }
+      }
+    }
+  }
+  tc_fence_before();
+  __syncthreads();
+  cluster_sync_all();                                 // the peer's TMEM reads and remote arrivals are done
+  if (warp == 1) {
+    tc_fence_after();
+    tmem_dealloc2(tmem_base, Cfg::TMEM_COLS);
+  }
+}
+
+}  // namespace tc
+}  // namespace inr
