@@ -367,6 +367,12 @@ bool tc_fused_mode() {
   if (v < 0) { const char* e = getenv("INR_TC_FUSED"); v = (e && e[0] == '0') ? 0 : 1; }
   return v != 0;
 }
+// INR_TC_FUSED_LAST=0 keeps the head / loss / dZ_L in k_tc_last + k_tc_colsum after the fused forward (A/B baseline)
+bool tc_fused_last_mode() {
+  static int v = -1;
+  if (v < 0) { const char* e = getenv("INR_TC_FUSED_LAST"); v = (e && e[0] == '0') ? 0 : 1; }
+  return v != 0;
+}
 static bool fused_ok(const inr_siren_desc* d) {
   return tc_fused_mode() && tc_pair_mode() && (d->hidden_features == 128 || d->hidden_features == 256) &&
          d->hidden_layers >= 1 && d->hidden_layers <= FUSED_MAX_L;
@@ -391,9 +397,13 @@ static int launch_fused(const FusedParams& p, cudaStream_t st) {
 
 // first layer + all hidden layers of one row chunk in ONE kernel; S[l] / C[l] (l = 0..L) are the stash images to
 // write (NULL entries are skipped: inference keeps only S_L)
+struct FusedLast {   // arguments of the fused head + loss + dZ_L epilogue (FusedParams::fuse_last)
+  const float* target; const float* extra_g; int loss_kind; float grad_scale; float* grads; double* loss_acc; float* out;
+};
+
 static int fused_forward(const inr_siren_desc* d, const float* params, const __nv_bfloat16* Wf, const float* coords,
                          int64_t rows, int tiles, int64_t g0, int64_t T_total, float scale, __nv_bfloat16* const* S,
-                         __nv_bfloat16* const* C, cudaStream_t st) {
+                         __nv_bfloat16* const* C, const FusedLast* fl, cudaStream_t st) {
   SirenLayout lay = layout_of(d);
   FusedParams p;
   p.Wf = Wf; p.W0 = params + lay.w_off(0); p.B0 = params + lay.b_off(0);
@@ -403,6 +413,11 @@ static int fused_forward(const inr_siren_desc* d, const float* params, const __n
   for (int l = 0; l <= lay.L; ++l) { p.S[l] = S[l]; p.C[l] = C ? C[l] : nullptr; }
   p.coords = coords; p.in = lay.in; p.L = lay.L; p.num_tiles = tiles; p.rows = rows; p.g0 = g0; p.T_total = T_total;
   p.scale = scale; p.omega0 = d->first_omega_0; p.omega_h = d->hidden_omega_0;
+  p.fuse_last = fl ? 1 : 0; p.loss_kind = fl ? fl->loss_kind : 0; p.grad_scale = fl ? fl->grad_scale : 0.f;
+  p.w_last = params + lay.w_off(lay.L + 1); p.b_last = params + lay.b_off(lay.L + 1);
+  p.target = fl ? fl->target : nullptr; p.extra_g = fl ? fl->extra_g : nullptr; p.out = fl ? fl->out : nullptr;
+  p.g_wlast = fl ? fl->grads + lay.w_off(lay.L + 1) : nullptr; p.g_blast = fl ? fl->grads + lay.b_off(lay.L + 1) : nullptr;
+  p.loss_acc = fl ? fl->loss_acc : nullptr;
   return lay.H == 256 ? launch_fused<256>(p, st) : launch_fused<128>(p, st);
 }
 
@@ -517,7 +532,7 @@ int siren_tc_forward(const inr_siren_desc* d, const float* params, const float* 
       __nv_bfloat16* Sl[FUSED_MAX_L + 1] = {nullptr};
       Sl[L] = S[0];
       if ((rc = fused_forward(d, params, w.Wf, coords ? coords + r0 * lay.in : nullptr, rows, tiles, i0 + r0, T_total, scale,
-                              Sl, nullptr, st)))
+                              Sl, nullptr, nullptr, st)))
         return rc;
       if ((rc = last_layer(d, params, S[0], nullptr, nullptr, nullptr, rows, tiles, 0, 0.f, nullptr, nullptr, nullptr,
                            out + r0, 0, st)))
@@ -564,11 +579,19 @@ int siren_tc_train(const inr_siren_desc* d, const float* params, const float* co
     auto S = [&](int l) { return w.img + (int64_t)l * w.img_elems; };
     auto C = [&](int l) { return w.img + (int64_t)(L + 1 + l) * w.img_elems; };
     const float* xc = coords ? coords + r0 * lay.in : nullptr;
+    bool fused_tail = false;
     if (phase & 1) {
       if (fused_ok(d)) {   // one kernel: S_l never re-read from HBM, only the stash the backward needs is written
         __nv_bfloat16 *Sl[FUSED_MAX_L + 1], *Cl[FUSED_MAX_L + 1];
         for (int l = 0; l <= L; ++l) { Sl[l] = S(l); Cl[l] = C(l); }
-        if ((rc = fused_forward(d, params, w.Wf, xc, rows, tiles, i0 + r0, T_total, scale, Sl, Cl, st))) return rc;
+        // the fused step with the nn.Linear head also runs the head, the loss and dZ_L in the same kernel:
+        // S_L / C_L never reach HBM (dZ_L is written where C_L would go)
+        fused_tail = (phase == 3) && d->outermost_linear && tc_fused_last_mode();
+        FusedLast fl = {target ? target + r0 : nullptr, extra_gout ? extra_gout + r0 : nullptr, loss_kind, grad_scale, grads,
+                        opt ? &opt->loss_acc[0] : nullptr, out ? out + r0 : nullptr};
+        if (fused_tail) Sl[L] = nullptr;
+        if ((rc = fused_forward(d, params, w.Wf, xc, rows, tiles, i0 + r0, T_total, scale, Sl, Cl, fused_tail ? &fl : nullptr, st)))
+          return rc;
       } else {
       if ((rc = first_layer(d, params, xc, rows, rows_pad, i0 + r0, T_total, scale, S(0), C(0), st))) return rc;
       for (int l = 1; l <= L; ++l) {
@@ -584,12 +607,14 @@ int siren_tc_train(const inr_siren_desc* d, const float* params, const float* co
         continue;
       }
     }
+    if (!fused_tail) {
     if ((rc = last_layer(d, params, S(L), C(L), target ? target + r0 : nullptr, extra_gout ? extra_gout + r0 : nullptr, rows,
                          tiles, loss_kind, grad_scale, w.gvec, grads, opt, out ? out + r0 : nullptr, 1, st)))
       return rc;
     // last-layer weight gradient: gw_out[f] += sum_r g[r] S_L[r][f]
     if ((rc = colsum(S(L), H, tiles, w.gvec, nullptr, 1, rows, 0, 1, 1.f, nullptr, grads + lay.w_off(L + 1), 1, 1, st)))
       return rc;
+    }
     for (int l = L; l >= 1; --l) {
       DwParams dp;
       dp.dZ = C(l); dp.S = S(l - 1); dp.gW = grads + lay.w_off(l); dp.gb = grads + lay.b_off(l); dp.num_tiles = tiles;

@@ -62,7 +62,10 @@ struct FusedCfg {
   static constexpr int OFF_BIAS = OFF_W + STAGES * W_STAGE_BYTES;   // omega * b_l, l = 1..L (FUSED_MAX_L x H floats)
   static constexpr int OFF_W0 = OFF_BIAS + FUSED_MAX_L * H * 4;     // first-layer weight (H x in, in <= 2)
   static constexpr int OFF_B0 = OFF_W0 + 2 * H * 4;
-  static constexpr int OFF_BAR = OFF_B0 + H * 4;
+  static constexpr int OFF_WL = OFF_B0 + H * 4;                     // last nn.Linear weight (H floats)
+  static constexpr int OFF_DOT = OFF_WL + H * 4;                    // partial output dots [job parity][half][128 rows]
+  static constexpr int OFF_G = OFF_DOT + 2 * 2 * TILE_ROWS * 4;     // d loss / d out per row of the current tile
+  static constexpr int OFF_BAR = OFF_G + TILE_ROWS * 4;
   static constexpr int SMEM_BYTES = OFF_BAR + 256;
   static constexpr int THREADS = 320;
   static_assert(H == 128 || H == 256, "fused forward: hidden width 128 or 256");
@@ -80,6 +83,20 @@ struct FusedParams {
   int in, L, num_tiles;
   int64_t rows, g0, T_total;
   float scale, omega0, omega_h;
+  // fuse_last: the final nn.Linear (models.py:258-262), the time-domain loss (run.py:124-125,161-169) and the first
+  // backward step run in the epilogue of layer L: out = S_L w + b, g = d loss/d out (+ extra_g),
+  // dZ_L = g w omega C_L is written where C_L would go (C[L]); S_L / C_L never reach HBM; the last layer's weight
+  // and bias gradients and the loss numerator are reduced in the kernel.
+  int fuse_last, loss_kind;
+  float grad_scale;
+  const float* w_last;         // (H), bias (1)
+  const float* b_last;
+  const float* target;         // (rows) or NULL
+  const float* extra_g;        // (rows) upstream gradient or NULL
+  float* out;                  // (rows) or NULL
+  float* g_wlast;              // gradient of w_last (H), of b_last (1): accumulated with atomics
+  float* g_blast;
+  double* loss_acc;            // += sum (out - target)^2 or |out - target|
 };
 
 template <int H>
@@ -94,6 +111,9 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(FusedCfg<H>::THREADS
   float* s_bias = reinterpret_cast<float*>(smem + Cfg::OFF_BIAS);
   float* s_w0 = reinterpret_cast<float*>(smem + Cfg::OFF_W0);
   float* s_b0 = reinterpret_cast<float*>(smem + Cfg::OFF_B0);
+  float* s_wl = reinterpret_cast<float*>(smem + Cfg::OFF_WL);
+  float* s_dot = reinterpret_cast<float*>(smem + Cfg::OFF_DOT);
+  float* s_g = reinterpret_cast<float*>(smem + Cfg::OFF_G);
   const uint32_t bar0 = smem_base + Cfg::OFF_BAR;
   auto bar_wfull = [&](int s) { return bar0 + 8u * s; };
   auto bar_wempty = [&](int s) { return bar0 + 8u * (Cfg::STAGES + s); };
@@ -120,6 +140,8 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(FusedCfg<H>::THREADS
     for (int i = threadIdx.x; i < H; i += blockDim.x) s_bias[l * H + i] = p.omega_h * p.bias[l][i];
   for (int i = threadIdx.x; i < H * p.in; i += blockDim.x) s_w0[i] = p.W0[i];
   for (int i = threadIdx.x; i < H; i += blockDim.x) s_b0[i] = p.B0[i];
+  if (p.fuse_last)
+    for (int i = threadIdx.x; i < H; i += blockDim.x) s_wl[i] = p.w_last[i];
   __syncthreads();
   cluster_sync_all();                                 // both CTAs' barriers exist before anything can signal them
   if (warp == 1) {
@@ -259,6 +281,14 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(FusedCfg<H>::THREADS
       signal_ready(b);
     };
 
+    // fuse_last accumulators: loss numerator, bias gradient (half 0 threads), weight gradient (lane = column % 32)
+    double loss_local = 0.0;
+    float gb_local = 0.f;
+    float gw_acc[8];
+#pragma unroll
+    for (int i = 0; i < 8; ++i) gw_acc[i] = 0.f;
+    int last_jobs = 0;
+
     if (n_k > 0) gen_first(0, 0);
     if (n_k > 1) gen_first(1, 1);
     for (int r = 0; 2 * r < n_k; ++r) {
@@ -272,7 +302,110 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(FusedCfg<H>::THREADS
           const bool valid = tile < p.num_tiles;
           mbar_wait(bar_tfull(b), par);
           tc_fence_after();
-          if (valid) {
+          if (l == L && p.fuse_last) {
+            // ---------- last hidden layer + nn.Linear head + loss + dZ_L ----------
+            // pass A: S_L = sin(.) (bf16) -> the slot's image (free: no layer L+1) + this thread's part of the output dot
+            // pass B: cos(.) from the accumulator again -> dZ_L = g w omega C_L -> HBM
+            // pass C: g_w[f] += sum_r g[r] S_L[r][f] from the image (one thread = 8 features x 128/TPG rows)
+            const size_t tile_off = (size_t)tile * (TILE_ROWS * H);
+            const int64_t grow = (int64_t)tile * TILE_ROWS + row;
+            const bool live = valid && grow < p.rows;
+            uint8_t* img = smem_gen + Cfg::OFF_A + b * Cfg::A_BYTES;
+            float dot = 0.f;
+            if (valid) {
+#pragma unroll
+              for (int ci = 0; ci < NCH; ++ci) {
+                const int c = half + 2 * ci;
+                const int g0 = (c * 32) >> 3;
+                float v[32];
+                tmem_ld32(tmem_base + b * NP + c * 32 + ((uint32_t)(quad * 32) << 16), v);
+                tmem_ld_wait();
+#pragma unroll
+                for (int j = 0; j < 4; ++j) {
+                  uint32_t o0[4];
+#pragma unroll
+                  for (int h = 0; h < 4; ++h) {
+                    const int cc = j * 8 + h * 2;
+                    const float s0 = __sinf(__fmaf_rn(v[cc], p.omega_h, bias_l[c * 32 + cc]));
+                    const float s1 = __sinf(__fmaf_rn(v[cc + 1], p.omega_h, bias_l[c * 32 + cc + 1]));
+                    o0[h] = pack_bf16x2(s0, s1);
+                    const float2 sb = unpack_bf16x2(o0[h]);   // the head sees the bf16 S_L, as on the layer-major path
+                    dot = __fmaf_rn(sb.x, s_wl[c * 32 + cc], dot);
+                    dot = __fmaf_rn(sb.y, s_wl[c * 32 + cc + 1], dot);
+                  }
+                  *reinterpret_cast<uint4*>(img + ((size_t)(g0 + j) * TILE_ROWS + row) * 16) = make_uint4(o0[0], o0[1], o0[2], o0[3]);
+                }
+              }
+            }
+            float* sd = s_dot + (last_jobs & 1) * (2 * TILE_ROWS);
+            sd[half * TILE_ROWS + row] = dot;
+            asm volatile("bar.sync 1, 256;" ::: "memory");      // the 8 epilogue warps: both column halves of every row
+            const float o = sd[row] + sd[TILE_ROWS + row] + p.b_last[0];
+            ++last_jobs;
+            float g = 0.f;
+            if (live) {
+              if (p.out && half == 0) p.out[grow] = o;
+              if (p.target) {
+                const float diff = o - p.target[grow];
+                if (p.loss_kind == INR_LOSS_MAE) {
+                  if (half == 0) loss_local += (double)fabsf(diff);
+                  g = p.grad_scale * ((diff > 0.f) ? 1.f : ((diff < 0.f) ? -1.f : 0.f));
+                } else {
+                  if (half == 0) loss_local += (double)diff * (double)diff;
+                  g = p.grad_scale * 2.f * diff;
+                }
+              }
+              if (p.extra_g) g += p.extra_g[grow];
+              if (half == 0) gb_local += g;
+            }
+            if (half == 0) s_g[row] = g;
+            if (valid) {
+              const float gw = g * p.omega_h;
+#pragma unroll
+              for (int ci = 0; ci < NCH; ++ci) {
+                const int c = half + 2 * ci;
+                const int g0 = (c * 32) >> 3;
+                float v[32];
+                tmem_ld32(tmem_base + b * NP + c * 32 + ((uint32_t)(quad * 32) << 16), v);
+                tmem_ld_wait();
+#pragma unroll
+                for (int j = 0; j < 4; ++j) {
+                  uint32_t o1[4];
+#pragma unroll
+                  for (int h = 0; h < 4; ++h) {
+                    const int cc = j * 8 + h * 2;
+                    // same roundings as k_tc_last on the stored bf16 C_L image
+                    const float2 cb = unpack_bf16x2(pack_bf16x2(__cosf(__fmaf_rn(v[cc], p.omega_h, bias_l[c * 32 + cc])),
+                                                                __cosf(__fmaf_rn(v[cc + 1], p.omega_h, bias_l[c * 32 + cc + 1]))));
+                    o1[h] = pack_bf16x2(gw * s_wl[c * 32 + cc] * cb.x, gw * s_wl[c * 32 + cc + 1] * cb.y);
+                  }
+                  const size_t loc = ((size_t)(g0 + j) * TILE_ROWS + row) * 8;
+                  *reinterpret_cast<uint4*>(p.C[L] + tile_off + loc) = make_uint4(o1[0], o1[1], o1[2], o1[3]);
+                }
+              }
+            }
+            asm volatile("bar.sync 1, 256;" ::: "memory");      // S_L image and s_g complete
+            if (valid) {
+              constexpr int TPG = 256 / (H / 8);                 // threads per feature group: 8 (H = 256), 16 (H = 128)
+              constexpr int RPT = TILE_ROWS / TPG;               // rows per thread
+              const int et = threadIdx.x - 64;                   // 0..255 over the epilogue warps
+              const int fg = et / TPG, r0 = (et % TPG) * RPT;
+#pragma unroll 4
+              for (int rr = 0; rr < RPT; ++rr) {
+                const uint4 u = *reinterpret_cast<const uint4*>(img + ((size_t)fg * TILE_ROWS + r0 + rr) * 16);
+                const float gr = s_g[r0 + rr];
+                const uint32_t uw[4] = {u.x, u.y, u.z, u.w};
+#pragma unroll
+                for (int h = 0; h < 4; ++h) {
+                  const float2 f = unpack_bf16x2(uw[h]);
+                  gw_acc[2 * h] = __fmaf_rn(gr, f.x, gw_acc[2 * h]);
+                  gw_acc[2 * h + 1] = __fmaf_rn(gr, f.y, gw_acc[2 * h + 1]);
+                }
+              }
+            }
+            // the image is overwritten by the next gen_first (of ANY warp): all 8 warps leave it first
+            asm volatile("bar.sync 1, 256;" ::: "memory");
+          } else if (valid) {
             const size_t tile_off = (size_t)tile * (TILE_ROWS * H);
             uint8_t* img = smem_gen + Cfg::OFF_A + b * Cfg::A_BYTES;
             __nv_bfloat16* Sl = p.S[l];
@@ -311,6 +444,23 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(FusedCfg<H>::THREADS
             gen_first(b, k + 2);                          // the slot's next double tile (also releases the accumulator)
           }
         }
+      }
+    }
+    if (p.fuse_last) {
+      constexpr int TPG = 256 / (H / 8);
+      const int et = threadIdx.x - 64;
+#pragma unroll
+      for (int i = 0; i < 8; ++i) {
+        float a = gw_acc[i];
+#pragma unroll
+        for (int o = TPG / 2; o > 0; o >>= 1) a += __shfl_xor_sync(0xffffffffu, a, o);
+        if ((et % TPG) == 0) atomicAdd(p.g_wlast + (et / TPG) * 8 + i, a);
+      }
+      loss_local = warp_sum(loss_local);
+      gb_local = warp_sum(gb_local);
+      if (lane == 0 && half == 0) {
+        if (p.target) atomicAdd(p.loss_acc, loss_local);
+        atomicAdd(p.g_blast, gb_local);
       }
     }
   }
