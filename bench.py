@@ -30,6 +30,10 @@ WORKLOADS = {
     # configs[0] model shape on a synthetic clip of gt_bach's length (parity case; not a bench line by default)
     "c1": dict(kind="siren", T=264600, H=256, L=3, seed=0,
                desc="SIREN 3x256, synthetic 6 s @ 44.1 kHz (T=264600), mse, Adam lr 1e-3"),
+    # run.py:30's DEFAULT architecture (num_sine=2, num_snake=2, a_initial=0.5) on the C1-sized clip: Snake layers in
+    # the tcgen05 mode (informational, not a BASELINE.json config)
+    "c1snake": dict(kind="siren", T=264600, H=256, L=2, nk=2, seed=0,
+                    desc="SirenWithSnakeTanh 2 sine + 2 snake x256 (run.py default stack), synthetic 6 s (T=264600), mse"),
     # configs[2]: MDCT-domain + waveform loss on a synthetic 30 s clip (alpha = 0.2, a value run.py:456,486 uses)
     "c3": dict(kind="siren", T=1323000, H=256, L=3, seed=1, spectral="mdct", alpha=0.2,
                desc="SIREN 3x256, synthetic 30 s (T=1323000), 0.8*mse + 0.2*MDCT-domain L1 (N=2048, KBD), Adam lr 1e-3"),
@@ -150,7 +154,8 @@ def oracle_fit_rate(wl, rows, steps, warmup, threads):
             loss = torch.mean((O.kan_forward(coords, ls) - gt) ** 2)
             return loss.detach(), torch.autograd.grad(loss, req)
     else:
-        spec = O.SirenSpec(1, wl["H"], wl["L"], 1, True)
+        spec = O.SirenSpec(1, wl["H"], wl["L"], 1, True, 30.0, 30.0, num_snake=wl.get("nk", 0), num_tanh=wl.get("nt", 0),
+                           a_initial=0.5)
         params = O.siren_init(spec, seed=wl["seed"])
         alpha = wl.get("alpha", 0.0)
         sl = {"mdct": lambda o, g: O.mdct_loss(o, g, 2048, "l1"), "stft": O.stft_loss, None: None}[wl.get("spectral")]
@@ -240,9 +245,13 @@ class Job:
                 self.spec = self.model.spec
                 self.flops_per_coord = 3566592.0        # dense-equivalent fwd+bwd flops per coordinate
             else:
-                self.model = P.Siren(1, wl["H"], wl["L"], 1, True)
+                if wl.get("nk") or wl.get("nt"):
+                    self.model = P.SirenWithSnakeTanh(1, 1, wl["H"], wl["L"], wl.get("nk", 0), wl.get("nt", 0),
+                                                      first_omega_0=30, hidden_omega_0=30.0, a_initial=0.5)
+                else:
+                    self.model = P.Siren(1, wl["H"], wl["L"], 1, True)
                 self.spec = self.model.spec
-                self.flops_per_coord = 6.0 * wl["L"] * wl["H"] ** 2
+                self.flops_per_coord = 6.0 * self.spec.total_hidden * wl["H"] ** 2
         self.target = self.host_target.to(dev, non_blocking=True)
 
     def make(self, use_graph):

@@ -86,7 +86,8 @@ __global__ void __launch_bounds__(128) k_tc_last(const __nv_bfloat16* __restrict
                                                  int64_t rows, int num_tiles, int H, float omega_prev, float omega_hidden,
                                                  int outermost_linear, int loss_kind, float grad_scale,
                                                  float* __restrict__ gvec, float* __restrict__ gb,
-                                                 double* __restrict__ loss_acc, float* __restrict__ out, int training) {
+                                                 double* __restrict__ loss_acc, float* __restrict__ out, int training,
+                                                 __nv_bfloat16* __restrict__ Eimg) {
   extern __shared__ float s_w[];   // H floats
   __shared__ double s_red[4];
   __shared__ float s_gb[4];
@@ -151,6 +152,17 @@ __global__ void __launch_bounds__(128) k_tc_last(const __nv_bfloat16* __restrict
         ow[h] = pack_bf16x2(gw * s_w[kg * 8 + 2 * h] * f.x, gw * s_w[kg * 8 + 2 * h + 1] * f.y);
       }
       *reinterpret_cast<uint4*>(cp) = make_uint4(ow[0], ow[1], ow[2], ow[3]);
+      if (Eimg) {   // layer L is a Snake layer: dY_L * dy/da = g w E in place over E (column-summed afterwards -> grad of a)
+        __nv_bfloat16* ep = Eimg + tile_off + ((size_t)kg * TILE_ROWS + r) * 8;
+        const uint4 eu = *reinterpret_cast<const uint4*>(ep);
+        const uint32_t ew[4] = {eu.x, eu.y, eu.z, eu.w};
+#pragma unroll
+        for (int h = 0; h < 4; ++h) {
+          const float2 f = unpack_bf16x2(ew[h]);
+          ow[h] = pack_bf16x2(g * s_w[kg * 8 + 2 * h] * f.x, g * s_w[kg * 8 + 2 * h + 1] * f.y);
+        }
+        *reinterpret_cast<uint4*>(ep) = make_uint4(ow[0], ow[1], ow[2], ow[3]);
+      }
     }
   }
   if (!training) return;
@@ -241,10 +253,14 @@ __global__ void __launch_bounds__(256) k_tc_colsum(const __nv_bfloat16* __restri
 }
 
 // ------------------------------------------------------------------------------------------------ host side
+bool tc_pair_mode();
 bool siren_tc_supported(const inr_siren_desc* d) {
   const int H = d->hidden_features;
-  return (H == 128 || H == 256 || H == 512) && d->hidden_layers >= 1 && d->out_features == 1 && d->num_snake == 0 &&
-         d->num_tanh == 0 && d->first_linear == 0;   // sine-only stacks; Snake/Tanh stacks run in the fp32 mode
+  const int Ltot = d->hidden_layers + d->num_snake + d->num_tanh;
+  // Snake / Tanh hidden layers exist in the CTA-pair kernel only; a Linear+Snake FIRST layer runs in the fp32 mode
+  const bool sine_only = d->num_snake == 0 && d->num_tanh == 0;
+  return (H == 128 || H == 256 || H == 512) && Ltot >= 1 && d->out_features == 1 && d->first_linear == 0 &&
+         (sine_only || tc_pair_mode());
 }
 
 // INR_TC_PAIR=0 selects the single-CTA layer kernel of tc_gemm.cuh (kept as the A/B baseline of profiles/r01_*);
@@ -265,9 +281,10 @@ struct TcPlan {
 
 static TcPlan plan_of(const inr_siren_desc* d, int training) {
   TcPlan pl;
-  const int64_t H = d->hidden_features, L = d->hidden_layers;
+  const SirenLayout lay = layout_of(d);
+  const int64_t H = lay.H, L = lay.L;
   pl.pack_bytes = 2 * L * H * H * 2;
-  pl.n_images = training ? 2 * (int)(L + 1) : 2;
+  pl.n_images = training ? 2 * (int)(L + 1) + lay.num_snake_layers() : 2;   // + one dy/da image per Snake layer
   pl.img_bytes_per_row = pl.n_images * H * 2 + (training ? 4 : 0);   // + gvec
   pl.fixed_bytes = round_up(pl.pack_bytes, 1024) + 4096;
   pl.gvec_bytes = 0;
@@ -327,13 +344,27 @@ static int launch_layer2(const LayerParams& p, cudaStream_t st) {
   int pairs = (num_sms() / 2) / Cfg::NQ * Cfg::NQ;
   const int max_useful = ((p.num_tiles + 1) / 2) * Cfg::NQ;
   if (pairs > max_useful) pairs = max_useful;
-  { LaunchScope ls(MODE == MODE_FWD ? "k_tc_layer_fwd" : "k_tc_layer_bwd", st);
+  { LaunchScope ls(mode_is_fwd(MODE) ? "k_tc_layer_fwd" : "k_tc_layer_bwd", st);
     k_tc_layer2<H, MODE><<<2 * pairs, Cfg::THREADS, Cfg::SMEM_BYTES, st>>>(p); }
   INR_LAUNCH_CHECK();
   return INR_OK;
 }
 
+template <int MODE>
+static int launch_layer2_h(int H, const LayerParams& p, cudaStream_t st) {
+  switch (H) {
+    case 128: return launch_layer2<128, MODE>(p, st);
+    case 256: return launch_layer2<256, MODE>(p, st);
+    case 512: return launch_layer2<512, MODE>(p, st);
+  }
+  set_error("tcgen05 layer kernel: unsupported H=%d", H);
+  return INR_E_UNSUPPORTED;
+}
+
 int tc_layer(int H, int mode, const LayerParams& p, cudaStream_t st) {
+  if (mode == MODE_FWD_SNAKE) return launch_layer2_h<MODE_FWD_SNAKE>(H, p, st);
+  if (mode == MODE_FWD_TANH) return launch_layer2_h<MODE_FWD_TANH>(H, p, st);
+  if (mode == MODE_BWD_SNAKE) return launch_layer2_h<MODE_BWD_SNAKE>(H, p, st);
   if (tc_pair_mode()) {
     switch (H) {
       case 128: return mode == MODE_FWD ? launch_layer2<128, MODE_FWD>(p, st) : launch_layer2<128, MODE_BWD>(p, st);
@@ -375,7 +406,8 @@ bool tc_fused_last_mode() {
 }
 static bool fused_ok(const inr_siren_desc* d) {
   return tc_fused_mode() && tc_pair_mode() && (d->hidden_features == 128 || d->hidden_features == 256) &&
-         d->hidden_layers >= 1 && d->hidden_layers <= FUSED_MAX_L;
+         d->hidden_layers >= 1 && d->hidden_layers <= FUSED_MAX_L && d->num_snake == 0 && d->num_tanh == 0 &&
+         d->first_linear == 0;
 }
 
 template <int H>
@@ -425,6 +457,7 @@ static LayerParams layer_params(int H, const __nv_bfloat16* A, const __nv_bfloat
                                 __nv_bfloat16* out0, __nv_bfloat16* out1, const __nv_bfloat16* Cin, int tiles) {
   LayerParams p;
   p.A = A; p.Bpack = Bp; p.bias = bias; p.omega = omega; p.out0 = out0; p.out1 = out1; p.Cin = Cin; p.num_tiles = tiles;
+  p.avec = nullptr; p.out2 = nullptr;
   p.a_lbo = TILE_ROWS * 16; p.a_sbo = 128;            // K-major, no swizzle: LBO = next 8-feature group, SBO = next 8 rows
   p.b_lbo = (uint32_t)ns_of(H) * 16; p.b_sbo = 128;
   return p;
@@ -459,7 +492,7 @@ struct TcWorkspace {
 
 static int carve(const inr_siren_desc* d, int training, int64_t n, void* ws, int64_t ws_bytes, TcWorkspace* w) {
   const TcPlan pl = plan_of(d, training);
-  const int64_t H = d->hidden_features, L = d->hidden_layers;
+  const int64_t H = d->hidden_features, L = layout_of(d).L;
   uint8_t* base = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(ws) + 255) & ~(uintptr_t)255);
   const int64_t usable = ws_bytes - (base - reinterpret_cast<uint8_t*>(ws));
   w->Wf = reinterpret_cast<__nv_bfloat16*>(base);
@@ -502,17 +535,33 @@ static int first_layer(const inr_siren_desc* d, const float* params, const float
 
 static int last_layer(const inr_siren_desc* d, const float* params, const __nv_bfloat16* SL, __nv_bfloat16* CL,
                       const float* target, const float* extra_g, int64_t rows, int tiles, int loss_kind, float grad_scale,
-                      float* gvec, float* grads, inr_opt_state* opt, float* out, int training, cudaStream_t st) {
+                      float* gvec, float* grads, inr_opt_state* opt, float* out, int training, cudaStream_t st,
+                      __nv_bfloat16* EL = nullptr) {
   SirenLayout lay = layout_of(d);
   const int last = lay.L + 1;
+  // sine layers keep cos(omega z) in C_L (times omega here); Snake / Tanh layers keep the whole derivative
+  const float dfac = lay.kind(lay.L) == ACT_SINE ? d->hidden_omega_0 : 1.f;
   int blocks = std::min(tiles, num_sms() * 8);
   { LaunchScope ls("k_tc_last", st);
     k_tc_last<<<blocks, 128, lay.H * sizeof(float), st>>>(
         SL, CL, params + lay.w_off(last), params + lay.b_off(last), target, extra_g, rows, tiles, lay.H,
-        d->hidden_omega_0, d->hidden_omega_0, d->outermost_linear, loss_kind, grad_scale, gvec,
-        grads ? grads + lay.b_off(last) : nullptr, opt ? &opt->loss_acc[0] : nullptr, out, training); }
+        dfac, d->hidden_omega_0, d->outermost_linear, loss_kind, grad_scale, gvec,
+        grads ? grads + lay.b_off(last) : nullptr, opt ? &opt->loss_acc[0] : nullptr, out, training, training ? EL : nullptr); }
   INR_LAUNCH_CHECK();
   return INR_OK;
+}
+
+// forward of hidden layer l (1..L) by its activation kind: Sout = act(Sin W^T + b), Cout = derivative image,
+// Eout = dy/da image (Snake layers)
+static int fwd_layer_tc(const inr_siren_desc* d, const SirenLayout& lay, const float* params, const TcWorkspace& w, int l,
+                        const __nv_bfloat16* Sin, __nv_bfloat16* Sout, __nv_bfloat16* Cout, __nv_bfloat16* Eout, int tiles,
+                        cudaStream_t st) {
+  const int H = lay.H;
+  const int kind = lay.kind(l);
+  LayerParams p = layer_params(H, Sin, w.Wf + (int64_t)(l - 1) * H * H, params + lay.b_off(l),
+                               kind == ACT_SINE ? d->hidden_omega_0 : 1.f, Sout, Cout, nullptr, tiles);
+  if (kind == ACT_SNAKE) { p.avec = params + lay.a_off(l); p.out2 = Eout; }
+  return tc_layer(H, kind == ACT_SINE ? MODE_FWD : (kind == ACT_SNAKE ? MODE_FWD_SNAKE : MODE_FWD_TANH), p, st);
 }
 
 int siren_tc_forward(const inr_siren_desc* d, const float* params, const float* coords, int64_t n, int64_t i0,
@@ -544,9 +593,7 @@ int siren_tc_forward(const inr_siren_desc* d, const float* params, const float* 
       return rc;
     int cur = 0;
     for (int l = 1; l <= L; ++l) {
-      LayerParams p = layer_params(H, S[cur], w.Wf + (int64_t)(l - 1) * H * H, params + lay.b_off(l), d->hidden_omega_0,
-                                   S[cur ^ 1], nullptr, nullptr, tiles);
-      if ((rc = tc_layer(H, MODE_FWD, p, st))) return rc;
+      if ((rc = fwd_layer_tc(d, lay, params, w, l, S[cur], S[cur ^ 1], nullptr, nullptr, tiles, st))) return rc;
       cur ^= 1;
     }
     if ((rc = last_layer(d, params, S[cur], nullptr, nullptr, nullptr, rows, tiles, 0, 0.f, nullptr, nullptr, nullptr,
@@ -578,6 +625,10 @@ int siren_tc_train(const inr_siren_desc* d, const float* params, const float* co
     const int tiles = (int)(rows_pad / TILE_ROWS);
     auto S = [&](int l) { return w.img + (int64_t)l * w.img_elems; };
     auto C = [&](int l) { return w.img + (int64_t)(L + 1 + l) * w.img_elems; };
+    // dy/da image of Snake layer l (NULL for the other kinds)
+    auto E = [&](int l) -> __nv_bfloat16* {
+      return lay.kind(l) == ACT_SNAKE ? w.img + (int64_t)(2 * (L + 1) + lay.snakes_before(l)) * w.img_elems : nullptr;
+    };
     const float* xc = coords ? coords + r0 * lay.in : nullptr;
     bool fused_tail = false;
     if (phase & 1) {
@@ -594,11 +645,8 @@ int siren_tc_train(const inr_siren_desc* d, const float* params, const float* co
           return rc;
       } else {
       if ((rc = first_layer(d, params, xc, rows, rows_pad, i0 + r0, T_total, scale, S(0), C(0), st))) return rc;
-      for (int l = 1; l <= L; ++l) {
-        LayerParams p = layer_params(H, S(l - 1), w.Wf + (int64_t)(l - 1) * H * H, params + lay.b_off(l), d->hidden_omega_0,
-                                     S(l), C(l), nullptr, tiles);
-        if ((rc = tc_layer(H, MODE_FWD, p, st))) return rc;
-      }
+      for (int l = 1; l <= L; ++l)
+        if ((rc = fwd_layer_tc(d, lay, params, w, l, S(l - 1), S(l), C(l), E(l), tiles, st))) return rc;
       }
       if (phase == 1) {
         if ((rc = last_layer(d, params, S(L), nullptr, nullptr, nullptr, rows, tiles, 0, 0.f, nullptr, nullptr, nullptr,
@@ -609,7 +657,10 @@ int siren_tc_train(const inr_siren_desc* d, const float* params, const float* co
     }
     if (!fused_tail) {
     if ((rc = last_layer(d, params, S(L), C(L), target ? target + r0 : nullptr, extra_gout ? extra_gout + r0 : nullptr, rows,
-                         tiles, loss_kind, grad_scale, w.gvec, grads, opt, out ? out + r0 : nullptr, 1, st)))
+                         tiles, loss_kind, grad_scale, w.gvec, grads, opt, out ? out + r0 : nullptr, 1, st, E(L))))
+      return rc;
+    // Snake layer L: its `a` gradient = column sums of the g w dy/da products k_tc_last left in E(L)
+    if (E(L) && (rc = colsum(E(L), H, tiles, nullptr, nullptr, 1, rows, 0, 1, 1.f, grads + lay.a_off(L), nullptr, 1, 0, st)))
       return rc;
     // last-layer weight gradient: gw_out[f] += sum_r g[r] S_L[r][f]
     if ((rc = colsum(S(L), H, tiles, w.gvec, nullptr, 1, rows, 0, 1, 1.f, nullptr, grads + lay.w_off(L + 1), 1, 1, st)))
@@ -620,9 +671,19 @@ int siren_tc_train(const inr_siren_desc* d, const float* params, const float* co
       dp.dZ = C(l); dp.S = S(l - 1); dp.gW = grads + lay.w_off(l); dp.gb = grads + lay.b_off(l); dp.num_tiles = tiles;
       dp.lbo = 128; dp.sbo = TILE_ROWS * 16;   // MN-major, no swizzle: LBO = next 8 rows (K), SBO = next 8-feature group
       if ((rc = tc_dw(H, dp, st))) return rc;
-      const float om_prev = (l - 1 == 0) ? d->first_omega_0 : d->hidden_omega_0;
+      // dZ_{l-1} = (dZ_l W_l) * d y_{l-1}/d z_{l-1}: sine layers keep cos(omega z) (times omega here), Snake / Tanh the
+      // whole derivative; a Snake layer also takes its `a` gradient from the same product against its dy/da image
+      const int kprev = lay.kind(l - 1);
+      const float om_prev = kprev != ACT_SINE ? 1.f : ((l - 1 == 0) ? d->first_omega_0 : d->hidden_omega_0);
       LayerParams p = layer_params(H, C(l), w.Wb + (int64_t)(l - 1) * H * H, nullptr, om_prev, C(l - 1), nullptr, C(l - 1), tiles);
-      if ((rc = tc_layer(H, MODE_BWD, p, st))) return rc;
+      if (kprev == ACT_SNAKE) {
+        p.out2 = E(l - 1);
+        if ((rc = tc_layer(H, MODE_BWD_SNAKE, p, st))) return rc;
+        if ((rc = colsum(E(l - 1), H, tiles, nullptr, nullptr, 1, rows, 0, 1, 1.f, grads + lay.a_off(l - 1), nullptr, 1, 0, st)))
+          return rc;
+      } else if ((rc = tc_layer(H, MODE_BWD, p, st))) {
+        return rc;
+      }
     }
     // first layer: gW_0[f][i] += sum_r dZ_0[r][f] x[r][i], gb_0 += colsum(dZ_0)
     if ((rc = colsum(C(0), H, tiles, nullptr, xc, lay.in, rows, i0 + r0, T_total, scale, grads + lay.b_off(0),

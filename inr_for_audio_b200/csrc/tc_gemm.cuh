@@ -19,7 +19,14 @@
 namespace inr {
 namespace tc {
 
-enum { MODE_FWD = 0, MODE_BWD = 1 };
+// MODE_FWD / MODE_BWD: SineLayer.  The Snake / Tanh variants (Linear+Snake, Linear+Tanh layers of SirenWithSnakeTanh,
+// models.py:185-241,356-372) exist in the CTA-pair kernel (tc_gemm2.cuh) only:
+//   MODE_FWD_SNAKE : y = z + sin^2(a z)/a -> out0, dy/dz -> out1, dy/da -> out2      (z = acc + b, a = avec[col])
+//   MODE_FWD_TANH  : y = tanh(z) -> out0, 1 - y^2 -> out1
+//   MODE_BWD_SNAKE : dZ_{l-1} = v * Cin (Cin = dy/dz) and, in place over E (= dy/da), the products v * E whose column
+//                    sums are the gradient of `a` (k_tc_colsum afterwards)
+enum { MODE_FWD = 0, MODE_BWD = 1, MODE_FWD_SNAKE = 2, MODE_FWD_TANH = 3, MODE_BWD_SNAKE = 4 };
+__host__ __device__ constexpr bool mode_is_fwd(int m) { return m == MODE_FWD || m == MODE_FWD_SNAKE || m == MODE_FWD_TANH; }
 
 template <int H>
 struct LayerCfg {
@@ -47,6 +54,8 @@ struct LayerParams {
   __nv_bfloat16* out0;         // fwd: S_l;  bwd: dZ_{l-1}
   __nv_bfloat16* out1;         // fwd: C_l or NULL (inference)
   const __nv_bfloat16* Cin;    // bwd: C_{l-1} (may alias out0: read before written, same thread)
+  const float* avec;           // MODE_FWD_SNAKE: the layer's `a` (H floats)
+  __nv_bfloat16* out2;         // MODE_FWD_SNAKE: dy/da image;  MODE_BWD_SNAKE: dy/da image, overwritten with v * dy/da
   int num_tiles;
   uint32_t a_lbo, a_sbo, b_lbo, b_sbo;  // descriptor strides (bytes); passed in so a test can probe the convention
 };

@@ -39,10 +39,12 @@ struct Layer2Cfg {
   static constexpr int TMEM_COLS = 2 * NP;          // two accumulator buffers
   static constexpr int OFF_A = B_BYTES;
   static constexpr int OFF_BIAS = OFF_A + STAGES * A_STAGE_BYTES;
-  static constexpr int OFF_BAR = OFF_BIAS + NP * 4;
+  static constexpr int OFF_AVEC = OFF_BIAS + NP * 4;   // Snake `a` of this N slice (forward)
+  static constexpr int OFF_BAR = OFF_AVEC + NP * 4;
   static constexpr int SMEM_BYTES = OFF_BAR + 256;
   static constexpr int THREADS = 320;
   static_assert(H == 128 || H == 256 || H == 512, "hidden width");
+  static_assert(SMEM_BYTES <= 232448, "shared-memory budget");
 };
 
 template <int H, int MODE>
@@ -55,6 +57,8 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(Layer2Cfg<H>::THREAD
   const uint32_t sB = smem_base;
   const uint32_t sA = smem_base + Cfg::OFF_A;
   float* s_bias = reinterpret_cast<float*>(smem + Cfg::OFF_BIAS);
+  float* s_a = reinterpret_cast<float*>(smem + Cfg::OFF_AVEC);
+  constexpr bool IS_FWD = mode_is_fwd(MODE);
   const uint32_t bar0 = smem_base + Cfg::OFF_BAR;
   auto bar_full = [&](int s) { return bar0 + 8u * s; };
   auto bar_empty = [&](int s) { return bar0 + 8u * (Cfg::STAGES + s); };
@@ -79,8 +83,11 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(Layer2Cfg<H>::THREAD
     mbar_init(bar_bfull, leader ? 2 : 1);
     mbar_fence_init();
   }
-  if (MODE == MODE_FWD) {
-    for (int i = threadIdx.x; i < NP; i += blockDim.x) s_bias[i] = p.omega * p.bias[q * NP + i];
+  if (IS_FWD) {   // sine: omega * b (the argument is omega*acc + omega*b); Snake / Tanh: b
+    for (int i = threadIdx.x; i < NP; i += blockDim.x) s_bias[i] = (MODE == MODE_FWD ? p.omega : 1.f) * p.bias[q * NP + i];
+  }
+  if (MODE == MODE_FWD_SNAKE) {
+    for (int i = threadIdx.x; i < NP; i += blockDim.x) s_a[i] = p.avec[q * NP + i];
   }
   __syncthreads();
   cluster_sync_all();                                 // both CTAs' barriers exist before anything can signal them
@@ -173,7 +180,7 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(Layer2Cfg<H>::THREAD
       const int g0 = (q * NP + (half + 2 * ci) * 32) >> 3;
       return reinterpret_cast<const uint4*>(p.Cin + (size_t)tile * (TILE_ROWS * H) + ((size_t)(g0 + j) * TILE_ROWS + row) * 8);
     };
-    if (MODE == MODE_BWD && 2 * dt0 + (int)rank < p.num_tiles) {
+    if (!IS_FWD && 2 * dt0 + (int)rank < p.num_tiles) {
 #pragma unroll
       for (int ci = 0; ci < NCH; ++ci)
 #pragma unroll
@@ -200,7 +207,39 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(Layer2Cfg<H>::THREAD
           for (int j = 0; j < 4; ++j) {
             uint32_t o0[4], o1[4];
             const size_t off = tile_off + ((size_t)(g0 + j) * TILE_ROWS + row) * 8;
-            if (MODE == MODE_FWD) {
+            if (MODE == MODE_FWD_SNAKE || MODE == MODE_FWD_TANH) {
+              uint32_t o2[4];
+#pragma unroll
+              for (int h = 0; h < 4; ++h) {
+                const int cc = j * 8 + h * 2;
+                float y[2], dz[2], da[2];
+#pragma unroll
+                for (int u = 0; u < 2; ++u) {
+                  const float z = v[cc + u] + s_bias[c * 32 + cc + u];
+                  if (MODE == MODE_FWD_SNAKE) {
+                    const float a = s_a[c * 32 + cc + u], ia = __fdividef(1.0f, a);
+                    float sn, cs;
+                    __sincosf(z * a, &sn, &cs);
+                    const float s2 = sn * sn, sc2 = 2.f * sn * cs;
+                    y[u] = __fmaf_rn(ia, s2, z);
+                    dz[u] = 1.f + sc2;
+                    da[u] = ia * (z * sc2 - ia * s2);
+                  } else {
+                    float th;
+                    asm("tanh.approx.f32 %0, %1;" : "=f"(th) : "f"(z));
+                    y[u] = th;
+                    dz[u] = __fmaf_rn(-th, th, 1.f);
+                    da[u] = 0.f;
+                  }
+                }
+                o0[h] = pack_bf16x2(y[0], y[1]);
+                o1[h] = pack_bf16x2(dz[0], dz[1]);
+                o2[h] = pack_bf16x2(da[0], da[1]);
+              }
+              *reinterpret_cast<uint4*>(p.out0 + off) = make_uint4(o0[0], o0[1], o0[2], o0[3]);
+              if (p.out1) *reinterpret_cast<uint4*>(p.out1 + off) = make_uint4(o1[0], o1[1], o1[2], o1[3]);
+              if (MODE == MODE_FWD_SNAKE && p.out2) *reinterpret_cast<uint4*>(p.out2 + off) = make_uint4(o2[0], o2[1], o2[2], o2[3]);
+            } else if (MODE == MODE_FWD) {
 #pragma unroll
               for (int h = 0; h < 4; ++h) {
                 const int cc = j * 8 + h * 2;
@@ -223,6 +262,17 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(Layer2Cfg<H>::THREAD
                 o0[h] = pack_bf16x2(v[cc] * p.omega * cf.x, v[cc + 1] * p.omega * cf.y);
               }
               *reinterpret_cast<uint4*>(p.out0 + off) = make_uint4(o0[0], o0[1], o0[2], o0[3]);
+              if (MODE == MODE_BWD_SNAKE) {   // v * dy/da in place over the dy/da image (column-summed afterwards)
+                const uint4 eu = *reinterpret_cast<const uint4*>(p.out2 + off);
+                const uint32_t ew[4] = {eu.x, eu.y, eu.z, eu.w};
+#pragma unroll
+                for (int h = 0; h < 4; ++h) {
+                  const int cc = j * 8 + h * 2;
+                  const float2 ef = unpack_bf16x2(ew[h]);
+                  o1[h] = pack_bf16x2(v[cc] * ef.x, v[cc + 1] * ef.y);
+                }
+                *reinterpret_cast<uint4*>(p.out2 + off) = make_uint4(o1[0], o1[1], o1[2], o1[3]);
+              }
               if (next_tile < p.num_tiles) cin[ci][j] = *cin_ptr(next_tile, ci, j);
             }
           }

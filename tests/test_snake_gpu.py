@@ -130,9 +130,52 @@ def test_ragged_sizes_against_oracle(pkg):
         assert np.linalg.norm(grads.cpu().numpy() - go) <= 5e-5 * np.linalg.norm(go) + 1e-12
 
 
-def test_bf16_mode_rejects_snake_stacks(pkg):
+@pytest.mark.parametrize("H,ns,nk,nt,last_lin,n", [(128, 1, 1, 1, True, 4099), (256, 2, 2, 0, True, 20000),
+                                                   (128, 0, 2, 0, True, 1000), (256, 1, 0, 2, False, 3000),
+                                                   (512, 1, 1, 0, True, 2500)])
+def test_bf16_mode_snake_tanh_against_oracle(pkg, H, ns, nk, nt, last_lin, n):
+    """Snake / Tanh hidden layers in the tcgen05 mode (CTA-pair layer kernel, MODE_FWD_SNAKE / MODE_FWD_TANH /
+    MODE_BWD_SNAKE): loss within 1e-3 relative, gradients (incl. the Snake `a` gradients) within bf16 rounding noise
+    of the fp32 oracle."""
+    from oracle import inr_oracle as O
+    ospec = O.SirenSpec(1, H, ns, 1, last_lin, 30.0, 30.0, num_snake=nk, num_tanh=nt, a_initial=0.5)
+    spec = pkg.SirenSpec(1, H, ns, 1, last_lin, 30.0, 30.0, nk, nt, False)
+    ps = O.siren_init(ospec, seed=H + ns)
+    flat = torch.cat([p.reshape(-1) for p in ps])
+    gt = torch.from_numpy(pkg.utils.synth_waveform(max(n, 2), seed=3)[:n].copy())
+    coords = O.get_coord(n, 1).view(-1, 1)
+    loss_o, _, grads_o, out_o = O.siren_loss_and_grads(ospec, ps, coords, gt.view(-1, 1))
+    f = pkg.SirenFitter(spec, flat, gt.to(dev()), precision="bf16", use_graph=False)
+    loss, grads, out = f.loss_and_grads()
+    assert abs(loss - float(loss_o)) <= 1e-3 * abs(float(loss_o)) + 1e-9, (loss, float(loss_o))
+    assert float(np.abs(out.cpu().numpy() - out_o.numpy().ravel()).max()) <= 3e-2
+    go = torch.cat([x.reshape(-1) for x in grads_o]).numpy().astype(np.float64)
+    gn = grads.cpu().numpy().astype(np.float64)
+    gerr = np.linalg.norm(gn - go) / np.linalg.norm(go)
+    # the `a` gradients alone
+    offs = np.cumsum([0] + spec.param_sizes())
+    kinds = spec.layer_kinds()
+    aerr, pi = 0.0, 0
+    for k in kinds + [None]:
+        pi += 2
+        if k == "snake":
+            ga, gr = gn[offs[pi]:offs[pi + 1]], go[offs[pi]:offs[pi + 1]]
+            aerr = max(aerr, float(np.linalg.norm(ga - gr) / (np.linalg.norm(gr) + 1e-30)))
+            pi += 1
+    print("bf16 snake/tanh H=%d %d/%d/%d n=%d: loss rel err %.2e, grad rel err %.2e, a-grad rel err %.2e" % (
+        H, ns, nk, nt, n, abs(loss - float(loss_o)) / float(loss_o), gerr, aerr))
+    assert gerr <= 5e-2 and aerr <= 5e-2
+    f2 = pkg.SirenFitter(spec, flat, gt.to(dev()), precision="bf16")
+    f2.step(5)
+    ls = f2.losses()
+    assert np.all(np.isfinite(ls)) and ls.min() < 2 * ls[0]      # full-batch Adam at lr 1e-3 is not monotone
+    np.testing.assert_allclose(f2.forward().cpu().numpy(), f2.forward().cpu().numpy())
+
+
+def test_bf16_mode_rejects_first_linear(pkg):
+    """a Linear+Snake FIRST layer (first_linear=True) exists in the fp32 mode only"""
     from inr_for_audio_b200 import _lib as L
-    spec = pkg.SirenSpec(1, 128, 1, 1, True, 30.0, 30.0, 1, 0, False)
+    spec = pkg.SirenSpec(1, 128, 1, 1, True, 30.0, 30.0, 1, 0, True)
     with pytest.raises(L.InrLibraryError):
         pkg.SirenFitter(spec, torch.zeros(spec.num_params()), torch.zeros(256, device=dev()), precision="bf16")
 
