@@ -381,7 +381,38 @@ int tc_layer(int H, int mode, const LayerParams& p, cudaStream_t st) {
   return INR_E_UNSUPPORTED;
 }
 
+template <int H>
+static int launch_dw2(const DwParams& p, cudaStream_t st) {
+  using Cfg = Dw2Cfg<H>;
+  static bool attr_set = false;
+  if (!attr_set) {
+    INR_CUDA_CHECK(cudaFuncSetAttribute(k_tc_dw2<H>, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg::SMEM_BYTES));
+    attr_set = true;
+  }
+  int pairs = (num_sms() / 2) / Cfg::NBLOCKS * Cfg::NBLOCKS;
+  const int max_useful = (int)std::min<int64_t>((int64_t)p.num_tiles * Cfg::NBLOCKS, 1 << 30);
+  if (pairs > max_useful) pairs = max_useful;
+  { LaunchScope ls("k_tc_dw", st);
+    k_tc_dw2<H><<<2 * pairs, Cfg::THREADS, Cfg::SMEM_BYTES, st>>>(p); }
+  INR_LAUNCH_CHECK();
+  return INR_OK;
+}
+
+// INR_TC_DW_PAIR=1 selects the CTA-pair dW kernel k_tc_dw2 (H >= 256).  Measured on B200 (profiles/r01c_notes.md): it
+// cuts the L2->SM operand traffic by a third and is parity-green, but the step time does not move (C2 6.99 vs 6.95 ms
+// for the five dW launches, C1 0.223 vs 0.203 ms) -- the fabric was not the limiter -- so the single-CTA kernel of
+// tc_gemm.cuh stays the default.
+static bool tc_dw_pair_mode() {
+  static int v = -1;
+  if (v < 0) { const char* e = getenv("INR_TC_DW_PAIR"); v = (e && e[0] == '1') ? 1 : 0; }
+  return v != 0;
+}
+
 int tc_dw(int H, const DwParams& p, cudaStream_t st) {
+  if (tc_dw_pair_mode() && tc_pair_mode()) {
+    if (H == 256) return launch_dw2<256>(p, st);
+    if (H == 512) return launch_dw2<512>(p, st);
+  }
   switch (H) {
     case 128: return launch_dw<128>(p, st);
     case 256: return launch_dw<256>(p, st);

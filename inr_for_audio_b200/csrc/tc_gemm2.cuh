@@ -295,5 +295,163 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(Layer2Cfg<H>::THREAD
   }
 }
 
+// ------------------------------------------------------------------------------------------------------------
+// k_tc_dw2<H> -- CTA-pair version of k_tc_dw (tc_gemm.cuh) for H >= 256.
+//
+// Why (profiles/r01b_ncu_full_summary.md): the single-CTA dW kernel moves 96 KB of operands per 128x256x128 MMA
+// block through the L2->SM fabric -- 16.3 GB per launch at H = 512, i.e. 13.5 TB/s, the fabric ceiling -- while DRAM
+// (55 %) and the tensor pipe (69 %) idle.  A pair runs ONE M = 256 MMA per K step: each CTA stages its own 128
+// out-features of dZ (32 KB) and only HALF of the S block's in-features (32 KB), and receives its own 128 x NB block of
+// dW in its own TMEM: 64 KB per CTA per row tile instead of 96 KB, 3 ring stages instead of 2.
+//
+//   grid = 2 * pairs; pair g handles block (mp, nb) = g % (MPAIRS*NBLK) of row tiles g / (MPAIRS*NBLK), + stride, ...
+//   CTA rank r of the pair owns out-feature block mb = 2*mp + r.
+// Barriers: full[s] leader 2 (own producer tx + peer relay) / peer 1; empty[s] 1 (multicast commit); tfull 1 (multicast).
+template <int H>
+struct Dw2Cfg {
+  static constexpr int NB = 256;                       // in-feature block (MMA N)
+  static constexpr int MPAIRS = H / 256;               // out-feature blocks of 256 (MMA M over the pair)
+  static constexpr int NBLK = H / NB;
+  static constexpr int NBLOCKS = MPAIRS * NBLK;        // pair-blocks per row tile
+  static constexpr int A_BYTES = 128 * TILE_ROWS * 2;  // own 16 feature groups of dZ: 32 KB
+  static constexpr int B_BYTES = (NB / 2) * TILE_ROWS * 2;   // own half of the S block: 32 KB
+  static constexpr int STAGE_BYTES = A_BYTES + B_BYTES;
+  static constexpr int STAGES = 3;
+  static constexpr int TMEM_COLS = 2 * NB;             // [0,NB) dW block, [NB,NB+16) bias column sums
+  static constexpr int OFF_ONES = STAGES * STAGE_BYTES;
+  static constexpr int OFF_BAR = OFF_ONES + 512;
+  static constexpr int SMEM_BYTES = OFF_BAR + 128;
+  static constexpr int THREADS = 192;                  // producer, MMA / relay, 4 epilogue warps
+  static_assert(H == 256 || H == 512, "pair dW kernel: hidden width 256 or 512");
+};
+
+template <int H>
+__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(Dw2Cfg<H>::THREADS, 1) k_tc_dw2(const DwParams p) {
+  using Cfg = Dw2Cfg<H>;
+  extern __shared__ __align__(128) uint8_t smem[];
+  const uint32_t smem_base = smem_u32(smem);
+  const uint32_t bar0 = smem_base + Cfg::OFF_BAR;
+  auto bar_full = [&](int s) { return bar0 + 8u * s; };
+  auto bar_empty = [&](int s) { return bar0 + 8u * (Cfg::STAGES + s); };
+  const uint32_t bar_tfull = bar0 + 8u * (2 * Cfg::STAGES);
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(smem + Cfg::OFF_BAR + 8 * (2 * Cfg::STAGES + 1));
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const uint32_t rank = cluster_ctarank();
+  const bool leader = rank == 0;
+  const int pair = blockIdx.x >> 1;
+  const int npairs = gridDim.x >> 1;
+  const int blk = pair % Cfg::NBLOCKS;
+  const int mp = blk / Cfg::NBLK, nb = blk % Cfg::NBLK;
+  const int mb = 2 * mp + (int)rank;                   // this CTA's 128 out-features
+  const int tile0 = pair / Cfg::NBLOCKS;
+  const int tile_stride = npairs / Cfg::NBLOCKS;
+  const bool has_work = tile0 < p.num_tiles;
+  const bool do_bias = (p.gb != nullptr);
+
+  if (threadIdx.x == 0) {
+    for (int s = 0; s < Cfg::STAGES; ++s) { mbar_init(bar_full(s), leader ? 2 : 1); mbar_init(bar_empty(s), 1); }
+    mbar_init(bar_tfull, 1);
+    mbar_fence_init();
+  }
+  for (int i = threadIdx.x; i < 128; i += blockDim.x) reinterpret_cast<uint32_t*>(smem + Cfg::OFF_ONES)[i] = 0x3F803F80u;
+  fence_proxy_async_smem();
+  __syncthreads();
+  cluster_sync_all();
+  if (warp == 1) {
+    tmem_alloc2(smem_u32(tmem_slot), Cfg::TMEM_COLS);
+    tmem_relinquish2();
+  }
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot;
+
+  if (warp == 0) {
+    if (lane == 0) {
+      int s = 0;
+      uint32_t phase = 0;
+      for (int tile = tile0; tile < p.num_tiles; tile += tile_stride) {
+        const uint8_t* a_src = reinterpret_cast<const uint8_t*>(p.dZ) + (size_t)tile * (TILE_ROWS * H * 2) +
+                               (size_t)(mb * 16) * (TILE_ROWS * 16);
+        const uint8_t* b_src = reinterpret_cast<const uint8_t*>(p.S) + (size_t)tile * (TILE_ROWS * H * 2) +
+                               (size_t)(nb * (Cfg::NB / 8) + (int)rank * (Cfg::NB / 16)) * (TILE_ROWS * 16);
+        mbar_wait(bar_empty(s), phase ^ 1);
+        mbar_arrive_expect_tx(bar_full(s), Cfg::STAGE_BYTES);
+        const uint32_t dst = smem_base + s * Cfg::STAGE_BYTES;
+        bulk_g2s(dst, a_src, Cfg::A_BYTES, bar_full(s));
+        bulk_g2s(dst + Cfg::A_BYTES, b_src, Cfg::B_BYTES, bar_full(s));
+        if (++s == Cfg::STAGES) { s = 0; phase ^= 1; }
+      }
+    }
+  } else if (warp == 1) {
+    if (lane == 0 && has_work) {
+      if (leader) {
+        constexpr uint32_t idesc = make_idesc_bf16(256, Cfg::NB, 1, 1);   // both operands MN-major
+        int s = 0;
+        uint32_t phase = 0;
+        int it = 0;
+        for (int tile = tile0; tile < p.num_tiles; tile += tile_stride, ++it) {
+          mbar_wait(bar_full(s), phase);
+          tc_fence_after();
+          const uint32_t a0 = smem_base + s * Cfg::STAGE_BYTES;
+          const uint32_t b0 = a0 + Cfg::A_BYTES;
+#pragma unroll
+          for (int kk = 0; kk < TILE_ROWS / 16; ++kk) {   // K = 16 rows per MMA
+            const uint64_t ad = make_smem_desc(a0 + kk * 256, p.lbo, p.sbo);
+            const uint64_t bd = make_smem_desc(b0 + kk * 256, p.lbo, p.sbo);
+            umma2_bf16(tmem_base, ad, bd, idesc, (it | kk) != 0 ? 1u : 0u);
+          }
+          if (do_bias && (it % Cfg::NBLK) == nb) {   // gb = dZ^T 1: N = 16 ones-MMA (8 ones columns from each CTA)
+            constexpr uint32_t idesc1 = make_idesc_bf16(256, 16, 1, 1);
+            const uint64_t od = make_smem_desc(smem_base + Cfg::OFF_ONES, 128, 256);
+#pragma unroll
+            for (int kk = 0; kk < TILE_ROWS / 16; ++kk)
+              umma2_bf16(tmem_base + Cfg::NB, make_smem_desc(a0 + kk * 256, p.lbo, p.sbo), od, idesc1,
+                         (it >= Cfg::NBLK || kk != 0) ? 1u : 0u);
+          }
+          umma2_commit_mc(bar_empty(s), 3);
+          if (++s == Cfg::STAGES) { s = 0; phase ^= 1; }
+        }
+        umma2_commit_mc(bar_tfull, 3);
+      } else {
+        int s = 0;
+        uint32_t phase = 0;
+        for (int tile = tile0; tile < p.num_tiles; tile += tile_stride) {
+          mbar_wait(bar_full(s), phase);
+          mbar_arrive_remote(bar_full(s), 0);
+          if (++s == Cfg::STAGES) { s = 0; phase ^= 1; }
+        }
+      }
+    }
+  } else if (has_work) {
+    const int quad = warp & 3;
+    const int row = quad * 32 + lane;                 // out-feature index inside this CTA's M block
+    mbar_wait(bar_tfull, 0);
+    tc_fence_after();
+    float* grow = p.gW + (size_t)(mb * 128 + row) * H + nb * Cfg::NB;
+    for (int c = 0; c < Cfg::NB / 32; ++c) {
+      float v[32];
+      tmem_ld32(tmem_base + c * 32 + ((uint32_t)(quad * 32) << 16), v);
+      tmem_ld_wait();
+#pragma unroll
+      for (int j = 0; j < 8; ++j) red_add_v4(grow + c * 32 + j * 4, v[4 * j], v[4 * j + 1], v[4 * j + 2], v[4 * j + 3]);
+    }
+    if (do_bias && (p.num_tiles - tile0 + tile_stride - 1) / tile_stride > nb) {   // this pair issued at least one bias MMA
+      float v[32];
+      tmem_ld32(tmem_base + Cfg::NB + ((uint32_t)(quad * 32) << 16), v);   // columns 0..15 all hold the column sum
+      tmem_ld_wait();
+      atomicAdd(p.gb + mb * 128 + row, v[0]);
+    }
+  }
+  tc_fence_before();
+  __syncthreads();
+  cluster_sync_all();
+  if (warp == 1) {
+    tc_fence_after();
+    tmem_dealloc2(tmem_base, Cfg::TMEM_COLS);
+  }
+}
+
 }  // namespace tc
 }  // namespace inr
