@@ -59,7 +59,8 @@ def parse_args():
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--workload", default=os.environ.get("INR_BENCH_WORKLOAD", "c2"), choices=sorted(WORKLOADS))
-    ap.add_argument("--streams", type=int, default=4, help="clip-parallel: concurrent streams per GPU")
+    ap.add_argument("--streams", type=int, default=8, help="clip-parallel: concurrent streams per GPU")
+    ap.add_argument("--no-sm-partition", action="store_true", help="clip-parallel: every kernel sized for the whole GPU")
     ap.add_argument("--precision", default=os.environ.get("INR_BENCH_PRECISION", "auto"))
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--cpu-budget-s", type=float, default=20.0)
@@ -258,7 +259,7 @@ class Job:
         P, wl = self.P, self.wl
         if self.kind == "clips":
             return P.ClipBatchFitter(self.spec, self.flat0, self.target, precision=self.prec, n_streams=self.args.streams,
-                                     use_graph=use_graph, hist_cap=256)
+                                     use_graph=use_graph, hist_cap=256, sm_partition=not self.args.no_sm_partition)
         kw = dict(i0=self.i0, T_total=wl["T"], process_group=self.pg, use_graph=use_graph, hist_cap=4096)
         if self.kind == "kan":
             return P.KanFitter(self.spec, self.model.flat_parameters(), self.model.flat_grids(), self.target, None,

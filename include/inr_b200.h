@@ -89,6 +89,12 @@ int inr_version(void);
  * by CUDA events on its stream; inr_profile_end synchronises the device and writes "tag,launches,total_ms\n"
  * lines into buf (returns the full length).  Not usable during CUDA-graph capture. */
 int64_t inr_launch_count(void);
+
+/* Grid-size limit for the persistent kernels: launches enqueued after this call occupy at most n_sms SMs (rounded down
+ * to an even number, at least 8; 0 = all SMs).  Used by the clip-parallel batch fitter (BASELINE.json config 5: many independent
+ * clips, engine.ClipBatchFitter) so that the per-clip steps it enqueues on several streams run concurrently on disjoint
+ * SMs.  Process-global; returns the limit in effect (0 = none). */
+int inr_set_sm_limit(int n_sms);
 int inr_profile_begin(void);
 int64_t inr_profile_end(char* buf, int64_t cap);
 

@@ -52,6 +52,7 @@ SIGNATURES = {
     "inr_last_error": (C.c_char_p, []),
     "inr_version": (_i, []),
     "inr_launch_count": (_i64, []),
+    "inr_set_sm_limit": (_i, [_i]),
     "inr_profile_begin": (_i, []),
     "inr_profile_end": (_i64, [C.c_char_p, _i64]),
     "inr_siren_num_params": (_i64, [C.POINTER(SirenDesc)]),

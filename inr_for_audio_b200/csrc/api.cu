@@ -22,7 +22,13 @@ void set_error(const char* fmt, ...) {
   va_end(ap);
 }
 
+// inr_set_sm_limit: the persistent kernels size their grids from num_sms(); a limit below the device's SM count makes
+// every launch occupy only that many SMs, so that independent fits enqueued on different streams (clip-parallel mode)
+// run side by side on disjoint SMs instead of one after the other with one short tile loop per CTA.
+static int g_sm_limit = 0;
+
 int num_sms() {
+  if (g_sm_limit > 0) return g_sm_limit;
   static int n = 0;
   if (n == 0) {
     int dev = 0, v = 0;
@@ -106,6 +112,14 @@ const char* inr_last_error(void) { return g_err; }
 int inr_version(void) { return 100; }
 
 int64_t inr_launch_count(void) { return g_launches.load(); }
+
+int inr_set_sm_limit(int n_sms) {
+  INR_REQUIRE(n_sms >= 0, INR_E_BADARG, "sm limit must be >= 0 (0 = all SMs)");
+  int dev = 0, v = 148;
+  if (cudaGetDevice(&dev) == cudaSuccess) cudaDeviceGetAttribute(&v, cudaDevAttrMultiProcessorCount, dev);
+  g_sm_limit = (n_sms == 0 || n_sms >= v) ? 0 : std::max(8, n_sms / 2 * 2);   // whole CTA pairs; the launchers round further
+  return g_sm_limit;
+}
 
 int inr_profile_begin(void) {
   std::lock_guard<std::mutex> lk(g_prof_mu);

@@ -366,10 +366,14 @@ class ClipBatchFitter:
     """
 
     def __init__(self, spec: SirenSpec, params0: torch.Tensor, targets: torch.Tensor, *, precision: str = "fp32",
-                 loss_mode: str = "mse", lr: float = 1e-3, min_lr: float = 1e-6, n_streams: int = 4,
-                 hist_cap: int = 4096, use_graph: bool = True):
+                 loss_mode: str = "mse", lr: float = 1e-3, min_lr: float = 1e-6, n_streams: int = 8,
+                 hist_cap: int = 4096, use_graph: bool = True, sm_partition: bool = True):
         _require_cuda(targets, "targets")
         assert targets.dim() == 2 and params0.dim() == 2 and params0.shape[0] == targets.shape[0]
+        # sm_partition: every stream's kernels are sized for 1/n_streams of the SMs (inr_set_sm_limit), so the streams'
+        # clips run side by side on disjoint SMs (longer tile loops per CTA, launch gaps overlapped) instead of
+        # time-slicing the whole GPU with one short persistent kernel after the other
+        self.sm_partition = bool(sm_partition)
         self.K, self.T = targets.shape
         self.device = targets.device
         self.spec = spec
@@ -393,10 +397,16 @@ class ClipBatchFitter:
     def _enqueue_batch_step(self, main: torch.cuda.Stream):
         for s in self.streams:
             s.wait_stream(main)
-        for si, s in enumerate(self.streams):
-            with torch.cuda.stream(s):
-                for k in range(si, self.K, self.n_streams):
-                    self.fitters[k]._enqueue_step()
+        if self.sm_partition and self.n_streams > 1:
+            sms = torch.cuda.get_device_properties(self.device).multi_processor_count
+            L.check(L.lib().inr_set_sm_limit(max(8, sms // self.n_streams)))
+        try:
+            for si, s in enumerate(self.streams):
+                with torch.cuda.stream(s):
+                    for k in range(si, self.K, self.n_streams):
+                        self.fitters[k]._enqueue_step()
+        finally:
+            L.check(L.lib().inr_set_sm_limit(0))
         for s in self.streams:
             main.wait_stream(s)
 
