@@ -441,6 +441,34 @@ static bool fused_ok(const inr_siren_desc* d) {
          d->first_linear == 0;
 }
 
+// INR_TC_FUSED_BWD=1 selects the fused backward chain k_tc_fused_bwd (H <= 256).  Measured on B200
+// (profiles/r01c_notes.md): parity-identical gradients, 6 instead of 10 HBM units at L = 3, but its 8 epilogue warps
+// fetch the C_l stash with per-thread loads and reach only 3.2 TB/s: C1 0.254 ms against 0.204 + 0.040 ms for the three
+// layer-major BWD launches + the first-layer column sums, C3 1.20 against 1.05 ms.  Default off until the epilogue is
+// widened.
+bool tc_fused_bwd_mode() {
+  static int v = -1;
+  if (v < 0) { const char* e = getenv("INR_TC_FUSED_BWD"); v = (e && e[0] == '1') ? 1 : 0; }
+  return v != 0;
+}
+
+template <int H>
+static int launch_fused_bwd(const FusedBwdParams& p, cudaStream_t st) {
+  using Cfg = FusedCfg<H>;
+  static bool attr_set = false;
+  if (!attr_set) {
+    INR_CUDA_CHECK(cudaFuncSetAttribute(k_tc_fused_bwd<H>, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg::SMEM_BYTES));
+    attr_set = true;
+  }
+  int pairs = num_sms() / 2;
+  const int num_dt = (p.num_tiles + 1) / 2;
+  if (pairs > num_dt) pairs = num_dt;
+  { LaunchScope ls("k_tc_fused_bwd", st);
+    k_tc_fused_bwd<H><<<2 * pairs, Cfg::THREADS, Cfg::SMEM_BYTES, st>>>(p); }
+  INR_LAUNCH_CHECK();
+  return INR_OK;
+}
+
 template <int H>
 static int launch_fused(const FusedParams& p, cudaStream_t st) {
   using Cfg = FusedCfg<H>;
@@ -697,11 +725,24 @@ int siren_tc_train(const inr_siren_desc* d, const float* params, const float* co
     if ((rc = colsum(S(L), H, tiles, w.gvec, nullptr, 1, rows, 0, 1, 1.f, nullptr, grads + lay.w_off(L + 1), 1, 1, st)))
       return rc;
     }
+    const bool fused_bwd = fused_ok(d) && tc_fused_bwd_mode();
+    if (fused_bwd) {
+      // the whole chain dZ_L -> dZ_0 in one kernel: dZ_{L-1}..dZ_1 land in place over C_{L-1}..C_1 for the dW launches
+      // below, dZ_0 never leaves the SM (the first-layer gradients are reduced there)
+      FusedBwdParams bp;
+      bp.Wb = w.Wb; bp.dZL = C(L);
+      for (int l = 0; l < FUSED_MAX_L; ++l) bp.C[l] = l < L ? C(l) : nullptr;
+      bp.coords = xc; bp.gW0 = grads + lay.w_off(0); bp.gb0 = grads + lay.b_off(0);
+      bp.in = lay.in; bp.L = L; bp.num_tiles = tiles; bp.rows = rows; bp.g0 = i0 + r0; bp.T_total = T_total;
+      bp.scale = scale; bp.omega0 = d->first_omega_0; bp.omega_h = d->hidden_omega_0;
+      if ((rc = (H == 256 ? launch_fused_bwd<256>(bp, st) : launch_fused_bwd<128>(bp, st)))) return rc;
+    }
     for (int l = L; l >= 1; --l) {
       DwParams dp;
       dp.dZ = C(l); dp.S = S(l - 1); dp.gW = grads + lay.w_off(l); dp.gb = grads + lay.b_off(l); dp.num_tiles = tiles;
       dp.lbo = 128; dp.sbo = TILE_ROWS * 16;   // MN-major, no swizzle: LBO = next 8 rows (K), SBO = next 8-feature group
       if ((rc = tc_dw(H, dp, st))) return rc;
+      if (fused_bwd) continue;
       // dZ_{l-1} = (dZ_l W_l) * d y_{l-1}/d z_{l-1}: sine layers keep cos(omega z) (times omega here), Snake / Tanh the
       // whole derivative; a Snake layer also takes its `a` gradient from the same product against its dy/da image
       const int kprev = lay.kind(l - 1);
@@ -717,7 +758,7 @@ int siren_tc_train(const inr_siren_desc* d, const float* params, const float* co
       }
     }
     // first layer: gW_0[f][i] += sum_r dZ_0[r][f] x[r][i], gb_0 += colsum(dZ_0)
-    if ((rc = colsum(C(0), H, tiles, nullptr, xc, lay.in, rows, i0 + r0, T_total, scale, grads + lay.b_off(0),
+    if (!fused_bwd && (rc = colsum(C(0), H, tiles, nullptr, xc, lay.in, rows, i0 + r0, T_total, scale, grads + lay.b_off(0),
                      grads + lay.w_off(0), lay.in, lay.in, st)))
       return rc;
   }
