@@ -452,36 +452,44 @@ bool tc_fused_bwd_mode() {
   return v != 0;
 }
 
-template <int H>
+// INR_TC_FUSED_EW=8 runs the fused kernels with 8 epilogue warps (320 threads, the first version); the default is 16
+// (576 threads, <= 112 registers): four warps per scheduler hide the MUFU / TMEM / global-load latency of the epilogue.
+static int tc_fused_ew() {
+  static int v = -1;
+  if (v < 0) { const char* e = getenv("INR_TC_FUSED_EW"); v = (e && e[0] == '8') ? 8 : 16; }
+  return v;
+}
+
+template <int H, int EW>
 static int launch_fused_bwd(const FusedBwdParams& p, cudaStream_t st) {
   using Cfg = FusedCfg<H>;
   static bool attr_set = false;
   if (!attr_set) {
-    INR_CUDA_CHECK(cudaFuncSetAttribute(k_tc_fused_bwd<H>, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg::SMEM_BYTES));
+    INR_CUDA_CHECK(cudaFuncSetAttribute(k_tc_fused_bwd<H, EW>, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg::SMEM_BYTES));
     attr_set = true;
   }
   int pairs = num_sms() / 2;
   const int num_dt = (p.num_tiles + 1) / 2;
   if (pairs > num_dt) pairs = num_dt;
   { LaunchScope ls("k_tc_fused_bwd", st);
-    k_tc_fused_bwd<H><<<2 * pairs, Cfg::THREADS, Cfg::SMEM_BYTES, st>>>(p); }
+    k_tc_fused_bwd<H, EW><<<2 * pairs, 64 + 32 * EW, Cfg::SMEM_BYTES, st>>>(p); }
   INR_LAUNCH_CHECK();
   return INR_OK;
 }
 
-template <int H>
+template <int H, int EW>
 static int launch_fused(const FusedParams& p, cudaStream_t st) {
   using Cfg = FusedCfg<H>;
   static bool attr_set = false;
   if (!attr_set) {
-    INR_CUDA_CHECK(cudaFuncSetAttribute(k_tc_fused_fwd<H>, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg::SMEM_BYTES));
+    INR_CUDA_CHECK(cudaFuncSetAttribute(k_tc_fused_fwd<H, EW>, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg::SMEM_BYTES));
     attr_set = true;
   }
   int pairs = num_sms() / 2;
   const int num_dt = (p.num_tiles + 1) / 2;
   if (pairs > num_dt) pairs = num_dt;
   { LaunchScope ls("k_tc_fused_fwd", st);
-    k_tc_fused_fwd<H><<<2 * pairs, Cfg::THREADS, Cfg::SMEM_BYTES, st>>>(p); }
+    k_tc_fused_fwd<H, EW><<<2 * pairs, 64 + 32 * EW, Cfg::SMEM_BYTES, st>>>(p); }
   INR_LAUNCH_CHECK();
   return INR_OK;
 }
@@ -509,7 +517,8 @@ static int fused_forward(const inr_siren_desc* d, const float* params, const __n
   p.target = fl ? fl->target : nullptr; p.extra_g = fl ? fl->extra_g : nullptr; p.out = fl ? fl->out : nullptr;
   p.g_wlast = fl ? fl->grads + lay.w_off(lay.L + 1) : nullptr; p.g_blast = fl ? fl->grads + lay.b_off(lay.L + 1) : nullptr;
   p.loss_acc = fl ? fl->loss_acc : nullptr;
-  return lay.H == 256 ? launch_fused<256>(p, st) : launch_fused<128>(p, st);
+  if (tc_fused_ew() == 8) return lay.H == 256 ? launch_fused<256, 8>(p, st) : launch_fused<128, 8>(p, st);
+  return lay.H == 256 ? launch_fused<256, 16>(p, st) : launch_fused<128, 16>(p, st);
 }
 
 static LayerParams layer_params(int H, const __nv_bfloat16* A, const __nv_bfloat16* Bp, const float* bias, float omega,
@@ -735,7 +744,9 @@ int siren_tc_train(const inr_siren_desc* d, const float* params, const float* co
       bp.coords = xc; bp.gW0 = grads + lay.w_off(0); bp.gb0 = grads + lay.b_off(0);
       bp.in = lay.in; bp.L = L; bp.num_tiles = tiles; bp.rows = rows; bp.g0 = i0 + r0; bp.T_total = T_total;
       bp.scale = scale; bp.omega0 = d->first_omega_0; bp.omega_h = d->hidden_omega_0;
-      if ((rc = (H == 256 ? launch_fused_bwd<256>(bp, st) : launch_fused_bwd<128>(bp, st)))) return rc;
+      if (tc_fused_ew() == 8) rc = H == 256 ? launch_fused_bwd<256, 8>(bp, st) : launch_fused_bwd<128, 8>(bp, st);
+      else rc = H == 256 ? launch_fused_bwd<256, 16>(bp, st) : launch_fused_bwd<128, 16>(bp, st);
+      if (rc) return rc;
     }
     for (int l = L; l >= 1; --l) {
       DwParams dp;

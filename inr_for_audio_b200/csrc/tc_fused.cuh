@@ -63,11 +63,10 @@ struct FusedCfg {
   static constexpr int OFF_W0 = OFF_BIAS + FUSED_MAX_L * H * 4;     // first-layer weight (H x in, in <= 2)
   static constexpr int OFF_B0 = OFF_W0 + 2 * H * 4;
   static constexpr int OFF_WL = OFF_B0 + H * 4;                     // last nn.Linear weight (H floats)
-  static constexpr int OFF_DOT = OFF_WL + H * 4;                    // partial output dots [job parity][half][128 rows]
-  static constexpr int OFF_G = OFF_DOT + 2 * 2 * TILE_ROWS * 4;     // d loss / d out per row of the current tile
+  static constexpr int OFF_DOT = OFF_WL + H * 4;                    // partial output dots [job parity][column part <= 4][128 rows]
+  static constexpr int OFF_G = OFF_DOT + 2 * 4 * TILE_ROWS * 4;     // d loss / d out per row of the current tile
   static constexpr int OFF_BAR = OFF_G + TILE_ROWS * 4;
   static constexpr int SMEM_BYTES = OFF_BAR + 256;
-  static constexpr int THREADS = 320;
   static_assert(H == 128 || H == 256, "fused forward: hidden width 128 or 256");
   static_assert(SMEM_BYTES <= 232448, "shared-memory budget");
 };
@@ -99,8 +98,9 @@ struct FusedParams {
   double* loss_acc;            // += sum (out - target)^2 or |out - target|
 };
 
-template <int H>
-__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(FusedCfg<H>::THREADS, 1) k_tc_fused_fwd(const FusedParams p) {
+// EW = number of epilogue warps (8 or 16): warp%4 picks the TMEM lane quadrant, (warp-2)/4 the column part.
+template <int H, int EW>
+__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(64 + 32 * EW, 1) k_tc_fused_fwd(const FusedParams p) {
   using Cfg = FusedCfg<H>;
   constexpr int NP = Cfg::NP;
   constexpr int NC = Cfg::NC;
@@ -133,7 +133,7 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(FusedCfg<H>::THREADS
 
   if (threadIdx.x == 0) {
     for (int s = 0; s < Cfg::STAGES; ++s) { mbar_init(bar_wfull(s), leader ? 2 : 1); mbar_init(bar_wempty(s), 1); }
-    for (int b = 0; b < 2; ++b) { mbar_init(bar_tfull(b), 1); mbar_init(bar_aready(b), 16); }
+    for (int b = 0; b < 2; ++b) { mbar_init(bar_tfull(b), 1); mbar_init(bar_aready(b), 2 * EW); }
     mbar_fence_init();
   }
   for (int l = 0; l < L; ++l)
@@ -225,7 +225,8 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(FusedCfg<H>::THREADS
     const int quad = warp & 3;
     const int half = e >> 2;
     const int row = quad * 32 + lane;
-    constexpr int NCH = NP / 64;                          // 32-column chunks per warp
+    constexpr int NPART = EW / 4;                         // column parts (warps per TMEM lane quadrant)
+    constexpr int NCH = NP / (32 * NPART);                // 32-column chunks per warp
     uint8_t* smem_gen = smem;                             // generic-proxy view of the slot images
 
     auto signal_ready = [&](int b) {
@@ -254,7 +255,7 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(FusedCfg<H>::THREADS
         uint8_t* img = smem_gen + Cfg::OFF_A + b * Cfg::A_BYTES;
 #pragma unroll 1
         for (int ci = 0; ci < NCH; ++ci) {
-          const int g0 = ((half + 2 * ci) * 32) >> 3;
+          const int g0 = ((half + NPART * ci) * 32) >> 3;
 #pragma unroll
           for (int j = 0; j < 4; ++j) {
             uint32_t so[4], co[4];
@@ -315,7 +316,7 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(FusedCfg<H>::THREADS
             if (valid) {
 #pragma unroll
               for (int ci = 0; ci < NCH; ++ci) {
-                const int c = half + 2 * ci;
+                const int c = half + NPART * ci;
                 const int g0 = (c * 32) >> 3;
                 float v[32];
                 tmem_ld32(tmem_base + b * NP + c * 32 + ((uint32_t)(quad * 32) << 16), v);
@@ -337,10 +338,12 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(FusedCfg<H>::THREADS
                 }
               }
             }
-            float* sd = s_dot + (last_jobs & 1) * (2 * TILE_ROWS);
+            float* sd = s_dot + (last_jobs & 1) * (NPART * TILE_ROWS);
             sd[half * TILE_ROWS + row] = dot;
-            asm volatile("bar.sync 1, 256;" ::: "memory");      // the 8 epilogue warps: both column halves of every row
-            const float o = sd[row] + sd[TILE_ROWS + row] + p.b_last[0];
+            asm volatile("bar.sync 1, %0;" ::"n"(32 * EW) : "memory");      // the 8 epilogue warps: both column halves of every row
+            float o = p.b_last[0];
+#pragma unroll
+            for (int q = NPART - 1; q >= 0; --q) o += sd[q * TILE_ROWS + row];
             ++last_jobs;
             float g = 0.f;
             if (live) {
@@ -363,7 +366,7 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(FusedCfg<H>::THREADS
               const float gw = g * p.omega_h;
 #pragma unroll
               for (int ci = 0; ci < NCH; ++ci) {
-                const int c = half + 2 * ci;
+                const int c = half + NPART * ci;
                 const int g0 = (c * 32) >> 3;
                 float v[32];
                 tmem_ld32(tmem_base + b * NP + c * 32 + ((uint32_t)(quad * 32) << 16), v);
@@ -384,9 +387,9 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(FusedCfg<H>::THREADS
                 }
               }
             }
-            asm volatile("bar.sync 1, 256;" ::: "memory");      // S_L image and s_g complete
+            asm volatile("bar.sync 1, %0;" ::"n"(32 * EW) : "memory");      // S_L image and s_g complete
             if (valid) {
-              constexpr int TPG = 256 / (H / 8);                 // threads per feature group: 8 (H = 256), 16 (H = 128)
+              constexpr int TPG = (32 * EW) / (H / 8);                 // threads per feature group: 8 (H = 256), 16 (H = 128)
               constexpr int RPT = TILE_ROWS / TPG;               // rows per thread
               const int et = threadIdx.x - 64;                   // 0..255 over the epilogue warps
               const int fg = et / TPG, r0 = (et % TPG) * RPT;
@@ -404,7 +407,7 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(FusedCfg<H>::THREADS
               }
             }
             // the image is overwritten by the next gen_first (of ANY warp): all 8 warps leave it first
-            asm volatile("bar.sync 1, 256;" ::: "memory");
+            asm volatile("bar.sync 1, %0;" ::"n"(32 * EW) : "memory");
           } else if (valid) {
             const size_t tile_off = (size_t)tile * (TILE_ROWS * H);
             uint8_t* img = smem_gen + Cfg::OFF_A + b * Cfg::A_BYTES;
@@ -412,7 +415,7 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(FusedCfg<H>::THREADS
             __nv_bfloat16* Cl = p.C[l];
 #pragma unroll
             for (int ci = 0; ci < NCH; ++ci) {
-              const int c = half + 2 * ci;
+              const int c = half + NPART * ci;
               const int g0 = (c * 32) >> 3;
               float v[32];
               tmem_ld32(tmem_base + b * NP + c * 32 + ((uint32_t)(quad * 32) << 16), v);
@@ -447,7 +450,7 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(FusedCfg<H>::THREADS
       }
     }
     if (p.fuse_last) {
-      constexpr int TPG = 256 / (H / 8);
+      constexpr int TPG = (32 * EW) / (H / 8);
       const int et = threadIdx.x - 64;
 #pragma unroll
       for (int i = 0; i < 8; ++i) {
@@ -497,8 +500,8 @@ struct FusedBwdParams {
   float scale, omega0, omega_h;
 };
 
-template <int H>
-__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(FusedCfg<H>::THREADS, 1) k_tc_fused_bwd(const FusedBwdParams p) {
+template <int H, int EW>
+__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(64 + 32 * EW, 1) k_tc_fused_bwd(const FusedBwdParams p) {
   using Cfg = FusedCfg<H>;
   constexpr int NP = Cfg::NP;
   constexpr int NC = Cfg::NC;
@@ -526,7 +529,7 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(FusedCfg<H>::THREADS
 
   if (threadIdx.x == 0) {
     for (int s = 0; s < Cfg::STAGES; ++s) { mbar_init(bar_wfull(s), leader ? 2 : 1); mbar_init(bar_wempty(s), 1); }
-    for (int b = 0; b < 2; ++b) { mbar_init(bar_tfull(b), 1); mbar_init(bar_aready(b), 16); }
+    for (int b = 0; b < 2; ++b) { mbar_init(bar_tfull(b), 1); mbar_init(bar_aready(b), 2 * EW); }
     mbar_fence_init();
   }
   __syncthreads();
@@ -610,8 +613,9 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(FusedCfg<H>::THREADS
     const int quad = warp & 3;
     const int half = e >> 2;
     const int row = quad * 32 + lane;
-    constexpr int NCH = NP / 64;
-    constexpr int TPG = 256 / (H / 8);                  // threads per feature group in the column-sum pass
+    constexpr int NPART = EW / 4;
+    constexpr int NCH = NP / (32 * NPART);
+    constexpr int TPG = (32 * EW) / (H / 8);                  // threads per feature group in the column-sum pass
     constexpr int RPT = TILE_ROWS / TPG;
     const int et = threadIdx.x - 64;
     uint8_t* smem_gen = smem;
@@ -636,14 +640,14 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(FusedCfg<H>::THREADS
         for (int ci = 0; ci < NCH; ++ci)
 #pragma unroll
           for (int j = 0; j < 4; ++j) {
-            const size_t loc = ((size_t)((((half + 2 * ci) * 32) >> 3) + j) * TILE_ROWS + row) * 8;
+            const size_t loc = ((size_t)((((half + NPART * ci) * 32) >> 3) + j) * TILE_ROWS + row) * 8;
             u[ci][j] = *reinterpret_cast<const uint4*>(p.dZL + tile_off + loc);
           }
 #pragma unroll
         for (int ci = 0; ci < NCH; ++ci)
 #pragma unroll
           for (int j = 0; j < 4; ++j) {
-            const size_t loc = ((size_t)((((half + 2 * ci) * 32) >> 3) + j) * TILE_ROWS + row) * 8;
+            const size_t loc = ((size_t)((((half + NPART * ci) * 32) >> 3) + j) * TILE_ROWS + row) * 8;
             *reinterpret_cast<uint4*>(img + loc * 2) = u[ci][j];
           }
       }
@@ -676,7 +680,7 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(FusedCfg<H>::THREADS
             for (int ci = 0; ci < NCH; ++ci)
 #pragma unroll
               for (int j = 0; j < 4; ++j) {
-                const size_t loc = ((size_t)((((half + 2 * ci) * 32) >> 3) + j) * TILE_ROWS + row) * 8;
+                const size_t loc = ((size_t)((((half + NPART * ci) * 32) >> 3) + j) * TILE_ROWS + row) * 8;
                 cin[ci][j] = *reinterpret_cast<const uint4*>(Cp + tile_off + loc);
               }
           }
@@ -685,7 +689,7 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(FusedCfg<H>::THREADS
           if (valid) {
 #pragma unroll
             for (int ci = 0; ci < NCH; ++ci) {
-              const int c = half + 2 * ci;
+              const int c = half + NPART * ci;
               const int g0 = (c * 32) >> 3;
               float v[32];
               tmem_ld32(tmem_base + b * NP + c * 32 + ((uint32_t)(quad * 32) << 16), v);
@@ -725,7 +729,7 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(FusedCfg<H>::THREADS
               s_x[row * 2] = x0;
               s_x[row * 2 + 1] = x1;
             }
-            asm volatile("bar.sync 1, 256;" ::: "memory");
+            asm volatile("bar.sync 1, %0;" ::"n"(32 * EW) : "memory");
             if (valid) {
               const int fg = et / TPG, r0 = (et % TPG) * RPT;
 #pragma unroll 4
@@ -745,7 +749,7 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(FusedCfg<H>::THREADS
                 }
               }
             }
-            asm volatile("bar.sync 1, 256;" ::: "memory");      // the image is free for the slot's next tile
+            asm volatile("bar.sync 1, %0;" ::"n"(32 * EW) : "memory");      // the image is free for the slot's next tile
             if (k + 2 < n_k) load_first(b, k + 2);
           }
         }
