@@ -517,6 +517,7 @@ static int fused_forward(const inr_siren_desc* d, const float* params, const __n
   p.target = fl ? fl->target : nullptr; p.extra_g = fl ? fl->extra_g : nullptr; p.out = fl ? fl->out : nullptr;
   p.g_wlast = fl ? fl->grads + lay.w_off(lay.L + 1) : nullptr; p.g_blast = fl ? fl->grads + lay.b_off(lay.L + 1) : nullptr;
   p.loss_acc = fl ? fl->loss_acc : nullptr;
+  { static int dbg = -1; if (dbg < 0) { const char* e = getenv("INR_TC_FUSED_DBG"); dbg = e ? atoi(e) : 0; } p.dbg = dbg; }
   if (tc_fused_ew() == 8) return lay.H == 256 ? launch_fused<256, 8>(p, st) : launch_fused<128, 8>(p, st);
   return lay.H == 256 ? launch_fused<256, 16>(p, st) : launch_fused<128, 16>(p, st);
 }

@@ -96,6 +96,9 @@ struct FusedParams {
   float* g_wlast;              // gradient of w_last (H), of b_last (1): accumulated with atomics
   float* g_blast;
   double* loss_acc;            // += sum (out - target)^2 or |out - target|
+  // timing ablations (INR_TC_FUSED_DBG bit mask, results are WRONG when set; profiles/r01c_notes.md):
+  // 1 = no stash stores to HBM, 2 = no sin/cos (raw accumulator values), 4 = head: dot + loss only (no dZ_L, no g_w)
+  int dbg;
 };
 
 // EW = number of epilogue warps (8 or 16): warp%4 picks the TMEM lane quadrant, (warp-2)/4 the column part.
@@ -274,8 +277,8 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(64 + 32 * EW, 1) k_t
             }
             const size_t loc = ((size_t)(g0 + j) * TILE_ROWS + row) * 8;   // elements inside the tile image
             *reinterpret_cast<uint4*>(img + loc * 2) = make_uint4(so[0], so[1], so[2], so[3]);
-            if (p.S[0]) *reinterpret_cast<uint4*>(p.S[0] + tile_off + loc) = make_uint4(so[0], so[1], so[2], so[3]);
-            if (p.C[0]) *reinterpret_cast<uint4*>(p.C[0] + tile_off + loc) = make_uint4(co[0], co[1], co[2], co[3]);
+            if (p.S[0] && !(p.dbg & 1)) *reinterpret_cast<uint4*>(p.S[0] + tile_off + loc) = make_uint4(so[0], so[1], so[2], so[3]);
+            if (p.C[0] && !(p.dbg & 1)) *reinterpret_cast<uint4*>(p.C[0] + tile_off + loc) = make_uint4(co[0], co[1], co[2], co[3]);
           }
         }
       }
@@ -362,7 +365,7 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(64 + 32 * EW, 1) k_t
               if (half == 0) gb_local += g;
             }
             if (half == 0) s_g[row] = g;
-            if (valid) {
+            if (valid && !(p.dbg & 4)) {
               const float gw = g * p.omega_h;
 #pragma unroll
               for (int ci = 0; ci < NCH; ++ci) {
@@ -388,7 +391,7 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(64 + 32 * EW, 1) k_t
               }
             }
             asm volatile("bar.sync 1, %0;" ::"n"(32 * EW) : "memory");      // S_L image and s_g complete
-            if (valid) {
+            if (valid && !(p.dbg & 4)) {
               constexpr int TPG = (32 * EW) / (H / 8);                 // threads per feature group: 8 (H = 256), 16 (H = 128)
               constexpr int RPT = TILE_ROWS / TPG;               // rows per thread
               const int et = threadIdx.x - 64;                   // 0..255 over the epilogue warps
@@ -429,15 +432,15 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(64 + 32 * EW, 1) k_t
                   const float t0 = __fmaf_rn(v[cc], p.omega_h, bias_l[c * 32 + cc]);
                   const float t1 = __fmaf_rn(v[cc + 1], p.omega_h, bias_l[c * 32 + cc + 1]);
                   float s0, c0, s1, c1;
-                  __sincosf(t0, &s0, &c0);
-                  __sincosf(t1, &s1, &c1);
+                  if (p.dbg & 2) { s0 = t0; c0 = t0; s1 = t1; c1 = t1; }
+                  else { __sincosf(t0, &s0, &c0); __sincosf(t1, &s1, &c1); }
                   o0[h] = pack_bf16x2(s0, s1);
                   o1[h] = pack_bf16x2(c0, c1);
                 }
                 const size_t loc = ((size_t)(g0 + j) * TILE_ROWS + row) * 8;
                 if (l < L) *reinterpret_cast<uint4*>(img + loc * 2) = make_uint4(o0[0], o0[1], o0[2], o0[3]);
-                if (Sl) *reinterpret_cast<uint4*>(Sl + tile_off + loc) = make_uint4(o0[0], o0[1], o0[2], o0[3]);
-                if (Cl) *reinterpret_cast<uint4*>(Cl + tile_off + loc) = make_uint4(o1[0], o1[1], o1[2], o1[3]);
+                if (Sl && !(p.dbg & 1)) *reinterpret_cast<uint4*>(Sl + tile_off + loc) = make_uint4(o0[0], o0[1], o0[2], o0[3]);
+                if (Cl && !(p.dbg & 1)) *reinterpret_cast<uint4*>(Cl + tile_off + loc) = make_uint4(o1[0], o1[1], o1[2], o1[3]);
               }
             }
           }
