@@ -156,6 +156,10 @@ int inr_siren_train_backward(const inr_siren_desc* d, const float* params, const
  * the transpose, (N/2, F), float64).  N in {256, 512, 1024, 2048, 4096}. */
 int64_t inr_stmdct_num_frames(int64_t T, int N);
 int inr_stmdct_forward(const float* x, int64_t T, int N, const float* window, float* coef, void* stream);
+/* mdct.py:74-113 ISTMDCT(coef, N) on the device: per frame IMDCT (mdct.py:29-35,46-48, factor 2), the same window,
+ * overlap-add at hop N/2, last half frame dropped: out has (N/2) * num_frames samples.  coef is FRAME-major as above
+ * (the reference takes the transpose (N/2, F)).  Deterministic (one writer per output sample). */
+int inr_istmdct(const float* coef, int64_t num_frames, int N, const float* window, float* out, void* stream);
 /* MDCT-domain loss (BASELINE.json config 3): weight * sum |STMDCT(pred) - target_coef| (INR_LOSS_MAE) or squared
  * (INR_LOSS_MSE), and its exact adjoint.  Deterministic (one writer per output sample). */
 int inr_mdct_loss(const float* pred, const float* target_coef, int64_t T, int N, const float* window, int kind,

