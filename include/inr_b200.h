@@ -240,6 +240,10 @@ int inr_dbg_tc_layer(int H, int mode, const float* A, const float* W, const floa
 int inr_dbg_tc_dw(int H, const float* dZ, const float* S, float* gW, int64_t rows, int variant, void* scratch,
                   int64_t scratch_bytes, void* stream);
 
+/* debug: clock64 stamps of the slot hand-offs of the fused forward kernel (pair 0), 4 per job */
+int inr_dbg_fused_trace_enable(int on);
+int inr_dbg_fused_trace_read(long long* host_out, int n);
+
 #ifdef __cplusplus
 }
 #endif

@@ -496,6 +496,10 @@ static int launch_fused(const FusedParams& p, cudaStream_t st) {
 
 // first layer + all hidden layers of one row chunk in ONE kernel; S[l] / C[l] (l = 0..L) are the stash images to
 // write (NULL entries are skipped: inference keeps only S_L)
+// hand-off trace buffer of k_tc_fused_fwd (allocated by inr_dbg_fused_trace_enable; NULL = tracing off)
+static long long* g_fused_trace = nullptr;
+constexpr int kFusedTraceJobs = 96;
+
 struct FusedLast {   // arguments of the fused head + loss + dZ_L epilogue (FusedParams::fuse_last)
   const float* target; const float* extra_g; int loss_kind; float grad_scale; float* grads; double* loss_acc; float* out;
 };
@@ -518,6 +522,7 @@ static int fused_forward(const inr_siren_desc* d, const float* params, const __n
   p.g_wlast = fl ? fl->grads + lay.w_off(lay.L + 1) : nullptr; p.g_blast = fl ? fl->grads + lay.b_off(lay.L + 1) : nullptr;
   p.loss_acc = fl ? fl->loss_acc : nullptr;
   { static int dbg = -1; if (dbg < 0) { const char* e = getenv("INR_TC_FUSED_DBG"); dbg = e ? atoi(e) : 0; } p.dbg = dbg; }
+  p.trace = g_fused_trace; p.trace_jobs = g_fused_trace ? kFusedTraceJobs : 0;
   if (tc_fused_ew() == 8) return lay.H == 256 ? launch_fused<256, 8>(p, st) : launch_fused<128, 8>(p, st);
   return lay.H == 256 ? launch_fused<256, 16>(p, st) : launch_fused<128, 16>(p, st);
 }
@@ -786,3 +791,23 @@ int siren_tc_loss_backward(const inr_siren_desc* d, const float* params, const f
 }
 
 }  // namespace inr
+
+// ---- debug: clock64 stamps of the slot hand-offs in pair 0 of k_tc_fused_fwd (profiles/r01c_notes.md)
+extern "C" int inr_dbg_fused_trace_enable(int on) {
+  using namespace inr;
+  if (on && !g_fused_trace) {
+    INR_CUDA_CHECK(cudaMalloc(&g_fused_trace, kFusedTraceJobs * 4 * sizeof(long long)));
+    INR_CUDA_CHECK(cudaMemset(g_fused_trace, 0, kFusedTraceJobs * 4 * sizeof(long long)));
+  } else if (!on && g_fused_trace) {
+    cudaFree(g_fused_trace);
+    g_fused_trace = nullptr;
+  }
+  return INR_OK;
+}
+extern "C" int inr_dbg_fused_trace_read(long long* host_out, int n) {
+  using namespace inr;
+  INR_REQUIRE(g_fused_trace && host_out && n > 0, INR_E_BADARG, "trace not enabled");
+  INR_CUDA_CHECK(cudaDeviceSynchronize());
+  INR_CUDA_CHECK(cudaMemcpy(host_out, g_fused_trace, std::min(n, kFusedTraceJobs * 4) * sizeof(long long), cudaMemcpyDeviceToHost));
+  return INR_OK;
+}

@@ -99,6 +99,10 @@ struct FusedParams {
   // timing ablations (INR_TC_FUSED_DBG bit mask, results are WRONG when set; profiles/r01c_notes.md):
   // 1 = no stash stores to HBM, 2 = no sin/cos (raw accumulator values), 4 = head: dot + loss only (no dZ_L, no g_w)
   int dbg;
+  // hand-off trace (inr_dbg_fused_trace): pair 0's leader CTA writes clock64() stamps, 4 per job in MMA order:
+  // [MMA thread passed aready, MMA thread committed tfull, epilogue warp 0 passed tfull, epilogue warp 0 signalled]
+  long long* trace;
+  int trace_jobs;
 };
 
 // EW = number of epilogue warps (8 or 16): warp%4 picks the TMEM lane quadrant, (warp-2)/4 the column part.
@@ -191,6 +195,8 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(64 + 32 * EW, 1) k_t
             for (int b = 0; b < nslots; ++b) {
               mbar_wait(bar_aready(b), par);          // image written in both CTAs, accumulator drained
               tc_fence_after();
+              const int tj = (r * L + l - 1) * 2 + b;
+              if (p.trace && blockIdx.x == 0 && tj < p.trace_jobs) p.trace[tj * 4 + 0] = clock64();
               const uint32_t d_tmem = tmem_base + b * NP;
               for (int c = 0; c < Cfg::NCHUNK; ++c) {
                 mbar_wait(bar_wfull(s), phase);
@@ -205,6 +211,7 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(64 + 32 * EW, 1) k_t
                 if (++s == Cfg::STAGES) { s = 0; phase ^= 1; }
               }
               umma2_commit_mc(bar_tfull(b), 3);
+              if (p.trace && blockIdx.x == 0 && tj < p.trace_jobs) p.trace[tj * 4 + 1] = clock64();
             }
           }
         }
@@ -306,6 +313,9 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(64 + 32 * EW, 1) k_t
           const bool valid = tile < p.num_tiles;
           mbar_wait(bar_tfull(b), par);
           tc_fence_after();
+          const int tj = (r * L + l - 1) * 2 + b;
+          const bool tr = p.trace && blockIdx.x == 0 && e == 0 && lane == 0 && tj < p.trace_jobs;
+          if (tr) p.trace[tj * 4 + 2] = clock64();
           if (l == L && p.fuse_last) {
             // ---------- last hidden layer + nn.Linear head + loss + dZ_L ----------
             // pass A: S_L = sin(.) (bf16) -> the slot's image (free: no layer L+1) + this thread's part of the output dot
@@ -449,6 +459,7 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(64 + 32 * EW, 1) k_t
           } else if (k + 2 < n_k) {
             gen_first(b, k + 2);                          // the slot's next double tile (also releases the accumulator)
           }
+          if (tr) p.trace[tj * 4 + 3] = clock64();
         }
       }
     }
