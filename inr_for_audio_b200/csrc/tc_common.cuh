@@ -138,12 +138,17 @@ __device__ __forceinline__ void cluster_sync_all() {
   asm volatile("barrier.cluster.arrive.release.aligned;" ::: "memory");
   asm volatile("barrier.cluster.wait.acquire.aligned;" ::: "memory");
 }
-// arrive (count 1) on the mbarrier at the same shared-memory offset in CTA `rank` of the cluster
+// arrive (count 1) on the mbarrier at the same shared-memory offset in CTA `rank` of the cluster.
+// Release at CTA scope (the PTX default, what CUTLASS' ClusterBarrier::arrive(cta_id) emits), NOT .release.cluster: a
+// cluster-scope release makes the arriving thread wait until all its earlier GLOBAL stores (the S_l / C_l stash of the
+// epilogue) are performed at L2 -- 6-8 k cycles per hand-off in the peer CTA of a pair (tools/fused_trace.py).  What the
+// leader's MMA consumes from the peer is shared memory (made visible to the async proxy by fence.proxy.async before the
+// arrive) and TMEM (tcgen05.wait::ld + tcgen05.fence::before_thread_sync before the arrive); neither needs the stores.
 __device__ __forceinline__ void mbar_arrive_remote(uint32_t bar, uint32_t rank) {
   asm volatile(
       "{\n\t.reg .b32 ra;\n\t"
       "mapa.shared::cluster.u32 ra, %0, %1;\n\t"
-      "mbarrier.arrive.release.cluster.shared::cluster.b64 _, [ra];\n\t}" ::"r"(bar), "r"(rank)
+      "mbarrier.arrive.release.cta.shared::cluster.b64 _, [ra];\n\t}" ::"r"(bar), "r"(rank)
       : "memory");
 }
 __device__ __forceinline__ void tmem_alloc2(uint32_t dst_smem, uint32_t ncols) {  // one full warp in EACH CTA of the pair
