@@ -398,18 +398,18 @@ static int launch_dw2(const DwParams& p, cudaStream_t st) {
   return INR_OK;
 }
 
-// INR_TC_DW_PAIR=1 selects the CTA-pair dW kernel k_tc_dw2 (H >= 256).  Measured on B200 (profiles/r01c_notes.md): it
-// cuts the L2->SM operand traffic by a third and is parity-green, but the step time does not move (C2 6.99 vs 6.95 ms
-// for the five dW launches, C1 0.223 vs 0.203 ms) -- the fabric was not the limiter -- so the single-CTA kernel of
-// tc_gemm.cuh stays the default.
-static bool tc_dw_pair_mode() {
-  static int v = -1;
-  if (v < 0) { const char* e = getenv("INR_TC_DW_PAIR"); v = (e && e[0] == '1') ? 1 : 0; }
-  return v != 0;
+// CTA-pair dW kernel k_tc_dw2: default at H = 512, where it cuts the five dW launches of a C2 step by ~15 % (same box,
+// back to back, under the power cap: 6.2-6.5 vs 7.3-7.7 ms; step 27.2 vs 27.5 ms); at H = 256 the single-CTA kernel is
+// faster (C1 0.203 vs 0.223 ms).  INR_TC_DW_PAIR=0 / 1 forces one or the other (profiles/r01c_notes.md).
+static int tc_dw_pair_mode() {   // -1 = by width, 0 / 1 = forced
+  static int v = -2;
+  if (v == -2) { const char* e = getenv("INR_TC_DW_PAIR"); v = !e ? -1 : (e[0] == '1' ? 1 : 0); }
+  return v;
 }
 
 int tc_dw(int H, const DwParams& p, cudaStream_t st) {
-  if (tc_dw_pair_mode() && tc_pair_mode()) {
+  const int pm = tc_dw_pair_mode();
+  if (tc_pair_mode() && (pm == 1 || (pm == -1 && H == 512))) {
     if (H == 256) return launch_dw2<256>(p, st);
     if (H == 512) return launch_dw2<512>(p, st);
   }
