@@ -38,7 +38,9 @@ namespace tc {
 // angle goes to the SFU (MUFU.SIN/COS, abs error ~5e-7 on [-pi, pi]) -- two orders below the bf16 rounding of the
 // stored result.
 __device__ __forceinline__ void sincos_reduced(float t, float* s, float* c) {
-  const float k = rintf(t * 0.15915494309189535f);
+  // k = rint(t / 2pi) by the 1.5 * 2^23 magic constant: two FMA-pipe instructions instead of an FRND on the XU pipe,
+  // which the two MUFUs below already saturate (|t / 2pi| < 2^22 holds for any omega_0 * z of interest)
+  const float k = __fadd_rn(__fmaf_rn(t, 0.15915494309189535f, 12582912.0f), -12582912.0f);
   float r = __fmaf_rn(-k, 6.2831854820251465f, t);      // C1 = fl32(2 pi)
   r = __fmaf_rn(-k, -1.7484555e-7f, r);                 // C2 = 2 pi - C1
   *s = __sinf(r);
