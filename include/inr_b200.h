@@ -48,7 +48,8 @@ extern "C" {
  * flat params = state_dict order: W, b per layer, with a Snake layer's `a` (H floats) right after its bias.
  * The bf16 tcgen05 mode takes the sine-only stack; Snake/Tanh stacks run in INR_PREC_FP32. */
 typedef struct {
-  int32_t in_features;     /* 1 (waveform) or 2 (MDCT image)                      */
+  int32_t in_features;     /* 1 (waveform), 2 (MDCT image), or the width of an encoded
+                              coordinate (2*num_freq, run.py:81-82; fp32 mode only)  */
   int32_t hidden_features; /* H                                                   */
   int32_t hidden_layers;   /* number of HxH SineLayers (num_sine)                 */
   int32_t out_features;    /* must be 1                                           */
@@ -112,6 +113,21 @@ int inr_coords_linspace(float* out, int64_t i0, int64_t n, int64_t T_total, floa
 /* utils.py:382-403 MDCTFitting 2-D grid: out[(r*W + c), :] = (lin(H)[r], lin(W)[c]) for flat index
  * i0 <= r*W+c < i0+n. */
 int inr_coords_grid2d(float* out, int64_t i0, int64_t n, int64_t height, int64_t width, void* stream);
+
+/* Input encodings applied to the coordinates once, in front of the first layer (the network then has
+ * in_features = the encoded width).  coords == NULL (in_features == 1 only): row j encodes
+ * linspace(-scale,scale,T_total)[i0 + j] generated in the kernel; otherwise coords is (n, in_features).
+ *
+ * run.py:141-144 `rff.layers.GaussianEncoding(10.0, 1, num_freq)` (third-party `rff`, un-vendored and absent here:
+ * PARITY UNPINNED, restated from its published definition): vp = (2*pi*v) @ b^T with b (encoded_size, in_features)
+ * drawn once as sigma * randn by the caller; out (n, 2*encoded_size) = [cos(vp) | sin(vp)]. */
+int inr_encode_gaussian(const float* coords, int in_features, int64_t n, int64_t i0, int64_t T_total, float scale,
+                        const float* b, int encoded_size, float* out, void* stream);
+/* models.py:14-59 PosEncodingNeRF.forward: out (n, in + 2*in*num_frequencies) =
+ * [x, sin(s^0 pi x_0), cos(s^0 pi x_0), sin(s^0 pi x_1), ..., sin(s^1 pi x_0), ...], s = freq_scale,
+ * num_frequencies <= 32. */
+int inr_encode_nerf(const float* coords, int in_features, int64_t n, int64_t i0, int64_t T_total, float scale,
+                    int num_frequencies, float freq_scale, float* out, void* stream);
 
 /* models.py:271-275 / 388-394  Siren.forward:  out[n, 1] = net(coords).
  * coords == NULL (in_features == 1 only): row j uses linspace(-scale,scale,T_total)[i0 + j] generated in

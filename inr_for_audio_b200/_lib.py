@@ -59,6 +59,8 @@ SIGNATURES = {
     "inr_siren_workspace_bytes": (_i64, [C.POINTER(SirenDesc), _i64, _i]),
     "inr_coords_linspace": (_i, [_p, _i64, _i64, _i64, _f, _p]),
     "inr_coords_grid2d": (_i, [_p, _i64, _i64, _i64, _i64, _p]),
+    "inr_encode_gaussian": (_i, [_p, _i, _i64, _i64, _i64, _f, _p, _i, _p, _p]),
+    "inr_encode_nerf": (_i, [_p, _i, _i64, _i64, _i64, _f, _i, _f, _p, _p]),
     "inr_siren_forward": (_i, [C.POINTER(SirenDesc), _p, _p, _i64, _i64, _i64, _f, _p, _p, _i64, _p]),
     "inr_siren_loss_backward": (_i, [C.POINTER(SirenDesc), _p, _p, _p, _i64, _i64, _i64, _f, _i, _f, _p, _p, _p, _p,
                                      _p, _i64, _p]),

@@ -67,7 +67,7 @@ LaunchScope::~LaunchScope() {
 
 static int check_desc(const inr_siren_desc* d) {
   INR_REQUIRE(d != nullptr, INR_E_BADARG, "desc is NULL");
-  INR_REQUIRE(d->in_features == 1 || d->in_features == 2, INR_E_UNSUPPORTED, "in_features must be 1 or 2, got %d",
+  INR_REQUIRE(d->in_features >= 1 && d->in_features <= 4096, INR_E_UNSUPPORTED, "in_features must be in [1,4096], got %d",
               d->in_features);
   INR_REQUIRE(d->out_features == 1, INR_E_UNSUPPORTED, "out_features must be 1, got %d", d->out_features);
   INR_REQUIRE(d->hidden_features >= 8 && d->hidden_features % 8 == 0 && d->hidden_features <= 1024,
@@ -82,9 +82,9 @@ static int check_desc(const inr_siren_desc* d) {
               d->precision);
   if (d->precision == INR_PREC_BF16)
     INR_REQUIRE(siren_tc_supported(d), INR_E_UNSUPPORTED,
-                "bf16 tcgen05 path needs hidden_features in {128,256,512}, hidden_layers >= 1 and a sine-only stack "
-                "(got H=%d sine=%d snake=%d tanh=%d first_linear=%d); use INR_PREC_FP32",
-                d->hidden_features, d->hidden_layers, d->num_snake, d->num_tanh, d->first_linear);
+                "bf16 tcgen05 path needs in_features <= 2, hidden_features in {128,256,512}, >= 1 hidden layer and "
+                "first_linear == 0 (got in=%d H=%d sine=%d snake=%d tanh=%d first_linear=%d); use INR_PREC_FP32",
+                d->in_features, d->hidden_features, d->hidden_layers, d->num_snake, d->num_tanh, d->first_linear);
   return INR_OK;
 }
 

@@ -47,6 +47,42 @@ static int fwd_layer(const inr_siren_desc* d, const float* params, int layer, co
   return INR_OK;
 }
 
+// first layer for any in_features: 1 or 2 inputs (raw coordinates) run the elementwise kernel (bit-exact with F.linear at
+// in = 1); wider inputs -- encoded coordinates, run.py:81-82,141-144 -- are a GEMM with K = in_features
+static int first_layer_any(const inr_siren_desc* d, const float* params, const float* xc, int64_t rows, int64_t g0,
+                           int64_t T_total, float scale, float* S0, float* C0, float* E0, cudaStream_t st) {
+  if (d->in_features <= 2) return launch_first_layer<float>(d, params, xc, rows, g0, T_total, scale, S0, C0, E0, st);
+  const SirenLayout lay = layout_of(d);
+  const int H = lay.H, K = lay.in;
+  dim3 grid((unsigned)cdiv(rows, BM), (unsigned)cdiv(H, BN), 1);
+  if (lay.first_snake) {
+    LaunchScope ls("k_sgemm_first_snake", st);
+    k_sgemm<true, true, EPI_SNAKE><<<grid, 256, 0, st>>>(xc, K, 1, params + lay.w_off(0), K, 1, rows, H, K, K,
+                                                         params + lay.b_off(0), 1.f, S0, C0, H, params + lay.a_off(0), E0);
+  } else {
+    LaunchScope ls("k_sgemm_first_sincos", st);
+    k_sgemm<true, true, EPI_SINCOS><<<grid, 256, 0, st>>>(xc, K, 1, params + lay.w_off(0), K, 1, rows, H, K, K,
+                                                          params + lay.b_off(0), d->first_omega_0, S0, C0, H);
+  }
+  INR_LAUNCH_CHECK();
+  return INR_OK;
+}
+
+// gW_0 (H x in) += dZ_0^T X, gb_0 += colsum(dZ_0)
+static int first_layer_grad_any(const inr_siren_desc* d, const float* dZ0, const float* xc, int64_t rows, int64_t g0,
+                                int64_t T_total, float scale, float* gW, float* gb, cudaStream_t st) {
+  if (d->in_features <= 2) return launch_first_layer_grad<float>(d, dZ0, xc, rows, g0, T_total, scale, gW, gb, st);
+  const int H = d->hidden_features, K = d->in_features;
+  const int64_t want = std::max<int64_t>(1, (int64_t)num_sms() * 2 / (cdiv(H, BM) * cdiv(K, BN)));
+  const int64_t k_chunk = round_up(std::max<int64_t>(cdiv(rows, want), 256), BK);
+  dim3 gdw((unsigned)cdiv(H, BM), (unsigned)cdiv(K, BN), (unsigned)cdiv(rows, k_chunk));
+  { LaunchScope ls("k_sgemm_dw0", st);
+    k_sgemm<false, false, EPI_ATOMIC><<<gdw, 256, 0, st>>>(dZ0, 1, H, xc, 1, K, H, K, rows, k_chunk, nullptr, 0.f, gW,
+                                                           nullptr, K); }
+  INR_LAUNCH_CHECK();
+  return launch_colsum<float>(dZ0, rows, H, gb, st);
+}
+
 int siren_fp32_forward(const inr_siren_desc* d, const float* params, const float* coords, int64_t n, int64_t i0,
                        int64_t T_total, float scale, float* out, void* ws, int64_t ws_bytes, cudaStream_t st) {
   const SirenLayout lay = layout_of(d);
@@ -57,8 +93,8 @@ int siren_fp32_forward(const inr_siren_desc* d, const float* params, const float
   for (int64_t r0 = 0; r0 < n; r0 += chunk) {
     const int64_t rows = std::min(chunk, n - r0);
     float* S[2] = {(float*)ws, (float*)ws + rows * H};
-    int rc = launch_first_layer<float>(d, params, coords ? coords + r0 * d->in_features : nullptr, rows, i0 + r0,
-                                       T_total, scale, S[0], nullptr, nullptr, st);
+    int rc = first_layer_any(d, params, coords ? coords + r0 * d->in_features : nullptr, rows, i0 + r0, T_total, scale,
+                             S[0], nullptr, nullptr, st);
     if (rc) return rc;
     int cur = 0;
     for (int l = 1; l <= L; ++l) {
@@ -98,7 +134,7 @@ int siren_fp32_train(const inr_siren_desc* d, const float* params, const float* 
     const float* xc = coords ? coords + r0 * d->in_features : nullptr;
     int rc;
     if (phase & 1) {
-      rc = launch_first_layer<float>(d, params, xc, rows, i0 + r0, T_total, scale, S(0), C(0), E(0), st);
+      rc = first_layer_any(d, params, xc, rows, i0 + r0, T_total, scale, S(0), C(0), E(0), st);
       if (rc) return rc;
       for (int l = 1; l <= L; ++l) {
         rc = fwd_layer(d, params, l, S(l - 1), S(l), C(l), E(l), rows, st);
@@ -144,8 +180,7 @@ int siren_fp32_train(const inr_siren_desc* d, const float* params, const float* 
       }
       INR_LAUNCH_CHECK();
     }
-    rc = launch_first_layer_grad<float>(d, C(0), xc, rows, i0 + r0, T_total, scale, grads + lay.w_off(0),
-                                        grads + lay.b_off(0), st);
+    rc = first_layer_grad_any(d, C(0), xc, rows, i0 + r0, T_total, scale, grads + lay.w_off(0), grads + lay.b_off(0), st);
     if (rc) return rc;
   }
   return INR_OK;

@@ -260,6 +260,7 @@ bool siren_tc_supported(const inr_siren_desc* d) {
   // Snake / Tanh hidden layers exist in the CTA-pair kernel only; a Linear+Snake FIRST layer runs in the fp32 mode
   const bool sine_only = d->num_snake == 0 && d->num_tanh == 0;
   return (H == 128 || H == 256 || H == 512) && Ltot >= 1 && d->out_features == 1 && d->first_linear == 0 &&
+         d->in_features <= 2 &&   // encoded inputs (in_features = 2*num_freq) run in the fp32 mode
          (sine_only || tc_pair_mode());
 }
 

@@ -19,6 +19,7 @@ import torch
 from torch import nn
 
 from . import _lib as L
+from .encoding import GaussianEncoding, PosEncodingNeRF  # noqa: F401  (models.py:14-59; rff.layers.GaussianEncoding)
 from .engine import SirenSpec, Workspace
 
 

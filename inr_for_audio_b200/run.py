@@ -17,6 +17,7 @@ import torch
 from scipy.io import wavfile
 
 from . import mdct
+from .encoding import GaussianEncoding
 from .engine import SirenFitter
 from .models import SirenWithSnakeTanh
 from .utils import MDCTFitting, WaveformFitting, calculate_snr, get_coord
@@ -100,8 +101,10 @@ def train(experiment_path: str, tag: str, inst: str, duration: int, num_channels
     os.makedirs(experiment_folder)
     decimation = int(decimation)
     takelog = False
-    if num_freq is not None:
-        raise NotImplementedError("num_freq (rff Gaussian encoding, run.py:141-144) is SURVEY.md §8(f)-4, not built")
+    if num_freq is not None and method != 'wave':
+        raise ValueError("num_freq: the reference's GaussianEncoding(10.0, 1, num_freq) takes 1-D coordinates (run.py:142)")
+    if num_freq is not None and (arch == 'kan' or precision != 'fp32'):
+        raise NotImplementedError("num_freq (encoded first layer, in_features = 2*num_freq) runs in the fp32 SIREN mode only")
     if arch == 'kan' and (method != 'wave' or alpha != 0.0 or loss_mode == 'snr'):
         raise NotImplementedError("arch='kan' is waveform-only (run.py:93,110) with the mse/mae losses on the device path")
     if alpha != 0.0 and method != 'wave':
@@ -126,6 +129,8 @@ def train(experiment_path: str, tag: str, inst: str, duration: int, num_channels
         torch.manual_seed(seed)
     if arch == 'kan':
         return _train_kan(locals())
+    if num_freq is not None:
+        input_dimension = int(num_freq) * 2                                             # run.py:81-82
     model = SirenWithSnakeTanh(in_features=input_dimension, out_features=1, hidden_features=num_hidden_features,
                                num_sine=num_sine, num_snake=num_snake, num_tanh=num_tanh, num_freq=num_freq,
                                first_linear=first_linear, last_linear=last_linear, first_omega_0=omega,
@@ -138,6 +143,16 @@ def train(experiment_path: str, tag: str, inst: str, duration: int, num_channels
     model.cuda()
     dev = model.flat_parameters().device
 
+    encoding = None
+    if num_freq is not None:
+        # run.py:141-144: rff.layers.GaussianEncoding(10.0, 1, num_freq), drawn after the model (same RNG order), applied
+        # once to the coordinates; here the coordinates themselves are generated inside the encoding kernel
+        # (the reference does not checkpoint b, so its resumed runs draw a new one; here the checkpoint carries it)
+        if checkpoint is not None and checkpoint.get('encoding_b') is not None:
+            encoding = GaussianEncoding(b=checkpoint['encoding_b'].clone()).to(dev)
+        else:
+            encoding = GaussianEncoding(10.0, 1, int(num_freq)).to(dev)
+        coords = encoding(n=len(target_np))
     target = torch.from_numpy(target_np).to(dev)
     fitter = SirenFitter(model.spec, model.flat_parameters(), target,
                          None if coords is None else coords.to(dev), loss_mode=loss_mode, lr=learning_rate,
@@ -165,7 +180,7 @@ def train(experiment_path: str, tag: str, inst: str, duration: int, num_channels
 
     if bwe and method == 'wave':
         n_bwe = input_data.original_sample_rate * duration
-        final = fitter.forward(n=n_bwe, i0=0, T_total=n_bwe)
+        final = fitter.forward(encoding(n=n_bwe)) if encoding is not None else fitter.forward(n=n_bwe, i0=0, T_total=n_bwe)
         recover_sample_rate = input_data.original_sample_rate
     else:
         final = fitter.forward()
@@ -192,7 +207,8 @@ def train(experiment_path: str, tag: str, inst: str, duration: int, num_channels
 
     ckpt_path = f'{experiment_folder}/saved_ckpt.pt'
     torch.save({'model_state_dict': {k: v.detach().cpu().clone() for k, v in model.state_dict().items()},
-                'optimizer_state_dict': _adam_state_dict(model, fitter, learning_rate)}, ckpt_path)
+                'optimizer_state_dict': _adam_state_dict(model, fitter, learning_rate),
+                'encoding_b': None if encoding is None else encoding.b.detach().cpu().clone()}, ckpt_path)
     save_parameters(experiment_folder, experiment_path=experiment_path, tag=tag, inst=inst, duration=duration,
                     num_channels=num_channels, method=method, arch=arch, loss_mode=loss_mode, mode=mode,
                     decimation=decimation, bwe=bwe, num_hidden_features=num_hidden_features, num_sine=num_sine,

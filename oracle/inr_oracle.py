@@ -201,6 +201,27 @@ def siren_forward(spec: SirenSpec, params: Sequence[torch.Tensor], coords: torch
     return x
 
 
+def pos_encoding_nerf(coords: torch.Tensor, num_frequencies: int, scale=2) -> torch.Tensor:
+    """models.py:48-59 PosEncodingNeRF.forward: the coordinates, then per frequency i and input feature j the pair
+    sin((scale**i) * pi * c_j), cos(...), concatenated on the last axis."""
+    in_features = coords.shape[-1]
+    parts = [coords]
+    for i in range(num_frequencies):
+        for j in range(in_features):
+            c = coords[..., j]
+            parts.append(torch.sin((scale ** i) * np.pi * c).unsqueeze(-1))
+            parts.append(torch.cos((scale ** i) * np.pi * c).unsqueeze(-1))
+    return torch.cat(parts, dim=-1)
+
+
+def gaussian_encoding(v: torch.Tensor, b: torch.Tensor) -> torch.Tensor:
+    """run.py:141-144 -> third-party `rff.layers.GaussianEncoding.forward` = rff.functional.gaussian_encoding (package not
+    vendored, not installed, no version pinned: PARITY UNPINNED; restated from its published definition):
+    vp = 2*pi*v @ b.T;  cat(cos(vp), sin(vp)).  b = sigma * randn(encoded_size, input_size) (rff.functional.sample_b)."""
+    vp = 2 * np.pi * v @ b.T
+    return torch.cat((torch.cos(vp), torch.sin(vp)), dim=-1)
+
+
 def time_loss(out: torch.Tensor, gt: torch.Tensor, loss_mode: str) -> torch.Tensor:
     """run.py:124-125,161-169: nn.L1Loss / nn.MSELoss (mean over all elements) / auraloss SNRLoss."""
     if loss_mode == "mae":

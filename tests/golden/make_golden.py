@@ -88,6 +88,46 @@ def make_snake():
     np.savez_compressed(os.path.join(HERE, "snake.npz"), **out)
 
 
+def make_encoding():
+    """PosEncodingNeRF (models.py:14-59) outputs, and a reference Siren whose first layer takes an encoded coordinate
+    (in_features = 2*num_freq as run.py:81-82 builds it; the encoding itself comes from the absent third-party `rff`, so
+    the encoded input here is PosEncodingNeRF's, which the reference does carry): forward + teacher-forced steps."""
+    out = {}
+    c1 = ref.utils.get_coord(1000, 1)
+    pe1 = ref.models.PosEncodingNeRF(in_features=1, num_frequencies=6)
+    out["nerf1"] = pe1(c1).numpy()
+    pe1n = ref.models.PosEncodingNeRF(in_features=1, fn_samples=4096)          # nyquist rule: floor(log2(4096/4)) = 10
+    out["nerf1_nyq_nf"] = np.array(pe1n.num_frequencies)
+    out["nerf1_nyq"] = pe1n(c1).numpy()
+    c2 = ref.utils.get_coord(24, 2)
+    pe2 = ref.models.PosEncodingNeRF(in_features=2, num_frequencies=3, scale=1.5)
+    out["nerf2"] = pe2(c2).numpy()
+    sr, data = gt_bach(4096, 44100)
+    gt = torch.from_numpy(data / np.max(np.abs(data))).view(1, -1, 1)
+    out["gt"] = gt.numpy().ravel()
+    enc = ref.models.PosEncodingNeRF(in_features=1, num_frequencies=8)(ref.utils.get_coord(4096, 1))   # (4096, 17)
+    x = enc[:, 1:].contiguous().view(1, 4096, 16)                                                 # 16 = 2*num_freq inputs
+    out["x"] = x.numpy().reshape(4096, 16)
+    cases = {
+        "s": (lambda: ref.models.Siren(16, 48, 2, 1, outermost_linear=True, first_omega_0=30, hidden_omega_0=30.0), "mse"),
+        "w": (lambda: ref.models.SirenWithSnakeTanh(in_features=16, out_features=1, hidden_features=40, num_sine=1,
+                                                     num_snake=1, num_tanh=0, first_omega_0=30, hidden_omega_0=30.0,
+                                                     a_initial=0.5), "mse"),
+        "l": (lambda: ref.models.SirenWithSnakeTanh(in_features=16, out_features=1, hidden_features=32, num_sine=1,
+                                                     num_snake=0, num_tanh=1, first_linear=True, a_initial=2.0), "mae"),
+    }
+    for name, (ctor, loss_mode) in cases.items():
+        torch.manual_seed(11)
+        m = ctor()
+        out[name + "_p0"] = np.concatenate([p.detach().numpy().ravel() for p in m.parameters()])
+        out[name + "_out0"] = m(x).detach().numpy().ravel()
+        losses, lrs, rec = ref_fit(m, x, gt, 6, loss_mode=loss_mode, record_steps=(0, 1, 5))
+        out[name + "_losses"] = np.array(losses, dtype=np.float64)
+        for k, v in rec.items():
+            out[name + "_" + k] = v
+    np.savez_compressed(os.path.join(HERE, "encoding.npz"), **out)
+
+
 # ---------------------------------------------------------------- SIREN (models.py)
 def gt_bach(n=None, start=0):
     from scipy.io import wavfile
@@ -300,7 +340,7 @@ def make_kan():
 
 
 if __name__ == "__main__":
-    which = sys.argv[1:] or ["coords", "siren", "snake", "mdct", "kan", "converge"]
+    which = sys.argv[1:] or ["coords", "siren", "snake", "encoding", "mdct", "kan", "converge"]
     for w in which:
         print("making", w)
         globals()["make_" + w]()

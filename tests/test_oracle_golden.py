@@ -230,3 +230,59 @@ def test_snake_tanh_stacks_against_reference(golden, name):
         assert np.linalg.norm(_flat(grads) - gref) <= (1e-3 if loss_mode == "mae" else 1e-4) * np.linalg.norm(gref)
     losses, _, _ = O.siren_fit(spec, ps, coords, gt, 3, loss_mode=loss_mode)
     np.testing.assert_allclose(losses, g[name + "_losses"][:3], rtol=1e-4)
+
+
+# ------------------------------------------------------------------ encoded first layer
+ENC_SPECS = {
+    # the oracle's SirenSpec for the cases of tests/golden/make_golden.py make_encoding (in_features = 16 = 2*num_freq)
+    "s": (O.SirenSpec(16, 48, 2, 1, True, 30.0, 30.0), "mse"),
+    "w": (O.SirenSpec(16, 40, 1, 1, True, 30.0, 30.0, num_snake=1, num_tanh=0, a_initial=0.5), "mse"),
+    "l": (O.SirenSpec(16, 32, 1, 1, True, 30.0, 30.0, num_snake=0, num_tanh=1, first_linear=True, a_initial=2.0), "mae"),
+}
+
+
+def test_pos_encoding_nerf_against_reference(golden):
+    """models.py:14-59: layout [x, sin, cos per frequency and feature], the nyquist frequency-count rule."""
+    g = golden("encoding")
+    c1 = O.get_coord(1000, 1)
+    assert np.array_equal(O.pos_encoding_nerf(c1, 6).numpy(), g["nerf1"])
+    assert int(g["nerf1_nyq_nf"]) == 10
+    assert np.array_equal(O.pos_encoding_nerf(c1, 10).numpy(), g["nerf1_nyq"])
+    c2 = O.get_coord(24, 2)
+    assert np.array_equal(O.pos_encoding_nerf(c2, 3, scale=1.5).numpy(), g["nerf2"])
+
+
+def test_gaussian_encoding_definition():
+    """rff GaussianEncoding (third-party, absent: parity unpinned): shape, cos|sin halves, unit modulus, b = 0 -> (1, 0)."""
+    torch.manual_seed(0)
+    b = torch.randn(8, 1) * 10.0
+    v = O.get_coord(100, 1)
+    e = O.gaussian_encoding(v, b)
+    assert e.shape == (100, 16)
+    np.testing.assert_allclose((e[:, :8] ** 2 + e[:, 8:] ** 2).numpy(), 1.0, atol=1e-6)
+    vp = (2 * np.pi * v.double()) @ b.double().T
+    np.testing.assert_allclose(e[:, :8].numpy(), np.cos(vp.numpy()), atol=2e-5)
+    np.testing.assert_allclose(e[:, 8:].numpy(), np.sin(vp.numpy()), atol=2e-5)
+    z = O.gaussian_encoding(v, torch.zeros(3, 1))
+    assert torch.equal(z[:, :3], torch.ones(100, 3)) and torch.equal(z[:, 3:], torch.zeros(100, 3))
+
+
+@pytest.mark.parametrize("name", sorted(ENC_SPECS))
+def test_encoded_first_layer_against_reference(golden, name):
+    """run.py:81-82: the network on an encoded coordinate (in_features = 2*num_freq): seeded init, forward, teacher-forced
+    loss + gradients, first free-running losses, against outputs of the reference itself."""
+    g = golden("encoding")
+    spec, loss_mode = ENC_SPECS[name]
+    ps = O.siren_init(spec, seed=11)
+    assert np.array_equal(_flat(ps), g[name + "_p0"])
+    x = torch.from_numpy(g["x"]).view(1, 4096, 16)
+    gt = torch.from_numpy(g["gt"]).view(1, -1, 1)
+    np.testing.assert_allclose(O.siren_forward(spec, ps, x).numpy().ravel(), g[name + "_out0"], atol=2e-5)
+    for k in (0, 1, 5):
+        pk = _split_sizes(g[f"{name}_p_{k}"], ps)
+        loss, _, grads, out = O.siren_loss_and_grads(spec, pk, x, gt, loss_mode)
+        assert abs(float(loss) - g[name + "_losses"][k]) <= 1e-5 * g[name + "_losses"][k]
+        gref = g[f"{name}_g_{k}"].astype(np.float64)
+        assert np.linalg.norm(_flat(grads) - gref) <= (1e-3 if loss_mode == "mae" else 1e-4) * np.linalg.norm(gref)
+    losses, _, _ = O.siren_fit(spec, ps, x, gt, 3, loss_mode=loss_mode)
+    np.testing.assert_allclose(losses, g[name + "_losses"][:3], rtol=1e-4)
