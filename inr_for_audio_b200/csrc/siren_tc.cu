@@ -176,6 +176,200 @@ __global__ void __launch_bounds__(128) k_tc_last(const __nv_bfloat16* __restrict
   }
 }
 
+// ------------------------------------------------------------------------------------------------ last layer, one pass
+// k_tc_last2<H, SNAKE>: the head, the loss, dZ_L AND the last-layer weight gradient (+ the `a` gradient of a Snake layer
+// L) in ONE pass over S_L / C_L: 3 units of HBM traffic instead of the 4 (5) of k_tc_last + k_tc_colsum_w (+ k_tc_colsum).
+//
+// Work unit = 32 rows of a tile (one lane per row).  512 threads; a 16-byte cp.async ring (NSTAGE stages of [S | C] slabs,
+// 2 ahead in flight) decouples the HBM latency from the two block barriers a unit needs:
+//   phase A   warp w owns feature groups w, w+16, ..: partial dots of its 32 rows from the S slab (kept in registers)
+//   barrier   every warp sums the 16 partials (fixed order), forms g = dloss/dout redundantly; warp 0 writes out / loss
+//   phase C   dZ_L = g w omega C_L straight to global, acc_w[f] += g S[f] in registers (one butterfly at the very end)
+template <int H>
+struct Last2Cfg {
+  static constexpr int G = H / 8;                  // feature groups
+  static constexpr int KPW = G / 16;               // groups per warp
+  static constexpr int SLAB = G * 32 * 16;         // bytes of a 32-row slab of one image
+  static constexpr int NSTAGE = (H >= 512) ? 3 : 4;
+  static constexpr int OFF_W = NSTAGE * 2 * SLAB;
+  static constexpr int OFF_DOT = OFF_W + H * 4;
+  static constexpr int SMEM_BYTES = OFF_DOT + 16 * 32 * 4;
+  static_assert(H == 128 || H == 256 || H == 512, "hidden width");
+  static_assert(SMEM_BYTES <= 232448, "shared-memory budget");
+};
+
+__device__ __forceinline__ void cp_async16(uint32_t dst, const void* src) {
+  asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(dst), "l"(src) : "memory");
+}
+__device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
+template <int N>
+__device__ __forceinline__ void cp_async_wait() { asm volatile("cp.async.wait_group %0;" ::"n"(N) : "memory"); }
+
+template <int H, bool SNAKE>
+__global__ void __launch_bounds__(512, 1) k_tc_last2(const __nv_bfloat16* __restrict__ S, __nv_bfloat16* __restrict__ CdZ,
+                                                     const float* __restrict__ w, const float* __restrict__ bptr,
+                                                     const float* __restrict__ target, const float* __restrict__ extra_g,
+                                                     int64_t rows, int num_tiles, float omega_prev, float omega_hidden,
+                                                     int outermost_linear, int loss_kind, float grad_scale,
+                                                     float* __restrict__ gw, float* __restrict__ gb,
+                                                     double* __restrict__ loss_acc, float* __restrict__ out, int training,
+                                                     const __nv_bfloat16* __restrict__ Eimg, float* __restrict__ ga) {
+  using Cfg = Last2Cfg<H>;
+  constexpr int KPW = Cfg::KPW;
+  extern __shared__ __align__(128) uint8_t smem[];
+  const uint32_t smem_base = smem_u32(smem);
+  float* s_w = reinterpret_cast<float*>(smem + Cfg::OFF_W);
+  float* s_dot = reinterpret_cast<float*>(smem + Cfg::OFF_DOT);
+  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  for (int i = tid; i < H; i += 512) s_w[i] = w[i];
+  __syncthreads();
+  const float bias = bptr[0];
+  const int num_units = num_tiles * 4;
+
+  auto issue = [&](int unit, int stage) {
+    if (unit < num_units) {
+      const int tile = unit >> 2, rb = unit & 3;
+      const size_t tile_off = (size_t)tile * (TILE_ROWS * (size_t)H);
+      const uint32_t dstS = smem_base + stage * (2 * Cfg::SLAB);
+#pragma unroll
+      for (int c = tid; c < Cfg::G * 32; c += 512) {
+        const int kg = c >> 5, r = c & 31;
+        const size_t off = tile_off + ((size_t)kg * TILE_ROWS + rb * 32 + r) * 8;
+        cp_async16(dstS + c * 16, S + off);
+        if (training) cp_async16(dstS + Cfg::SLAB + c * 16, CdZ + off);
+      }
+    }
+    cp_async_commit();
+  };
+
+  float acc_w[KPW][8], acc_a[SNAKE ? KPW : 1][8];
+#pragma unroll
+  for (int i = 0; i < KPW; ++i)
+#pragma unroll
+    for (int j = 0; j < 8; ++j) { acc_w[i][j] = 0.f; if (SNAKE) acc_a[i][j] = 0.f; }
+  double loss_local = 0.0;
+  float gb_local = 0.f;
+
+#pragma unroll
+  for (int s = 0; s < Cfg::NSTAGE - 1; ++s) issue(blockIdx.x + s * gridDim.x, s);
+  int it = 0;
+  for (int unit = blockIdx.x; unit < num_units; unit += gridDim.x, ++it) {
+    const int stage = it % Cfg::NSTAGE;
+    const int tile = unit >> 2, rb = unit & 3;
+    const int r = rb * 32 + lane;
+    const int64_t row = (int64_t)tile * TILE_ROWS + r;
+    const bool valid = row < rows;
+    // g needs the target: fetch it before the ring wait (every warp forms g itself; same addresses -> L1 hits)
+    float tgt = 0.f, eg = 0.f;
+    if (training && valid) {
+      if (target) tgt = target[row];
+      if (extra_g) eg = extra_g[row];
+    }
+    cp_async_wait<Cfg::NSTAGE - 2>();
+    __syncthreads();   // this unit's slabs have landed for every thread; the stage refilled below is no longer read
+    issue(unit + (Cfg::NSTAGE - 1) * gridDim.x, (it + Cfg::NSTAGE - 1) % Cfg::NSTAGE);
+    const uint8_t* sS = smem + stage * (2 * Cfg::SLAB);
+    const uint8_t* sC = sS + Cfg::SLAB;
+    uint4 sv[KPW];
+    float pd = 0.f;
+#pragma unroll
+    for (int i = 0; i < KPW; ++i) {
+      const int kg = warp + 16 * i;
+      sv[i] = *reinterpret_cast<const uint4*>(sS + (kg * 32 + lane) * 16);
+      const uint32_t uw[4] = {sv[i].x, sv[i].y, sv[i].z, sv[i].w};
+#pragma unroll
+      for (int h = 0; h < 4; ++h) {
+        const float2 f = unpack_bf16x2(uw[h]);
+        pd = __fmaf_rn(f.x, s_w[kg * 8 + 2 * h], pd);
+        pd = __fmaf_rn(f.y, s_w[kg * 8 + 2 * h + 1], pd);
+      }
+    }
+    s_dot[warp * 32 + lane] = pd;
+    __syncthreads();
+    float dot = 0.f;
+#pragma unroll
+    for (int q = 0; q < 16; ++q) dot += s_dot[q * 32 + lane];
+    const float z = dot + bias;
+    float o = z, dact = 1.f;
+    if (!outermost_linear) {
+      float sn, cs;
+      sincosf(omega_hidden * z, &sn, &cs);
+      o = sn;
+      dact = omega_hidden * cs;
+    }
+    if (warp == 0 && out && valid) out[row] = o;
+    if (!training) continue;
+    float g = 0.f;
+    if (valid) {
+      if (target) {
+        const float diff = o - tgt;
+        if (loss_kind == INR_LOSS_MAE) {
+          if (warp == 0) loss_local += (double)fabsf(diff);
+          g = grad_scale * ((diff > 0.f) ? 1.f : ((diff < 0.f) ? -1.f : 0.f));
+        } else {
+          if (warp == 0) loss_local += (double)diff * (double)diff;
+          g = grad_scale * 2.f * diff;
+        }
+      }
+      g = (g + eg) * dact;
+    }
+    if (warp == 0) gb_local += g;
+    const float gwm = g * omega_prev;
+    const size_t tile_off = (size_t)tile * (TILE_ROWS * (size_t)H);
+#pragma unroll
+    for (int i = 0; i < KPW; ++i) {
+      const int kg = warp + 16 * i;
+      const uint4 cu = *reinterpret_cast<const uint4*>(sC + (kg * 32 + lane) * 16);
+      const uint32_t cw[4] = {cu.x, cu.y, cu.z, cu.w};
+      const uint32_t uw[4] = {sv[i].x, sv[i].y, sv[i].z, sv[i].w};
+      const size_t off = tile_off + ((size_t)kg * TILE_ROWS + r) * 8;
+      uint32_t ow[4];
+#pragma unroll
+      for (int h = 0; h < 4; ++h) {
+        const float2 c = unpack_bf16x2(cw[h]);
+        const float2 f = unpack_bf16x2(uw[h]);
+        ow[h] = pack_bf16x2(gwm * s_w[kg * 8 + 2 * h] * c.x, gwm * s_w[kg * 8 + 2 * h + 1] * c.y);
+        acc_w[i][2 * h] = __fmaf_rn(g, f.x, acc_w[i][2 * h]);
+        acc_w[i][2 * h + 1] = __fmaf_rn(g, f.y, acc_w[i][2 * h + 1]);
+      }
+      *reinterpret_cast<uint4*>(CdZ + off) = make_uint4(ow[0], ow[1], ow[2], ow[3]);
+      if (SNAKE) {   // layer L is a Snake layer: grad a[f] = w[f] * sum_r g[r] (dy/da)[r][f]
+        const uint4 eu = *reinterpret_cast<const uint4*>(Eimg + off);
+        const uint32_t ew[4] = {eu.x, eu.y, eu.z, eu.w};
+#pragma unroll
+        for (int h = 0; h < 4; ++h) {
+          const float2 e = unpack_bf16x2(ew[h]);
+          acc_a[i][2 * h] = __fmaf_rn(g, e.x, acc_a[i][2 * h]);
+          acc_a[i][2 * h + 1] = __fmaf_rn(g, e.y, acc_a[i][2 * h + 1]);
+        }
+      }
+    }
+  }
+  cp_async_wait<0>();
+  if (!training) return;
+#pragma unroll
+  for (int i = 0; i < KPW; ++i) {
+    const int kg = warp + 16 * i;
+#pragma unroll
+    for (int j = 0; j < 8; ++j) {
+      const float sw = warp_sum(acc_w[i][j]);
+      if (lane == j) atomicAdd(&gw[kg * 8 + j], sw);
+      if (SNAKE) {
+        const float sa = warp_sum(acc_a[i][j]);
+        if (lane == j) atomicAdd(&ga[kg * 8 + j], s_w[kg * 8 + j] * sa);
+      }
+    }
+  }
+  if (warp == 0) {
+    loss_local = warp_sum(loss_local);
+    gb_local = warp_sum(gb_local);
+    if (lane == 0) {
+      if (target) atomicAdd(loss_acc, loss_local);
+      atomicAdd(gb, gb_local);
+    }
+  }
+}
+
 // ------------------------------------------------------------------------------------------------ column sums
 // out_plain[f] += sum_r X[r][f]          (bias gradients)
 // out_w[f*wstride + j] += sum_r wrow_j[r] X[r][f]   (last-layer weight: wrow = gvec; first layer: wrow = coordinates)
@@ -608,22 +802,77 @@ static int first_layer(const inr_siren_desc* d, const float* params, const float
   return INR_OK;
 }
 
+// INR_TC_LAST2=0 keeps k_tc_last + the separate column-sum launches (A/B baseline of profiles/r01e_notes.md)
+static bool tc_last2_mode() {
+  static int v = -1;
+  if (v < 0) { const char* e = getenv("INR_TC_LAST2"); v = (e && e[0] == '0') ? 0 : 1; }
+  return v != 0;
+}
+
+template <int H, bool SNAKE>
+static int launch_last2(const __nv_bfloat16* SL, __nv_bfloat16* CL, const float* w, const float* b, const float* target,
+                        const float* extra_g, int64_t rows, int tiles, float dfac, float omega_h, int outermost_linear,
+                        int loss_kind, float grad_scale, float* gw, float* gb, double* loss_acc, float* out, int training,
+                        const __nv_bfloat16* EL, float* ga, cudaStream_t st) {
+  using Cfg = Last2Cfg<H>;
+  static bool attr_done = false;
+  if (!attr_done) {
+    INR_CUDA_CHECK(cudaFuncSetAttribute(k_tc_last2<H, SNAKE>, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg::SMEM_BYTES));
+    attr_done = true;
+  }
+  const int blocks = std::max(1, std::min(tiles * 4, num_sms()));
+  { LaunchScope ls("k_tc_last", st);
+    k_tc_last2<H, SNAKE><<<blocks, 512, Cfg::SMEM_BYTES, st>>>(SL, CL, w, b, target, extra_g, rows, tiles, dfac, omega_h,
+                                                               outermost_linear, loss_kind, grad_scale, gw, gb, loss_acc,
+                                                               out, training, EL, ga); }
+  INR_LAUNCH_CHECK();
+  return INR_OK;
+}
+
+// out = act(S_L w + b); training: loss, g = dloss/dout, dZ_L over C_L, last-layer gradients (and the `a` gradient of a
+// Snake layer L from its dy/da image EL)
 static int last_layer(const inr_siren_desc* d, const float* params, const __nv_bfloat16* SL, __nv_bfloat16* CL,
                       const float* target, const float* extra_g, int64_t rows, int tiles, int loss_kind, float grad_scale,
                       float* gvec, float* grads, inr_opt_state* opt, float* out, int training, cudaStream_t st,
                       __nv_bfloat16* EL = nullptr) {
   SirenLayout lay = layout_of(d);
   const int last = lay.L + 1;
+  const int H = lay.H;
   // sine layers keep cos(omega z) in C_L (times omega here); Snake / Tanh layers keep the whole derivative
   const float dfac = lay.kind(lay.L) == ACT_SINE ? d->hidden_omega_0 : 1.f;
+  const float* w = params + lay.w_off(last);
+  const float* b = params + lay.b_off(last);
+  float* gw = grads ? grads + lay.w_off(last) : nullptr;
+  float* gb = grads ? grads + lay.b_off(last) : nullptr;
+  double* loss_acc = opt ? &opt->loss_acc[0] : nullptr;
+  if (!training) EL = nullptr;
+  if (tc_last2_mode()) {
+    float* ga = (EL && grads) ? grads + lay.a_off(lay.L) : nullptr;
+#define INR_LAST2(HH)                                                                                                   \
+    return EL ? launch_last2<HH, true>(SL, CL, w, b, target, extra_g, rows, tiles, dfac, d->hidden_omega_0,            \
+                                       d->outermost_linear, loss_kind, grad_scale, gw, gb, loss_acc, out, training, EL, \
+                                       ga, st)                                                                          \
+              : launch_last2<HH, false>(SL, CL, w, b, target, extra_g, rows, tiles, dfac, d->hidden_omega_0,           \
+                                        d->outermost_linear, loss_kind, grad_scale, gw, gb, loss_acc, out, training,    \
+                                        nullptr, nullptr, st)
+    if (H == 512) { INR_LAST2(512); }
+    if (H == 256) { INR_LAST2(256); }
+    INR_LAST2(128);
+#undef INR_LAST2
+  }
   int blocks = std::min(tiles, num_sms() * 8);
   { LaunchScope ls("k_tc_last", st);
-    k_tc_last<<<blocks, 128, lay.H * sizeof(float), st>>>(
-        SL, CL, params + lay.w_off(last), params + lay.b_off(last), target, extra_g, rows, tiles, lay.H,
-        dfac, d->hidden_omega_0, d->outermost_linear, loss_kind, grad_scale, gvec,
-        grads ? grads + lay.b_off(last) : nullptr, opt ? &opt->loss_acc[0] : nullptr, out, training, training ? EL : nullptr); }
+    k_tc_last<<<blocks, 128, H * sizeof(float), st>>>(SL, CL, w, b, target, extra_g, rows, tiles, H, dfac,
+                                                      d->hidden_omega_0, d->outermost_linear, loss_kind, grad_scale, gvec,
+                                                      gb, loss_acc, out, training, EL); }
   INR_LAUNCH_CHECK();
-  return INR_OK;
+  if (!training) return INR_OK;
+  int rc;
+  // Snake layer L: its `a` gradient = column sums of the g w dy/da products k_tc_last left in E(L)
+  if (EL && (rc = colsum(EL, H, tiles, nullptr, nullptr, 1, rows, 0, 1, 1.f, grads + lay.a_off(lay.L), nullptr, 1, 0, st)))
+    return rc;
+  // last-layer weight gradient: gw_out[f] += sum_r g[r] S_L[r][f]
+  return colsum(SL, H, tiles, gvec, nullptr, 1, rows, 0, 1, 1.f, nullptr, gw, 1, 1, st);
 }
 
 // forward of hidden layer l (1..L) by its activation kind: Sout = act(Sin W^T + b), Cout = derivative image,
@@ -733,12 +982,6 @@ int siren_tc_train(const inr_siren_desc* d, const float* params, const float* co
     if (!fused_tail) {
     if ((rc = last_layer(d, params, S(L), C(L), target ? target + r0 : nullptr, extra_gout ? extra_gout + r0 : nullptr, rows,
                          tiles, loss_kind, grad_scale, w.gvec, grads, opt, out ? out + r0 : nullptr, 1, st, E(L))))
-      return rc;
-    // Snake layer L: its `a` gradient = column sums of the g w dy/da products k_tc_last left in E(L)
-    if (E(L) && (rc = colsum(E(L), H, tiles, nullptr, nullptr, 1, rows, 0, 1, 1.f, grads + lay.a_off(L), nullptr, 1, 0, st)))
-      return rc;
-    // last-layer weight gradient: gw_out[f] += sum_r g[r] S_L[r][f]
-    if ((rc = colsum(S(L), H, tiles, w.gvec, nullptr, 1, rows, 0, 1, 1.f, nullptr, grads + lay.w_off(L + 1), 1, 1, st)))
       return rc;
     }
     const bool fused_bwd = fused_ok(d) && tc_fused_bwd_mode();
