@@ -363,7 +363,7 @@ static int kan_layer_fwd(const KanLayout& k, int l, const float* x, const float*
   INR_LAUNCH_CHECK();
   dim3 grid((unsigned)cdiv(rows, BM), (unsigned)cdiv(out, BN), 1);
   { LaunchScope ls("k_sgemm_kan_fwd", st);
-    k_sgemm<true, true, EPI_STORE><<<grid, 256, 0, st>>>(w.phi, Kf, 1, w.wc[l], Kf, 1, rows, out, Kf, Kf, nullptr, 0.f, y, nullptr, out); }
+    sgemm_launch<true, true, EPI_STORE>(grid, st, w.phi, Kf, 1, w.wc[l], Kf, 1, rows, out, Kf, Kf, nullptr, 0.f, y, nullptr, out); }
   INR_LAUNCH_CHECK();
   return INR_OK;
 }
@@ -461,7 +461,7 @@ int kan_loss_backward(const inr_kan_desc* d, const float* params, const float* g
         const int64_t k_chunk = round_up(std::max<int64_t>(cdiv(rows, want), 256), BK);
         dim3 gdw((unsigned)cdiv(outw, BM), (unsigned)cdiv(Kf, BN), (unsigned)cdiv(rows, k_chunk));
         LaunchScope ls("k_sgemm_kan_dw", st);
-        k_sgemm<false, false, EPI_ATOMIC><<<gdw, 256, 0, st>>>(g, 1, outw, w.phi, 1, Kf, outw, Kf, rows, k_chunk, nullptr, 0.f,
+        sgemm_launch<false, false, EPI_ATOMIC>(gdw, st, g, 1, outw, w.phi, 1, Kf, outw, Kf, rows, k_chunk, nullptr, 0.f,
                                                                w.gwc, nullptr, Kf);
       }
       INR_LAUNCH_CHECK();
@@ -469,7 +469,7 @@ int kan_loss_backward(const inr_kan_desc* d, const float* params, const float* g
         // dPhi (rows x Kf) = g Wc, in place over Phi; then dx
         dim3 gdp((unsigned)cdiv(rows, BM), (unsigned)cdiv(Kf, BN), 1);
         { LaunchScope ls("k_sgemm_kan_dphi", st);
-          k_sgemm<true, false, EPI_STORE><<<gdp, 256, 0, st>>>(g, outw, 1, w.wc[l], 1, Kf, rows, Kf, outw, outw, nullptr, 0.f,
+          sgemm_launch<true, false, EPI_STORE>(gdp, st, g, outw, 1, w.wc[l], 1, Kf, rows, Kf, outw, outw, nullptr, 0.f,
                                                                w.phi, nullptr, Kf); }
         INR_LAUNCH_CHECK();
         { LaunchScope ls("k_kan_dx", st);

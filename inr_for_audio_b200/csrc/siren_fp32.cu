@@ -30,17 +30,17 @@ static int fwd_layer(const inr_siren_desc* d, const float* params, int layer, co
   switch (lay.kind(layer)) {
     case ACT_SINE: {
       LaunchScope ls("k_sgemm_fwd_sincos", st);
-      k_sgemm<true, true, EPI_SINCOS><<<grid, 256, 0, st>>>(Sin, H, 1, W, H, 1, rows, H, H, H, b, d->hidden_omega_0, Sout,
+      sgemm_launch<true, true, EPI_SINCOS>(grid, st, Sin, H, 1, W, H, 1, rows, H, H, H, b, d->hidden_omega_0, Sout,
                                                             Cout, H);
     } break;
     case ACT_SNAKE: {
       LaunchScope ls("k_sgemm_fwd_snake", st);
-      k_sgemm<true, true, EPI_SNAKE><<<grid, 256, 0, st>>>(Sin, H, 1, W, H, 1, rows, H, H, H, b, 1.f, Sout, Cout, H,
+      sgemm_launch<true, true, EPI_SNAKE>(grid, st, Sin, H, 1, W, H, 1, rows, H, H, H, b, 1.f, Sout, Cout, H,
                                                            params + lay.a_off(layer), Eout);
     } break;
     default: {
       LaunchScope ls("k_sgemm_fwd_tanh", st);
-      k_sgemm<true, true, EPI_TANH><<<grid, 256, 0, st>>>(Sin, H, 1, W, H, 1, rows, H, H, H, b, 1.f, Sout, Cout, H);
+      sgemm_launch<true, true, EPI_TANH>(grid, st, Sin, H, 1, W, H, 1, rows, H, H, H, b, 1.f, Sout, Cout, H);
     } break;
   }
   INR_LAUNCH_CHECK();
@@ -57,11 +57,11 @@ static int first_layer_any(const inr_siren_desc* d, const float* params, const f
   dim3 grid((unsigned)cdiv(rows, BM), (unsigned)cdiv(H, BN), 1);
   if (lay.first_snake) {
     LaunchScope ls("k_sgemm_first_snake", st);
-    k_sgemm<true, true, EPI_SNAKE><<<grid, 256, 0, st>>>(xc, K, 1, params + lay.w_off(0), K, 1, rows, H, K, K,
+    sgemm_launch<true, true, EPI_SNAKE>(grid, st, xc, K, 1, params + lay.w_off(0), K, 1, rows, H, K, K,
                                                          params + lay.b_off(0), 1.f, S0, C0, H, params + lay.a_off(0), E0);
   } else {
     LaunchScope ls("k_sgemm_first_sincos", st);
-    k_sgemm<true, true, EPI_SINCOS><<<grid, 256, 0, st>>>(xc, K, 1, params + lay.w_off(0), K, 1, rows, H, K, K,
+    sgemm_launch<true, true, EPI_SINCOS>(grid, st, xc, K, 1, params + lay.w_off(0), K, 1, rows, H, K, K,
                                                           params + lay.b_off(0), d->first_omega_0, S0, C0, H);
   }
   INR_LAUNCH_CHECK();
@@ -77,7 +77,7 @@ static int first_layer_grad_any(const inr_siren_desc* d, const float* dZ0, const
   const int64_t k_chunk = round_up(std::max<int64_t>(cdiv(rows, want), 256), BK);
   dim3 gdw((unsigned)cdiv(H, BM), (unsigned)cdiv(K, BN), (unsigned)cdiv(rows, k_chunk));
   { LaunchScope ls("k_sgemm_dw0", st);
-    k_sgemm<false, false, EPI_ATOMIC><<<gdw, 256, 0, st>>>(dZ0, 1, H, xc, 1, K, H, K, rows, k_chunk, nullptr, 0.f, gW,
+    sgemm_launch<false, false, EPI_ATOMIC>(gdw, st, dZ0, 1, H, xc, 1, K, H, K, rows, k_chunk, nullptr, 0.f, gW,
                                                            nullptr, K); }
   INR_LAUNCH_CHECK();
   return launch_colsum<float>(dZ0, rows, H, gb, st);
@@ -157,7 +157,7 @@ int siren_fp32_train(const inr_siren_desc* d, const float* params, const float* 
       int64_t k_chunk = round_up(std::max<int64_t>(cdiv(rows, want), 256), BK);
       dim3 gdw((unsigned)cdiv(H, BM), (unsigned)cdiv(H, BN), (unsigned)cdiv(rows, k_chunk));
       { LaunchScope ls("k_sgemm_dw", st);
-      k_sgemm<false, false, EPI_ATOMIC><<<gdw, 256, 0, st>>>(C(l), 1, H, S(l - 1), 1, H, H, H, rows, k_chunk, nullptr,
+      sgemm_launch<false, false, EPI_ATOMIC>(gdw, st, C(l), 1, H, S(l - 1), 1, H, H, H, rows, k_chunk, nullptr,
                                                              0.f, grads + lay.w_off(l), nullptr, H); }
       INR_LAUNCH_CHECK();
       rc = launch_colsum<float>(C(l), rows, H, grads + lay.b_off(l), st);
@@ -169,13 +169,13 @@ int siren_fp32_train(const inr_siren_desc* d, const float* params, const float* 
       const int kprev = lay.kind(l - 1);
       if (kprev == ACT_SNAKE) {
         LaunchScope ls("k_sgemm_bwd_snake", st);
-        k_sgemm<true, false, EPI_DMUL_GA><<<gbw, 256, 0, st>>>(C(l), H, 1, params + lay.w_off(l), 1, H, rows, H, H, H,
+        sgemm_launch<true, false, EPI_DMUL_GA>(gbw, st, C(l), H, 1, params + lay.w_off(l), 1, H, rows, H, H, H,
                                                                nullptr, 1.f, C(l - 1), nullptr, H, E(l - 1),
                                                                grads + lay.a_off(l - 1));
       } else {
         const float om = kprev == ACT_TANH ? 1.f : ((l - 1 == 0) ? d->first_omega_0 : d->hidden_omega_0);
         LaunchScope ls("k_sgemm_bwd_cosmul", st);
-        k_sgemm<true, false, EPI_COSMUL><<<gbw, 256, 0, st>>>(C(l), H, 1, params + lay.w_off(l), 1, H, rows, H, H, H,
+        sgemm_launch<true, false, EPI_COSMUL>(gbw, st, C(l), H, 1, params + lay.w_off(l), 1, H, rows, H, H, H,
                                                               nullptr, om, C(l - 1), nullptr, H);
       }
       INR_LAUNCH_CHECK();
