@@ -2,7 +2,7 @@
 with torch eager on the same GPU, for the converge.npz configuration."""
 import os, sys
 import numpy as np, torch
-ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+ROOT = os.path.dirname(os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 sys.path.insert(0, ROOT)
 import inr_for_audio_b200 as P
 from oracle import inr_oracle as O

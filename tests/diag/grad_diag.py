@@ -1,7 +1,7 @@
 """Per-tensor gradient error of the bf16 mode against the fp32 oracle (diagnostic): python tools/grad_diag.py H L n"""
 import os, sys
 import numpy as np, torch
-ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+ROOT = os.path.dirname(os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 sys.path.insert(0, ROOT)
 import inr_for_audio_b200 as P
 from oracle import inr_oracle as O
