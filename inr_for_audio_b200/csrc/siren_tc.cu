@@ -42,7 +42,9 @@ __global__ void __launch_bounds__(256) k_tc_first(const float* __restrict__ W, c
                                                   const float* __restrict__ coords, int in, int H, int64_t rows,
                                                   int64_t rows_pad, int64_t g0, int64_t T_total, float scale,
                                                   float omega, __nv_bfloat16* __restrict__ S0,
-                                                  __nv_bfloat16* __restrict__ C0) {
+                                                  __nv_bfloat16* __restrict__ C0, const float* __restrict__ Aparam,
+                                                  __nv_bfloat16* __restrict__ E0) {
+  // Aparam != NULL: first_linear (models.py:343-347), layer 0 = nn.Linear + Snake: S0 = y, C0 = dy/dz, E0 = dy/da
   const int lg = 31 - __clz(H >> 3);                      // H/8 feature groups: a power of two on this path
   const int64_t total = rows_pad << lg;
   for (int64_t idx = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; idx < total; idx += (int64_t)gridDim.x * blockDim.x) {
@@ -59,22 +61,34 @@ __global__ void __launch_bounds__(256) k_tc_first(const float* __restrict__ W, c
     } else {
       x0 = linspace_at(g0 + row, T_total, scale);
     }
-    uint32_t so[4], co[4];
+    uint32_t so[4], co[4], eo[4];
 #pragma unroll
     for (int h = 0; h < 4; ++h) {
-      float s[2], c[2];
+      float s[2], c[2], e[2] = {0.f, 0.f};
 #pragma unroll
       for (int u = 0; u < 2; ++u) {
         const int f = kg * 8 + h * 2 + u;
         const float z = (in == 1) ? __fmaf_rn(x0, W[f], B[f]) : (__fmaf_rn(x1, W[f * 2 + 1], x0 * W[f * 2]) + B[f]);
-        sincos_reduced(omega * z, &s[u], &c[u]);
+        if (Aparam) {
+          const float a = Aparam[f], ia = 1.0f / a;
+          float sn, cs;
+          sincos_reduced(z * a, &sn, &cs);
+          const float s2 = sn * sn, sc2 = 2.f * sn * cs;
+          s[u] = __fmaf_rn(ia, s2, z);
+          c[u] = 1.f + sc2;
+          e[u] = ia * (z * sc2 - ia * s2);
+        } else {
+          sincos_reduced(omega * z, &s[u], &c[u]);
+        }
       }
       so[h] = pack_bf16x2(s[0], s[1]);
       co[h] = pack_bf16x2(c[0], c[1]);
+      eo[h] = pack_bf16x2(e[0], e[1]);
     }
     const int64_t off = idx * 8;   // == ((tile*groups + kg)*128 + r)*8
     *reinterpret_cast<uint4*>(S0 + off) = make_uint4(so[0], so[1], so[2], so[3]);
     if (C0) *reinterpret_cast<uint4*>(C0 + off) = make_uint4(co[0], co[1], co[2], co[3]);
+    if (Aparam && E0) *reinterpret_cast<uint4*>(E0 + off) = make_uint4(eo[0], eo[1], eo[2], eo[3]);
   }
 }
 
@@ -451,9 +465,9 @@ bool tc_pair_mode();
 bool siren_tc_supported(const inr_siren_desc* d) {
   const int H = d->hidden_features;
   const int Ltot = d->hidden_layers + d->num_snake + d->num_tanh;
-  // Snake / Tanh hidden layers exist in the CTA-pair kernel only; a Linear+Snake FIRST layer runs in the fp32 mode
-  const bool sine_only = d->num_snake == 0 && d->num_tanh == 0;
-  return (H == 128 || H == 256 || H == 512) && Ltot >= 1 && d->out_features == 1 && d->first_linear == 0 &&
+  // Snake / Tanh layers (hidden, or a Linear+Snake first layer) exist in the CTA-pair kernel only
+  const bool sine_only = d->num_snake == 0 && d->num_tanh == 0 && d->first_linear == 0;
+  return (H == 128 || H == 256 || H == 512) && Ltot >= 1 && d->out_features == 1 &&
          d->in_features <= 2 &&   // encoded inputs (in_features = 2*num_freq) run in the fp32 mode
          (sine_only || tc_pair_mode());
 }
@@ -791,13 +805,15 @@ static int pack_weights(const inr_siren_desc* d, const float* params, const TcWo
 }
 
 static int first_layer(const inr_siren_desc* d, const float* params, const float* coords, int64_t rows, int64_t rows_pad,
-                       int64_t g0, int64_t T_total, float scale, __nv_bfloat16* S0, __nv_bfloat16* C0, cudaStream_t st) {
+                       int64_t g0, int64_t T_total, float scale, __nv_bfloat16* S0, __nv_bfloat16* C0, cudaStream_t st,
+                       __nv_bfloat16* E0 = nullptr) {
   SirenLayout lay = layout_of(d);
   const int64_t total = rows_pad * (lay.H / 8);
   int blocks = (int)std::min<int64_t>(cdiv(total, 256), (int64_t)num_sms() * 16);
   { LaunchScope ls("k_tc_first", st);
     k_tc_first<<<blocks, 256, 0, st>>>(params + lay.w_off(0), params + lay.b_off(0), coords, lay.in, lay.H, rows, rows_pad,
-                                       g0, T_total, scale, d->first_omega_0, S0, C0); }
+                                       g0, T_total, scale, d->first_omega_0, S0, C0,
+                                       lay.first_snake ? params + lay.a_off(0) : nullptr, E0); }
   INR_LAUNCH_CHECK();
   return INR_OK;
 }
@@ -968,7 +984,7 @@ int siren_tc_train(const inr_siren_desc* d, const float* params, const float* co
         if ((rc = fused_forward(d, params, w.Wf, xc, rows, tiles, i0 + r0, T_total, scale, Sl, Cl, fused_tail ? &fl : nullptr, st)))
           return rc;
       } else {
-      if ((rc = first_layer(d, params, xc, rows, rows_pad, i0 + r0, T_total, scale, S(0), C(0), st))) return rc;
+      if ((rc = first_layer(d, params, xc, rows, rows_pad, i0 + r0, T_total, scale, S(0), C(0), st, E(0)))) return rc;
       for (int l = 1; l <= L; ++l)
         if ((rc = fwd_layer_tc(d, lay, params, w, l, S(l - 1), S(l), C(l), E(l), tiles, st))) return rc;
       }

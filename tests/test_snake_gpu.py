@@ -130,18 +130,21 @@ def test_ragged_sizes_against_oracle(pkg):
         assert np.linalg.norm(grads.cpu().numpy() - go) <= 5e-5 * np.linalg.norm(go) + 1e-12
 
 
-@pytest.mark.parametrize("H,ns,nk,nt,last_lin,n", [(128, 1, 1, 1, True, 4099), (256, 2, 2, 0, True, 20000),
-                                                   (128, 0, 2, 0, True, 1000), (256, 1, 0, 2, False, 3000),
-                                                   (512, 1, 1, 0, True, 2500)])
-def test_bf16_mode_snake_tanh_against_oracle(pkg, H, ns, nk, nt, last_lin, n):
+@pytest.mark.parametrize("H,ns,nk,nt,last_lin,n,fl", [(128, 1, 1, 1, True, 4099, False), (256, 2, 2, 0, True, 20000, False),
+                                                      (128, 0, 2, 0, True, 1000, False), (256, 1, 0, 2, False, 3000, False),
+                                                      (512, 1, 1, 0, True, 2500, False),
+                                                      # first_linear: layer 0 = nn.Linear + Snake (models.py:343-347)
+                                                      (128, 1, 1, 0, True, 3001, True), (256, 2, 0, 1, True, 5000, True)])
+def test_bf16_mode_snake_tanh_against_oracle(pkg, H, ns, nk, nt, last_lin, n, fl):
     """Snake / Tanh hidden layers in the tcgen05 mode (CTA-pair layer kernel, MODE_FWD_SNAKE / MODE_FWD_TANH /
     MODE_BWD_SNAKE): loss within 1e-3 relative, gradients (incl. the Snake `a` gradients) within bf16 rounding noise
     of the fp32 oracle."""
     from oracle import inr_oracle as O
-    ospec = O.SirenSpec(1, H, ns, 1, last_lin, 30.0, 30.0, num_snake=nk, num_tanh=nt, a_initial=0.5)
-    spec = pkg.SirenSpec(1, H, ns, 1, last_lin, 30.0, 30.0, nk, nt, False)
+    ospec = O.SirenSpec(1, H, ns, 1, last_lin, 30.0, 30.0, num_snake=nk, num_tanh=nt, first_linear=fl, a_initial=0.5)
+    spec = pkg.SirenSpec(1, H, ns, 1, last_lin, 30.0, 30.0, nk, nt, fl)
     ps = O.siren_init(ospec, seed=H + ns)
     flat = torch.cat([p.reshape(-1) for p in ps])
+    assert flat.numel() == spec.num_params()
     gt = torch.from_numpy(pkg.utils.synth_waveform(max(n, 2), seed=3)[:n].copy())
     coords = O.get_coord(n, 1).view(-1, 1)
     loss_o, _, grads_o, out_o = O.siren_loss_and_grads(ospec, ps, coords, gt.view(-1, 1))
@@ -172,12 +175,13 @@ def test_bf16_mode_snake_tanh_against_oracle(pkg, H, ns, nk, nt, last_lin, n):
     np.testing.assert_allclose(f2.forward().cpu().numpy(), f2.forward().cpu().numpy())
 
 
-def test_bf16_mode_rejects_first_linear(pkg):
-    """a Linear+Snake FIRST layer (first_linear=True) exists in the fp32 mode only"""
+def test_bf16_mode_rejects_wide_inputs(pkg):
+    """an encoded coordinate (in_features > 2) exists in the fp32 mode only: the bf16 mode refuses it loudly"""
     from inr_for_audio_b200 import _lib as L
-    spec = pkg.SirenSpec(1, 128, 1, 1, True, 30.0, 30.0, 1, 0, True)
+    spec = pkg.SirenSpec(16, 128, 1, 1, True, 30.0, 30.0)
     with pytest.raises(L.InrLibraryError):
-        pkg.SirenFitter(spec, torch.zeros(spec.num_params()), torch.zeros(256, device=dev()), precision="bf16")
+        pkg.SirenFitter(spec, torch.zeros(spec.num_params()), torch.zeros(256, device=dev()),
+                        torch.zeros(256, 16, device=dev()), precision="bf16")
 
 
 def test_train_dropin_default_architecture(pkg, tmp_path):
