@@ -49,7 +49,7 @@ extern "C" {
  * The bf16 tcgen05 mode takes the sine-only stack; Snake/Tanh stacks run in INR_PREC_FP32. */
 typedef struct {
   int32_t in_features;     /* 1 (waveform), 2 (MDCT image), or the width of an encoded
-                              coordinate (2*num_freq, run.py:81-82; fp32 mode only)  */
+                              coordinate (2*num_freq, run.py:81-82; bf16 mode: <= hidden_features) */
   int32_t hidden_features; /* H                                                   */
   int32_t hidden_layers;   /* number of HxH SineLayers (num_sine)                 */
   int32_t out_features;    /* must be 1                                           */

@@ -82,7 +82,7 @@ static int check_desc(const inr_siren_desc* d) {
               d->precision);
   if (d->precision == INR_PREC_BF16)
     INR_REQUIRE(siren_tc_supported(d), INR_E_UNSUPPORTED,
-                "bf16 tcgen05 path needs in_features <= 2, hidden_features in {128,256,512} and >= 1 hidden layer "
+                "bf16 tcgen05 path needs in_features <= hidden_features, hidden_features in {128,256,512} and >= 1 hidden layer "
                 "(got in=%d H=%d sine=%d snake=%d tanh=%d first_linear=%d); use INR_PREC_FP32",
                 d->in_features, d->hidden_features, d->hidden_layers, d->num_snake, d->num_tanh, d->first_linear);
   return INR_OK;

@@ -35,6 +35,50 @@ __global__ void __launch_bounds__(256) k_tc_pack(const float* __restrict__ param
   }
 }
 
+// ------------------------------------------------------------------------------------------------ wide inputs
+// Encoded coordinates (in_features = 2*num_freq > 2, run.py:81-82,141-144) on the tcgen05 path: the input rows become one
+// more tile image X (bf16, zero-padded to H columns) and layer 0 one more H x H layer GEMM with W_0 zero-padded to H
+// input columns; its weight gradient is the dW GEMM against X, cut back to (H x in).  Needs in_features <= H.
+__global__ void __launch_bounds__(256) k_tc_pack0(const float* __restrict__ W0, int in, int H, int NS,
+                                                  __nv_bfloat16* __restrict__ Wf0) {
+  const int total = H * H;
+  for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < total; i += gridDim.x * blockDim.x) {
+    const int o = i / H, k = i - o * H;
+    const float v = k < in ? W0[(int64_t)o * in + k] : 0.f;
+    Wf0[(int64_t)(o / NS) * ((int64_t)H * NS) + ((int64_t)(k >> 3) * NS + (o % NS)) * 8 + (k & 7)] = __float2bfloat16_rn(v);
+  }
+}
+
+// X[tile][group][row][8] <- coords (rows x in) fp32, zero beyond `in` columns and `rows` rows
+__global__ void __launch_bounds__(256) k_tc_rows_to_image(const float* __restrict__ coords, int in, int H, int64_t rows,
+                                                          int64_t rows_pad, __nv_bfloat16* __restrict__ X) {
+  const int lg = 31 - __clz(H >> 3);
+  const int64_t total = rows_pad << lg;
+  for (int64_t idx = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; idx < total; idx += (int64_t)gridDim.x * blockDim.x) {
+    const int r = (int)(idx & (TILE_ROWS - 1));
+    const int64_t tg = idx >> 7;
+    const int kg = (int)(tg & ((1 << lg) - 1));
+    const int64_t row = (tg >> lg) * TILE_ROWS + r;
+    float v[8];
+#pragma unroll
+    for (int j = 0; j < 8; ++j) {
+      const int f = kg * 8 + j;
+      v[j] = (row < rows && f < in) ? coords[row * in + f] : 0.f;
+    }
+    *reinterpret_cast<uint4*>(X + idx * 8) = make_uint4(pack_bf16x2(v[0], v[1]), pack_bf16x2(v[2], v[3]),
+                                                        pack_bf16x2(v[4], v[5]), pack_bf16x2(v[6], v[7]));
+  }
+}
+
+// gW_0 (H x in) += the first `in` columns of the padded H x H gradient
+__global__ void __launch_bounds__(256) k_tc_unpad_add(const float* __restrict__ gpad, int in, int H, float* __restrict__ gW) {
+  const int total = H * in;
+  for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < total; i += gridDim.x * blockDim.x) {
+    const int o = i / in, k = i - o * in;
+    gW[i] += gpad[(int64_t)o * H + k];
+  }
+}
+
 // ------------------------------------------------------------------------------------------------ first layer
 // one thread = one row x one feature group (8 features); consecutive threads = consecutive rows of a tile.
 // sincos_reduced (tc_fused.cuh): fp32 argument omega*z as the reference forms it, Cody-Waite reduction, MUFU sincos.
@@ -468,7 +512,7 @@ bool siren_tc_supported(const inr_siren_desc* d) {
   // Snake / Tanh layers (hidden, or a Linear+Snake first layer) exist in the CTA-pair kernel only
   const bool sine_only = d->num_snake == 0 && d->num_tanh == 0 && d->first_linear == 0;
   return (H == 128 || H == 256 || H == 512) && Ltot >= 1 && d->out_features == 1 &&
-         d->in_features <= 2 &&   // encoded inputs (in_features = 2*num_freq) run in the fp32 mode
+         (d->in_features <= 2 || d->in_features <= H) &&   // encoded inputs: zero-padded to H (k_tc_rows_to_image)
          (sine_only || tc_pair_mode());
 }
 
@@ -492,8 +536,9 @@ static TcPlan plan_of(const inr_siren_desc* d, int training) {
   TcPlan pl;
   const SirenLayout lay = layout_of(d);
   const int64_t H = lay.H, L = lay.L;
-  pl.pack_bytes = 2 * L * H * H * 2;
-  pl.n_images = training ? 2 * (int)(L + 1) + lay.num_snake_layers() : 2;   // + one dy/da image per Snake layer
+  const bool wide = lay.in > 2;
+  pl.pack_bytes = 2 * L * H * H * 2 + (wide ? H * H * 2 + H * H * 4 : 0);   // + padded W_0 operand, padded gW_0 scratch
+  pl.n_images = (training ? 2 * (int)(L + 1) + lay.num_snake_layers() : 2) + (wide ? 1 : 0);   // + dy/da images, + X
   pl.img_bytes_per_row = pl.n_images * H * 2 + (training ? 4 : 0);   // + gvec
   pl.fixed_bytes = round_up(pl.pack_bytes, 1024) + 4096;
   pl.gvec_bytes = 0;
@@ -647,7 +692,7 @@ bool tc_fused_last_mode() {
 static bool fused_ok(const inr_siren_desc* d) {
   return tc_fused_mode() && tc_pair_mode() && (d->hidden_features == 128 || d->hidden_features == 256) &&
          d->hidden_layers >= 1 && d->hidden_layers <= FUSED_MAX_L && d->num_snake == 0 && d->num_tanh == 0 &&
-         d->first_linear == 0;
+         d->first_linear == 0 && d->in_features <= 2;
 }
 
 // INR_TC_FUSED_BWD=1 selects the fused backward chain k_tc_fused_bwd (H <= 256).  Measured on B200
@@ -767,6 +812,9 @@ static int colsum(const __nv_bfloat16* X, int H, int tiles, const float* wrow, c
 
 struct TcWorkspace {
   __nv_bfloat16 *Wf, *Wb;
+  __nv_bfloat16* Wf0;   // wide inputs: W_0 zero-padded to H x H (forward operand)
+  float* gW0;           // wide inputs: H x H fp32 scratch of the padded first-layer weight gradient
+  int x_image;          // wide inputs: index of the input image X, else -1
   float* gvec;
   __nv_bfloat16* img;
   int64_t chunk_rows;   // multiple of 128
@@ -780,6 +828,9 @@ static int carve(const inr_siren_desc* d, int training, int64_t n, void* ws, int
   const int64_t usable = ws_bytes - (base - reinterpret_cast<uint8_t*>(ws));
   w->Wf = reinterpret_cast<__nv_bfloat16*>(base);
   w->Wb = w->Wf + L * H * H;
+  w->Wf0 = w->Wb + L * H * H;
+  w->gW0 = reinterpret_cast<float*>(w->Wf0 + H * H);
+  w->x_image = d->in_features > 2 ? pl.n_images - 1 : -1;
   int64_t avail = usable - pl.fixed_bytes;
   int64_t rows = avail / pl.img_bytes_per_row / TILE_ROWS * TILE_ROWS;
   INR_REQUIRE(rows >= TILE_ROWS, INR_E_WORKSPACE, "workspace of %lld bytes is too small for one 128-row tile", (long long)ws_bytes);
@@ -801,6 +852,11 @@ static int pack_weights(const inr_siren_desc* d, const float* params, const TcWo
   { LaunchScope ls("k_tc_pack", st);
     k_tc_pack<<<blocks, 256, 0, st>>>(params, lay, ns_of(lay.H), w.Wf, w.Wb); }
   INR_LAUNCH_CHECK();
+  if (lay.in > 2) {
+    LaunchScope ls("k_tc_pack", st);
+    k_tc_pack0<<<(lay.H * lay.H + 255) / 256, 256, 0, st>>>(params + lay.w_off(0), lay.in, lay.H, ns_of(lay.H), w.Wf0);
+    INR_LAUNCH_CHECK();
+  }
   return INR_OK;
 }
 
@@ -904,6 +960,23 @@ static int fwd_layer_tc(const inr_siren_desc* d, const SirenLayout& lay, const f
   return tc_layer(H, kind == ACT_SINE ? MODE_FWD : (kind == ACT_SNAKE ? MODE_FWD_SNAKE : MODE_FWD_TANH), p, st);
 }
 
+// layer 0 on an encoded coordinate: X image from the rows, then the layer GEMM with the padded W_0
+static int first_layer_wide(const inr_siren_desc* d, const SirenLayout& lay, const float* params, const TcWorkspace& w,
+                            const float* xc, int64_t rows, int64_t rows_pad, __nv_bfloat16* X, __nv_bfloat16* S0,
+                            __nv_bfloat16* C0, __nv_bfloat16* E0, int tiles, cudaStream_t st) {
+  const int H = lay.H;
+  const int64_t total = rows_pad * (H / 8);
+  const int blocks = (int)std::min<int64_t>(cdiv(total, 256), (int64_t)num_sms() * 16);
+  { LaunchScope ls("k_tc_rows_to_image", st);
+    k_tc_rows_to_image<<<blocks, 256, 0, st>>>(xc, lay.in, H, rows, rows_pad, X); }
+  INR_LAUNCH_CHECK();
+  const int kind = lay.kind(0);
+  LayerParams p = layer_params(H, X, w.Wf0, params + lay.b_off(0), kind == ACT_SINE ? d->first_omega_0 : 1.f, S0, C0,
+                               nullptr, tiles);
+  if (kind == ACT_SNAKE) { p.avec = params + lay.a_off(0); p.out2 = E0; }
+  return tc_layer(H, kind == ACT_SINE ? MODE_FWD : MODE_FWD_SNAKE, p, st);
+}
+
 int siren_tc_forward(const inr_siren_desc* d, const float* params, const float* coords, int64_t n, int64_t i0,
                      int64_t T_total, float scale, float* out, void* ws, int64_t ws_bytes, cudaStream_t st) {
   SirenLayout lay = layout_of(d);
@@ -928,9 +1001,14 @@ int siren_tc_forward(const inr_siren_desc* d, const float* params, const float* 
         return rc;
       continue;
     }
-    if ((rc = first_layer(d, params, coords ? coords + r0 * lay.in : nullptr, rows, rows_pad, i0 + r0, T_total, scale, S[0],
-                          nullptr, st)))
-      return rc;
+    if (w.x_image >= 0) {
+      rc = first_layer_wide(d, lay, params, w, coords + r0 * lay.in, rows, rows_pad, w.img + (int64_t)w.x_image * w.img_elems,
+                            S[0], nullptr, nullptr, tiles, st);
+    } else {
+      rc = first_layer(d, params, coords ? coords + r0 * lay.in : nullptr, rows, rows_pad, i0 + r0, T_total, scale, S[0],
+                       nullptr, st);
+    }
+    if (rc) return rc;
     int cur = 0;
     for (int l = 1; l <= L; ++l) {
       if ((rc = fwd_layer_tc(d, lay, params, w, l, S[cur], S[cur ^ 1], nullptr, nullptr, tiles, st))) return rc;
@@ -984,7 +1062,13 @@ int siren_tc_train(const inr_siren_desc* d, const float* params, const float* co
         if ((rc = fused_forward(d, params, w.Wf, xc, rows, tiles, i0 + r0, T_total, scale, Sl, Cl, fused_tail ? &fl : nullptr, st)))
           return rc;
       } else {
-      if ((rc = first_layer(d, params, xc, rows, rows_pad, i0 + r0, T_total, scale, S(0), C(0), st, E(0)))) return rc;
+      if (w.x_image >= 0) {
+        rc = first_layer_wide(d, lay, params, w, xc, rows, rows_pad, w.img + (int64_t)w.x_image * w.img_elems, S(0), C(0),
+                              E(0), tiles, st);
+      } else {
+        rc = first_layer(d, params, xc, rows, rows_pad, i0 + r0, T_total, scale, S(0), C(0), st, E(0));
+      }
+      if (rc) return rc;
       for (int l = 1; l <= L; ++l)
         if ((rc = fwd_layer_tc(d, lay, params, w, l, S(l - 1), S(l), C(l), E(l), tiles, st))) return rc;
       }
@@ -1033,6 +1117,18 @@ int siren_tc_train(const inr_siren_desc* d, const float* params, const float* co
       } else if ((rc = tc_layer(H, MODE_BWD, p, st))) {
         return rc;
       }
+    }
+    if (w.x_image >= 0) {
+      // encoded input: gW_0 = dZ_0^T X as one more dW GEMM into the padded scratch, cut back to (H x in); gb_0 with it
+      INR_CUDA_CHECK(cudaMemsetAsync(w.gW0, 0, (size_t)H * H * sizeof(float), st));
+      DwParams dp;
+      dp.dZ = C(0); dp.S = w.img + (int64_t)w.x_image * w.img_elems; dp.gW = w.gW0; dp.gb = grads + lay.b_off(0);
+      dp.num_tiles = tiles; dp.lbo = 128; dp.sbo = TILE_ROWS * 16;
+      if ((rc = tc_dw(H, dp, st))) return rc;
+      { LaunchScope ls("k_tc_unpad_add", st);
+        k_tc_unpad_add<<<(H * lay.in + 255) / 256, 256, 0, st>>>(w.gW0, lay.in, H, grads + lay.w_off(0)); }
+      INR_LAUNCH_CHECK();
+      continue;
     }
     // first layer: gW_0[f][i] += sum_r dZ_0[r][f] x[r][i], gb_0 += colsum(dZ_0)
     if (!fused_bwd && (rc = colsum(C(0), H, tiles, nullptr, xc, lay.in, rows, i0 + r0, T_total, scale, grads + lay.b_off(0),

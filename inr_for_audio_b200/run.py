@@ -103,8 +103,8 @@ def train(experiment_path: str, tag: str, inst: str, duration: int, num_channels
     takelog = False
     if num_freq is not None and method != 'wave':
         raise ValueError("num_freq: the reference's GaussianEncoding(10.0, 1, num_freq) takes 1-D coordinates (run.py:142)")
-    if num_freq is not None and (arch == 'kan' or precision != 'fp32'):
-        raise NotImplementedError("num_freq (encoded first layer, in_features = 2*num_freq) runs in the fp32 SIREN mode only")
+    if num_freq is not None and arch == 'kan':
+        raise NotImplementedError("num_freq: KAN([1,H,H,1]) hard-codes one input (run.py:93,110)")
     if arch == 'kan' and (method != 'wave' or alpha != 0.0 or loss_mode == 'snr'):
         raise NotImplementedError("arch='kan' is waveform-only (run.py:93,110) with the mse/mae losses on the device path")
     if alpha != 0.0 and method != 'wave':

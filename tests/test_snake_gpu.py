@@ -176,12 +176,12 @@ def test_bf16_mode_snake_tanh_against_oracle(pkg, H, ns, nk, nt, last_lin, n, fl
 
 
 def test_bf16_mode_rejects_wide_inputs(pkg):
-    """an encoded coordinate (in_features > 2) exists in the fp32 mode only: the bf16 mode refuses it loudly"""
+    """the bf16 mode pads an encoded coordinate to H columns: in_features > H is refused loudly (fp32 mode takes it)"""
     from inr_for_audio_b200 import _lib as L
-    spec = pkg.SirenSpec(16, 128, 1, 1, True, 30.0, 30.0)
+    spec = pkg.SirenSpec(200, 128, 1, 1, True, 30.0, 30.0)
     with pytest.raises(L.InrLibraryError):
         pkg.SirenFitter(spec, torch.zeros(spec.num_params()), torch.zeros(256, device=dev()),
-                        torch.zeros(256, 16, device=dev()), precision="bf16")
+                        torch.zeros(256, 200, device=dev()), precision="bf16")
 
 
 def test_train_dropin_default_architecture(pkg, tmp_path):
