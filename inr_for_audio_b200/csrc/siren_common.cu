@@ -111,7 +111,10 @@ template int launch_first_layer<__nv_bfloat16>(const inr_siren_desc*, const floa
 // ------------------------------------------------------------------------------------------------
 constexpr int kMaxHPerLane = 32;  // H <= 1024
 
-template <typename ActT, bool SNAKE>
+// NPER = per-lane feature slots (H <= 32*NPER), a compile-time bound so that the three per-lane arrays take NPER registers
+// each: at H = 256 that is ~50 registers instead of ~110, i.e. five resident blocks per SM instead of two -- this kernel
+// lives on memory-level parallelism (one row per warp in flight).
+template <typename ActT, bool SNAKE, int NPER>
 __global__ void __launch_bounds__(256) k_last_layer(const ActT* __restrict__ S, ActT* __restrict__ CdZ,
                                                     const ActT* __restrict__ E, float* __restrict__ gA,
                                                     const float* __restrict__ w, const float* __restrict__ bptr,
@@ -129,9 +132,9 @@ __global__ void __launch_bounds__(256) k_last_layer(const ActT* __restrict__ S, 
     for (int i = threadIdx.x; i <= (SNAKE ? 2 * H : H); i += blockDim.x) s_gw[i] = 0.f;
     __syncthreads();
   }
-  float wreg[kMaxHPerLane], gacc[kMaxHPerLane], aacc[SNAKE ? kMaxHPerLane : 1];
+  float wreg[NPER], gacc[NPER], aacc[SNAKE ? NPER : 1];
 #pragma unroll
-  for (int j = 0; j < kMaxHPerLane; ++j) {
+  for (int j = 0; j < NPER; ++j) {
     const int h = j * 32 + lane;
     wreg[j] = (j < nper && h < H) ? w[h] : 0.f;
     gacc[j] = 0.f;
@@ -144,10 +147,10 @@ __global__ void __launch_bounds__(256) k_last_layer(const ActT* __restrict__ S, 
   const int64_t nwarps = (int64_t)gridDim.x * warps_per_block;
   for (int64_t r = warp0; r < rows; r += nwarps) {
     const ActT* srow = S + r * H;
-    float sreg[kMaxHPerLane];
+    float sreg[NPER];
     float dot = 0.f;
 #pragma unroll
-    for (int j = 0; j < kMaxHPerLane; ++j) {
+    for (int j = 0; j < NPER; ++j) {
       const int h = j * 32 + lane;
       if (j < nper && h < H) {
         sreg[j] = to_f(srow[h]);
@@ -184,7 +187,7 @@ __global__ void __launch_bounds__(256) k_last_layer(const ActT* __restrict__ S, 
     ActT* crow = CdZ + r * H;
     const float gw = g * omega_prev;
 #pragma unroll
-    for (int j = 0; j < kMaxHPerLane; ++j) {
+    for (int j = 0; j < NPER; ++j) {
       const int h = j * 32 + lane;
       if (j < nper && h < H) {
         gacc[j] = __fmaf_rn(g, sreg[j], gacc[j]);
@@ -196,7 +199,7 @@ __global__ void __launch_bounds__(256) k_last_layer(const ActT* __restrict__ S, 
   }
   if (!training) return;
 #pragma unroll
-  for (int j = 0; j < kMaxHPerLane; ++j) {
+  for (int j = 0; j < NPER; ++j) {
     const int h = j * 32 + lane;
     if (j < nper && h < H) {
       atomicAdd(&s_gw[h], gacc[j]);
@@ -230,17 +233,31 @@ int launch_last_layer(const inr_siren_desc* d, const float* params, const ActT* 
   const bool snake = training && kindL == ACT_SNAKE && EL != nullptr;
   int blocks = (int)std::min<int64_t>(cdiv(rows, 8), (int64_t)num_sms() * 4);
   if (blocks < 1) blocks = 1;
+  const int nper = (H + 31) / 32;
+  blocks = (int)std::min<int64_t>(cdiv(rows, 8), (int64_t)num_sms() * (nper <= 8 ? 10 : 4));
+  if (blocks < 1) blocks = 1;
   { LaunchScope ls("k_last_layer", st);
-  if (snake)
-    k_last_layer<ActT, true><<<blocks, 256, (2 * H + 1) * sizeof(float), st>>>(
-        SL, CL_dZ, EL, grads + lay.a_off(lay.L), params + lay.w_off(last), params + lay.b_off(last), target, extra_gout,
-        rows, H, dfac, d->hidden_omega_0, d->outermost_linear, loss_kind, grad_scale, grads + lay.w_off(last),
-        grads + lay.b_off(last), opt ? &opt->loss_acc[0] : nullptr, out, training);
-  else
-    k_last_layer<ActT, false><<<blocks, 256, (H + 1) * sizeof(float), st>>>(
-        SL, CL_dZ, nullptr, nullptr, params + lay.w_off(last), params + lay.b_off(last), target, extra_gout, rows, H,
-        dfac, d->hidden_omega_0, d->outermost_linear, loss_kind, grad_scale, grads ? grads + lay.w_off(last) : nullptr,
-        grads ? grads + lay.b_off(last) : nullptr, opt ? &opt->loss_acc[0] : nullptr, out, training); }
+#define INR_LAST_LAUNCH(NP)                                                                                              \
+  do {                                                                                                                   \
+    if (snake)                                                                                                           \
+      k_last_layer<ActT, true, NP><<<blocks, 256, (2 * H + 1) * sizeof(float), st>>>(                                    \
+          SL, CL_dZ, EL, grads + lay.a_off(lay.L), params + lay.w_off(last), params + lay.b_off(last), target,           \
+          extra_gout, rows, H, dfac, d->hidden_omega_0, d->outermost_linear, loss_kind, grad_scale,                      \
+          grads + lay.w_off(last), grads + lay.b_off(last), opt ? &opt->loss_acc[0] : nullptr, out, training);           \
+    else                                                                                                                 \
+      k_last_layer<ActT, false, NP><<<blocks, 256, (H + 1) * sizeof(float), st>>>(                                       \
+          SL, CL_dZ, nullptr, nullptr, params + lay.w_off(last), params + lay.b_off(last), target, extra_gout, rows, H,  \
+          dfac, d->hidden_omega_0, d->outermost_linear, loss_kind, grad_scale,                                           \
+          grads ? grads + lay.w_off(last) : nullptr, grads ? grads + lay.b_off(last) : nullptr,                          \
+          opt ? &opt->loss_acc[0] : nullptr, out, training);                                                             \
+  } while (0)
+    if (nper <= 2) INR_LAST_LAUNCH(2);
+    else if (nper <= 4) INR_LAST_LAUNCH(4);
+    else if (nper <= 8) INR_LAST_LAUNCH(8);
+    else if (nper <= 16) INR_LAST_LAUNCH(16);
+    else INR_LAST_LAUNCH(32);
+#undef INR_LAST_LAUNCH
+  }
   INR_LAUNCH_CHECK();
   return INR_OK;
 }

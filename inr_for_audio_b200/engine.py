@@ -204,6 +204,18 @@ class SirenFitter:
         self._graph = None
         self.launches_per_step = None
 
+    def set_precision(self, precision: str):
+        """Continue the same fit (parameters, Adam moments, step count, plateau scheduler, loss history) in the other
+        arithmetic mode: 'bf16' (tcgen05 throughput mode) <-> 'fp32' (parity mode).  The 16-bit mode's operand rounding
+        puts a floor under the loss late in a fit (profiles/r01e_c1_snr.md); a fit that starts in bf16 and finishes in
+        fp32 keeps most of the speed and the fp32 floor."""
+        if precision == self.precision:
+            return
+        self.desc = self.spec.desc(precision)
+        self.precision = precision
+        self.ws.get(self.desc, self.n, True)
+        self._graph = None
+
     # -- one step -------------------------------------------------------------------------------
     def _w(self):
         return 1.0 - self.alpha
