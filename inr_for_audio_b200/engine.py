@@ -347,6 +347,39 @@ class SirenFitter:
         return siren_forward(self.desc, self.params, coords, int(n), self.ws, int(i0 or 0), int(T_total or n),
                              self.coord_scale)
 
+    def rounding_noise_ratio(self) -> float:
+        """How much of the current fit error is the 16-bit mode's own rounding: mean((out_bf16 - out_fp32)^2) /
+        mean((out_fp32 - target)^2) at the current parameters (two forward passes; summed over the ranks of a sharded
+        fit).  Far below 1 the bf16 gradients are as good as fp32 ones; near 1 the fit sits on the bf16 noise floor."""
+        buf0 = self.ws.buf
+        o16 = siren_forward(self.spec.desc("bf16"), self.params, self.coords, self.n, self.ws, self.i0, self.T_total,
+                            self.coord_scale)
+        o32 = siren_forward(self.spec.desc("fp32"), self.params, self.coords, self.n, self.ws, self.i0, self.T_total,
+                            self.coord_scale)
+        sums = torch.stack([((o16 - o32).double() ** 2).sum(), ((o32 - self.target).double() ** 2).sum()])
+        if self.pg is not None and self.world > 1:
+            torch.distributed.all_reduce(sums, group=self.pg)
+        self.ws.get(self.desc, self.n, True)      # back to this mode's training workspace
+        if self.ws.buf is not buf0:
+            self._graph = None                    # the scratch buffer grew: the captured step holds the old pointer
+        num, den = (float(x) for x in sums.cpu())
+        return num / max(den, 1e-300)
+
+    def step_auto(self, n_steps: int, check_every: int = 250, threshold: float = 0.05):
+        """n_steps steps that start in the bf16 tcgen05 mode and move to the fp32 mode once the bf16 rounding noise is
+        more than `threshold` of the fit error (checked every `check_every` steps: two forward passes, one host
+        sync).  Returns the step index at which the fit switched (None if it stayed in bf16)."""
+        switched = None
+        done = 0
+        while done < n_steps:
+            k = min(check_every, n_steps - done) if self.precision == "bf16" else n_steps - done
+            self.step(k)
+            done += k
+            if self.precision == "bf16" and done < n_steps and self.rounding_noise_ratio() > threshold:
+                self.set_precision("fp32")
+                switched = self.steps_done
+        return switched
+
     def loss_and_grads(self, extra_gout: Optional[torch.Tensor] = None):
         """One forward+backward without the optimiser: (loss, flat grads clone, output) -- teacher-forced tests."""
         self.grads.zero_()

@@ -89,7 +89,8 @@ def train(experiment_path: str, tag: str, inst: str, duration: int, num_channels
           a_initial=0.5, total_steps=20000, learning_rate=1e-3, min_learning_rate=1e-6, alpha=0.0,
           prev_ckpt_path=None, visualization=False, *, precision='fp32', data_dir='data', seed=None, verbose=True,
           spectral='stft'):
-    """run.py:30.  Extra keyword-only arguments: precision ('fp32' CUDA-core parity mode | 'bf16' tcgen05 mode),
+    """run.py:30.  Extra keyword-only arguments: precision ('fp32' CUDA-core parity mode | 'bf16' tcgen05 mode | 'auto' =
+    start in bf16 and continue in fp32 once the bf16 rounding noise shows in the fit error, SirenFitter.step_auto),
     data_dir (the reference hard-codes 'data/'), seed (torch.manual_seed before model construction), spectral (which
     windowed-transform loss `alpha` mixes in: 'stft' = auraloss STFTLoss as run.py:128,160 does, 'mdct' / 'mdct_mse' =
     the MDCT-domain loss of BASELINE.json config 3)."""
@@ -100,6 +101,11 @@ def train(experiment_path: str, tag: str, inst: str, duration: int, num_channels
         experiment_folder = f'{experiment_path}/{inst}-{method}-{tag}'
     os.makedirs(experiment_folder)
     decimation = int(decimation)
+    auto_precision = precision == 'auto'
+    if auto_precision:
+        if arch == 'kan':
+            raise NotImplementedError("precision='auto' is a SIREN schedule (SirenFitter.step_auto)")
+        precision = 'bf16'
     takelog = False
     if num_freq is not None and method != 'wave':
         raise ValueError("num_freq: the reference's GaussianEncoding(10.0, 1, num_freq) takes 1-D coordinates (run.py:142)")
@@ -162,7 +168,11 @@ def train(experiment_path: str, tag: str, inst: str, duration: int, num_channels
         fitter.load_adam_state(checkpoint['optimizer_state_dict'])
 
     start_time = time.time()
-    fitter.step(int(total_steps))
+    switched_at = None
+    if auto_precision:
+        switched_at = fitter.step_auto(int(total_steps))
+    else:
+        fitter.step(int(total_steps))
     torch.cuda.synchronize(dev)
     total_time = (time.time() - start_time) / 60
     loss_hist = fitter.losses()
@@ -215,7 +225,8 @@ def train(experiment_path: str, tag: str, inst: str, duration: int, num_channels
                     num_snake=num_snake, num_tanh=num_tanh, num_freq=num_freq, omega=omega, hidden_omega=hidden_omega,
                     a_initial=a_initial, total_steps=total_steps, learning_rate=learning_rate,
                     min_learning_rate=min_learning_rate, alpha=alpha, prev_ckpt_path=prev_ckpt_path,
-                    curr_ckpt_path=ckpt_path, visualization=visualization, precision=precision,
+                    curr_ckpt_path=ckpt_path, visualization=visualization,
+                    precision=('auto' if auto_precision else precision), switched_to_fp32_at_step=switched_at,
                     **{'parameter_size(KB)': param_size / 1024, 'total_model_size(KB)': model_size,
                        'total_trainig_time(min)': total_time, 'SNR': snr_final,
                        'final_loss_dB': losses[-1] if losses else None})

@@ -19,11 +19,21 @@ MARKS = [2000, 5000, 10000, 14000, 16000, 18000, 19000, 20000]
 
 
 def main():
-    switches = [int(a) for a in sys.argv[1:]] or [20000, 18000, 16000, 10000]
+    switches = [int(a) for a in sys.argv[1:] if a != "auto"] or ([] if "auto" in sys.argv[1:] else [20000, 18000, 16000, 10000])
     dev = torch.device("cuda:0")
     gtn = P.WaveformFitting(os.path.join(ROOT, "data", "gt_bach.wav"), duration=6, verbose=False).normalised()
     flat0 = torch.cat([p.reshape(-1) for p in O.siren_init(O.SirenSpec(1, 256, 3, 1, True, 30.0, 30.0), seed=0)])
     spec = P.SirenSpec(1, 256, 3, 1, True, 30.0, 30.0)
+    if "auto" in sys.argv[1:]:
+        f = P.SirenFitter(spec, flat0.clone(), torch.from_numpy(gtn).to(dev), None, precision="bf16", hist_cap=TOTAL)
+        torch.cuda.synchronize()
+        t0 = time.time()
+        sw = f.step_auto(TOTAL)
+        torch.cuda.synchronize()
+        print(json.dumps({"arm": "auto (step_auto: noise ratio > 0.05)", "switched_at": sw,
+                          "snr_db": {TOTAL: round(float(P.calculate_snr(gtn, f.forward().cpu().numpy())), 3)},
+                          "last_loss": float(f.losses()[-1]), "final_lr": f.last_lr(), "wall_s": round(time.time() - t0, 2)}),
+              flush=True)
     for sw in switches:
         f = P.SirenFitter(spec, flat0.clone(), torch.from_numpy(gtn).to(dev), None, precision="bf16", hist_cap=TOTAL)
         torch.cuda.synchronize()

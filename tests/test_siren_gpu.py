@@ -291,3 +291,35 @@ def test_bf16_convergence_envelope(pkg, golden):
     for step, ours, lo, hi, sd in _envelope_vs_ensemble(pkg, golden, "bf16", 2e-3):
         tol = 1.0 if step <= 300 else 6.0
         assert lo - tol - sd <= ours <= hi + tol + sd, (step, ours, lo, hi, sd)
+
+
+def test_set_precision_and_step_auto(pkg, golden):
+    """A fit continued in the other arithmetic mode keeps its parameters, Adam moments, step count and loss history;
+    step_auto leaves the bf16 mode once its rounding noise shows in the fit error (profiles/r01e_c1_snr.md)."""
+    from scipy.io import wavfile
+    sr, data = wavfile.read(os.path.join(ROOT, "data", "gt_bach.wav"))
+    data = data.astype(np.float32)[44100:44100 + 8192]
+    gt = torch.from_numpy(data / np.max(np.abs(data))).to(dev())
+    torch.manual_seed(0)
+    model = pkg.Siren(1, 128, 2, 1, True)
+    spec, flat = model.spec, model.flat_parameters().detach().clone()
+    f = pkg.SirenFitter(spec, flat, gt, precision="bf16", hist_cap=4096)
+    f.step(200)
+    p_before = f.params.clone()
+    r0 = f.rounding_noise_ratio()
+    assert 0.0 < r0 < 0.05                                   # early in the fit the rounding noise is far below the error
+    assert torch.equal(f.params, p_before)                   # the probe does not touch the state
+    f.set_precision("fp32")
+    assert f.precision == "fp32" and f.opt_state().step == 200
+    f.step(100)
+    ls = f.losses()
+    assert len(ls) == 300 and np.all(np.isfinite(ls)) and ls[-1] < ls[150]
+    f.set_precision("bf16")
+    f.step(10)
+    assert f.opt_state().step == 310
+    # threshold 0 forces the switch at the first check; a huge threshold never switches
+    f2 = pkg.SirenFitter(spec, flat, gt, precision="bf16", hist_cap=4096)
+    assert f2.step_auto(300, check_every=100, threshold=0.0) == 100 and f2.precision == "fp32"
+    f3 = pkg.SirenFitter(spec, flat, gt, precision="bf16", hist_cap=4096)
+    assert f3.step_auto(300, check_every=100, threshold=1e9) is None and f3.precision == "bf16"
+    np.testing.assert_allclose(f2.losses()[:100], f3.losses()[:100], rtol=0.2)
