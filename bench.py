@@ -393,12 +393,12 @@ def run_ours(args, wl):
     flops = job.flops_per_coord * prof_units              # dense contraction flops of the profiled rows, fwd + bwd
     achieved = flops / (gemm_ms * 1e-3) / 1e12 if gemm_ms > 0 else 0.0
     # DRAM bytes per launch (dram__bytes_read.sum + dram__bytes_write.sum) of the GEMM kernels from the committed
-    # `ncu --set full` capture of this workload (profiles/r01d_traffic.json <- tools/ncu_summary.py), averaged over the
+    # `ncu --set full` capture of this workload (profiles/r01e_traffic.json <- tools/ncu_summary.py), averaged over the
     # launches of one step; null for workloads without a capture.
     traffic = None
     if args.workload == "c2" and prec == "bf16" and world == 1:
         try:
-            with open(os.path.join(ROOT, "profiles", "r01d_traffic.json")) as f:
+            with open(os.path.join(ROOT, "profiles", "r01e_traffic.json")) as f:
                 tj = json.load(f)
             per_step = {"k_tc_layer2<512, 0>": wl["L"], "k_tc_layer2<512, 1>": wl["L"], "k_tc_dw2<512>": wl["L"]}
             traffic = sum(tj[k]["dram_bytes_per_launch"] * n for k, n in per_step.items()) / sum(per_step.values())
@@ -406,7 +406,7 @@ def run_ours(args, wl):
             traffic = None
     roofline = {"bound": "tensor", "achieved": achieved, "peak": pk["bf16_sus"], "unit": "TFLOP/s",
                 "frac": achieved / pk["bf16_sus"], "traffic": traffic,
-                "traffic_note": "avg DRAM bytes per launch of the three tcgen05 GEMM kernels (ncu, profiles/r01d_*); "
+                "traffic_note": "avg DRAM bytes per launch of the three tcgen05 GEMM kernels (ncu, profiles/r01e_*); "
                                 "algorithmic: 8.13 GB layer FWD/BWD, 5.42 GB dW" if traffic else None,
                 "kernel": "+".join(sorted(gemm_tags)), "flops_per_launch": flops / max(gemm_launches, 1),
                 "avg_launch_ms": gemm_ms / max(gemm_launches, 1), "gemm_share_of_step": gemm_ms / max(prof_total_ms, 1e-9),
