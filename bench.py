@@ -2,7 +2,7 @@
 """bench.py -- coord-samples/sec of the SIREN fit step (fwd + loss + bwd + Adam [+ allreduce]).
 
     python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference] [--workload c2|c1|c5clip]
-                    [--precision bf16|fp32]
+                    [--precision fp16|fp32]   (KAN: bf16|fp32)
 
 N > 1 is launched by the driver under torch.distributed.run (one rank per GPU, NCCL); the coordinates of the ONE
 waveform are sharded by rank and every step has one sum-allreduce of [grads | loss]  => "scaling": "strong".
@@ -310,8 +310,8 @@ def run_ours(args, wl):
         prec = "bf16" if prec == "auto" else prec
     elif prec == "auto":
         try:
-            L.check(L.lib().inr_siren_workspace_bytes(P.SirenSpec(1, wl["H"], wl["L"], 1, True).desc("bf16"), 1024, 1))
-            prec = "bf16"
+            L.check(L.lib().inr_siren_workspace_bytes(P.SirenSpec(1, wl["H"], wl["L"], 1, True).desc("fp16"), 1024, 1))
+            prec = "fp16"
         except L.InrLibraryError:
             prec = "fp32"
     job = Job(args, wl, rank, world, dev, pg, prec)
@@ -396,7 +396,7 @@ def run_ours(args, wl):
     # `ncu --set full` capture of this workload (profiles/r01e_traffic.json <- tools/ncu_summary.py), averaged over the
     # launches of one step; null for workloads without a capture.
     traffic = None
-    if args.workload == "c2" and prec == "bf16" and world == 1:
+    if args.workload == "c2" and prec == "fp16" and world == 1:
         try:
             with open(os.path.join(ROOT, "profiles", "r01e_traffic.json")) as f:
                 tj = json.load(f)
@@ -411,7 +411,7 @@ def run_ours(args, wl):
                 "kernel": "+".join(sorted(gemm_tags)), "flops_per_launch": flops / max(gemm_launches, 1),
                 "avg_launch_ms": gemm_ms / max(gemm_launches, 1), "gemm_share_of_step": gemm_ms / max(prof_total_ms, 1e-9),
                 "peak_source": pk["src"] + ", sustained bf16 (kernel timed inside a long step)",
-                "mma_kind": "tcgen05 kind::f16 (bf16)" if prec == "bf16" else "none: fp32 FFMA on CUDA cores (parity mode)"}
+                "mma_kind": "tcgen05 kind::f16 (%s operands)" % prec if prec in ("bf16", "fp16") else "none: fp32 FFMA on CUDA cores (parity mode)"}
     # HBM-bound stages (north star: elementwise / spline / MDCT stages as achieved GB/s of the measured copy peak)
     stages = {}
 
@@ -449,7 +449,7 @@ def run_ours(args, wl):
         par = ("clip-parallel x%d (no collective)" % world) if job.kind == "clips" else ("coord-shard x%d" % world)
         line = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps,
                 "warmup": args.warmup, "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": "strong",
-                "vs_baseline": None, "dtype": "bf16" if prec == "bf16" else "f32", "data": "synthetic",
+                "vs_baseline": None, "dtype": prec if prec in ("bf16", "fp16") else "f32", "data": "synthetic",
                 "config": {"workload": wl["desc"], "precision": prec, "parallelism": par,
                            "units_per_rank": job.n_local, "l2": "working set (activation workspace, GBs) >> 126 MB L2; no flush needed",
                            "cuda_graph": True},

@@ -31,7 +31,11 @@ extern "C" {
 
 /* arithmetic of the hidden HxH contractions */
 #define INR_PREC_FP32 0 /* CUDA-core fp32 FMA (the parity mode: matches the fp32 reference to ~1e-6)   */
-#define INR_PREC_BF16 1 /* tcgen05 kind::f16 bf16 operands, fp32 TMEM accumulation (the fast mode)     */
+#define INR_PREC_BF16 1 /* tcgen05 kind::f16, bf16 operands, fp32 TMEM accumulation: the KAN tensor-core mode.
+                           SIREN descriptors are refused: 8-bit significands floor a SIREN fit at ~24 dB      */
+#define INR_PREC_FP16 2 /* tcgen05 kind::f16, IEEE fp16 operands (11-bit significands) with a power-of-two loss
+                           scale on dZ, fp32 TMEM accumulation; first layer, sin/cos arguments, loss, reductions
+                           and Adam master weights in fp32: the SIREN tensor-core mode                         */
 
 /* time-domain loss, run.py:124-125,161-169 */
 #define INR_LOSS_MSE 0
@@ -46,10 +50,11 @@ extern "C" {
  *   num_tanh       x   nn.Linear(H->H) + nn.Tanh()
  *   last               nn.Linear(H->1) (outermost_linear)   or SineLayer(H->1)
  * flat params = state_dict order: W, b per layer, with a Snake layer's `a` (H floats) right after its bias.
- * The bf16 tcgen05 mode takes the sine-only stack; Snake/Tanh stacks run in INR_PREC_FP32. */
+ * Both modes (INR_PREC_FP32, INR_PREC_FP16) take every stack; INR_PREC_FP16 needs H in {128,256,512}, at least one
+ * HxH layer and in_features <= H. */
 typedef struct {
   int32_t in_features;     /* 1 (waveform), 2 (MDCT image), or the width of an encoded
-                              coordinate (2*num_freq, run.py:81-82; bf16 mode: <= hidden_features) */
+                              coordinate (2*num_freq, run.py:81-82; fp16 mode: <= hidden_features) */
   int32_t hidden_features; /* H                                                   */
   int32_t hidden_layers;   /* number of HxH SineLayers (num_sine)                 */
   int32_t out_features;    /* must be 1                                           */
@@ -79,6 +84,11 @@ typedef struct {
   float last_loss;     /* loss of the most recent step                             */
   float step_size;     /* lr/(1-beta1^t) for the NEXT step, computed in float64    */
   float bc2_sqrt;      /* sqrt(1-beta2^t) for the NEXT step, computed in float64   */
+  float gmax_acc;      /* max |d loss/d out| seen this step (float bits, atomicMax) */
+  float gmax_prev;     /* ... of the previous step: sets the fp16 loss scale         */
+  float omb1, omb2;    /* (float)(1.0 - beta1), (float)(1.0 - beta2) formed in float64, as torch passes them */
+  int32_t hist_base;   /* Adam step at which loss_hist[0] was written (resume)      */
+  int32_t reserved0;
   double loss_acc[4];  /* [0] time-loss numerator sum, [1] spectral loss, [2..3] scratch; zeroed per step */
 } inr_opt_state;
 

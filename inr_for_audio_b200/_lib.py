@@ -11,9 +11,9 @@ HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.path.join(HERE, "libinr_b200.so")
 
 INR_OK, INR_E_BADARG, INR_E_UNSUPPORTED, INR_E_CUDA, INR_E_WORKSPACE = 0, -1, -2, -3, -4
-PREC_FP32, PREC_BF16 = 0, 1
+PREC_FP32, PREC_BF16, PREC_FP16 = 0, 1, 2
 LOSS_MSE, LOSS_MAE = 0, 1
-PRECISIONS = {"fp32": PREC_FP32, "bf16": PREC_BF16}
+PRECISIONS = {"fp32": PREC_FP32, "bf16": PREC_BF16, "fp16": PREC_FP16}
 
 
 class SirenDesc(C.Structure):
@@ -36,6 +36,8 @@ class OptState(C.Structure):
                 ("sched_eps", C.c_float), ("beta1", C.c_float), ("beta2", C.c_float), ("adam_eps", C.c_float),
                 ("patience", C.c_int32), ("num_bad", C.c_int32), ("step", C.c_int32), ("hist_cap", C.c_int32),
                 ("best", C.c_float), ("last_loss", C.c_float), ("step_size", C.c_float), ("bc2_sqrt", C.c_float),
+                ("gmax_acc", C.c_float), ("gmax_prev", C.c_float), ("omb1", C.c_float), ("omb2", C.c_float),
+                ("hist_base", C.c_int32), ("reserved0", C.c_int32),
                 ("loss_acc", C.c_double * 4)]
 
 

@@ -336,7 +336,7 @@ __global__ void __launch_bounds__(KanFwdCfg::THREADS, 1) k_kan_tc_fwd(const floa
             for (int jj = 0; jj < 3; ++jj) {
               const uint64_t ad = make_smem_desc(a0 + t * Cfg::A_TILE_BYTES + jj * 2 * (TILE_ROWS * 16), TILE_ROWS * 16, 128);
               const uint64_t bd = make_smem_desc(b0 + jj * 2 * (Cfg::OUT * 16), Cfg::OUT * 16, 128);
-              umma_bf16(tmem_base + t * Cfg::OUT, ad, bd, idesc, (st | jj) != 0 ? 1u : 0u);
+              umma_f16(tmem_base + t * Cfg::OUT, ad, bd, idesc, (st | jj) != 0 ? 1u : 0u);
             }
           umma_commit(bar_empty(s));
           if (++s == Cfg::STAGES) { s = 0; phase ^= 1; }
@@ -581,7 +581,7 @@ __global__ void __launch_bounds__(KanBwdCfg::THREADS, 1) k_kan_tc_bwd(const floa
             const int kk = h * 8 + k8;
             const uint64_t ad = make_smem_desc(sG + kk * 2 * (TILE_ROWS * 16), TILE_ROWS * 16, 128);
             const uint64_t bd = make_smem_desc(sWB + kk * 2 * (KT_SLABF * 16), KT_SLABF * 16, 128);
-            umma_bf16(tmem_base + Cfg::COL_DPHI, ad, bd, idesc_dphi, kk != 0 ? 1u : 0u);
+            umma_f16(tmem_base + Cfg::COL_DPHI, ad, bd, idesc_dphi, kk != 0 ? 1u : 0u);
           }
           if (h == 1) umma_commit(bar_dphi_full);
           // dWc[128h .. +128, slab] += g[:, 128h ..]^T Phi  (both MN-major, K = 16 rows per step)
@@ -589,7 +589,7 @@ __global__ void __launch_bounds__(KanBwdCfg::THREADS, 1) k_kan_tc_bwd(const floa
           for (int kk = 0; kk < TILE_ROWS / 16; ++kk) {
             const uint64_t ad = make_smem_desc(sG + h * Cfg::G_HALF + kk * 256, 128, TILE_ROWS * 16);
             const uint64_t bd = make_smem_desc(sPhi + kk * 256, 128, TILE_ROWS * 16);
-            umma_bf16(tmem_base + Cfg::COL_DW + h * KT_SLABF, ad, bd, idesc_dw, (it | kk) != 0 ? 1u : 0u);
+            umma_f16(tmem_base + Cfg::COL_DW + h * KT_SLABF, ad, bd, idesc_dw, (it | kk) != 0 ? 1u : 0u);
           }
           umma_commit(bar_g_empty(h));
         }

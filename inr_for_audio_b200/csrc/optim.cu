@@ -12,7 +12,7 @@ __global__ void __launch_bounds__(256) k_adam(float* __restrict__ p, float* __re
                                               float* __restrict__ v, int64_t P, const inr_opt_state* __restrict__ st) {
   const float b1 = st->beta1, b2 = st->beta2, eps = st->adam_eps;
   const float step_size = st->step_size, bc2_sqrt = st->bc2_sqrt;
-  const float w1 = 1.f - b1, w2 = 1.f - b2;
+  const float w1 = st->omb1, w2 = st->omb2;   // (float)(1.0 - beta) formed in float64, as torch's Python scalars are
   const int64_t stride = (int64_t)gridDim.x * blockDim.x * 4;
   for (int64_t i = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) * 4; i < P; i += stride) {
     if (i + 3 < P && ((reinterpret_cast<uintptr_t>(p + i) & 15) == 0)) {
@@ -57,6 +57,8 @@ __global__ void k_opt_init(inr_opt_state* st, float lr, float min_lr, int hist_c
   st->beta1 = 0.9f; st->beta2 = 0.999f; st->adam_eps = 1e-8f;
   st->patience = 200; st->num_bad = 0; st->step = 0; st->hist_cap = hist_cap;
   st->best = __int_as_float(0x7f800000); st->last_loss = 0.f;
+  st->gmax_acc = 0.f; st->gmax_prev = 0.f; st->hist_base = 0; st->reserved0 = 0;
+  st->omb1 = (float)(1.0 - 0.9); st->omb2 = (float)(1.0 - 0.999);
   for (int i = 0; i < 4; ++i) st->loss_acc[i] = 0.0;
   opt_prepare_next(st);
 }
@@ -65,7 +67,9 @@ __global__ void k_opt_init(inr_opt_state* st, float lr, float min_lr, int hist_c
 __global__ void k_opt_post(inr_opt_state* st, float loss_scale, float* loss_hist) {
   const float loss = (float)(st->loss_acc[0] * (double)loss_scale + st->loss_acc[1]);
   st->last_loss = loss;
-  if (loss_hist && st->hist_cap > 0) loss_hist[st->step % st->hist_cap] = loss;
+  if (loss_hist && st->hist_cap > 0) loss_hist[(st->step - st->hist_base) % st->hist_cap] = loss;
+  st->gmax_prev = st->gmax_acc;
+  st->gmax_acc = 0.f;
   // python: current < best * (1 - threshold), evaluated in float64 on a float32-valued loss
   const double thr = (double)st->best * (1.0 - (double)st->threshold);
   if ((double)loss < thr) { st->best = loss; st->num_bad = 0; } else { st->num_bad += 1; }

@@ -104,7 +104,6 @@ int launch_first_layer(const inr_siren_desc* d, const float* params, const float
   return INR_OK;
 }
 template int launch_first_layer<float>(const inr_siren_desc*, const float*, const float*, int64_t, int64_t, int64_t, float, float*, float*, float*, cudaStream_t);
-template int launch_first_layer<__nv_bfloat16>(const inr_siren_desc*, const float*, const float*, int64_t, int64_t, int64_t, float, __nv_bfloat16*, __nv_bfloat16*, __nv_bfloat16*, cudaStream_t);
 
 // ------------------------------------------------------------------------------------------------
 // last layer + loss + first backward step.  One warp per row (grid-stride); lane j owns h = j, j+32, ...
@@ -262,7 +261,6 @@ int launch_last_layer(const inr_siren_desc* d, const float* params, const ActT* 
   return INR_OK;
 }
 template int launch_last_layer<float>(const inr_siren_desc*, const float*, const float*, float*, const float*, const float*, const float*, int64_t, int, float, float*, inr_opt_state*, float*, int, cudaStream_t);
-template int launch_last_layer<__nv_bfloat16>(const inr_siren_desc*, const float*, const __nv_bfloat16*, __nv_bfloat16*, const __nv_bfloat16*, const float*, const float*, int64_t, int, float, float*, inr_opt_state*, float*, int, cudaStream_t);
 
 // ------------------------------------------------------------------------------------------------
 // column reductions over coordinates: gb[h] += sum_r dZ[r,h];  gW[h*in+i] += sum_r dZ[r,h] * x[r,i]
@@ -329,8 +327,6 @@ int launch_colsum(const ActT* dZ, int64_t rows, int H, float* gb, cudaStream_t s
   return launch_colsum_impl<ActT, false>(dZ, nullptr, 1, rows, H, 0, 1, 1.f, nullptr, gb, st);
 }
 template int launch_first_layer_grad<float>(const inr_siren_desc*, const float*, const float*, int64_t, int64_t, int64_t, float, float*, float*, cudaStream_t);
-template int launch_first_layer_grad<__nv_bfloat16>(const inr_siren_desc*, const __nv_bfloat16*, const float*, int64_t, int64_t, int64_t, float, float*, float*, cudaStream_t);
 template int launch_colsum<float>(const float*, int64_t, int, float*, cudaStream_t);
-template int launch_colsum<__nv_bfloat16>(const __nv_bfloat16*, int64_t, int, float*, cudaStream_t);
 
 }  // namespace inr

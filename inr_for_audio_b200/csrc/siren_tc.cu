@@ -1,8 +1,8 @@
-// siren_tc.cu -- the bf16 tensor-core SIREN fit path (INR_PREC_BF16): host orchestration + the streaming kernels
-// around the tcgen05 GEMMs of tc_gemm.cuh.  All activations live in HBM as bf16 "tile images" (tc_common.cuh).
+// siren_tc.cu -- the fp16 tensor-core SIREN fit path (INR_PREC_FP16): host orchestration + the streaming kernels
+// around the tcgen05 GEMMs of tc_gemm.cuh.  All activations live in HBM as fp16 "tile images" (tc_common.cuh).
 //
-//   per step and row chunk (DESIGN.md "bf16 path"):
-//     k_tc_pack        fp32 master weights -> bf16 UMMA operand images W_l (fwd) and W_l^T (dX)      once per call
+//   per step and row chunk (DESIGN.md "fp16 path"):
+//     k_tc_pack        fp32 master weights -> fp16 UMMA operand images W_l (fwd) and W_l^T (dX)      once per call
 //     k_tc_first       S_0, C_0 = sincos(omega_0 (W_0 x + b_0))      fp32, accurate sincosf (models.py:114-115)
 //     k_tc_layer<FWD>  S_l, C_l = sincos(omega (S_{l-1} W_l^T + b_l))                               l = 1..L
 //     k_tc_last        out = S_L w + b; loss; g = dloss/dout; dZ_L = g w omega C_L (over C_L); g -> gvec
@@ -19,7 +19,7 @@ using namespace tc;
 
 // ------------------------------------------------------------------------------------------------ pack
 __global__ void __launch_bounds__(256) k_tc_pack(const float* __restrict__ params, SirenLayout lay, int NS,
-                                                 __nv_bfloat16* __restrict__ Wf, __nv_bfloat16* __restrict__ Wb) {
+                                                 op16* __restrict__ Wf, op16* __restrict__ Wb) {
   const int H = lay.H;
   const int64_t per = (int64_t)H * H;
   const int64_t total = per * lay.L;
@@ -27,7 +27,7 @@ __global__ void __launch_bounds__(256) k_tc_pack(const float* __restrict__ param
     const int l = (int)(i / per);
     const int rem = (int)(i - (int64_t)l * per);
     const int o = rem / H, in = rem - o * H;
-    const __nv_bfloat16 w = __float2bfloat16_rn(params[lay.w_off(l + 1) + rem]);
+    const op16 w = to_op(params[lay.w_off(l + 1) + rem]);
     // forward operand: B[n = out][k = in]
     Wf[(int64_t)l * per + (int64_t)(o / NS) * ((int64_t)H * NS) + ((int64_t)(in >> 3) * NS + (o % NS)) * 8 + (in & 7)] = w;
     // dX operand: B[n = in][k = out]
@@ -37,21 +37,21 @@ __global__ void __launch_bounds__(256) k_tc_pack(const float* __restrict__ param
 
 // ------------------------------------------------------------------------------------------------ wide inputs
 // Encoded coordinates (in_features = 2*num_freq > 2, run.py:81-82,141-144) on the tcgen05 path: the input rows become one
-// more tile image X (bf16, zero-padded to H columns) and layer 0 one more H x H layer GEMM with W_0 zero-padded to H
+// more tile image X (fp16, zero-padded to H columns) and layer 0 one more H x H layer GEMM with W_0 zero-padded to H
 // input columns; its weight gradient is the dW GEMM against X, cut back to (H x in).  Needs in_features <= H.
 __global__ void __launch_bounds__(256) k_tc_pack0(const float* __restrict__ W0, int in, int H, int NS,
-                                                  __nv_bfloat16* __restrict__ Wf0) {
+                                                  op16* __restrict__ Wf0) {
   const int total = H * H;
   for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < total; i += gridDim.x * blockDim.x) {
     const int o = i / H, k = i - o * H;
     const float v = k < in ? W0[(int64_t)o * in + k] : 0.f;
-    Wf0[(int64_t)(o / NS) * ((int64_t)H * NS) + ((int64_t)(k >> 3) * NS + (o % NS)) * 8 + (k & 7)] = __float2bfloat16_rn(v);
+    Wf0[(int64_t)(o / NS) * ((int64_t)H * NS) + ((int64_t)(k >> 3) * NS + (o % NS)) * 8 + (k & 7)] = to_op(v);
   }
 }
 
 // X[tile][group][row][8] <- coords (rows x in) fp32, zero beyond `in` columns and `rows` rows
 __global__ void __launch_bounds__(256) k_tc_rows_to_image(const float* __restrict__ coords, int in, int H, int64_t rows,
-                                                          int64_t rows_pad, __nv_bfloat16* __restrict__ X) {
+                                                          int64_t rows_pad, op16* __restrict__ X) {
   const int lg = 31 - __clz(H >> 3);
   const int64_t total = rows_pad << lg;
   for (int64_t idx = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; idx < total; idx += (int64_t)gridDim.x * blockDim.x) {
@@ -65,8 +65,8 @@ __global__ void __launch_bounds__(256) k_tc_rows_to_image(const float* __restric
       const int f = kg * 8 + j;
       v[j] = (row < rows && f < in) ? coords[row * in + f] : 0.f;
     }
-    *reinterpret_cast<uint4*>(X + idx * 8) = make_uint4(pack_bf16x2(v[0], v[1]), pack_bf16x2(v[2], v[3]),
-                                                        pack_bf16x2(v[4], v[5]), pack_bf16x2(v[6], v[7]));
+    *reinterpret_cast<uint4*>(X + idx * 8) = make_uint4(pack_op2(v[0], v[1]), pack_op2(v[2], v[3]),
+                                                        pack_op2(v[4], v[5]), pack_op2(v[6], v[7]));
   }
 }
 
@@ -85,9 +85,9 @@ __global__ void __launch_bounds__(256) k_tc_unpad_add(const float* __restrict__ 
 __global__ void __launch_bounds__(256) k_tc_first(const float* __restrict__ W, const float* __restrict__ B,
                                                   const float* __restrict__ coords, int in, int H, int64_t rows,
                                                   int64_t rows_pad, int64_t g0, int64_t T_total, float scale,
-                                                  float omega, __nv_bfloat16* __restrict__ S0,
-                                                  __nv_bfloat16* __restrict__ C0, const float* __restrict__ Aparam,
-                                                  __nv_bfloat16* __restrict__ E0) {
+                                                  float omega, op16* __restrict__ S0,
+                                                  op16* __restrict__ C0, const float* __restrict__ Aparam,
+                                                  op16* __restrict__ E0) {
   // Aparam != NULL: first_linear (models.py:343-347), layer 0 = nn.Linear + Snake: S0 = y, C0 = dy/dz, E0 = dy/da
   const int lg = 31 - __clz(H >> 3);                      // H/8 feature groups: a power of two on this path
   const int64_t total = rows_pad << lg;
@@ -125,112 +125,14 @@ __global__ void __launch_bounds__(256) k_tc_first(const float* __restrict__ W, c
           sincos_reduced(omega * z, &s[u], &c[u]);
         }
       }
-      so[h] = pack_bf16x2(s[0], s[1]);
-      co[h] = pack_bf16x2(c[0], c[1]);
-      eo[h] = pack_bf16x2(e[0], e[1]);
+      so[h] = pack_op2(s[0], s[1]);
+      co[h] = pack_op2(c[0], c[1]);
+      eo[h] = pack_op2(e[0], e[1]);
     }
     const int64_t off = idx * 8;   // == ((tile*groups + kg)*128 + r)*8
     *reinterpret_cast<uint4*>(S0 + off) = make_uint4(so[0], so[1], so[2], so[3]);
     if (C0) *reinterpret_cast<uint4*>(C0 + off) = make_uint4(co[0], co[1], co[2], co[3]);
     if (Aparam && E0) *reinterpret_cast<uint4*>(E0 + off) = make_uint4(eo[0], eo[1], eo[2], eo[3]);
-  }
-}
-
-// ------------------------------------------------------------------------------------------------ last layer
-// one thread = one row; block = 128 threads = one tile
-__global__ void __launch_bounds__(128) k_tc_last(const __nv_bfloat16* __restrict__ S, __nv_bfloat16* __restrict__ CdZ,
-                                                 const float* __restrict__ w, const float* __restrict__ bptr,
-                                                 const float* __restrict__ target, const float* __restrict__ extra_g,
-                                                 int64_t rows, int num_tiles, int H, float omega_prev, float omega_hidden,
-                                                 int outermost_linear, int loss_kind, float grad_scale,
-                                                 float* __restrict__ gvec, float* __restrict__ gb,
-                                                 double* __restrict__ loss_acc, float* __restrict__ out, int training,
-                                                 __nv_bfloat16* __restrict__ Eimg) {
-  extern __shared__ float s_w[];   // H floats
-  __shared__ double s_red[4];
-  __shared__ float s_gb[4];
-  for (int i = threadIdx.x; i < H; i += blockDim.x) s_w[i] = w[i];
-  __syncthreads();
-  const int groups = H >> 3;
-  const float bias = bptr[0];
-  const int r = threadIdx.x;
-  double loss_local = 0.0;
-  float gb_local = 0.f;
-  for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
-    const int64_t row = (int64_t)tile * TILE_ROWS + r;
-    const size_t tile_off = (size_t)tile * (TILE_ROWS * (size_t)H);
-    float dot = 0.f;
-    for (int kg = 0; kg < groups; ++kg) {
-      const uint4 u = *reinterpret_cast<const uint4*>(S + tile_off + ((size_t)kg * TILE_ROWS + r) * 8);
-      const uint32_t uw[4] = {u.x, u.y, u.z, u.w};
-#pragma unroll
-      for (int h = 0; h < 4; ++h) {
-        const float2 f = unpack_bf16x2(uw[h]);
-        dot = __fmaf_rn(f.x, s_w[kg * 8 + 2 * h], dot);
-        dot = __fmaf_rn(f.y, s_w[kg * 8 + 2 * h + 1], dot);
-      }
-    }
-    const float z = dot + bias;
-    float o = z, dact = 1.f;
-    if (!outermost_linear) {
-      float sn, cs;
-      sincosf(omega_hidden * z, &sn, &cs);
-      o = sn;
-      dact = omega_hidden * cs;
-    }
-    const bool valid = row < rows;
-    if (out && valid) out[row] = o;
-    if (!training) continue;
-    float g = 0.f;
-    if (valid) {
-      if (target) {
-        const float diff = o - target[row];
-        if (loss_kind == INR_LOSS_MAE) {
-          loss_local += (double)fabsf(diff);
-          g = grad_scale * ((diff > 0.f) ? 1.f : ((diff < 0.f) ? -1.f : 0.f));
-        } else {
-          loss_local += (double)diff * (double)diff;
-          g = grad_scale * 2.f * diff;
-        }
-      }
-      if (extra_g) g += extra_g[row];
-      g *= dact;
-    }
-    gb_local += g;
-    gvec[(int64_t)tile * TILE_ROWS + r] = g;
-    const float gw = g * omega_prev;
-    for (int kg = 0; kg < groups; ++kg) {
-      __nv_bfloat16* cp = CdZ + tile_off + ((size_t)kg * TILE_ROWS + r) * 8;
-      const uint4 u = *reinterpret_cast<const uint4*>(cp);
-      const uint32_t uw[4] = {u.x, u.y, u.z, u.w};
-      uint32_t ow[4];
-#pragma unroll
-      for (int h = 0; h < 4; ++h) {
-        const float2 f = unpack_bf16x2(uw[h]);
-        ow[h] = pack_bf16x2(gw * s_w[kg * 8 + 2 * h] * f.x, gw * s_w[kg * 8 + 2 * h + 1] * f.y);
-      }
-      *reinterpret_cast<uint4*>(cp) = make_uint4(ow[0], ow[1], ow[2], ow[3]);
-      if (Eimg) {   // layer L is a Snake layer: dY_L * dy/da = g w E in place over E (column-summed afterwards -> grad of a)
-        __nv_bfloat16* ep = Eimg + tile_off + ((size_t)kg * TILE_ROWS + r) * 8;
-        const uint4 eu = *reinterpret_cast<const uint4*>(ep);
-        const uint32_t ew[4] = {eu.x, eu.y, eu.z, eu.w};
-#pragma unroll
-        for (int h = 0; h < 4; ++h) {
-          const float2 f = unpack_bf16x2(ew[h]);
-          ow[h] = pack_bf16x2(g * s_w[kg * 8 + 2 * h] * f.x, g * s_w[kg * 8 + 2 * h + 1] * f.y);
-        }
-        *reinterpret_cast<uint4*>(ep) = make_uint4(ow[0], ow[1], ow[2], ow[3]);
-      }
-    }
-  }
-  if (!training) return;
-  loss_local = warp_sum(loss_local);
-  gb_local = warp_sum(gb_local);
-  if ((threadIdx.x & 31) == 0) { s_red[threadIdx.x >> 5] = loss_local; s_gb[threadIdx.x >> 5] = gb_local; }
-  __syncthreads();
-  if (threadIdx.x == 0) {
-    if (target) atomicAdd(loss_acc, s_red[0] + s_red[1] + s_red[2] + s_red[3]);
-    atomicAdd(gb, s_gb[0] + s_gb[1] + s_gb[2] + s_gb[3]);
   }
 }
 
@@ -264,14 +166,15 @@ template <int N>
 __device__ __forceinline__ void cp_async_wait() { asm volatile("cp.async.wait_group %0;" ::"n"(N) : "memory"); }
 
 template <int H, bool SNAKE>
-__global__ void __launch_bounds__(512, 1) k_tc_last2(const __nv_bfloat16* __restrict__ S, __nv_bfloat16* __restrict__ CdZ,
+__global__ void __launch_bounds__(512, 1) k_tc_last2(const op16* __restrict__ S, op16* __restrict__ CdZ,
                                                      const float* __restrict__ w, const float* __restrict__ bptr,
                                                      const float* __restrict__ target, const float* __restrict__ extra_g,
                                                      int64_t rows, int num_tiles, float omega_prev, float omega_hidden,
                                                      int outermost_linear, int loss_kind, float grad_scale,
                                                      float* __restrict__ gw, float* __restrict__ gb,
                                                      double* __restrict__ loss_acc, float* __restrict__ out, int training,
-                                                     const __nv_bfloat16* __restrict__ Eimg, float* __restrict__ ga) {
+                                                     const op16* __restrict__ Eimg, float* __restrict__ ga,
+                                                     const float* __restrict__ gsc, unsigned* __restrict__ gmax_acc) {
   using Cfg = Last2Cfg<H>;
   constexpr int KPW = Cfg::KPW;
   extern __shared__ __align__(128) uint8_t smem[];
@@ -283,6 +186,8 @@ __global__ void __launch_bounds__(512, 1) k_tc_last2(const __nv_bfloat16* __rest
   __syncthreads();
   const float bias = bptr[0];
   const int num_units = num_tiles * 4;
+  const float gs = (training && gsc) ? gsc[0] : 1.f;   // power-of-two loss scale of the fp16 dZ images (set_gscale)
+  float gmax_local = 0.f;
 
   auto issue = [&](int unit, int stage) {
     if (unit < num_units) {
@@ -337,7 +242,7 @@ __global__ void __launch_bounds__(512, 1) k_tc_last2(const __nv_bfloat16* __rest
       const uint32_t uw[4] = {sv[i].x, sv[i].y, sv[i].z, sv[i].w};
 #pragma unroll
       for (int h = 0; h < 4; ++h) {
-        const float2 f = unpack_bf16x2(uw[h]);
+        const float2 f = unpack_op2(uw[h]);
         pd = __fmaf_rn(f.x, s_w[kg * 8 + 2 * h], pd);
         pd = __fmaf_rn(f.y, s_w[kg * 8 + 2 * h + 1], pd);
       }
@@ -371,8 +276,8 @@ __global__ void __launch_bounds__(512, 1) k_tc_last2(const __nv_bfloat16* __rest
       }
       g = (g + eg) * dact;
     }
-    if (warp == 0) gb_local += g;
-    const float gwm = g * omega_prev;
+    if (warp == 0) { gb_local += g; gmax_local = fmaxf(gmax_local, fabsf(g)); }
+    const float gwm = g * gs * omega_prev;
     const size_t tile_off = (size_t)tile * (TILE_ROWS * (size_t)H);
 #pragma unroll
     for (int i = 0; i < KPW; ++i) {
@@ -384,9 +289,9 @@ __global__ void __launch_bounds__(512, 1) k_tc_last2(const __nv_bfloat16* __rest
       uint32_t ow[4];
 #pragma unroll
       for (int h = 0; h < 4; ++h) {
-        const float2 c = unpack_bf16x2(cw[h]);
-        const float2 f = unpack_bf16x2(uw[h]);
-        ow[h] = pack_bf16x2(gwm * s_w[kg * 8 + 2 * h] * c.x, gwm * s_w[kg * 8 + 2 * h + 1] * c.y);
+        const float2 c = unpack_op2(cw[h]);
+        const float2 f = unpack_op2(uw[h]);
+        ow[h] = pack_op2(gwm * s_w[kg * 8 + 2 * h] * c.x, gwm * s_w[kg * 8 + 2 * h + 1] * c.y);
         acc_w[i][2 * h] = __fmaf_rn(g, f.x, acc_w[i][2 * h]);
         acc_w[i][2 * h + 1] = __fmaf_rn(g, f.y, acc_w[i][2 * h + 1]);
       }
@@ -396,7 +301,7 @@ __global__ void __launch_bounds__(512, 1) k_tc_last2(const __nv_bfloat16* __rest
         const uint32_t ew[4] = {eu.x, eu.y, eu.z, eu.w};
 #pragma unroll
         for (int h = 0; h < 4; ++h) {
-          const float2 e = unpack_bf16x2(ew[h]);
+          const float2 e = unpack_op2(ew[h]);
           acc_a[i][2 * h] = __fmaf_rn(g, e.x, acc_a[i][2 * h]);
           acc_a[i][2 * h + 1] = __fmaf_rn(g, e.y, acc_a[i][2 * h + 1]);
         }
@@ -421,11 +326,40 @@ __global__ void __launch_bounds__(512, 1) k_tc_last2(const __nv_bfloat16* __rest
   if (warp == 0) {
     loss_local = warp_sum(loss_local);
     gb_local = warp_sum(gb_local);
+    for (int o = 16; o > 0; o >>= 1) gmax_local = fmaxf(gmax_local, __shfl_xor_sync(0xffffffffu, gmax_local, o));
     if (lane == 0) {
       if (target) atomicAdd(loss_acc, loss_local);
       atomicAdd(gb, gb_local);
+      if (gmax_acc) atomicMax(gmax_acc, __float_as_uint(gmax_local));   // non-negative floats order as unsigned ints
     }
   }
+}
+
+// ------------------------------------------------------------------------------------------------ loss scale
+// fp16 dZ images need a loss scale: g = d loss / d out is O(1/T).  gsc = {gs, 1/gs} with gs the power of two that puts
+// max |g| of the PREVIOUS step (opt->gmax_prev, measured by the last-layer kernels) at 2^10, so |dZ_L| = |g w omega C|
+// stays around 10^2 with two decades of head-room to 65504 (conversions saturate) and eight decades above the fp16
+// normal minimum.  Without history (first step, or no optimiser state: the autograd path) the estimate is
+// 4 * grad_scale (|2 diff| <= 4 for peak-normalised audio) plus max |extra_g|.  Consumers of dZ (dW, column sums)
+// multiply by 1/gs: exact, it is a power of two.
+__global__ void __launch_bounds__(256) k_tc_absmax(const float* __restrict__ x, int64_t n, unsigned* __restrict__ out) {
+  float m = 0.f;
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x)
+    m = fmaxf(m, fabsf(x[i]));
+  for (int o = 16; o > 0; o >>= 1) m = fmaxf(m, __shfl_xor_sync(0xffffffffu, m, o));
+  if ((threadIdx.x & 31) == 0 && m > 0.f) atomicMax(out, __float_as_uint(m));
+}
+__global__ void k_tc_gscale(const inr_opt_state* __restrict__ opt, const unsigned* __restrict__ extra_max, float grad_scale,
+                            int has_target, float* __restrict__ gsc) {
+  const float ex = extra_max ? __uint_as_float(*extra_max) : 0.f;
+  float est = opt ? opt->gmax_prev : 0.f;
+  if (!(est > 0.f)) est = (has_target ? 4.f * grad_scale : 0.f) + ex;
+  est = fmaxf(est, ex);
+  int e = 0;
+  if (est > 0.f && est < 3e38f) e = 10 - (int)ceilf(log2f(est));
+  e = max(-100, min(100, e));
+  gsc[0] = exp2f((float)e);
+  gsc[1] = exp2f((float)-e);
 }
 
 // ------------------------------------------------------------------------------------------------ column sums
@@ -434,11 +368,13 @@ __global__ void __launch_bounds__(512, 1) k_tc_last2(const __nv_bfloat16* __rest
 // A warp owns one feature group for a span of tiles: lane = row % 32, 16-byte loads (512 B per warp instruction),
 // 8 register accumulators per output, ONE butterfly reduction at the end, then atomics.
 template <int NW>   // number of weighted outputs per feature: 0, 1 or 2
-__global__ void __launch_bounds__(256) k_tc_colsum(const __nv_bfloat16* __restrict__ X, int H, int num_tiles,
+__global__ void __launch_bounds__(256) k_tc_colsum(const op16* __restrict__ X, int H, int num_tiles,
                                                    int tiles_per_task, const float* __restrict__ wrow,
                                                    const float* __restrict__ coords, int in, int64_t rows, int64_t g0,
                                                    int64_t T_total, float scale, float* __restrict__ out_plain,
-                                                   float* __restrict__ out_w, int wstride) {
+                                                   float* __restrict__ out_w, int wstride,
+                                                   const float* __restrict__ gsc) {
+  const float inv_gs = gsc ? gsc[1] : 1.f;   // X is a loss-scaled dZ-like image
   const int groups = H >> 3;
   const int lane = threadIdx.x & 31;
   const int64_t warp_id = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
@@ -457,7 +393,7 @@ __global__ void __launch_bounds__(256) k_tc_colsum(const __nv_bfloat16* __restri
       for (int q = 0; q < (NW > 0 ? NW : 1); ++q) accw[q][j] = 0.f;
     }
     for (int tile = t0; tile < t1; ++tile) {
-      const __nv_bfloat16* base = X + (size_t)tile * (TILE_ROWS * (size_t)H) + (size_t)kg * TILE_ROWS * 8;
+      const op16* base = X + (size_t)tile * (TILE_ROWS * (size_t)H) + (size_t)kg * TILE_ROWS * 8;
 #pragma unroll
       for (int rr = 0; rr < TILE_ROWS; rr += 32) {
         const int r = rr + lane;
@@ -480,7 +416,7 @@ __global__ void __launch_bounds__(256) k_tc_colsum(const __nv_bfloat16* __restri
         }
 #pragma unroll
         for (int h = 0; h < 4; ++h) {
-          const float2 f = unpack_bf16x2(uw[h]);
+          const float2 f = unpack_op2(uw[h]);
           acc[2 * h] += f.x;
           acc[2 * h + 1] += f.y;
 #pragma unroll
@@ -493,11 +429,11 @@ __global__ void __launch_bounds__(256) k_tc_colsum(const __nv_bfloat16* __restri
     }
 #pragma unroll
     for (int j = 0; j < 8; ++j) {
-      const float s = warp_sum(acc[j]);
+      const float s = warp_sum(acc[j]) * inv_gs;
       if (out_plain && lane == j) atomicAdd(&out_plain[kg * 8 + j], s);
 #pragma unroll
       for (int q = 0; q < NW; ++q) {
-        const float sw = warp_sum(accw[q][j]);
+        const float sw = warp_sum(accw[q][j]) * inv_gs;
         if (lane == j) atomicAdd(&out_w[(int64_t)(kg * 8 + j) * wstride + q], sw);
       }
     }
@@ -505,26 +441,15 @@ __global__ void __launch_bounds__(256) k_tc_colsum(const __nv_bfloat16* __restri
 }
 
 // ------------------------------------------------------------------------------------------------ host side
-bool tc_pair_mode();
 bool siren_tc_supported(const inr_siren_desc* d) {
   const int H = d->hidden_features;
   const int Ltot = d->hidden_layers + d->num_snake + d->num_tanh;
-  // Snake / Tanh layers (hidden, or a Linear+Snake first layer) exist in the CTA-pair kernel only
-  const bool sine_only = d->num_snake == 0 && d->num_tanh == 0 && d->first_linear == 0;
   return (H == 128 || H == 256 || H == 512) && Ltot >= 1 && d->out_features == 1 &&
-         (d->in_features <= 2 || d->in_features <= H) &&   // encoded inputs: zero-padded to H (k_tc_rows_to_image)
-         (sine_only || tc_pair_mode());
+         (d->in_features <= 2 || d->in_features <= H);   // encoded inputs: zero-padded to H (k_tc_rows_to_image)
 }
 
-// INR_TC_PAIR=0 selects the single-CTA layer kernel of tc_gemm.cuh (kept as the A/B baseline of profiles/r01_*);
-// the default is the CTA-pair kernel of tc_gemm2.cuh.
-bool tc_pair_mode() {
-  static int v = -1;
-  if (v < 0) { const char* e = getenv("INR_TC_PAIR"); v = (e && e[0] == '0') ? 0 : 1; }
-  return v != 0;
-}
-// columns of the packed weight slices ([slice][K/8][ns][8]): one slice per CTA
-int tc_ns(int H) { return tc_pair_mode() ? (H >= 256 ? 128 : H / 2) : (H >= 512 ? 128 : H); }
+// columns of the packed weight slices ([slice][K/8][ns][8]): one slice per CTA of a pair
+int tc_ns(int H) { return H >= 256 ? 128 : H / 2; }
 static int ns_of(int H) { return tc_ns(H); }
 
 struct TcPlan {
@@ -539,7 +464,7 @@ static TcPlan plan_of(const inr_siren_desc* d, int training) {
   const bool wide = lay.in > 2;
   pl.pack_bytes = 2 * L * H * H * 2 + (wide ? H * H * 2 + H * H * 4 : 0);   // + padded W_0 operand, padded gW_0 scratch
   pl.n_images = (training ? 2 * (int)(L + 1) + lay.num_snake_layers() : 2) + (wide ? 1 : 0);   // + dy/da images, + X
-  pl.img_bytes_per_row = pl.n_images * H * 2 + (training ? 4 : 0);   // + gvec
+  pl.img_bytes_per_row = pl.n_images * H * 2;
   pl.fixed_bytes = round_up(pl.pack_bytes, 1024) + 4096;
   pl.gvec_bytes = 0;
   return pl;
@@ -551,23 +476,6 @@ int64_t siren_tc_workspace_bytes(const inr_siren_desc* d, int64_t n_rows, int tr
   int64_t rows = round_up(std::max<int64_t>(n_rows, 1), TILE_ROWS);
   if (rows * pl.img_bytes_per_row > cap) rows = std::max<int64_t>(cap / pl.img_bytes_per_row / TILE_ROWS, 8) * TILE_ROWS;
   return pl.fixed_bytes + rows * pl.img_bytes_per_row + 1024;
-}
-
-template <int H, int MODE>
-static int launch_layer(const LayerParams& p, cudaStream_t st) {
-  using Cfg = LayerCfg<H>;
-  static bool attr_set = false;
-  if (!attr_set) {
-    INR_CUDA_CHECK(cudaFuncSetAttribute(k_tc_layer<H, MODE>, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg::SMEM_BYTES));
-    attr_set = true;
-  }
-  int grid = num_sms() / Cfg::NQ * Cfg::NQ;
-  const int max_useful = (int)std::min<int64_t>((int64_t)p.num_tiles * Cfg::NQ, 1 << 30);
-  if (grid > max_useful) grid = max_useful;
-  { LaunchScope ls(MODE == MODE_FWD ? "k_tc_layer_fwd" : "k_tc_layer_bwd", st);
-    k_tc_layer<H, MODE><<<grid, Cfg::THREADS, Cfg::SMEM_BYTES, st>>>(p); }
-  INR_LAUNCH_CHECK();
-  return INR_OK;
 }
 
 template <int H>
@@ -619,20 +527,8 @@ int tc_layer(int H, int mode, const LayerParams& p, cudaStream_t st) {
   if (mode == MODE_FWD_SNAKE) return launch_layer2_h<MODE_FWD_SNAKE>(H, p, st);
   if (mode == MODE_FWD_TANH) return launch_layer2_h<MODE_FWD_TANH>(H, p, st);
   if (mode == MODE_BWD_SNAKE) return launch_layer2_h<MODE_BWD_SNAKE>(H, p, st);
-  if (tc_pair_mode()) {
-    switch (H) {
-      case 128: return mode == MODE_FWD ? launch_layer2<128, MODE_FWD>(p, st) : launch_layer2<128, MODE_BWD>(p, st);
-      case 256: return mode == MODE_FWD ? launch_layer2<256, MODE_FWD>(p, st) : launch_layer2<256, MODE_BWD>(p, st);
-      case 512: return mode == MODE_FWD ? launch_layer2<512, MODE_FWD>(p, st) : launch_layer2<512, MODE_BWD>(p, st);
-    }
-  }
-  switch (H) {
-    case 128: return mode == MODE_FWD ? launch_layer<128, MODE_FWD>(p, st) : launch_layer<128, MODE_BWD>(p, st);
-    case 256: return mode == MODE_FWD ? launch_layer<256, MODE_FWD>(p, st) : launch_layer<256, MODE_BWD>(p, st);
-    case 512: return mode == MODE_FWD ? launch_layer<512, MODE_FWD>(p, st) : launch_layer<512, MODE_BWD>(p, st);
-  }
-  set_error("tcgen05 layer kernel: unsupported H=%d", H);
-  return INR_E_UNSUPPORTED;
+  if (mode == MODE_FWD) return launch_layer2_h<MODE_FWD>(H, p, st);
+  return launch_layer2_h<MODE_BWD>(H, p, st);
 }
 
 template <int H>
@@ -652,83 +548,23 @@ static int launch_dw2(const DwParams& p, cudaStream_t st) {
   return INR_OK;
 }
 
-// CTA-pair dW kernel k_tc_dw2: default at H = 512, where it cuts the five dW launches of a C2 step by ~15 % (same box,
-// back to back, under the power cap: 6.2-6.5 vs 7.3-7.7 ms; step 27.2 vs 27.5 ms); at H = 256 the single-CTA kernel is
-// faster (C1 0.203 vs 0.223 ms).  INR_TC_DW_PAIR=0 / 1 forces one or the other (profiles/r01c_notes.md).
-static int tc_dw_pair_mode() {   // -1 = by width, 0 / 1 = forced
-  static int v = -2;
-  if (v == -2) { const char* e = getenv("INR_TC_DW_PAIR"); v = !e ? -1 : (e[0] == '1' ? 1 : 0); }
-  return v;
-}
 
+// H = 512: the CTA-pair kernel k_tc_dw2 (64 KB instead of 96 KB of operands per tile and CTA; -15 % on the five dW
+// launches of a C2 step); H <= 256: the single-CTA kernel is faster (C1 0.203 vs 0.223 ms, profiles/r01c_notes.md).
 int tc_dw(int H, const DwParams& p, cudaStream_t st) {
-  const int pm = tc_dw_pair_mode();
-  if (tc_pair_mode() && (pm == 1 || (pm == -1 && H == 512))) {
-    if (H == 256) return launch_dw2<256>(p, st);
-    if (H == 512) return launch_dw2<512>(p, st);
-  }
   switch (H) {
     case 128: return launch_dw<128>(p, st);
     case 256: return launch_dw<256>(p, st);
-    case 512: return launch_dw<512>(p, st);
+    case 512: return launch_dw2<512>(p, st);
   }
   set_error("tcgen05 dW kernel: unsupported H=%d", H);
   return INR_E_UNSUPPORTED;
 }
 
-// INR_TC_FUSED=0 selects the layer-major forward (k_tc_first + one k_tc_layer2<FWD> per layer, kept as the A/B
-// baseline); the default for H <= 256 is the fused all-layer forward of tc_fused.cuh.
-bool tc_fused_mode() {
-  static int v = -1;
-  if (v < 0) { const char* e = getenv("INR_TC_FUSED"); v = (e && e[0] == '0') ? 0 : 1; }
-  return v != 0;
-}
-// INR_TC_FUSED_LAST=0 keeps the head / loss / dZ_L in k_tc_last + k_tc_colsum after the fused forward (A/B baseline)
-bool tc_fused_last_mode() {
-  static int v = -1;
-  if (v < 0) { const char* e = getenv("INR_TC_FUSED_LAST"); v = (e && e[0] == '0') ? 0 : 1; }
-  return v != 0;
-}
 static bool fused_ok(const inr_siren_desc* d) {
-  return tc_fused_mode() && tc_pair_mode() && (d->hidden_features == 128 || d->hidden_features == 256) &&
+  return (d->hidden_features == 128 || d->hidden_features == 256) &&
          d->hidden_layers >= 1 && d->hidden_layers <= FUSED_MAX_L && d->num_snake == 0 && d->num_tanh == 0 &&
          d->first_linear == 0 && d->in_features <= 2;
-}
-
-// INR_TC_FUSED_BWD=1 selects the fused backward chain k_tc_fused_bwd (H <= 256).  Measured on B200
-// (profiles/r01c_notes.md): parity-identical gradients, 6 instead of 10 HBM units at L = 3, but its 8 epilogue warps
-// fetch the C_l stash with per-thread loads and reach only 3.2 TB/s: C1 0.254 ms against 0.204 + 0.040 ms for the three
-// layer-major BWD launches + the first-layer column sums, C3 1.20 against 1.05 ms.  Default off until the epilogue is
-// widened.
-bool tc_fused_bwd_mode() {
-  static int v = -1;
-  if (v < 0) { const char* e = getenv("INR_TC_FUSED_BWD"); v = (e && e[0] == '1') ? 1 : 0; }
-  return v != 0;
-}
-
-// INR_TC_FUSED_EW=8 runs the fused kernels with 8 epilogue warps (320 threads, the first version); the default is 16
-// (576 threads, <= 112 registers): four warps per scheduler hide the MUFU / TMEM / global-load latency of the epilogue.
-static int tc_fused_ew() {
-  static int v = -1;
-  if (v < 0) { const char* e = getenv("INR_TC_FUSED_EW"); v = (e && e[0] == '8') ? 8 : 16; }
-  return v;
-}
-
-template <int H, int EW>
-static int launch_fused_bwd(const FusedBwdParams& p, cudaStream_t st) {
-  using Cfg = FusedCfg<H>;
-  static bool attr_set = false;
-  if (!attr_set) {
-    INR_CUDA_CHECK(cudaFuncSetAttribute(k_tc_fused_bwd<H, EW>, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg::SMEM_BYTES));
-    attr_set = true;
-  }
-  int pairs = num_sms() / 2;
-  const int num_dt = (p.num_tiles + 1) / 2;
-  if (pairs > num_dt) pairs = num_dt;
-  { LaunchScope ls("k_tc_fused_bwd", st);
-    k_tc_fused_bwd<H, EW><<<2 * pairs, 64 + 32 * EW, Cfg::SMEM_BYTES, st>>>(p); }
-  INR_LAUNCH_CHECK();
-  return INR_OK;
 }
 
 template <int H, int EW>
@@ -756,11 +592,12 @@ constexpr int kFusedTraceJobs = 96;
 
 struct FusedLast {   // arguments of the fused head + loss + dZ_L epilogue (FusedParams::fuse_last)
   const float* target; const float* extra_g; int loss_kind; float grad_scale; float* grads; double* loss_acc; float* out;
+  const float* gsc; unsigned* gmax_acc;
 };
 
-static int fused_forward(const inr_siren_desc* d, const float* params, const __nv_bfloat16* Wf, const float* coords,
-                         int64_t rows, int tiles, int64_t g0, int64_t T_total, float scale, __nv_bfloat16* const* S,
-                         __nv_bfloat16* const* C, const FusedLast* fl, cudaStream_t st) {
+static int fused_forward(const inr_siren_desc* d, const float* params, const op16* Wf, const float* coords,
+                         int64_t rows, int tiles, int64_t g0, int64_t T_total, float scale, op16* const* S,
+                         op16* const* C, const FusedLast* fl, cudaStream_t st) {
   SirenLayout lay = layout_of(d);
   FusedParams p;
   p.Wf = Wf; p.W0 = params + lay.w_off(0); p.B0 = params + lay.b_off(0);
@@ -775,14 +612,14 @@ static int fused_forward(const inr_siren_desc* d, const float* params, const __n
   p.target = fl ? fl->target : nullptr; p.extra_g = fl ? fl->extra_g : nullptr; p.out = fl ? fl->out : nullptr;
   p.g_wlast = fl ? fl->grads + lay.w_off(lay.L + 1) : nullptr; p.g_blast = fl ? fl->grads + lay.b_off(lay.L + 1) : nullptr;
   p.loss_acc = fl ? fl->loss_acc : nullptr;
-  { static int dbg = -1; if (dbg < 0) { const char* e = getenv("INR_TC_FUSED_DBG"); dbg = e ? atoi(e) : 0; } p.dbg = dbg; }
+  p.gsc = fl ? fl->gsc : nullptr; p.gmax_acc = fl ? fl->gmax_acc : nullptr;
+  p.dbg = 0;
   p.trace = g_fused_trace; p.trace_jobs = g_fused_trace ? kFusedTraceJobs : 0;
-  if (tc_fused_ew() == 8) return lay.H == 256 ? launch_fused<256, 8>(p, st) : launch_fused<128, 8>(p, st);
   return lay.H == 256 ? launch_fused<256, 16>(p, st) : launch_fused<128, 16>(p, st);
 }
 
-static LayerParams layer_params(int H, const __nv_bfloat16* A, const __nv_bfloat16* Bp, const float* bias, float omega,
-                                __nv_bfloat16* out0, __nv_bfloat16* out1, const __nv_bfloat16* Cin, int tiles) {
+static LayerParams layer_params(int H, const op16* A, const op16* Bp, const float* bias, float omega,
+                                op16* out0, op16* out1, const op16* Cin, int tiles) {
   LayerParams p;
   p.A = A; p.Bpack = Bp; p.bias = bias; p.omega = omega; p.out0 = out0; p.out1 = out1; p.Cin = Cin; p.num_tiles = tiles;
   p.avec = nullptr; p.out2 = nullptr;
@@ -791,9 +628,9 @@ static LayerParams layer_params(int H, const __nv_bfloat16* A, const __nv_bfloat
   return p;
 }
 
-static int colsum(const __nv_bfloat16* X, int H, int tiles, const float* wrow, const float* coords, int in, int64_t rows,
+static int colsum(const op16* X, int H, int tiles, const float* wrow, const float* coords, int in, int64_t rows,
                   int64_t g0, int64_t T_total, float scale, float* out_plain, float* out_w, int wstride, int nw,
-                  cudaStream_t st) {
+                  const float* gsc, cudaStream_t st) {
   const int groups = H / 8;
   int tiles_per_task = std::max(1, (int)cdiv((int64_t)tiles * groups, (int64_t)num_sms() * 32));
   const int64_t ntasks = (int64_t)groups * cdiv(tiles, tiles_per_task);
@@ -801,22 +638,22 @@ static int colsum(const __nv_bfloat16* X, int H, int tiles, const float* wrow, c
   if (blocks < 1) blocks = 1;
   { LaunchScope ls(nw == 0 ? "k_tc_colsum" : "k_tc_colsum_w", st);
     if (nw == 0)
-      k_tc_colsum<0><<<blocks, 256, 0, st>>>(X, H, tiles, tiles_per_task, wrow, coords, in, rows, g0, T_total, scale, out_plain, out_w, wstride);
+      k_tc_colsum<0><<<blocks, 256, 0, st>>>(X, H, tiles, tiles_per_task, wrow, coords, in, rows, g0, T_total, scale, out_plain, out_w, wstride, gsc);
     else if (nw == 1)
-      k_tc_colsum<1><<<blocks, 256, 0, st>>>(X, H, tiles, tiles_per_task, wrow, coords, in, rows, g0, T_total, scale, out_plain, out_w, wstride);
+      k_tc_colsum<1><<<blocks, 256, 0, st>>>(X, H, tiles, tiles_per_task, wrow, coords, in, rows, g0, T_total, scale, out_plain, out_w, wstride, gsc);
     else
-      k_tc_colsum<2><<<blocks, 256, 0, st>>>(X, H, tiles, tiles_per_task, wrow, coords, in, rows, g0, T_total, scale, out_plain, out_w, wstride); }
+      k_tc_colsum<2><<<blocks, 256, 0, st>>>(X, H, tiles, tiles_per_task, wrow, coords, in, rows, g0, T_total, scale, out_plain, out_w, wstride, gsc); }
   INR_LAUNCH_CHECK();
   return INR_OK;
 }
 
 struct TcWorkspace {
-  __nv_bfloat16 *Wf, *Wb;
-  __nv_bfloat16* Wf0;   // wide inputs: W_0 zero-padded to H x H (forward operand)
+  op16 *Wf, *Wb;
+  op16* Wf0;   // wide inputs: W_0 zero-padded to H x H (forward operand)
   float* gW0;           // wide inputs: H x H fp32 scratch of the padded first-layer weight gradient
   int x_image;          // wide inputs: index of the input image X, else -1
-  float* gvec;
-  __nv_bfloat16* img;
+  float* gsc;           // {gs, 1/gs}: loss scale of the fp16 dZ images of this call (k_tc_gscale); [2] = max |extra_g| bits
+  op16* img;
   int64_t chunk_rows;   // multiple of 128
   int64_t img_elems;    // elements per image
 };
@@ -826,7 +663,7 @@ static int carve(const inr_siren_desc* d, int training, int64_t n, void* ws, int
   const int64_t H = d->hidden_features, L = layout_of(d).L;
   uint8_t* base = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(ws) + 255) & ~(uintptr_t)255);
   const int64_t usable = ws_bytes - (base - reinterpret_cast<uint8_t*>(ws));
-  w->Wf = reinterpret_cast<__nv_bfloat16*>(base);
+  w->Wf = reinterpret_cast<op16*>(base);
   w->Wb = w->Wf + L * H * H;
   w->Wf0 = w->Wb + L * H * H;
   w->gW0 = reinterpret_cast<float*>(w->Wf0 + H * H);
@@ -838,10 +675,8 @@ static int carve(const inr_siren_desc* d, int training, int64_t n, void* ws, int
   w->chunk_rows = rows;
   w->img_elems = rows * H;
   uint8_t* p = base + pl.fixed_bytes;
-  w->gvec = reinterpret_cast<float*>(p);
-  if (training) p += rows * 4;
-  p = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(p) + 255) & ~(uintptr_t)255);
-  w->img = reinterpret_cast<__nv_bfloat16*>(p);
+  w->gsc = reinterpret_cast<float*>(p - 256);   // inside the 4 KB pad that follows the packed weights
+  w->img = reinterpret_cast<op16*>(p);
   return INR_OK;
 }
 
@@ -861,8 +696,8 @@ static int pack_weights(const inr_siren_desc* d, const float* params, const TcWo
 }
 
 static int first_layer(const inr_siren_desc* d, const float* params, const float* coords, int64_t rows, int64_t rows_pad,
-                       int64_t g0, int64_t T_total, float scale, __nv_bfloat16* S0, __nv_bfloat16* C0, cudaStream_t st,
-                       __nv_bfloat16* E0 = nullptr) {
+                       int64_t g0, int64_t T_total, float scale, op16* S0, op16* C0, cudaStream_t st,
+                       op16* E0 = nullptr) {
   SirenLayout lay = layout_of(d);
   const int64_t total = rows_pad * (lay.H / 8);
   int blocks = (int)std::min<int64_t>(cdiv(total, 256), (int64_t)num_sms() * 16);
@@ -874,18 +709,11 @@ static int first_layer(const inr_siren_desc* d, const float* params, const float
   return INR_OK;
 }
 
-// INR_TC_LAST2=0 keeps k_tc_last + the separate column-sum launches (A/B baseline of profiles/r01e_notes.md)
-static bool tc_last2_mode() {
-  static int v = -1;
-  if (v < 0) { const char* e = getenv("INR_TC_LAST2"); v = (e && e[0] == '0') ? 0 : 1; }
-  return v != 0;
-}
-
 template <int H, bool SNAKE>
-static int launch_last2(const __nv_bfloat16* SL, __nv_bfloat16* CL, const float* w, const float* b, const float* target,
+static int launch_last2(const op16* SL, op16* CL, const float* w, const float* b, const float* target,
                         const float* extra_g, int64_t rows, int tiles, float dfac, float omega_h, int outermost_linear,
                         int loss_kind, float grad_scale, float* gw, float* gb, double* loss_acc, float* out, int training,
-                        const __nv_bfloat16* EL, float* ga, cudaStream_t st) {
+                        const op16* EL, float* ga, const float* gsc, unsigned* gmax_acc, cudaStream_t st) {
   using Cfg = Last2Cfg<H>;
   static bool attr_done = false;
   if (!attr_done) {
@@ -896,17 +724,17 @@ static int launch_last2(const __nv_bfloat16* SL, __nv_bfloat16* CL, const float*
   { LaunchScope ls("k_tc_last", st);
     k_tc_last2<H, SNAKE><<<blocks, 512, Cfg::SMEM_BYTES, st>>>(SL, CL, w, b, target, extra_g, rows, tiles, dfac, omega_h,
                                                                outermost_linear, loss_kind, grad_scale, gw, gb, loss_acc,
-                                                               out, training, EL, ga); }
+                                                               out, training, EL, ga, gsc, gmax_acc); }
   INR_LAUNCH_CHECK();
   return INR_OK;
 }
 
 // out = act(S_L w + b); training: loss, g = dloss/dout, dZ_L over C_L, last-layer gradients (and the `a` gradient of a
 // Snake layer L from its dy/da image EL)
-static int last_layer(const inr_siren_desc* d, const float* params, const __nv_bfloat16* SL, __nv_bfloat16* CL,
+static int last_layer(const inr_siren_desc* d, const float* params, const op16* SL, op16* CL,
                       const float* target, const float* extra_g, int64_t rows, int tiles, int loss_kind, float grad_scale,
-                      float* gvec, float* grads, inr_opt_state* opt, float* out, int training, cudaStream_t st,
-                      __nv_bfloat16* EL = nullptr) {
+                      const float* gsc, float* grads, inr_opt_state* opt, float* out, int training, cudaStream_t st,
+                      op16* EL = nullptr) {
   SirenLayout lay = layout_of(d);
   const int last = lay.L + 1;
   const int H = lay.H;
@@ -917,40 +745,26 @@ static int last_layer(const inr_siren_desc* d, const float* params, const __nv_b
   float* gw = grads ? grads + lay.w_off(last) : nullptr;
   float* gb = grads ? grads + lay.b_off(last) : nullptr;
   double* loss_acc = opt ? &opt->loss_acc[0] : nullptr;
+  unsigned* gmax = (opt && training) ? reinterpret_cast<unsigned*>(&opt->gmax_acc) : nullptr;
   if (!training) EL = nullptr;
-  if (tc_last2_mode()) {
-    float* ga = (EL && grads) ? grads + lay.a_off(lay.L) : nullptr;
+  float* ga = (EL && grads) ? grads + lay.a_off(lay.L) : nullptr;
 #define INR_LAST2(HH)                                                                                                   \
-    return EL ? launch_last2<HH, true>(SL, CL, w, b, target, extra_g, rows, tiles, dfac, d->hidden_omega_0,            \
-                                       d->outermost_linear, loss_kind, grad_scale, gw, gb, loss_acc, out, training, EL, \
-                                       ga, st)                                                                          \
-              : launch_last2<HH, false>(SL, CL, w, b, target, extra_g, rows, tiles, dfac, d->hidden_omega_0,           \
-                                        d->outermost_linear, loss_kind, grad_scale, gw, gb, loss_acc, out, training,    \
-                                        nullptr, nullptr, st)
-    if (H == 512) { INR_LAST2(512); }
-    if (H == 256) { INR_LAST2(256); }
-    INR_LAST2(128);
+  return EL ? launch_last2<HH, true>(SL, CL, w, b, target, extra_g, rows, tiles, dfac, d->hidden_omega_0,              \
+                                     d->outermost_linear, loss_kind, grad_scale, gw, gb, loss_acc, out, training, EL,   \
+                                     ga, gsc, gmax, st)                                                                 \
+            : launch_last2<HH, false>(SL, CL, w, b, target, extra_g, rows, tiles, dfac, d->hidden_omega_0,             \
+                                      d->outermost_linear, loss_kind, grad_scale, gw, gb, loss_acc, out, training,      \
+                                      nullptr, nullptr, gsc, gmax, st)
+  if (H == 512) { INR_LAST2(512); }
+  if (H == 256) { INR_LAST2(256); }
+  INR_LAST2(128);
 #undef INR_LAST2
-  }
-  int blocks = std::min(tiles, num_sms() * 8);
-  { LaunchScope ls("k_tc_last", st);
-    k_tc_last<<<blocks, 128, H * sizeof(float), st>>>(SL, CL, w, b, target, extra_g, rows, tiles, H, dfac,
-                                                      d->hidden_omega_0, d->outermost_linear, loss_kind, grad_scale, gvec,
-                                                      gb, loss_acc, out, training, EL); }
-  INR_LAUNCH_CHECK();
-  if (!training) return INR_OK;
-  int rc;
-  // Snake layer L: its `a` gradient = column sums of the g w dy/da products k_tc_last left in E(L)
-  if (EL && (rc = colsum(EL, H, tiles, nullptr, nullptr, 1, rows, 0, 1, 1.f, grads + lay.a_off(lay.L), nullptr, 1, 0, st)))
-    return rc;
-  // last-layer weight gradient: gw_out[f] += sum_r g[r] S_L[r][f]
-  return colsum(SL, H, tiles, gvec, nullptr, 1, rows, 0, 1, 1.f, nullptr, gw, 1, 1, st);
 }
 
 // forward of hidden layer l (1..L) by its activation kind: Sout = act(Sin W^T + b), Cout = derivative image,
 // Eout = dy/da image (Snake layers)
 static int fwd_layer_tc(const inr_siren_desc* d, const SirenLayout& lay, const float* params, const TcWorkspace& w, int l,
-                        const __nv_bfloat16* Sin, __nv_bfloat16* Sout, __nv_bfloat16* Cout, __nv_bfloat16* Eout, int tiles,
+                        const op16* Sin, op16* Sout, op16* Cout, op16* Eout, int tiles,
                         cudaStream_t st) {
   const int H = lay.H;
   const int kind = lay.kind(l);
@@ -962,8 +776,8 @@ static int fwd_layer_tc(const inr_siren_desc* d, const SirenLayout& lay, const f
 
 // layer 0 on an encoded coordinate: X image from the rows, then the layer GEMM with the padded W_0
 static int first_layer_wide(const inr_siren_desc* d, const SirenLayout& lay, const float* params, const TcWorkspace& w,
-                            const float* xc, int64_t rows, int64_t rows_pad, __nv_bfloat16* X, __nv_bfloat16* S0,
-                            __nv_bfloat16* C0, __nv_bfloat16* E0, int tiles, cudaStream_t st) {
+                            const float* xc, int64_t rows, int64_t rows_pad, op16* X, op16* S0,
+                            op16* C0, op16* E0, int tiles, cudaStream_t st) {
   const int H = lay.H;
   const int64_t total = rows_pad * (H / 8);
   const int blocks = (int)std::min<int64_t>(cdiv(total, 256), (int64_t)num_sms() * 16);
@@ -989,9 +803,9 @@ int siren_tc_forward(const inr_siren_desc* d, const float* params, const float* 
     const int64_t rows = std::min(w.chunk_rows, n - r0);
     const int64_t rows_pad = round_up(rows, TILE_ROWS);
     const int tiles = (int)(rows_pad / TILE_ROWS);
-    __nv_bfloat16* S[2] = {w.img, w.img + w.img_elems};
+    op16* S[2] = {w.img, w.img + w.img_elems};
     if (fused_ok(d)) {   // all layers in one kernel; only S_L goes to HBM, for the output dot below
-      __nv_bfloat16* Sl[FUSED_MAX_L + 1] = {nullptr};
+      op16* Sl[FUSED_MAX_L + 1] = {nullptr};
       Sl[L] = S[0];
       if ((rc = fused_forward(d, params, w.Wf, coords ? coords + r0 * lay.in : nullptr, rows, tiles, i0 + r0, T_total, scale,
                               Sl, nullptr, nullptr, st)))
@@ -1021,6 +835,24 @@ int siren_tc_forward(const inr_siren_desc* d, const float* params, const float* 
   return INR_OK;
 }
 
+// loss scale of this call's dZ images -> w.gsc (see k_tc_gscale)
+static int set_gscale(const TcWorkspace& w, const inr_opt_state* opt, const float* extra_g, int64_t n, const float* target,
+                      float grad_scale, cudaStream_t st) {
+  unsigned* exmax = nullptr;
+  if (extra_g) {
+    exmax = reinterpret_cast<unsigned*>(w.gsc + 2);
+    INR_CUDA_CHECK(cudaMemsetAsync(exmax, 0, sizeof(unsigned), st));
+    const int blocks = (int)std::min<int64_t>(cdiv(n, 256 * 8), (int64_t)num_sms() * 4);
+    LaunchScope ls("k_tc_gscale", st);
+    k_tc_absmax<<<std::max(blocks, 1), 256, 0, st>>>(extra_g, n, exmax);
+    INR_LAUNCH_CHECK();
+  }
+  { LaunchScope ls("k_tc_gscale", st);
+    k_tc_gscale<<<1, 1, 0, st>>>(opt, exmax, grad_scale, target != nullptr, w.gsc); }
+  INR_LAUNCH_CHECK();
+  return INR_OK;
+}
+
 // phase bits: 1 = forward (activations kept in the workspace), 2 = backward.  phase 3 is the fused step (the last-layer
 // kernel computes the output, the loss gradient and dZ_L in one pass); phase 1 writes the model output and stops so a
 // spectral loss can be evaluated on it; phase 2 resumes from the SAME workspace with that loss's gradient in extra_gout.
@@ -1037,6 +869,7 @@ int siren_tc_train(const inr_siren_desc* d, const float* params, const float* co
               "split forward/backward needs the whole row range in one workspace chunk (%lld rows > %lld)", (long long)n,
               (long long)w.chunk_rows);
   if ((phase & 1) && (rc = pack_weights(d, params, w, st))) return rc;
+  if ((phase & 2) && (rc = set_gscale(w, opt, extra_gout, n, target, grad_scale, st))) return rc;
   for (int64_t r0 = 0; r0 < n; r0 += w.chunk_rows) {
     const int64_t rows = std::min(w.chunk_rows, n - r0);
     const int64_t rows_pad = round_up(rows, TILE_ROWS);
@@ -1044,33 +877,34 @@ int siren_tc_train(const inr_siren_desc* d, const float* params, const float* co
     auto S = [&](int l) { return w.img + (int64_t)l * w.img_elems; };
     auto C = [&](int l) { return w.img + (int64_t)(L + 1 + l) * w.img_elems; };
     // dy/da image of Snake layer l (NULL for the other kinds)
-    auto E = [&](int l) -> __nv_bfloat16* {
+    auto E = [&](int l) -> op16* {
       return lay.kind(l) == ACT_SNAKE ? w.img + (int64_t)(2 * (L + 1) + lay.snakes_before(l)) * w.img_elems : nullptr;
     };
     const float* xc = coords ? coords + r0 * lay.in : nullptr;
     bool fused_tail = false;
     if (phase & 1) {
       if (fused_ok(d)) {   // one kernel: S_l never re-read from HBM, only the stash the backward needs is written
-        __nv_bfloat16 *Sl[FUSED_MAX_L + 1], *Cl[FUSED_MAX_L + 1];
+        op16 *Sl[FUSED_MAX_L + 1], *Cl[FUSED_MAX_L + 1];
         for (int l = 0; l <= L; ++l) { Sl[l] = S(l); Cl[l] = C(l); }
         // the fused step with the nn.Linear head also runs the head, the loss and dZ_L in the same kernel:
         // S_L / C_L never reach HBM (dZ_L is written where C_L would go)
-        fused_tail = (phase == 3) && d->outermost_linear && tc_fused_last_mode();
+        fused_tail = (phase == 3) && d->outermost_linear;
         FusedLast fl = {target ? target + r0 : nullptr, extra_gout ? extra_gout + r0 : nullptr, loss_kind, grad_scale, grads,
-                        opt ? &opt->loss_acc[0] : nullptr, out ? out + r0 : nullptr};
+                        opt ? &opt->loss_acc[0] : nullptr, out ? out + r0 : nullptr, w.gsc,
+                        opt ? reinterpret_cast<unsigned*>(&opt->gmax_acc) : nullptr};
         if (fused_tail) Sl[L] = nullptr;
         if ((rc = fused_forward(d, params, w.Wf, xc, rows, tiles, i0 + r0, T_total, scale, Sl, Cl, fused_tail ? &fl : nullptr, st)))
           return rc;
       } else {
-      if (w.x_image >= 0) {
-        rc = first_layer_wide(d, lay, params, w, xc, rows, rows_pad, w.img + (int64_t)w.x_image * w.img_elems, S(0), C(0),
-                              E(0), tiles, st);
-      } else {
-        rc = first_layer(d, params, xc, rows, rows_pad, i0 + r0, T_total, scale, S(0), C(0), st, E(0));
-      }
-      if (rc) return rc;
-      for (int l = 1; l <= L; ++l)
-        if ((rc = fwd_layer_tc(d, lay, params, w, l, S(l - 1), S(l), C(l), E(l), tiles, st))) return rc;
+        if (w.x_image >= 0) {
+          rc = first_layer_wide(d, lay, params, w, xc, rows, rows_pad, w.img + (int64_t)w.x_image * w.img_elems, S(0), C(0),
+                                E(0), tiles, st);
+        } else {
+          rc = first_layer(d, params, xc, rows, rows_pad, i0 + r0, T_total, scale, S(0), C(0), st, E(0));
+        }
+        if (rc) return rc;
+        for (int l = 1; l <= L; ++l)
+          if ((rc = fwd_layer_tc(d, lay, params, w, l, S(l - 1), S(l), C(l), E(l), tiles, st))) return rc;
       }
       if (phase == 1) {
         if ((rc = last_layer(d, params, S(L), nullptr, nullptr, nullptr, rows, tiles, 0, 0.f, nullptr, nullptr, nullptr,
@@ -1079,31 +913,16 @@ int siren_tc_train(const inr_siren_desc* d, const float* params, const float* co
         continue;
       }
     }
-    if (!fused_tail) {
-    if ((rc = last_layer(d, params, S(L), C(L), target ? target + r0 : nullptr, extra_gout ? extra_gout + r0 : nullptr, rows,
-                         tiles, loss_kind, grad_scale, w.gvec, grads, opt, out ? out + r0 : nullptr, 1, st, E(L))))
+    if (!fused_tail &&
+        (rc = last_layer(d, params, S(L), C(L), target ? target + r0 : nullptr, extra_gout ? extra_gout + r0 : nullptr, rows,
+                         tiles, loss_kind, grad_scale, w.gsc, grads, opt, out ? out + r0 : nullptr, 1, st, E(L))))
       return rc;
-    }
-    const bool fused_bwd = fused_ok(d) && tc_fused_bwd_mode();
-    if (fused_bwd) {
-      // the whole chain dZ_L -> dZ_0 in one kernel: dZ_{L-1}..dZ_1 land in place over C_{L-1}..C_1 for the dW launches
-      // below, dZ_0 never leaves the SM (the first-layer gradients are reduced there)
-      FusedBwdParams bp;
-      bp.Wb = w.Wb; bp.dZL = C(L);
-      for (int l = 0; l < FUSED_MAX_L; ++l) bp.C[l] = l < L ? C(l) : nullptr;
-      bp.coords = xc; bp.gW0 = grads + lay.w_off(0); bp.gb0 = grads + lay.b_off(0);
-      bp.in = lay.in; bp.L = L; bp.num_tiles = tiles; bp.rows = rows; bp.g0 = i0 + r0; bp.T_total = T_total;
-      bp.scale = scale; bp.omega0 = d->first_omega_0; bp.omega_h = d->hidden_omega_0;
-      if (tc_fused_ew() == 8) rc = H == 256 ? launch_fused_bwd<256, 8>(bp, st) : launch_fused_bwd<128, 8>(bp, st);
-      else rc = H == 256 ? launch_fused_bwd<256, 16>(bp, st) : launch_fused_bwd<128, 16>(bp, st);
-      if (rc) return rc;
-    }
     for (int l = L; l >= 1; --l) {
       DwParams dp;
       dp.dZ = C(l); dp.S = S(l - 1); dp.gW = grads + lay.w_off(l); dp.gb = grads + lay.b_off(l); dp.num_tiles = tiles;
       dp.lbo = 128; dp.sbo = TILE_ROWS * 16;   // MN-major, no swizzle: LBO = next 8 rows (K), SBO = next 8-feature group
+      dp.gsc = w.gsc;
       if ((rc = tc_dw(H, dp, st))) return rc;
-      if (fused_bwd) continue;
       // dZ_{l-1} = (dZ_l W_l) * d y_{l-1}/d z_{l-1}: sine layers keep cos(omega z) (times omega here), Snake / Tanh the
       // whole derivative; a Snake layer also takes its `a` gradient from the same product against its dy/da image
       const int kprev = lay.kind(l - 1);
@@ -1112,7 +931,8 @@ int siren_tc_train(const inr_siren_desc* d, const float* params, const float* co
       if (kprev == ACT_SNAKE) {
         p.out2 = E(l - 1);
         if ((rc = tc_layer(H, MODE_BWD_SNAKE, p, st))) return rc;
-        if ((rc = colsum(E(l - 1), H, tiles, nullptr, nullptr, 1, rows, 0, 1, 1.f, grads + lay.a_off(l - 1), nullptr, 1, 0, st)))
+        if ((rc = colsum(E(l - 1), H, tiles, nullptr, nullptr, 1, rows, 0, 1, 1.f, grads + lay.a_off(l - 1), nullptr, 1, 0,
+                         w.gsc, st)))
           return rc;
       } else if ((rc = tc_layer(H, MODE_BWD, p, st))) {
         return rc;
@@ -1123,7 +943,7 @@ int siren_tc_train(const inr_siren_desc* d, const float* params, const float* co
       INR_CUDA_CHECK(cudaMemsetAsync(w.gW0, 0, (size_t)H * H * sizeof(float), st));
       DwParams dp;
       dp.dZ = C(0); dp.S = w.img + (int64_t)w.x_image * w.img_elems; dp.gW = w.gW0; dp.gb = grads + lay.b_off(0);
-      dp.num_tiles = tiles; dp.lbo = 128; dp.sbo = TILE_ROWS * 16;
+      dp.num_tiles = tiles; dp.lbo = 128; dp.sbo = TILE_ROWS * 16; dp.gsc = w.gsc;
       if ((rc = tc_dw(H, dp, st))) return rc;
       { LaunchScope ls("k_tc_unpad_add", st);
         k_tc_unpad_add<<<(H * lay.in + 255) / 256, 256, 0, st>>>(w.gW0, lay.in, H, grads + lay.w_off(0)); }
@@ -1131,8 +951,8 @@ int siren_tc_train(const inr_siren_desc* d, const float* params, const float* co
       continue;
     }
     // first layer: gW_0[f][i] += sum_r dZ_0[r][f] x[r][i], gb_0 += colsum(dZ_0)
-    if (!fused_bwd && (rc = colsum(C(0), H, tiles, nullptr, xc, lay.in, rows, i0 + r0, T_total, scale, grads + lay.b_off(0),
-                     grads + lay.w_off(0), lay.in, lay.in, st)))
+    if ((rc = colsum(C(0), H, tiles, nullptr, xc, lay.in, rows, i0 + r0, T_total, scale, grads + lay.b_off(0),
+                     grads + lay.w_off(0), lay.in, lay.in, w.gsc, st)))
       return rc;
   }
   return INR_OK;

@@ -14,6 +14,7 @@
 // lanes of its warp (conflict-free in shared memory, fully coalesced in global memory).
 #pragma once
 #include <cuda_bf16.h>
+#include <cuda_fp16.h>
 #include <cuda_runtime.h>
 #include <stdint.h>
 
@@ -94,7 +95,7 @@ __device__ __forceinline__ void tc_fence_before() { asm volatile("tcgen05.fence:
 __device__ __forceinline__ void tc_fence_after() { asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory"); }
 
 // D[tmem] (+)= A[smem] * B[smem]   (kind::f16: bf16 operands, fp32 accumulate).  One thread issues.
-__device__ __forceinline__ void umma_bf16(uint32_t d_tmem, uint64_t a_desc, uint64_t b_desc, uint32_t idesc,
+__device__ __forceinline__ void umma_f16(uint32_t d_tmem, uint64_t a_desc, uint64_t b_desc, uint32_t idesc,
                                           uint32_t accumulate) {
   asm volatile(
       "{\n\t.reg .pred p;\n\t"
@@ -160,7 +161,7 @@ __device__ __forceinline__ void tmem_relinquish2() {
 __device__ __forceinline__ void tmem_dealloc2(uint32_t taddr, uint32_t ncols) {
   asm volatile("tcgen05.dealloc.cta_group::2.sync.aligned.b32 %0, %1;" ::"r"(taddr), "r"(ncols) : "memory");
 }
-__device__ __forceinline__ void umma2_bf16(uint32_t d_tmem, uint64_t a_desc, uint64_t b_desc, uint32_t idesc,
+__device__ __forceinline__ void umma2_f16(uint32_t d_tmem, uint64_t a_desc, uint64_t b_desc, uint32_t idesc,
                                            uint32_t accumulate) {
   asm volatile(
       "{\n\t.reg .pred p;\n\t"
@@ -194,6 +195,31 @@ __device__ __forceinline__ uint64_t make_smem_desc(uint32_t smem_addr, uint32_t 
 __host__ __device__ constexpr uint32_t make_idesc_bf16(int M, int N, int a_mn_major, int b_mn_major) {
   return (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(a_mn_major & 1) << 15) | ((uint32_t)(b_mn_major & 1) << 16) |
          ((uint32_t)(N >> 3) << 17) | ((uint32_t)(M >> 4) << 24);
+}
+
+// ---------------------------------------------------------------------------------------------- SIREN operand format
+// The SIREN tensor-core path (INR_PREC_FP16) keeps its GEMM operands S_l, C_l, W_l, dZ_l as IEEE fp16: 11 significant
+// bits against bf16's 8 at the same 2 bytes and the same kind::f16 MMA rate.  bf16 operands put a rounding-noise floor
+// under the fit at ~24 dB on the gt_bach config (profiles/r01e_c1_snr.md); fp16 lowers it by 18 dB.  The price is range:
+// sin/cos images and SIREN weights are O(1) or smaller, but dZ_l ~ 1/T needs a power-of-two loss scale (gscale, siren_tc.cu)
+// and every conversion saturates (cvt.rn.satfinite) so a loss spike clips instead of producing inf.
+using op16 = __half;
+constexpr uint32_t OP16_ONE_X2 = 0x3C003C00u;   // two fp16 1.0
+__host__ __device__ constexpr uint32_t make_idesc_op(int M, int N, int a_mn_major, int b_mn_major) {
+  // kind::f16 instruction descriptor with a/b format F16 (0) at [7,10)/[10,13); the rest as make_idesc_bf16
+  return (1u << 4) | ((uint32_t)(a_mn_major & 1) << 15) | ((uint32_t)(b_mn_major & 1) << 16) | ((uint32_t)(N >> 3) << 17) |
+         ((uint32_t)(M >> 4) << 24);
+}
+__device__ __forceinline__ uint32_t pack_op2(float lo, float hi) {
+  uint32_t r;
+  asm("cvt.rn.satfinite.f16x2.f32 %0, %1, %2;" : "=r"(r) : "f"(hi), "f"(lo));
+  return r;
+}
+__device__ __forceinline__ float2 unpack_op2(uint32_t u) { return __half22float2(*reinterpret_cast<__half2*>(&u)); }
+__device__ __forceinline__ op16 to_op(float v) {
+  uint16_t r;
+  asm("cvt.rn.satfinite.f16.f32 %0, %1;" : "=h"(r) : "f"(v));
+  return __ushort_as_half(r);
 }
 
 // ---------------------------------------------------------------------------------------------- small helpers

@@ -9,28 +9,28 @@ int tc_layer(int H, int mode, const LayerParams& p, cudaStream_t st);
 int tc_dw(int H, const DwParams& p, cudaStream_t st);
 int tc_ns(int H);
 
-__global__ void k_img_from_rows(const float* __restrict__ X, int64_t rows, int64_t rows_pad, int H, __nv_bfloat16* img) {
+__global__ void k_img_from_rows(const float* __restrict__ X, int64_t rows, int64_t rows_pad, int H, op16* img) {
   const int64_t total = rows_pad * H;
   for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
     const int64_t r = i / H;
     const int f = (int)(i - r * H);
-    img[img_offset(H, r, f)] = __float2bfloat16_rn(r < rows ? X[i] : 0.f);
+    img[img_offset(H, r, f)] = to_op(r < rows ? X[i] : 0.f);
   }
 }
-__global__ void k_rows_from_img(const __nv_bfloat16* __restrict__ img, int64_t rows, int H, float* X) {
+__global__ void k_rows_from_img(const op16* __restrict__ img, int64_t rows, int H, float* X) {
   const int64_t total = rows * H;
   for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
     const int64_t r = i / H;
     const int f = (int)(i - r * H);
-    X[i] = __bfloat162float(img[img_offset(H, r, f)]);
+    X[i] = __half2float(img[img_offset(H, r, f)]);
   }
 }
-__global__ void k_pack_one(const float* __restrict__ W, int H, int NS, int transpose, __nv_bfloat16* out) {
+__global__ void k_pack_one(const float* __restrict__ W, int H, int NS, int transpose, op16* out) {
   const int64_t total = (int64_t)H * H;
   for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
     const int o = (int)(i / H), in = (int)(i % H);
     const int n = transpose ? in : o, k = transpose ? o : in;   // B[n][k]
-    out[(int64_t)(n / NS) * ((int64_t)H * NS) + ((int64_t)(k >> 3) * NS + (n % NS)) * 8 + (k & 7)] = __float2bfloat16_rn(W[i]);
+    out[(int64_t)(n / NS) * ((int64_t)H * NS) + ((int64_t)(k >> 3) * NS + (n % NS)) * 8 + (k & 7)] = to_op(W[i]);
   }
 }
 }  // namespace inr
@@ -54,11 +54,11 @@ int inr_dbg_tc_layer(int H, int mode, const float* A, const float* W, const floa
   INR_REQUIRE(scratch_bytes >= inr_dbg_tc_scratch_bytes(H, rows), INR_E_WORKSPACE, "scratch too small");
   const int64_t rp = round_up(rows, TILE_ROWS);
   const int NS = tc_ns(H);
-  __nv_bfloat16* iA = (__nv_bfloat16*)scratch;
-  __nv_bfloat16* iO0 = iA + rp * H;
-  __nv_bfloat16* iO1 = iO0 + rp * H;
-  __nv_bfloat16* iC = iO1 + rp * H;
-  __nv_bfloat16* Wp = iC + rp * H;
+  op16* iA = (op16*)scratch;
+  op16* iO0 = iA + rp * H;
+  op16* iO1 = iO0 + rp * H;
+  op16* iC = iO1 + rp * H;
+  op16* Wp = iC + rp * H;
   k_img_from_rows<<<592, 256, 0, st>>>(A, rows, rp, H, iA);
   if (mode == 1) k_img_from_rows<<<592, 256, 0, st>>>(Cin, rows, rp, H, iC);
   k_pack_one<<<592, 256, 0, st>>>(W, H, NS, mode == 1, Wp);
@@ -83,8 +83,8 @@ int inr_dbg_tc_dw(int H, const float* dZ, const float* S, float* gW, int64_t row
   INR_REQUIRE(H == 128 || H == 256 || H == 512, INR_E_UNSUPPORTED, "H=%d", H);
   INR_REQUIRE(scratch_bytes >= inr_dbg_tc_scratch_bytes(H, rows), INR_E_WORKSPACE, "scratch too small");
   const int64_t rp = round_up(rows, TILE_ROWS);
-  __nv_bfloat16* iZ = (__nv_bfloat16*)scratch;
-  __nv_bfloat16* iS = iZ + rp * H;
+  op16* iZ = (op16*)scratch;
+  op16* iS = iZ + rp * H;
   k_img_from_rows<<<592, 256, 0, st>>>(dZ, rows, rp, H, iZ);
   k_img_from_rows<<<592, 256, 0, st>>>(S, rows, rp, H, iS);
   DwParams p;

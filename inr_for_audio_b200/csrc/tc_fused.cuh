@@ -4,12 +4,12 @@
 // stack) without the activations leaving the SM between layers:
 //
 //   * a CTA pair owns two 256-row "slots" (X, Y), each CTA 128 rows of each; the current layer input of a slot lives
-//     in shared memory as a bf16 tile image (the UMMA K-major operand layout of tc_common.cuh) and is OVERWRITTEN by
+//     in shared memory as a fp16 tile image (the UMMA K-major operand layout of tc_common.cuh) and is OVERWRITTEN by
 //     the epilogue with the next layer's input -- S_l is never read back from HBM;
-//   * the weights are the streamed operand: every layer's packed bf16 matrix (L2-resident, 128 KB at H = 256) is
+//   * the weights are the streamed operand: every layer's packed fp16 matrix (L2-resident, 128 KB at H = 256) is
 //     pulled through a bulk-copy ring, each CTA staging its half of the N columns (cta_group::2 B split);
 //   * accumulators: one TMEM buffer per slot; while the 8 epilogue warps drain slot X (omega*acc + omega*b -> sincos ->
-//     bf16 -> shared-memory image + the S_l / C_l stash the backward needs), the tensor pipe runs slot Y;
+//     fp16 -> shared-memory image + the S_l / C_l stash the backward needs), the tensor pipe runs slot Y;
 //   * the first layer (fp32 FMA, Cody-Waite reduction, MUFU sincos) is computed by the epilogue warps straight into the
 //     slot's image, from coordinates generated in-kernel (0 HBM bytes) or given.
 //
@@ -35,7 +35,7 @@ namespace tc {
 // The argument omega*z of the first layer is formed in fp32 exactly as the reference does (Linear -> * omega_0 -> sin,
 // models.py:115); it can reach +-4.4e4 rad (run.py's default omega = 22000), so it is reduced with a two-constant
 // Cody-Waite step (k = rint(t/2pi); r = t - k*C1 - k*C2 with FMAs, error < 2e-7 rad for |t| < 1e6) and the reduced
-// angle goes to the SFU (MUFU.SIN/COS, abs error ~5e-7 on [-pi, pi]) -- two orders below the bf16 rounding of the
+// angle goes to the SFU (MUFU.SIN/COS, abs error ~5e-7 on [-pi, pi]) -- two orders below the fp16 rounding of the
 // stored result.
 __device__ __forceinline__ void sincos_reduced(float t, float* s, float* c) {
   // k = rint(t / 2pi) by the 1.5 * 2^23 magic constant: two FMA-pipe instructions instead of an FRND on the XU pipe,
@@ -74,12 +74,12 @@ struct FusedCfg {
 };
 
 struct FusedParams {
-  const __nv_bfloat16* Wf;     // packed hidden weights, layer l-1 at Wf + (l-1)*H*H: [2 slices][H/8][NC][8]
+  const op16* Wf;     // packed hidden weights, layer l-1 at Wf + (l-1)*H*H: [2 slices][H/8][NC][8]
   const float* W0;             // first layer weight (H x in), bias (H)
   const float* B0;
   const float* bias[FUSED_MAX_L];        // hidden biases b_1..b_L
-  __nv_bfloat16* S[FUSED_MAX_L + 1];     // stash of S_0..S_L (tile images) or NULL
-  __nv_bfloat16* C[FUSED_MAX_L + 1];     // stash of C_0..C_L or NULL
+  op16* S[FUSED_MAX_L + 1];     // stash of S_0..S_L (tile images) or NULL
+  op16* C[FUSED_MAX_L + 1];     // stash of C_0..C_L or NULL
   const float* coords;         // (rows, in) or NULL: generated from the global index
   int in, L, num_tiles;
   int64_t rows, g0, T_total;
@@ -98,6 +98,8 @@ struct FusedParams {
   float* g_wlast;              // gradient of w_last (H), of b_last (1): accumulated with atomics
   float* g_blast;
   double* loss_acc;            // += sum (out - target)^2 or |out - target|
+  const float* gsc;            // {gs, 1/gs}: power-of-two loss scale of the fp16 dZ images (siren_tc.cu k_tc_gscale)
+  unsigned* gmax_acc;          // max |g| of this step (float bits, atomicMax) or NULL: the next step's scale
   // timing ablations (INR_TC_FUSED_DBG bit mask, results are WRONG when set; profiles/r01c_notes.md):
   // 1 = no stash stores to HBM, 2 = no sin/cos (raw accumulator values), 4 = head: dot + loss only (no dZ_L, no g_w)
   int dbg;
@@ -187,7 +189,7 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(64 + 32 * EW, 1) k_t
     if (lane == 0) {
       if (leader) {
         // ===================== MMA issuer (one thread of the pair) =====================
-        constexpr uint32_t idesc = make_idesc_bf16(256, NP, 0, 0);
+        constexpr uint32_t idesc = make_idesc_op(256, NP, 0, 0);
         int s = 0;
         uint32_t phase = 0;
         for (int r = 0; 2 * r < n_k; ++r) {
@@ -207,7 +209,7 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(64 + 32 * EW, 1) k_t
                 for (int kk = 0; kk < Cfg::KC / 16; ++kk) {
                   const uint64_t ad = make_smem_desc(sA(b) + (c * (Cfg::KC / 8) + kk * 2) * (TILE_ROWS * 16), TILE_ROWS * 16, 128);
                   const uint64_t bd = make_smem_desc(sW + s * Cfg::W_STAGE_BYTES + kk * 2 * (NC * 16), NC * 16, 128);
-                  umma2_bf16(d_tmem, ad, bd, idesc, (c | kk) != 0 ? 1u : 0u);
+                  umma2_f16(d_tmem, ad, bd, idesc, (c | kk) != 0 ? 1u : 0u);
                 }
                 umma2_commit_mc(bar_wempty(s), 3);
                 if (++s == Cfg::STAGES) { s = 0; phase ^= 1; }
@@ -281,8 +283,8 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(64 + 32 * EW, 1) k_t
                                             : (__fmaf_rn(x1, s_w0[f * 2 + 1], x0 * s_w0[f * 2]) + s_b0[f]);
                 sincos_reduced(p.omega0 * z, &s[u], &c[u]);
               }
-              so[h] = pack_bf16x2(s[0], s[1]);
-              co[h] = pack_bf16x2(c[0], c[1]);
+              so[h] = pack_op2(s[0], s[1]);
+              co[h] = pack_op2(c[0], c[1]);
             }
             const size_t loc = ((size_t)(g0 + j) * TILE_ROWS + row) * 8;   // elements inside the tile image
             *reinterpret_cast<uint4*>(img + loc * 2) = make_uint4(so[0], so[1], so[2], so[3]);
@@ -296,7 +298,8 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(64 + 32 * EW, 1) k_t
 
     // fuse_last accumulators: loss numerator, bias gradient (half 0 threads), weight gradient (lane = column % 32)
     double loss_local = 0.0;
-    float gb_local = 0.f;
+    float gb_local = 0.f, gmax_local = 0.f;
+    const float gs = (p.fuse_last && p.gsc) ? p.gsc[0] : 1.f;
     float gw_acc[8];
 #pragma unroll
     for (int i = 0; i < 8; ++i) gw_acc[i] = 0.f;
@@ -320,7 +323,7 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(64 + 32 * EW, 1) k_t
           if (tr) p.trace[tj * 4 + 2] = clock64();
           if (l == L && p.fuse_last) {
             // ---------- last hidden layer + nn.Linear head + loss + dZ_L ----------
-            // pass A: S_L = sin(.) (bf16) -> the slot's image (free: no layer L+1) + this thread's part of the output dot
+            // pass A: S_L = sin(.) (fp16) -> the slot's image (free: no layer L+1) + this thread's part of the output dot
             // pass B: cos(.) from the accumulator again -> dZ_L = g w omega C_L -> HBM
             // pass C: g_w[f] += sum_r g[r] S_L[r][f] from the image (one thread = 8 features x 128/TPG rows)
             const size_t tile_off = (size_t)tile * (TILE_ROWS * H);
@@ -344,8 +347,8 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(64 + 32 * EW, 1) k_t
                     const int cc = j * 8 + h * 2;
                     const float s0 = __sinf(__fmaf_rn(v[cc], p.omega_h, bias_l[c * 32 + cc]));
                     const float s1 = __sinf(__fmaf_rn(v[cc + 1], p.omega_h, bias_l[c * 32 + cc + 1]));
-                    o0[h] = pack_bf16x2(s0, s1);
-                    const float2 sb = unpack_bf16x2(o0[h]);   // the head sees the bf16 S_L, as on the layer-major path
+                    o0[h] = pack_op2(s0, s1);
+                    const float2 sb = unpack_op2(o0[h]);   // the head sees the fp16 S_L, as on the layer-major path
                     dot = __fmaf_rn(sb.x, s_wl[c * 32 + cc], dot);
                     dot = __fmaf_rn(sb.y, s_wl[c * 32 + cc + 1], dot);
                   }
@@ -374,11 +377,11 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(64 + 32 * EW, 1) k_t
                 }
               }
               if (p.extra_g) g += p.extra_g[grow];
-              if (half == 0) gb_local += g;
+              if (half == 0) { gb_local += g; gmax_local = fmaxf(gmax_local, fabsf(g)); }
             }
             if (half == 0) s_g[row] = g;
             if (valid && !(p.dbg & 4)) {
-              const float gw = g * p.omega_h;
+              const float gw = g * gs * p.omega_h;
 #pragma unroll
               for (int ci = 0; ci < NCH; ++ci) {
                 const int c = half + NPART * ci;
@@ -392,10 +395,10 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(64 + 32 * EW, 1) k_t
 #pragma unroll
                   for (int h = 0; h < 4; ++h) {
                     const int cc = j * 8 + h * 2;
-                    // same roundings as k_tc_last on the stored bf16 C_L image
-                    const float2 cb = unpack_bf16x2(pack_bf16x2(__cosf(__fmaf_rn(v[cc], p.omega_h, bias_l[c * 32 + cc])),
+                    // same roundings as k_tc_last on the stored fp16 C_L image
+                    const float2 cb = unpack_op2(pack_op2(__cosf(__fmaf_rn(v[cc], p.omega_h, bias_l[c * 32 + cc])),
                                                                 __cosf(__fmaf_rn(v[cc + 1], p.omega_h, bias_l[c * 32 + cc + 1]))));
-                    o1[h] = pack_bf16x2(gw * s_wl[c * 32 + cc] * cb.x, gw * s_wl[c * 32 + cc + 1] * cb.y);
+                    o1[h] = pack_op2(gw * s_wl[c * 32 + cc] * cb.x, gw * s_wl[c * 32 + cc + 1] * cb.y);
                   }
                   const size_t loc = ((size_t)(g0 + j) * TILE_ROWS + row) * 8;
                   *reinterpret_cast<uint4*>(p.C[L] + tile_off + loc) = make_uint4(o1[0], o1[1], o1[2], o1[3]);
@@ -415,7 +418,7 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(64 + 32 * EW, 1) k_t
                 const uint32_t uw[4] = {u.x, u.y, u.z, u.w};
 #pragma unroll
                 for (int h = 0; h < 4; ++h) {
-                  const float2 f = unpack_bf16x2(uw[h]);
+                  const float2 f = unpack_op2(uw[h]);
                   gw_acc[2 * h] = __fmaf_rn(gr, f.x, gw_acc[2 * h]);
                   gw_acc[2 * h + 1] = __fmaf_rn(gr, f.y, gw_acc[2 * h + 1]);
                 }
@@ -426,8 +429,8 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(64 + 32 * EW, 1) k_t
           } else if (valid) {
             const size_t tile_off = (size_t)tile * (TILE_ROWS * H);
             uint8_t* img = smem_gen + Cfg::OFF_A + b * Cfg::A_BYTES;
-            __nv_bfloat16* Sl = p.S[l];
-            __nv_bfloat16* Cl = p.C[l];
+            op16* Sl = p.S[l];
+            op16* Cl = p.C[l];
 #pragma unroll
             for (int ci = 0; ci < NCH; ++ci) {
               const int c = half + NPART * ci;
@@ -446,8 +449,8 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(64 + 32 * EW, 1) k_t
                   float s0, c0, s1, c1;
                   if (p.dbg & 2) { s0 = t0; c0 = t0; s1 = t1; c1 = t1; }
                   else { __sincosf(t0, &s0, &c0); __sincosf(t1, &s1, &c1); }
-                  o0[h] = pack_bf16x2(s0, s1);
-                  o1[h] = pack_bf16x2(c0, c1);
+                  o0[h] = pack_op2(s0, s1);
+                  o1[h] = pack_op2(c0, c1);
                 }
                 const size_t loc = ((size_t)(g0 + j) * TILE_ROWS + row) * 8;
                 if (l < L) *reinterpret_cast<uint4*>(img + loc * 2) = make_uint4(o0[0], o0[1], o0[2], o0[3]);
@@ -477,320 +480,17 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(64 + 32 * EW, 1) k_t
       }
       loss_local = warp_sum(loss_local);
       gb_local = warp_sum(gb_local);
+      for (int o = 16; o > 0; o >>= 1) gmax_local = fmaxf(gmax_local, __shfl_xor_sync(0xffffffffu, gmax_local, o));
       if (lane == 0 && half == 0) {
         if (p.target) atomicAdd(p.loss_acc, loss_local);
         atomicAdd(p.g_blast, gb_local);
+        if (p.gmax_acc) atomicMax(p.gmax_acc, __float_as_uint(gmax_local));
       }
     }
   }
   tc_fence_before();
   __syncthreads();
   cluster_sync_all();                                 // the peer's TMEM reads and remote arrivals are done
-  if (warp == 1) {
-    tc_fence_after();
-    tmem_dealloc2(tmem_base, Cfg::TMEM_COLS);
-  }
-}
-
-// ------------------------------------------------------------------------------------------------------------
-// k_tc_fused_bwd<H> -- the backward chain dZ_L -> dZ_{L-1} -> ... -> dZ_0 of a row tile in ONE kernel (H <= 256).
-//
-// Same skeleton as k_tc_fused_fwd (two slots per CTA pair, layer input in a shared-memory tile image, transposed
-// weights W_l^T streamed through the ring, one TMEM accumulator per slot):
-//   load   dZ_L tile (written by the fused forward's head epilogue) -> slot image
-//   l = L..1:  acc = dZ_l W_l;  dZ_{l-1} = acc * omega_{l-1} * C_{l-1}   (C_{l-1} read from the stash, prefetched before
-//              the accumulator is ready)  -> slot image (next GEMM's input) and, for l > 1, HBM in place over C_{l-1}
-//              (the dW kernel of layer l-1 reads it)
-//   l = 1:     dZ_0 stays on chip: first-layer gradients gW_0 += dZ_0^T x, gb_0 += colsum(dZ_0) are reduced from the image
-// HBM traffic at L = 3: read dZ_3, C_2, C_1, C_0; write dZ_2, dZ_1 = 6 units, against 10 for three layer-major BWD
-// launches plus the first-layer column-sum kernel.
-struct FusedBwdParams {
-  const __nv_bfloat16* Wb;     // packed transposed hidden weights, layer l at Wb + (l-1)*H*H: [2 slices][H/8][NC][8]
-  const __nv_bfloat16* dZL;    // dZ_L tile images
-  __nv_bfloat16* C[FUSED_MAX_L];   // C_0..C_{L-1}: read; C_1..C_{L-1} overwritten in place with dZ_1..dZ_{L-1}
-  const float* coords;         // (rows, in) or NULL
-  float* gW0;                  // first-layer gradients (H x in), (H): accumulated with atomics
-  float* gb0;
-  int in, L, num_tiles;
-  int64_t rows, g0, T_total;
-  float scale, omega0, omega_h;
-};
-
-template <int H, int EW>
-__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(64 + 32 * EW, 1) k_tc_fused_bwd(const FusedBwdParams p) {
-  using Cfg = FusedCfg<H>;
-  constexpr int NP = Cfg::NP;
-  constexpr int NC = Cfg::NC;
-  extern __shared__ __align__(128) uint8_t smem[];
-  const uint32_t smem_base = smem_u32(smem);
-  auto sA = [&](int slot) { return smem_base + Cfg::OFF_A + slot * Cfg::A_BYTES; };
-  const uint32_t sW = smem_base + Cfg::OFF_W;
-  float* s_x = reinterpret_cast<float*>(smem + Cfg::OFF_DOT);   // coordinates of the current tile's rows [128][2]
-  const uint32_t bar0 = smem_base + Cfg::OFF_BAR;
-  auto bar_wfull = [&](int s) { return bar0 + 8u * s; };
-  auto bar_wempty = [&](int s) { return bar0 + 8u * (Cfg::STAGES + s); };
-  auto bar_tfull = [&](int b) { return bar0 + 8u * (2 * Cfg::STAGES + b); };
-  auto bar_aready = [&](int b) { return bar0 + 8u * (2 * Cfg::STAGES + 2 + b); };
-  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(smem + Cfg::OFF_BAR + 8 * (2 * Cfg::STAGES + 4));
-
-  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  const uint32_t rank = cluster_ctarank();
-  const bool leader = rank == 0;
-  const int pair = blockIdx.x >> 1;
-  const int npairs = gridDim.x >> 1;
-  const int num_dt = (p.num_tiles + 1) >> 1;
-  const int n_k = pair < num_dt ? (num_dt - pair + npairs - 1) / npairs : 0;
-  const int L = p.L;
-  auto dt_of = [&](int k) { return pair + k * npairs; };
-
-  if (threadIdx.x == 0) {
-    for (int s = 0; s < Cfg::STAGES; ++s) { mbar_init(bar_wfull(s), leader ? 2 : 1); mbar_init(bar_wempty(s), 1); }
-    for (int b = 0; b < 2; ++b) { mbar_init(bar_tfull(b), 1); mbar_init(bar_aready(b), 2 * EW); }
-    mbar_fence_init();
-  }
-  __syncthreads();
-  cluster_sync_all();
-  if (warp == 1) {
-    tmem_alloc2(smem_u32(tmem_slot), Cfg::TMEM_COLS);
-    tmem_relinquish2();
-  }
-  tc_fence_before();
-  __syncthreads();
-  tc_fence_after();
-  const uint32_t tmem_base = *tmem_slot;
-
-  if (warp == 0) {
-    // ===================== producer: W_l^T halves, l = L..1, once per slot of the round =====================
-    if (lane == 0) {
-      int s = 0;
-      uint32_t phase = 0;
-      for (int r = 0; 2 * r < n_k; ++r) {
-        const int nslots = (2 * r + 1 < n_k) ? 2 : 1;
-        for (int l = L; l >= 1; --l) {
-          const uint8_t* wsrc = reinterpret_cast<const uint8_t*>(p.Wb) + (size_t)(l - 1) * H * H * 2 +
-                                (size_t)rank * (H * NC * 2);
-          for (int b = 0; b < nslots; ++b) {
-            for (int c = 0; c < Cfg::NCHUNK; ++c) {
-              mbar_wait(bar_wempty(s), phase ^ 1);
-              mbar_arrive_expect_tx(bar_wfull(s), Cfg::W_STAGE_BYTES);
-              bulk_g2s(sW + s * Cfg::W_STAGE_BYTES, wsrc + (size_t)c * Cfg::W_STAGE_BYTES, Cfg::W_STAGE_BYTES, bar_wfull(s));
-              if (++s == Cfg::STAGES) { s = 0; phase ^= 1; }
-            }
-          }
-        }
-      }
-    }
-  } else if (warp == 1) {
-    if (lane == 0) {
-      if (leader) {
-        constexpr uint32_t idesc = make_idesc_bf16(256, NP, 0, 0);
-        int s = 0;
-        uint32_t phase = 0;
-        for (int r = 0; 2 * r < n_k; ++r) {
-          const int nslots = (2 * r + 1 < n_k) ? 2 : 1;
-          for (int j = 0; j < L; ++j) {
-            const uint32_t par = (uint32_t)(r * L + j) & 1u;
-            for (int b = 0; b < nslots; ++b) {
-              mbar_wait(bar_aready(b), par);
-              tc_fence_after();
-              const uint32_t d_tmem = tmem_base + b * NP;
-              for (int c = 0; c < Cfg::NCHUNK; ++c) {
-                mbar_wait(bar_wfull(s), phase);
-                tc_fence_after();
-#pragma unroll
-                for (int kk = 0; kk < Cfg::KC / 16; ++kk) {
-                  const uint64_t ad = make_smem_desc(sA(b) + (c * (Cfg::KC / 8) + kk * 2) * (TILE_ROWS * 16), TILE_ROWS * 16, 128);
-                  const uint64_t bd = make_smem_desc(sW + s * Cfg::W_STAGE_BYTES + kk * 2 * (NC * 16), NC * 16, 128);
-                  umma2_bf16(d_tmem, ad, bd, idesc, (c | kk) != 0 ? 1u : 0u);
-                }
-                umma2_commit_mc(bar_wempty(s), 3);
-                if (++s == Cfg::STAGES) { s = 0; phase ^= 1; }
-              }
-              umma2_commit_mc(bar_tfull(b), 3);
-            }
-          }
-        }
-      } else {
-        int s = 0;
-        uint32_t phase = 0;
-        for (int r = 0; 2 * r < n_k; ++r) {
-          const int nslots = (2 * r + 1 < n_k) ? 2 : 1;
-          for (int j = 0; j < L * nslots * Cfg::NCHUNK; ++j) {
-            mbar_wait(bar_wfull(s), phase);
-            mbar_arrive_remote(bar_wfull(s), 0);
-            if (++s == Cfg::STAGES) { s = 0; phase ^= 1; }
-          }
-        }
-      }
-    }
-  } else {
-    // ===================== epilogue: 8 warps, warp%4 = TMEM lane quadrant, two column-chunk parities =====
-    const int e = warp - 2;
-    const int quad = warp & 3;
-    const int half = e >> 2;
-    const int row = quad * 32 + lane;
-    constexpr int NPART = EW / 4;
-    constexpr int NCH = NP / (32 * NPART);
-    constexpr int TPG = (32 * EW) / (H / 8);                  // threads per feature group in the column-sum pass
-    constexpr int RPT = TILE_ROWS / TPG;
-    const int et = threadIdx.x - 64;
-    uint8_t* smem_gen = smem;
-
-    auto signal_ready = [&](int b) {
-      fence_proxy_async_smem();
-      tc_fence_before();
-      __syncwarp();
-      if (lane == 0) {
-        if (leader) mbar_arrive(bar_aready(b));
-        else mbar_arrive_remote(bar_aready(b), 0);
-      }
-    };
-    // dZ_L of double tile k -> slot b image (this CTA's 128 rows; this thread's row and column chunks)
-    auto load_first = [&](int b, int k) {
-      const int tile = 2 * dt_of(k) + (int)rank;
-      if (tile < p.num_tiles) {
-        const size_t tile_off = (size_t)tile * (TILE_ROWS * H);
-        uint8_t* img = smem_gen + Cfg::OFF_A + b * Cfg::A_BYTES;
-        uint4 u[NCH][4];
-#pragma unroll
-        for (int ci = 0; ci < NCH; ++ci)
-#pragma unroll
-          for (int j = 0; j < 4; ++j) {
-            const size_t loc = ((size_t)((((half + NPART * ci) * 32) >> 3) + j) * TILE_ROWS + row) * 8;
-            u[ci][j] = *reinterpret_cast<const uint4*>(p.dZL + tile_off + loc);
-          }
-#pragma unroll
-        for (int ci = 0; ci < NCH; ++ci)
-#pragma unroll
-          for (int j = 0; j < 4; ++j) {
-            const size_t loc = ((size_t)((((half + NPART * ci) * 32) >> 3) + j) * TILE_ROWS + row) * 8;
-            *reinterpret_cast<uint4*>(img + loc * 2) = u[ci][j];
-          }
-      }
-      signal_ready(b);
-    };
-
-    float acc_b[8], acc_w0[8], acc_w1[8];
-#pragma unroll
-    for (int i = 0; i < 8; ++i) { acc_b[i] = 0.f; acc_w0[i] = 0.f; acc_w1[i] = 0.f; }
-
-    if (n_k > 0) load_first(0, 0);
-    if (n_k > 1) load_first(1, 1);
-    for (int r = 0; 2 * r < n_k; ++r) {
-      const int nslots = (2 * r + 1 < n_k) ? 2 : 1;
-      for (int jl = 0; jl < L; ++jl) {
-        const int l = L - jl;                           // GEMM of layer l: acc = dZ_l W_l
-        const int lp = l - 1;                           // produces dZ_{l-1}, needs C_{l-1}
-        const uint32_t par = (uint32_t)(r * L + jl) & 1u;
-        const float om = (lp == 0) ? p.omega0 : p.omega_h;
-        for (int b = 0; b < nslots; ++b) {
-          const int k = 2 * r + b;
-          const int tile = 2 * dt_of(k) + (int)rank;
-          const bool valid = tile < p.num_tiles;
-          const size_t tile_off = (size_t)tile * (TILE_ROWS * H);
-          uint8_t* img = smem_gen + Cfg::OFF_A + b * Cfg::A_BYTES;
-          __nv_bfloat16* Cp = p.C[lp];
-          uint4 cin[NCH][4];
-          if (valid) {                                  // C_{l-1} before the accumulator is ready
-#pragma unroll
-            for (int ci = 0; ci < NCH; ++ci)
-#pragma unroll
-              for (int j = 0; j < 4; ++j) {
-                const size_t loc = ((size_t)((((half + NPART * ci) * 32) >> 3) + j) * TILE_ROWS + row) * 8;
-                cin[ci][j] = *reinterpret_cast<const uint4*>(Cp + tile_off + loc);
-              }
-          }
-          mbar_wait(bar_tfull(b), par);
-          tc_fence_after();
-          if (valid) {
-#pragma unroll
-            for (int ci = 0; ci < NCH; ++ci) {
-              const int c = half + NPART * ci;
-              const int g0 = (c * 32) >> 3;
-              float v[32];
-              tmem_ld32(tmem_base + b * NP + c * 32 + ((uint32_t)(quad * 32) << 16), v);
-              tmem_ld_wait();
-#pragma unroll
-              for (int j = 0; j < 4; ++j) {
-                const uint32_t cw[4] = {cin[ci][j].x, cin[ci][j].y, cin[ci][j].z, cin[ci][j].w};
-                uint32_t o0[4];
-#pragma unroll
-                for (int h = 0; h < 4; ++h) {
-                  const int cc = j * 8 + h * 2;
-                  const float2 cf = unpack_bf16x2(cw[h]);
-                  o0[h] = pack_bf16x2(v[cc] * om * cf.x, v[cc + 1] * om * cf.y);
-                }
-                const size_t loc = ((size_t)(g0 + j) * TILE_ROWS + row) * 8;
-                *reinterpret_cast<uint4*>(img + loc * 2) = make_uint4(o0[0], o0[1], o0[2], o0[3]);
-                if (l > 1) *reinterpret_cast<uint4*>(Cp + tile_off + loc) = make_uint4(o0[0], o0[1], o0[2], o0[3]);
-              }
-            }
-          }
-          if (l > 1) {
-            signal_ready(b);
-          } else {
-            // dZ_0 stays on chip: gb_0[f] += sum_r dZ_0[r][f], gW_0[f][i] += sum_r dZ_0[r][f] x_i[r] from the image
-            if (half == 0) {
-              int64_t grow = (int64_t)tile * TILE_ROWS + row;
-              if (grow >= p.rows) grow = p.rows - 1;    // pad rows carry dZ = 0
-              float x0 = 0.f, x1 = 0.f;
-              if (valid) {
-                if (p.coords) {
-                  x0 = p.coords[grow * p.in];
-                  if (p.in == 2) x1 = p.coords[grow * p.in + 1];
-                } else {
-                  x0 = linspace_at(p.g0 + grow, p.T_total, p.scale);
-                }
-              }
-              s_x[row * 2] = x0;
-              s_x[row * 2 + 1] = x1;
-            }
-            asm volatile("bar.sync 1, %0;" ::"n"(32 * EW) : "memory");
-            if (valid) {
-              const int fg = et / TPG, r0 = (et % TPG) * RPT;
-#pragma unroll 4
-              for (int rr = 0; rr < RPT; ++rr) {
-                const uint4 u = *reinterpret_cast<const uint4*>(img + ((size_t)fg * TILE_ROWS + r0 + rr) * 16);
-                const float x0 = s_x[(r0 + rr) * 2], x1 = s_x[(r0 + rr) * 2 + 1];
-                const uint32_t uw[4] = {u.x, u.y, u.z, u.w};
-#pragma unroll
-                for (int h = 0; h < 4; ++h) {
-                  const float2 f = unpack_bf16x2(uw[h]);
-                  acc_b[2 * h] += f.x;
-                  acc_b[2 * h + 1] += f.y;
-                  acc_w0[2 * h] = __fmaf_rn(x0, f.x, acc_w0[2 * h]);
-                  acc_w0[2 * h + 1] = __fmaf_rn(x0, f.y, acc_w0[2 * h + 1]);
-                  acc_w1[2 * h] = __fmaf_rn(x1, f.x, acc_w1[2 * h]);
-                  acc_w1[2 * h + 1] = __fmaf_rn(x1, f.y, acc_w1[2 * h + 1]);
-                }
-              }
-            }
-            asm volatile("bar.sync 1, %0;" ::"n"(32 * EW) : "memory");      // the image is free for the slot's next tile
-            if (k + 2 < n_k) load_first(b, k + 2);
-          }
-        }
-      }
-    }
-#pragma unroll
-    for (int i = 0; i < 8; ++i) {
-      float a = acc_b[i], w0 = acc_w0[i], w1 = acc_w1[i];
-#pragma unroll
-      for (int o = TPG / 2; o > 0; o >>= 1) {
-        a += __shfl_xor_sync(0xffffffffu, a, o);
-        w0 += __shfl_xor_sync(0xffffffffu, w0, o);
-        w1 += __shfl_xor_sync(0xffffffffu, w1, o);
-      }
-      if ((et % TPG) == 0) {
-        const int f = (et / TPG) * 8 + i;
-        atomicAdd(p.gb0 + f, a);
-        atomicAdd(p.gW0 + (size_t)f * p.in, w0);
-        if (p.in == 2) atomicAdd(p.gW0 + (size_t)f * p.in + 1, w1);
-      }
-    }
-  }
-  tc_fence_before();
-  __syncthreads();
-  cluster_sync_all();
   if (warp == 1) {
     tc_fence_after();
     tmem_dealloc2(tmem_base, Cfg::TMEM_COLS);

@@ -1,9 +1,9 @@
-// tc_gemm.cuh -- the two tcgen05 GEMM kernels of the bf16 SIREN path (sm_100a).
+// tc_gemm.cuh -- the two tcgen05 GEMM kernels of the fp16 SIREN path (sm_100a).
 //
 //  k_tc_layer<H, MODE>   weight-stationary layer GEMM over 128-row activation tiles
 //      MODE_FWD :  S_l, C_l  = sincos( omega * (S_{l-1} W_l^T + b_l) )          models.py:114-115
 //      MODE_BWD :  dZ_{l-1}  = (dZ_l W_l) * omega_{l-1} * C_{l-1}               (autograd of the above)
-//    Each CTA keeps its N-slice of the (pre-packed, bf16) weight matrix resident in shared memory for the whole
+//    Each CTA keeps its N-slice of the (pre-packed, fp16) weight matrix resident in shared memory for the whole
 //    kernel, streams A tiles (tile images, tc_common.cuh) through a 4-stage cp.async.bulk ring, accumulates in
 //    TMEM (two accumulator buffers) and drains them with 8 epilogue warps that apply the activation math in
 //    fp32 and write the next tile images with coalesced 16-byte stores.
@@ -28,219 +28,19 @@ namespace tc {
 enum { MODE_FWD = 0, MODE_BWD = 1, MODE_FWD_SNAKE = 2, MODE_FWD_TANH = 3, MODE_BWD_SNAKE = 4 };
 __host__ __device__ constexpr bool mode_is_fwd(int m) { return m == MODE_FWD || m == MODE_FWD_SNAKE || m == MODE_FWD_TANH; }
 
-template <int H>
-struct LayerCfg {
-  static constexpr int NS = (H >= 512) ? 128 : H;   // output features per CTA (B slice resident in smem)
-  static constexpr int NQ = H / NS;                 // N slices
-  static constexpr int KC = 64;                     // K columns per ring stage
-  static constexpr int NCHUNK = H / KC;
-  static constexpr int STAGES = 4;
-  static constexpr int A_STAGE_BYTES = (KC / 8) * TILE_ROWS * 16;  // 16 KB
-  static constexpr int B_BYTES = H * NS * 2;
-  static constexpr int TMEM_COLS = 2 * NS;          // two accumulator buffers (256 or 512: powers of two)
-  static constexpr int OFF_A = B_BYTES;
-  static constexpr int OFF_BIAS = OFF_A + STAGES * A_STAGE_BYTES;
-  static constexpr int OFF_BAR = OFF_BIAS + NS * 4;
-  static constexpr int SMEM_BYTES = OFF_BAR + 128;
-  static constexpr int THREADS = 320;
-  static_assert(H == 128 || H == 256 || H == 512, "hidden width");
-};
-
 struct LayerParams {
-  const __nv_bfloat16* A;      // input tile images: S_{l-1} (fwd) or dZ_l (bwd)
-  const __nv_bfloat16* Bpack;  // packed weights [NQ][H/8][NS][8]: W_l (fwd) or W_l^T (bwd)
+  const op16* A;      // input tile images: S_{l-1} (fwd) or dZ_l (bwd)
+  const op16* Bpack;  // packed weights [NQ][H/8][NS][8]: W_l (fwd) or W_l^T (bwd)
   const float* bias;           // fwd: b_l (H floats)
   float omega;                 // fwd: omega_l;  bwd: omega_{l-1}
-  __nv_bfloat16* out0;         // fwd: S_l;  bwd: dZ_{l-1}
-  __nv_bfloat16* out1;         // fwd: C_l or NULL (inference)
-  const __nv_bfloat16* Cin;    // bwd: C_{l-1} (may alias out0: read before written, same thread)
+  op16* out0;         // fwd: S_l;  bwd: dZ_{l-1}
+  op16* out1;         // fwd: C_l or NULL (inference)
+  const op16* Cin;    // bwd: C_{l-1} (may alias out0: read before written, same thread)
   const float* avec;           // MODE_FWD_SNAKE: the layer's `a` (H floats)
-  __nv_bfloat16* out2;         // MODE_FWD_SNAKE: dy/da image;  MODE_BWD_SNAKE: dy/da image, overwritten with v * dy/da
+  op16* out2;         // MODE_FWD_SNAKE: dy/da image;  MODE_BWD_SNAKE: dy/da image, overwritten with v * dy/da
   int num_tiles;
   uint32_t a_lbo, a_sbo, b_lbo, b_sbo;  // descriptor strides (bytes); passed in so a test can probe the convention
 };
-
-template <int H, int MODE>
-__global__ void __launch_bounds__(LayerCfg<H>::THREADS, 1) k_tc_layer(const LayerParams p) {
-  using Cfg = LayerCfg<H>;
-  constexpr int NS = Cfg::NS;
-  extern __shared__ __align__(128) uint8_t smem[];
-  const uint32_t smem_base = smem_u32(smem);
-  const uint32_t sB = smem_base;
-  const uint32_t sA = smem_base + Cfg::OFF_A;
-  float* s_bias = reinterpret_cast<float*>(smem + Cfg::OFF_BIAS);
-  const uint32_t bar0 = smem_base + Cfg::OFF_BAR;
-  // barriers (8 bytes each): full[4] empty[4] tfull[2] tempty[2] bfull ; then the TMEM base slot
-  auto bar_full = [&](int s) { return bar0 + 8u * s; };
-  auto bar_empty = [&](int s) { return bar0 + 8u * (Cfg::STAGES + s); };
-  auto bar_tfull = [&](int b) { return bar0 + 8u * (2 * Cfg::STAGES + b); };
-  auto bar_tempty = [&](int b) { return bar0 + 8u * (2 * Cfg::STAGES + 2 + b); };
-  const uint32_t bar_bfull = bar0 + 8u * (2 * Cfg::STAGES + 4);
-  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(smem + Cfg::OFF_BAR + 8 * (2 * Cfg::STAGES + 5));
-
-  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  const int q = blockIdx.x % Cfg::NQ;                 // N slice of this CTA
-  const int tile0 = blockIdx.x / Cfg::NQ;
-  const int tile_stride = gridDim.x / Cfg::NQ;
-
-  if (threadIdx.x == 0) {
-    for (int s = 0; s < Cfg::STAGES; ++s) { mbar_init(bar_full(s), 1); mbar_init(bar_empty(s), 1); }
-    for (int b = 0; b < 2; ++b) { mbar_init(bar_tfull(b), 1); mbar_init(bar_tempty(b), 8); }
-    mbar_init(bar_bfull, 1);
-    mbar_fence_init();
-  }
-  if (warp == 1) {
-    tmem_alloc(smem_u32(tmem_slot), Cfg::TMEM_COLS);
-    tmem_relinquish();
-  }
-  if (MODE == MODE_FWD) {
-    for (int i = threadIdx.x; i < NS; i += blockDim.x) s_bias[i] = p.omega * p.bias[q * NS + i];
-  }
-  tc_fence_before();
-  __syncthreads();
-  tc_fence_after();
-  const uint32_t tmem_base = *tmem_slot;
-
-  if (warp == 0) {
-    // ===================== producer: weights once, then A chunks through the ring =====================
-    if (lane == 0) {
-      mbar_arrive_expect_tx(bar_bfull, Cfg::B_BYTES);
-      const uint8_t* bsrc = reinterpret_cast<const uint8_t*>(p.Bpack) + (size_t)q * Cfg::B_BYTES;
-      for (int off = 0; off < Cfg::B_BYTES; off += 32768) bulk_g2s(sB + off, bsrc + off, 32768, bar_bfull);
-      // DRAM latency under load (~2 us, profiles/r01) times the ring's 64 KB would cap a CTA at ~35 GB/s, a third of
-      // what the MMA consumes; so every tile is pulled into L2 PF tiles ahead with cp.async.bulk.prefetch.L2 (no
-      // shared memory needed) and the ring's copies then run at L2-hit latency.  The NQ CTAs that share a row tile
-      // split its chunks between them; the BWD epilogue's C_{l-1} slice is prefetched the same way.
-      constexpr int PF = 4;
-      auto prefetch_tile = [&](int tile) {
-        if (tile >= p.num_tiles) return;
-        const uint8_t* asrc = reinterpret_cast<const uint8_t*>(p.A) + (size_t)tile * (TILE_ROWS * H * 2);
-        for (int c = q; c < Cfg::NCHUNK; c += Cfg::NQ) bulk_prefetch_l2(asrc + (size_t)c * Cfg::A_STAGE_BYTES, Cfg::A_STAGE_BYTES);
-        if (MODE == MODE_BWD)
-          bulk_prefetch_l2(reinterpret_cast<const uint8_t*>(p.Cin) + (size_t)tile * (TILE_ROWS * H * 2) +
-                               (size_t)q * (NS / 8) * (TILE_ROWS * 16), (NS / 8) * (TILE_ROWS * 16));
-      };
-      for (int d = 0; d < PF; ++d) prefetch_tile(tile0 + d * tile_stride);
-      int s = 0;
-      uint32_t phase = 0;
-      for (int tile = tile0; tile < p.num_tiles; tile += tile_stride) {
-        prefetch_tile(tile + PF * tile_stride);
-        const uint8_t* asrc = reinterpret_cast<const uint8_t*>(p.A) + (size_t)tile * (TILE_ROWS * H * 2);
-        for (int c = 0; c < Cfg::NCHUNK; ++c) {
-          mbar_wait(bar_empty(s), phase ^ 1);
-          mbar_arrive_expect_tx(bar_full(s), Cfg::A_STAGE_BYTES);
-          bulk_g2s(sA + s * Cfg::A_STAGE_BYTES, asrc + (size_t)c * Cfg::A_STAGE_BYTES, Cfg::A_STAGE_BYTES, bar_full(s));
-          if (++s == Cfg::STAGES) { s = 0; phase ^= 1; }
-        }
-      }
-    }
-  } else if (warp == 1) {
-    // ===================== MMA issuer (one thread) =====================
-    if (lane == 0) {
-      constexpr uint32_t idesc = make_idesc_bf16(128, NS, 0, 0);
-      mbar_wait(bar_bfull, 0);
-      int s = 0;
-      uint32_t phase = 0;
-      int it = 0;
-      for (int tile = tile0; tile < p.num_tiles; tile += tile_stride, ++it) {
-        const int buf = it & 1;
-        mbar_wait(bar_tempty(buf), ((it >> 1) & 1) ^ 1);   // epilogue drained this accumulator (2 tiles ago)
-        tc_fence_after();
-        const uint32_t d_tmem = tmem_base + buf * NS;
-        for (int c = 0; c < Cfg::NCHUNK; ++c) {
-          mbar_wait(bar_full(s), phase);
-          tc_fence_after();
-#pragma unroll
-          for (int kk = 0; kk < Cfg::KC / 16; ++kk) {
-            const uint64_t ad = make_smem_desc(sA + s * Cfg::A_STAGE_BYTES + kk * 2 * (TILE_ROWS * 16), p.a_lbo, p.a_sbo);
-            const uint64_t bd = make_smem_desc(sB + (c * (Cfg::KC / 8) + kk * 2) * (NS * 16), p.b_lbo, p.b_sbo);
-            umma_bf16(d_tmem, ad, bd, idesc, (c | kk) != 0 ? 1u : 0u);
-          }
-          umma_commit(bar_empty(s));                         // stage reusable once these MMAs have read it
-          if (++s == Cfg::STAGES) { s = 0; phase ^= 1; }
-        }
-        umma_commit(bar_tfull(buf));                         // accumulator complete -> epilogue
-      }
-    }
-  } else {
-    // ===================== epilogue: 8 warps, warp%4 = TMEM lane quadrant, two column-chunk parities =====
-    const int e = warp - 2;
-    const int quad = warp & 3;
-    const int half = e >> 2;
-    const int row = quad * 32 + lane;
-    int it = 0;
-    // BWD: the C_{l-1} operand of the epilogue comes from HBM; it does not depend on the MMA, so the loads for a
-    // tile are issued one whole tile ahead (into the registers the previous tile has just consumed) and their
-    // ~1 us latency hides behind the tile's MMA instead of serialising with it (profiles/r01: 63 % long_sb).
-    constexpr int NCH = NS / 64;                          // 32-column chunks per warp
-    uint4 cin[NCH][4];
-    auto cin_ptr = [&](int tile, int ci, int j) {
-      const int g0 = (q * NS + (half + 2 * ci) * 32) >> 3;
-      return reinterpret_cast<const uint4*>(p.Cin + (size_t)tile * (TILE_ROWS * H) + ((size_t)(g0 + j) * TILE_ROWS + row) * 8);
-    };
-    if (MODE == MODE_BWD && tile0 < p.num_tiles) {
-#pragma unroll
-      for (int ci = 0; ci < NCH; ++ci)
-#pragma unroll
-        for (int j = 0; j < 4; ++j) cin[ci][j] = *cin_ptr(tile0, ci, j);
-    }
-    for (int tile = tile0; tile < p.num_tiles; tile += tile_stride, ++it) {
-      const int buf = it & 1;
-      mbar_wait(bar_tfull(buf), (it >> 1) & 1);
-      tc_fence_after();
-      const size_t tile_off = (size_t)tile * (TILE_ROWS * H);
-      const int next_tile = tile + tile_stride;
-#pragma unroll
-      for (int ci = 0; ci < NCH; ++ci) {
-        const int c = half + 2 * ci;
-        const int g0 = (q * NS + c * 32) >> 3;                // first feature group of this 32-column chunk
-        float v[32];
-        tmem_ld32(tmem_base + buf * NS + c * 32 + ((uint32_t)(quad * 32) << 16), v);
-        tmem_ld_wait();
-#pragma unroll
-        for (int j = 0; j < 4; ++j) {
-          uint32_t o0[4], o1[4];
-          if (MODE == MODE_FWD) {
-#pragma unroll
-            for (int h = 0; h < 4; ++h) {
-              const int cc = j * 8 + h * 2;
-              const float t0 = __fmaf_rn(v[cc], p.omega, s_bias[c * 32 + cc]);
-              const float t1 = __fmaf_rn(v[cc + 1], p.omega, s_bias[c * 32 + cc + 1]);
-              float s0, c0, s1, c1;
-              __sincosf(t0, &s0, &c0);
-              __sincosf(t1, &s1, &c1);
-              o0[h] = pack_bf16x2(s0, s1);
-              o1[h] = pack_bf16x2(c0, c1);
-            }
-            const size_t off = tile_off + ((size_t)(g0 + j) * TILE_ROWS + row) * 8;
-            *reinterpret_cast<uint4*>(p.out0 + off) = make_uint4(o0[0], o0[1], o0[2], o0[3]);
-            if (p.out1) *reinterpret_cast<uint4*>(p.out1 + off) = make_uint4(o1[0], o1[1], o1[2], o1[3]);
-          } else {
-            const uint32_t cw[4] = {cin[ci][j].x, cin[ci][j].y, cin[ci][j].z, cin[ci][j].w};
-#pragma unroll
-            for (int h = 0; h < 4; ++h) {
-              const int cc = j * 8 + h * 2;
-              const float2 cf = unpack_bf16x2(cw[h]);
-              o0[h] = pack_bf16x2(v[cc] * p.omega * cf.x, v[cc + 1] * p.omega * cf.y);
-            }
-            const size_t off = tile_off + ((size_t)(g0 + j) * TILE_ROWS + row) * 8;
-            *reinterpret_cast<uint4*>(p.out0 + off) = make_uint4(o0[0], o0[1], o0[2], o0[3]);
-            if (next_tile < p.num_tiles) cin[ci][j] = *cin_ptr(next_tile, ci, j);
-          }
-        }
-      }
-      tc_fence_before();
-      __syncwarp();
-      if (lane == 0) mbar_arrive(bar_tempty(buf));
-    }
-  }
-  tc_fence_before();
-  __syncthreads();
-  if (warp == 1) {
-    tc_fence_after();
-    tmem_dealloc(tmem_base, Cfg::TMEM_COLS);
-  }
-}
 
 // ------------------------------------------------------------------------------------------------------------
 template <int H>
@@ -254,19 +54,20 @@ struct DwCfg {
   static constexpr int STAGE_BYTES = A_BYTES + B_BYTES;
   static constexpr int STAGES = 2;
   static constexpr int TMEM_COLS = 2 * NB;             // [0,NB) dW block, [NB,NB+16) bias column sums (power of two)
-  static constexpr int OFF_ONES = STAGES * STAGE_BYTES; // 512 B of bf16 1.0: the B operand of the bias-gradient MMA
+  static constexpr int OFF_ONES = STAGES * STAGE_BYTES; // 512 B of fp16 1.0: the B operand of the bias-gradient MMA
   static constexpr int OFF_BAR = OFF_ONES + 512;
   static constexpr int SMEM_BYTES = OFF_BAR + 64;
   static constexpr int THREADS = 192;                  // producer, MMA, 4 epilogue warps
 };
 
 struct DwParams {
-  const __nv_bfloat16* dZ;   // tile images of dZ_l   (M operand: out features)
-  const __nv_bfloat16* S;    // tile images of S_{l-1} (N operand: in features)
+  const op16* dZ;   // tile images of dZ_l   (M operand: out features)
+  const op16* S;    // tile images of S_{l-1} (N operand: in features)
   float* gW;                 // fp32 gradient of W_l, row-major [H out][H in], accumulated with atomics
   float* gb;                 // fp32 gradient of b_l (H), or NULL: gb[o] += sum_r dZ[r][o] = dZ^T 1, an N=16 MMA against ones
   int num_tiles;
   uint32_t lbo, sbo;         // MN-major strides: LBO = 128 (8-row k groups), SBO = 2048 (feature groups)
+  const float* gsc = nullptr; // {gs, 1/gs}: dZ carries the loss scale gs; the reduction into gW / gb multiplies by 1/gs
 };
 
 template <int H>
@@ -293,7 +94,7 @@ __global__ void __launch_bounds__(DwCfg<H>::THREADS, 1) k_tc_dw(const DwParams p
     mbar_init(bar_tfull, 1);
     mbar_fence_init();
   }
-  for (int i = threadIdx.x; i < 128; i += blockDim.x) reinterpret_cast<uint32_t*>(smem + Cfg::OFF_ONES)[i] = 0x3F803F80u;
+  for (int i = threadIdx.x; i < 128; i += blockDim.x) reinterpret_cast<uint32_t*>(smem + Cfg::OFF_ONES)[i] = OP16_ONE_X2;
   fence_proxy_async_smem();
   if (warp == 1) {
     tmem_alloc(smem_u32(tmem_slot), Cfg::TMEM_COLS);
@@ -337,7 +138,7 @@ __global__ void __launch_bounds__(DwCfg<H>::THREADS, 1) k_tc_dw(const DwParams p
     }
   } else if (warp == 1) {
     if (lane == 0 && has_work) {
-      constexpr uint32_t idesc = make_idesc_bf16(128, Cfg::NB, 1, 1);   // both operands MN-major
+      constexpr uint32_t idesc = make_idesc_op(128, Cfg::NB, 1, 1);   // both operands MN-major
       int s = 0;
       uint32_t phase = 0;
       int it = 0;
@@ -350,14 +151,14 @@ __global__ void __launch_bounds__(DwCfg<H>::THREADS, 1) k_tc_dw(const DwParams p
         for (int kk = 0; kk < TILE_ROWS / 16; ++kk) {   // K = 16 rows per MMA: 16 rows x 16 B inside each feature group
           const uint64_t ad = make_smem_desc(a0 + kk * 256, p.lbo, p.sbo);
           const uint64_t bd = make_smem_desc(b0 + kk * 256, p.lbo, p.sbo);
-          umma_bf16(tmem_base, ad, bd, idesc, (it | kk) != 0 ? 1u : 0u);
+          umma_f16(tmem_base, ad, bd, idesc, (it | kk) != 0 ? 1u : 0u);
         }
         if (do_bias && (it % Cfg::NBLK) == nb) {   // every element of the ones block is 1.0, so its strides only have to stay inside the block
-          constexpr uint32_t idesc1 = make_idesc_bf16(128, 16, 1, 1);
+          constexpr uint32_t idesc1 = make_idesc_op(128, 16, 1, 1);
           const uint64_t od = make_smem_desc(smem_base + Cfg::OFF_ONES, 128, 256);
 #pragma unroll
           for (int kk = 0; kk < TILE_ROWS / 16; ++kk)
-            umma_bf16(tmem_base + Cfg::NB, make_smem_desc(a0 + kk * 256, p.lbo, p.sbo), od, idesc1, (it >= Cfg::NBLK || kk != 0) ? 1u : 0u);
+            umma_f16(tmem_base + Cfg::NB, make_smem_desc(a0 + kk * 256, p.lbo, p.sbo), od, idesc1, (it >= Cfg::NBLK || kk != 0) ? 1u : 0u);
         }
         umma_commit(bar_empty(s));
         if (++s == Cfg::STAGES) { s = 0; phase ^= 1; }
@@ -370,18 +171,20 @@ __global__ void __launch_bounds__(DwCfg<H>::THREADS, 1) k_tc_dw(const DwParams p
     mbar_wait(bar_tfull, 0);
     tc_fence_after();
     float* grow = p.gW + (size_t)(mb * 128 + row) * H + nb * Cfg::NB;
+    const float inv = p.gsc ? p.gsc[1] : 1.f;
     for (int c = 0; c < Cfg::NB / 32; ++c) {
       float v[32];
       tmem_ld32(tmem_base + c * 32 + ((uint32_t)(quad * 32) << 16), v);
       tmem_ld_wait();
 #pragma unroll
-      for (int j = 0; j < 8; ++j) red_add_v4(grow + c * 32 + j * 4, v[4 * j], v[4 * j + 1], v[4 * j + 2], v[4 * j + 3]);
+      for (int j = 0; j < 8; ++j)
+        red_add_v4(grow + c * 32 + j * 4, v[4 * j] * inv, v[4 * j + 1] * inv, v[4 * j + 2] * inv, v[4 * j + 3] * inv);
     }
     if (do_bias && (p.num_tiles - tile0 + tile_stride - 1) / tile_stride > nb) {   // this CTA issued at least one bias MMA
       float v[32];
       tmem_ld32(tmem_base + Cfg::NB + ((uint32_t)(quad * 32) << 16), v);   // columns 0..15 all hold the column sum
       tmem_ld_wait();
-      atomicAdd(p.gb + mb * 128 + row, v[0]);
+      atomicAdd(p.gb + mb * 128 + row, v[0] * inv);
     }
   }
   tc_fence_before();

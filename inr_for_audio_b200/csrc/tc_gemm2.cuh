@@ -129,7 +129,7 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(Layer2Cfg<H>::THREAD
     if (lane == 0) {
       if (leader) {
         // ===================== MMA issuer (one thread of the pair) =====================
-        constexpr uint32_t idesc = make_idesc_bf16(256, NP, 0, 0);
+        constexpr uint32_t idesc = make_idesc_op(256, NP, 0, 0);
         mbar_wait(bar_bfull, 0);
         int s = 0;
         uint32_t phase = 0;
@@ -146,7 +146,7 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(Layer2Cfg<H>::THREAD
             for (int kk = 0; kk < Cfg::KC / 16; ++kk) {
               const uint64_t ad = make_smem_desc(sA + s * Cfg::A_STAGE_BYTES + kk * 2 * (TILE_ROWS * 16), p.a_lbo, p.a_sbo);
               const uint64_t bd = make_smem_desc(sB + (c * (Cfg::KC / 8) + kk * 2) * (NC * 16), p.b_lbo, p.b_sbo);
-              umma2_bf16(d_tmem, ad, bd, idesc, (c | kk) != 0 ? 1u : 0u);
+              umma2_f16(d_tmem, ad, bd, idesc, (c | kk) != 0 ? 1u : 0u);
             }
             umma2_commit_mc(bar_empty(s), 3);
             if (++s == Cfg::STAGES) { s = 0; phase ^= 1; }
@@ -232,9 +232,9 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(Layer2Cfg<H>::THREAD
                     da[u] = 0.f;
                   }
                 }
-                o0[h] = pack_bf16x2(y[0], y[1]);
-                o1[h] = pack_bf16x2(dz[0], dz[1]);
-                o2[h] = pack_bf16x2(da[0], da[1]);
+                o0[h] = pack_op2(y[0], y[1]);
+                o1[h] = pack_op2(dz[0], dz[1]);
+                o2[h] = pack_op2(da[0], da[1]);
               }
               *reinterpret_cast<uint4*>(p.out0 + off) = make_uint4(o0[0], o0[1], o0[2], o0[3]);
               if (p.out1) *reinterpret_cast<uint4*>(p.out1 + off) = make_uint4(o1[0], o1[1], o1[2], o1[3]);
@@ -248,8 +248,8 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(Layer2Cfg<H>::THREAD
                 float s0, c0, s1, c1;
                 __sincosf(t0, &s0, &c0);
                 __sincosf(t1, &s1, &c1);
-                o0[h] = pack_bf16x2(s0, s1);
-                o1[h] = pack_bf16x2(c0, c1);
+                o0[h] = pack_op2(s0, s1);
+                o1[h] = pack_op2(c0, c1);
               }
               *reinterpret_cast<uint4*>(p.out0 + off) = make_uint4(o0[0], o0[1], o0[2], o0[3]);
               if (p.out1) *reinterpret_cast<uint4*>(p.out1 + off) = make_uint4(o1[0], o1[1], o1[2], o1[3]);
@@ -258,8 +258,8 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(Layer2Cfg<H>::THREAD
 #pragma unroll
               for (int h = 0; h < 4; ++h) {
                 const int cc = j * 8 + h * 2;
-                const float2 cf = unpack_bf16x2(cw[h]);
-                o0[h] = pack_bf16x2(v[cc] * p.omega * cf.x, v[cc + 1] * p.omega * cf.y);
+                const float2 cf = unpack_op2(cw[h]);
+                o0[h] = pack_op2(v[cc] * p.omega * cf.x, v[cc + 1] * p.omega * cf.y);
               }
               *reinterpret_cast<uint4*>(p.out0 + off) = make_uint4(o0[0], o0[1], o0[2], o0[3]);
               if (MODE == MODE_BWD_SNAKE) {   // v * dy/da in place over the dy/da image (column-summed afterwards)
@@ -268,8 +268,8 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(Layer2Cfg<H>::THREAD
 #pragma unroll
                 for (int h = 0; h < 4; ++h) {
                   const int cc = j * 8 + h * 2;
-                  const float2 ef = unpack_bf16x2(ew[h]);
-                  o1[h] = pack_bf16x2(v[cc] * ef.x, v[cc + 1] * ef.y);
+                  const float2 ef = unpack_op2(ew[h]);
+                  o1[h] = pack_op2(v[cc] * ef.x, v[cc + 1] * ef.y);
                 }
                 *reinterpret_cast<uint4*>(p.out2 + off) = make_uint4(o1[0], o1[1], o1[2], o1[3]);
               }
@@ -354,7 +354,7 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(Dw2Cfg<H>::THREADS, 
     mbar_init(bar_tfull, 1);
     mbar_fence_init();
   }
-  for (int i = threadIdx.x; i < 128; i += blockDim.x) reinterpret_cast<uint32_t*>(smem + Cfg::OFF_ONES)[i] = 0x3F803F80u;
+  for (int i = threadIdx.x; i < 128; i += blockDim.x) reinterpret_cast<uint32_t*>(smem + Cfg::OFF_ONES)[i] = OP16_ONE_X2;
   fence_proxy_async_smem();
   __syncthreads();
   cluster_sync_all();
@@ -387,7 +387,7 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(Dw2Cfg<H>::THREADS, 
   } else if (warp == 1) {
     if (lane == 0 && has_work) {
       if (leader) {
-        constexpr uint32_t idesc = make_idesc_bf16(256, Cfg::NB, 1, 1);   // both operands MN-major
+        constexpr uint32_t idesc = make_idesc_op(256, Cfg::NB, 1, 1);   // both operands MN-major
         int s = 0;
         uint32_t phase = 0;
         int it = 0;
@@ -400,14 +400,14 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(Dw2Cfg<H>::THREADS, 
           for (int kk = 0; kk < TILE_ROWS / 16; ++kk) {   // K = 16 rows per MMA
             const uint64_t ad = make_smem_desc(a0 + kk * 256, p.lbo, p.sbo);
             const uint64_t bd = make_smem_desc(b0 + kk * 256, p.lbo, p.sbo);
-            umma2_bf16(tmem_base, ad, bd, idesc, (it | kk) != 0 ? 1u : 0u);
+            umma2_f16(tmem_base, ad, bd, idesc, (it | kk) != 0 ? 1u : 0u);
           }
           if (do_bias && (it % Cfg::NBLK) == nb) {   // gb = dZ^T 1: N = 16 ones-MMA (8 ones columns from each CTA)
-            constexpr uint32_t idesc1 = make_idesc_bf16(256, 16, 1, 1);
+            constexpr uint32_t idesc1 = make_idesc_op(256, 16, 1, 1);
             const uint64_t od = make_smem_desc(smem_base + Cfg::OFF_ONES, 128, 256);
 #pragma unroll
             for (int kk = 0; kk < TILE_ROWS / 16; ++kk)
-              umma2_bf16(tmem_base + Cfg::NB, make_smem_desc(a0 + kk * 256, p.lbo, p.sbo), od, idesc1,
+              umma2_f16(tmem_base + Cfg::NB, make_smem_desc(a0 + kk * 256, p.lbo, p.sbo), od, idesc1,
                          (it >= Cfg::NBLK || kk != 0) ? 1u : 0u);
           }
           umma2_commit_mc(bar_empty(s), 3);
@@ -430,18 +430,20 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(Dw2Cfg<H>::THREADS, 
     mbar_wait(bar_tfull, 0);
     tc_fence_after();
     float* grow = p.gW + (size_t)(mb * 128 + row) * H + nb * Cfg::NB;
+    const float inv = p.gsc ? p.gsc[1] : 1.f;
     for (int c = 0; c < Cfg::NB / 32; ++c) {
       float v[32];
       tmem_ld32(tmem_base + c * 32 + ((uint32_t)(quad * 32) << 16), v);
       tmem_ld_wait();
 #pragma unroll
-      for (int j = 0; j < 8; ++j) red_add_v4(grow + c * 32 + j * 4, v[4 * j], v[4 * j + 1], v[4 * j + 2], v[4 * j + 3]);
+      for (int j = 0; j < 8; ++j)
+        red_add_v4(grow + c * 32 + j * 4, v[4 * j] * inv, v[4 * j + 1] * inv, v[4 * j + 2] * inv, v[4 * j + 3] * inv);
     }
     if (do_bias && (p.num_tiles - tile0 + tile_stride - 1) / tile_stride > nb) {   // this pair issued at least one bias MMA
       float v[32];
       tmem_ld32(tmem_base + Cfg::NB + ((uint32_t)(quad * 32) << 16), v);   // columns 0..15 all hold the column sum
       tmem_ld_wait();
-      atomicAdd(p.gb + mb * 128 + row, v[0]);
+      atomicAdd(p.gb + mb * 128 + row, v[0] * inv);
     }
   }
   tc_fence_before();

@@ -206,8 +206,8 @@ class SirenFitter:
 
     def set_precision(self, precision: str):
         """Continue the same fit (parameters, Adam moments, step count, plateau scheduler, loss history) in the other
-        arithmetic mode: 'bf16' (tcgen05 throughput mode) <-> 'fp32' (parity mode).  The 16-bit mode's operand rounding
-        puts a floor under the loss late in a fit (profiles/r01e_c1_snr.md); a fit that starts in bf16 and finishes in
+        arithmetic mode: 'fp16' (tcgen05 throughput mode) <-> 'fp32' (parity mode).  The 16-bit mode's operand rounding
+        puts a floor under the loss late in a fit (profiles/r01e_c1_snr.md); a fit that starts in fp16 and finishes in
         fp32 keeps most of the speed and the fp32 floor."""
         if precision == self.precision:
             return
@@ -317,7 +317,8 @@ class SirenFitter:
                 step = int(ent["step"])
             o += n
         lr = float(osd["param_groups"][0]["lr"]) if osd.get("param_groups") else self.last_lr()
-        self.set_opt(step=step, lr=lr)
+        # hist_base: the loss ring restarts at this fitter's first step, whatever Adam's step count is
+        self.set_opt(step=step, lr=lr, hist_base=step)
 
     # -- read-backs (synchronising) -------------------------------------------------------------
     def opt_state(self) -> L.OptState:
@@ -348,11 +349,11 @@ class SirenFitter:
                              self.coord_scale)
 
     def rounding_noise_ratio(self) -> float:
-        """How much of the current fit error is the 16-bit mode's own rounding: mean((out_bf16 - out_fp32)^2) /
+        """How much of the current fit error is the 16-bit mode's own rounding: mean((out_fp16 - out_fp32)^2) /
         mean((out_fp32 - target)^2) at the current parameters (two forward passes; summed over the ranks of a sharded
-        fit).  Far below 1 the bf16 gradients are as good as fp32 ones; near 1 the fit sits on the bf16 noise floor."""
+        fit).  Far below 1 the fp16 gradients are as good as fp32 ones; near 1 the fit sits on the fp16 noise floor."""
         buf0 = self.ws.buf
-        o16 = siren_forward(self.spec.desc("bf16"), self.params, self.coords, self.n, self.ws, self.i0, self.T_total,
+        o16 = siren_forward(self.spec.desc("fp16"), self.params, self.coords, self.n, self.ws, self.i0, self.T_total,
                             self.coord_scale)
         o32 = siren_forward(self.spec.desc("fp32"), self.params, self.coords, self.n, self.ws, self.i0, self.T_total,
                             self.coord_scale)
@@ -366,16 +367,16 @@ class SirenFitter:
         return num / max(den, 1e-300)
 
     def step_auto(self, n_steps: int, check_every: int = 250, threshold: float = 0.05):
-        """n_steps steps that start in the bf16 tcgen05 mode and move to the fp32 mode once the bf16 rounding noise is
+        """n_steps steps that start in the fp16 tcgen05 mode and move to the fp32 mode once the fp16 rounding noise is
         more than `threshold` of the fit error (checked every `check_every` steps: two forward passes, one host
-        sync).  Returns the step index at which the fit switched (None if it stayed in bf16)."""
+        sync).  Returns the step index at which the fit switched (None if it stayed in fp16)."""
         switched = None
         done = 0
         while done < n_steps:
-            k = min(check_every, n_steps - done) if self.precision == "bf16" else n_steps - done
+            k = min(check_every, n_steps - done) if self.precision == "fp16" else n_steps - done
             self.step(k)
             done += k
-            if self.precision == "bf16" and done < n_steps and self.rounding_noise_ratio() > threshold:
+            if self.precision == "fp16" and done < n_steps and self.rounding_noise_ratio() > threshold:
                 self.set_precision("fp32")
                 switched = self.steps_done
         return switched

@@ -178,7 +178,7 @@ class SirenWithSnakeTanh(_FlatSirenBase):
     first_linear), num_sine SineLayers, num_snake x (nn.Linear + Snake), num_tanh x (nn.Linear + Tanh), then the
     final nn.Linear (last_linear) or SineLayer.  Same module tree, state_dict keys and RNG consumption as the
     reference.  Sine-only stacks are identical to Siren(outermost_linear=last_linear); every layer mix runs in either
-    precision (bf16: H in {128, 256, 512}, in_features <= 2)."""
+    precision (fp16: H in {128, 256, 512}, in_features <= 2)."""
 
     def __init__(self, in_features, out_features, hidden_features, num_sine, num_snake, num_tanh, first_linear=False,
                  last_linear=True, first_omega_0=30, hidden_omega_0=30., a_initial=50, num_freq=None, scale=2.0):

@@ -32,7 +32,6 @@ def save_parameters(experiment_folder, **kwargs):
 def _adam_state_dict(model, fitter: SirenFitter, lr: float):
     """torch.optim.Adam.state_dict() layout so that checkpoints interchange with the reference (run.py:357-363)."""
     state, o = {}, 0
-    names = list(model.state_dict().keys())
     step = float(fitter.opt_state().step)
     for i, (_, p) in enumerate(model.named_parameters()):
         n = p.numel()
@@ -41,7 +40,7 @@ def _adam_state_dict(model, fitter: SirenFitter, lr: float):
         o += n
     group = {"lr": fitter.last_lr(), "betas": (0.9, 0.999), "eps": 1e-8, "weight_decay": 0, "amsgrad": False,
              "maximize": False, "foreach": None, "capturable": False, "differentiable": False, "fused": None,
-             "decoupled_weight_decay": False, "params": list(range(len(names)))}
+             "decoupled_weight_decay": False, "params": list(range(len(state)))}   # parameters only: buffers (KAN grid) have no id
     return {"state": state, "param_groups": [group]}
 
 
@@ -89,8 +88,8 @@ def train(experiment_path: str, tag: str, inst: str, duration: int, num_channels
           a_initial=0.5, total_steps=20000, learning_rate=1e-3, min_learning_rate=1e-6, alpha=0.0,
           prev_ckpt_path=None, visualization=False, *, precision='fp32', data_dir='data', seed=None, verbose=True,
           spectral='stft'):
-    """run.py:30.  Extra keyword-only arguments: precision ('fp32' CUDA-core parity mode | 'bf16' tcgen05 mode | 'auto' =
-    start in bf16 and continue in fp32 once the bf16 rounding noise shows in the fit error, SirenFitter.step_auto),
+    """run.py:30.  Extra keyword-only arguments: precision ('fp32' CUDA-core parity mode | 'fp16' tcgen05 mode | 'auto' =
+    start in fp16 and continue in fp32 once the fp16 rounding noise shows in the fit error, SirenFitter.step_auto),
     data_dir (the reference hard-codes 'data/'), seed (torch.manual_seed before model construction), spectral (which
     windowed-transform loss `alpha` mixes in: 'stft' = auraloss STFTLoss as run.py:128,160 does, 'mdct' / 'mdct_mse' =
     the MDCT-domain loss of BASELINE.json config 3)."""
@@ -105,7 +104,7 @@ def train(experiment_path: str, tag: str, inst: str, duration: int, num_channels
     if auto_precision:
         if arch == 'kan':
             raise NotImplementedError("precision='auto' is a SIREN schedule (SirenFitter.step_auto)")
-        precision = 'bf16'
+        precision = 'fp16'
     takelog = False
     if num_freq is not None and method != 'wave':
         raise ValueError("num_freq: the reference's GaussianEncoding(10.0, 1, num_freq) takes 1-D coordinates (run.py:142)")

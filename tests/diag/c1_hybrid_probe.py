@@ -1,4 +1,4 @@
-"""C1 (gt_bach 6 s, SIREN 3x256, seed 0, 20 000 steps): the fit started in the bf16 tcgen05 mode and finished in the fp32
+"""C1 (gt_bach 6 s, SIREN 3x256, seed 0, 20 000 steps): the fit started in the fp16 tcgen05 mode and finished in the fp32
 mode (SirenFitter.set_precision), for several switch points; SNR = calculate_snr(target, model(coords)) (utils.py:77-97).
 One JSON line per arm.   python tests/diag/c1_hybrid_probe.py [switch_step ...]"""
 import json
@@ -25,7 +25,7 @@ def main():
     flat0 = torch.cat([p.reshape(-1) for p in O.siren_init(O.SirenSpec(1, 256, 3, 1, True, 30.0, 30.0), seed=0)])
     spec = P.SirenSpec(1, 256, 3, 1, True, 30.0, 30.0)
     if "auto" in sys.argv[1:]:
-        f = P.SirenFitter(spec, flat0.clone(), torch.from_numpy(gtn).to(dev), None, precision="bf16", hist_cap=TOTAL)
+        f = P.SirenFitter(spec, flat0.clone(), torch.from_numpy(gtn).to(dev), None, precision="fp16", hist_cap=TOTAL)
         torch.cuda.synchronize()
         t0 = time.time()
         sw = f.step_auto(TOTAL)
@@ -35,7 +35,7 @@ def main():
                           "last_loss": float(f.losses()[-1]), "final_lr": f.last_lr(), "wall_s": round(time.time() - t0, 2)}),
               flush=True)
     for sw in switches:
-        f = P.SirenFitter(spec, flat0.clone(), torch.from_numpy(gtn).to(dev), None, precision="bf16", hist_cap=TOTAL)
+        f = P.SirenFitter(spec, flat0.clone(), torch.from_numpy(gtn).to(dev), None, precision="fp16", hist_cap=TOTAL)
         torch.cuda.synchronize()
         t0 = time.time()
         snr, lrs, done = {}, {}, 0
@@ -49,7 +49,7 @@ def main():
             if m == sw and sw < TOTAL:
                 f.set_precision("fp32")
         torch.cuda.synchronize()
-        print(json.dumps({"arm": "bf16 -> fp32 at step %d" % sw if sw < TOTAL else "bf16 only", "snr_db": snr, "lr": lrs,
+        print(json.dumps({"arm": "fp16 -> fp32 at step %d" % sw if sw < TOTAL else "fp16 only", "snr_db": snr, "lr": lrs,
                           "last_loss": float(f.losses()[-1]), "wall_s": round(time.time() - t0, 2)}), flush=True)
 
 

@@ -1,4 +1,4 @@
-"""Per-tensor gradient error of the bf16 mode against the fp32 oracle (diagnostic): python tools/grad_diag.py H L n"""
+"""Per-tensor gradient error of the fp16 mode against the fp32 oracle (diagnostic): python tools/grad_diag.py H L n"""
 import os, sys
 import numpy as np, torch
 ROOT = os.path.dirname(os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
@@ -12,7 +12,7 @@ flat = torch.cat([p.reshape(-1) for p in ps])
 gt = torch.from_numpy(P.utils.synth_waveform(max(n, 2), seed=3)[:n].copy())
 coords = O.get_coord(n, 1).view(-1, 1)
 loss_o, _, grads_o, out_o = O.siren_loss_and_grads(ospec, ps, coords, gt.view(-1, 1))
-f = P.SirenFitter(spec, flat, gt.cuda(), precision="bf16", use_graph=False)
+f = P.SirenFitter(spec, flat, gt.cuda(), precision="fp16", use_graph=False)
 loss, grads, out = f.loss_and_grads()
 print("loss", loss, float(loss_o))
 o = 0

@@ -123,8 +123,8 @@ def test_encoded_network_against_reference(pkg, golden, name):
     np.testing.assert_allclose(f.losses(), g[name + "_losses"], rtol=2e-2)
 
 
-def test_module_route_and_bf16_refusal(pkg, golden):
-    """model(encoded coords) + loss.backward() (run.py:156-187) with in_features = 16; the bf16 tcgen05 mode refuses
+def test_module_route_and_fp16_refusal(pkg, golden):
+    """model(encoded coords) + loss.backward() (run.py:156-187) with in_features = 16; the fp16 tcgen05 mode refuses
     encoded inputs loudly instead of falling back."""
     g = golden("encoding")
     m, _ = _model(pkg, "s")
@@ -143,15 +143,15 @@ def test_module_route_and_bf16_refusal(pkg, golden):
     np.testing.assert_allclose(losses, g["s_losses"][:3], rtol=2e-5)
     spec = pkg.SirenSpec(16, 64, 2, 1, True, 30.0, 30.0)            # H = 64 is not a tcgen05 width
     with pytest.raises(Exception, match="in_features"):
-        pkg.SirenFitter(spec, torch.zeros(spec.num_params()), gt.view(-1), x.view(-1, 16), precision="bf16").step(1)
+        pkg.SirenFitter(spec, torch.zeros(spec.num_params()), gt.view(-1), x.view(-1, 16), precision="fp16").step(1)
 
 
 @pytest.mark.parametrize("K,H,ns,nk,fl,n", [(16, 128, 2, 0, False, 4099), (64, 256, 1, 1, False, 6000), (100, 128, 1, 0, True, 2000),
                                             (128, 128, 1, 0, False, 1000), (34, 512, 1, 0, False, 2500)])
-def test_bf16_mode_wide_inputs_against_oracle(pkg, K, H, ns, nk, fl, n):
+def test_fp16_mode_wide_inputs_against_oracle(pkg, K, H, ns, nk, fl, n):
     """Encoded coordinates in the tcgen05 mode: the rows become a zero-padded H-wide tile image, layer 0 one more layer GEMM,
     its weight gradient one more dW GEMM cut back to (H x in).  Loss within 1e-3 relative, gradients (and the first-layer
-    weight gradient on its own) within bf16 rounding noise of the fp32 oracle."""
+    weight gradient on its own) within fp16 rounding noise of the fp32 oracle."""
     from oracle import inr_oracle as O
     ospec = O.SirenSpec(K, H, ns, 1, True, 30.0, 30.0, num_snake=nk, num_tanh=0, first_linear=fl, a_initial=0.5)
     spec = pkg.SirenSpec(K, H, ns, 1, True, 30.0, 30.0, nk, 0, fl)
@@ -162,7 +162,7 @@ def test_bf16_mode_wide_inputs_against_oracle(pkg, K, H, ns, nk, fl, n):
     x = torch.rand(n, K) * 2 - 1
     gt = torch.sin(torch.linspace(0, 20, n))
     loss_o, _, grads_o, out_o = O.siren_loss_and_grads(ospec, ps, x, gt.view(-1, 1))
-    f = pkg.SirenFitter(spec, flat, gt.to(dev()), x.to(dev()), precision="bf16", use_graph=False)
+    f = pkg.SirenFitter(spec, flat, gt.to(dev()), x.to(dev()), precision="fp16", use_graph=False)
     loss, grads, out = f.loss_and_grads()
     assert abs(loss - float(loss_o)) <= 1e-3 * abs(float(loss_o)) + 1e-9, (loss, float(loss_o))
     assert float(np.abs(out.cpu().numpy() - out_o.numpy().ravel()).max()) <= 3e-2
@@ -172,12 +172,12 @@ def test_bf16_mode_wide_inputs_against_oracle(pkg, K, H, ns, nk, fl, n):
     n0 = H * K
     g0err = np.linalg.norm(gn[:n0] - go[:n0]) / np.linalg.norm(go[:n0])
     gb0err = np.linalg.norm(gn[n0:n0 + H] - go[n0:n0 + H]) / np.linalg.norm(go[n0:n0 + H])
-    print("bf16 wide K=%d H=%d: loss rel err %.2e, grad rel err %.2e, gW0 %.2e, gb0 %.2e" % (
+    print("fp16 wide K=%d H=%d: loss rel err %.2e, grad rel err %.2e, gW0 %.2e, gb0 %.2e" % (
         K, H, abs(loss - float(loss_o)) / float(loss_o), gerr, g0err, gb0err))
     assert gerr <= 5e-2 and g0err <= 5e-2 and gb0err <= 5e-2
     # forward-only entry and the graph-captured step
     np.testing.assert_allclose(f.forward().cpu().numpy(), out.cpu().numpy(), atol=1e-6)
-    f2 = pkg.SirenFitter(spec, flat, gt.to(dev()), x.to(dev()), precision="bf16")
+    f2 = pkg.SirenFitter(spec, flat, gt.to(dev()), x.to(dev()), precision="fp16")
     f2.step(5)
     ls = f2.losses()
     assert np.all(np.isfinite(ls)) and ls.min() < 2 * ls[0]
@@ -229,8 +229,8 @@ def test_train_dropin_num_freq(pkg, tmp_path):
     assert sr == 44100 and rec.shape == (44100,) and np.all(np.isfinite(rec))
     assert np.isfinite(json.load(open(os.path.join(os.path.dirname(ck2), "parameters.json")))["final_loss_dB"])
     with pytest.raises(Exception):                                  # H = 64 is not a tcgen05 width: loud refusal, no fallback
-        pkg.train(str(tmp_path), "rff3", total_steps=1, precision="bf16", **kw)
+        pkg.train(str(tmp_path), "rff3", total_steps=1, precision="fp16", **kw)
     kw.update(num_hidden_features=128)
-    ck3 = pkg.train(str(tmp_path), "rff4", total_steps=100, precision="bf16", **kw)   # 2*num_freq = 64 <= H = 128
+    ck3 = pkg.train(str(tmp_path), "rff4", total_steps=100, precision="fp16", **kw)   # 2*num_freq = 64 <= H = 128
     p3 = json.load(open(os.path.join(os.path.dirname(ck3), "parameters.json")))
     assert np.isfinite(p3["SNR"]) and p3["SNR"] > 3.0

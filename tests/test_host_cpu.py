@@ -37,7 +37,7 @@ def test_library_exports_every_declared_symbol(built):
 
 def test_opt_state_struct_matches_header(built):
     from inr_for_audio_b200 import _lib as L
-    assert L.OPT_STATE_BYTES == 96 and L.OPT_LOSS_ACC_OFFSET == 64
+    assert L.OPT_STATE_BYTES == 120 and L.OPT_LOSS_ACC_OFFSET == 88
     assert ctypes.sizeof(L.SirenDesc) == 44
 
 

@@ -234,11 +234,11 @@ def test_ragged_and_tiny_sizes(pkg, golden):
         assert np.linalg.norm(grads.cpu().numpy() - go) <= 3e-5 * np.linalg.norm(go) + 1e-12
 
 
-# ------------------------------------------------------------------------------------------------ bf16 tcgen05 mode
+# ------------------------------------------------------------------------------------------------ fp16 tcgen05 mode
 @pytest.mark.parametrize("H,Lh,n", [(128, 2, 4099), (256, 3, 20000), (512, 2, 3000), (128, 1, 1)])
-def test_bf16_mode_against_oracle(pkg, H, Lh, n):
-    """bf16 operands / fp32 accumulation on the tensor cores: loss within 1e-3 relative (north star), gradients
-    within bf16 rounding noise of the fp32 oracle."""
+def test_fp16_mode_against_oracle(pkg, H, Lh, n):
+    """fp16 operands / fp32 accumulation on the tensor cores: loss within 1e-3 relative (north star), gradients
+    within fp16 rounding noise of the fp32 oracle."""
     from oracle import inr_oracle as O
     spec = pkg.SirenSpec(1, H, Lh, 1, True)
     ospec = O.SirenSpec(1, H, Lh, 1, True)
@@ -247,55 +247,55 @@ def test_bf16_mode_against_oracle(pkg, H, Lh, n):
     gt = torch.from_numpy(pkg.utils.synth_waveform(max(n, 2), seed=3)[:n].copy())
     coords = O.get_coord(n, 1).view(-1, 1)
     loss_o, _, grads_o, out_o = O.siren_loss_and_grads(ospec, ps, coords, gt.view(-1, 1))
-    f = pkg.SirenFitter(spec, flat, gt.to(dev()), precision="bf16", use_graph=False)
+    f = pkg.SirenFitter(spec, flat, gt.to(dev()), precision="fp16", use_graph=False)
     loss, grads, out = f.loss_and_grads()
     assert abs(loss - float(loss_o)) <= 1e-3 * abs(float(loss_o)) + 1e-9, (loss, float(loss_o))
     assert float(np.abs(out.cpu().numpy() - out_o.numpy().ravel()).max()) <= 2e-2
     go = torch.cat([x.reshape(-1) for x in grads_o]).numpy().astype(np.float64)
     gerr = np.linalg.norm(grads.cpu().numpy() - go) / np.linalg.norm(go)
-    print("bf16 H=%d L=%d n=%d: loss rel err %.2e, grad rel err %.2e" % (H, Lh, n, abs(loss - float(loss_o)) / float(loss_o), gerr))
+    print("fp16 H=%d L=%d n=%d: loss rel err %.2e, grad rel err %.2e" % (H, Lh, n, abs(loss - float(loss_o)) / float(loss_o), gerr))
     assert gerr <= (5e-2 if n > 1 else 0.2)
     assert torch.equal(f.forward(), f.forward())
     np.testing.assert_allclose(f.forward().cpu().numpy(), out.cpu().numpy(), atol=1e-6)
 
 
-def test_bf16_c1_first_steps(pkg, golden):
+def test_fp16_c1_first_steps(pkg, golden):
     g = golden("siren")
     ds = pkg.WaveformFitting(os.path.join(ROOT, "data", "gt_bach.wav"), duration=6, verbose=False)
     torch.manual_seed(0)
     model = pkg.Siren(1, 256, 3, 1, True)
     tgt = torch.from_numpy(ds.normalised()).to(dev())
-    f = pkg.SirenFitter(model.spec, model.flat_parameters(), tgt, precision="bf16", use_graph=False)
+    f = pkg.SirenFitter(model.spec, model.flat_parameters(), tgt, precision="fp16", use_graph=False)
     loss, grads, out = f.loss_and_grads()
     assert abs(loss - g["c1_losses"][0]) <= 1e-3 * g["c1_losses"][0]
     gn = float(np.linalg.norm(grads.cpu().numpy().astype(np.float64)))
     assert abs(gn - float(g["c1_g0_norm"])) <= 3e-2 * float(g["c1_g0_norm"])
-    f2 = pkg.SirenFitter(model.spec, model.flat_parameters(), tgt, precision="bf16")
+    f2 = pkg.SirenFitter(model.spec, model.flat_parameters(), tgt, precision="fp16")
     f2.step(3)
-    # bf16 operands perturb step 0 by ~3e-5 in loss / 1.5e-3 in gradient; the chaotic map amplifies that per step
+    # fp16 operands perturb step 0 by ~3e-5 in loss / 1.5e-3 in gradient; the chaotic map amplifies that per step
     # (the fp32 reference against itself at another thread count: 1e-6, 3.6e-4, 2.4e-3 at steps 1, 5, 10)
     for k, tol in enumerate((1e-3, 3e-3, 1e-2)):
         assert abs(f2.losses()[k] - g["c1_losses"][k]) <= tol * g["c1_losses"][k], (k, f2.losses()[k], g["c1_losses"][k])
 
 
-def test_bf16_convergence_envelope(pkg, golden):
+def test_fp16_convergence_envelope(pkg, golden):
     """Same protocol as the fp32 envelope test, for the tensor-core mode (H=128 is the smallest width it takes):
-    bf16 operands perturb the first steps by ~1e-3, after which the run is one more member of the ensemble.
+    fp16 operands perturb the first steps by ~1e-3, after which the run is one more member of the ensemble.
 
-    bf16 is the THROUGHPUT mode, not the parity mode (fp32 is, see the test above).  Measured on B200 over 12 runs
+    fp16 is the THROUGHPUT mode, not the parity mode (fp32 is, see the test above).  Measured on B200 over 12 runs
     (tools/envelope_probe.py, profiles/r01c_notes.md; the split-K dW reduction uses floating-point atomics, so the
     trajectory is not bit-reproducible): best-so-far SNR 20.8 .. 21.4 dB at step 100 (reference ensemble 21.5 .. 21.7),
     23.6 .. 24.9 at step 300 (24.6 .. 25.5), 31.4 .. 37.7 at step 1500 (37.2 .. 44.8; fp32 mode 43.9): while the fit is
     far from converged the 16-bit mode tracks the ensemble within 1 dB, late in the fit its operand rounding (S, C, W,
     dZ to 8 mantissa bits) costs up to ~6 dB at the same step count.  The allowances below are those two numbers."""
-    for step, ours, lo, hi, sd in _envelope_vs_ensemble(pkg, golden, "bf16", 2e-3):
+    for step, ours, lo, hi, sd in _envelope_vs_ensemble(pkg, golden, "fp16", 2e-3):
         tol = 1.0 if step <= 300 else 6.0
         assert lo - tol - sd <= ours <= hi + tol + sd, (step, ours, lo, hi, sd)
 
 
 def test_set_precision_and_step_auto(pkg, golden):
     """A fit continued in the other arithmetic mode keeps its parameters, Adam moments, step count and loss history;
-    step_auto leaves the bf16 mode once its rounding noise shows in the fit error (profiles/r01e_c1_snr.md)."""
+    step_auto leaves the fp16 mode once its rounding noise shows in the fit error (profiles/r01e_c1_snr.md)."""
     from scipy.io import wavfile
     sr, data = wavfile.read(os.path.join(ROOT, "data", "gt_bach.wav"))
     data = data.astype(np.float32)[44100:44100 + 8192]
@@ -303,7 +303,7 @@ def test_set_precision_and_step_auto(pkg, golden):
     torch.manual_seed(0)
     model = pkg.Siren(1, 128, 2, 1, True)
     spec, flat = model.spec, model.flat_parameters().detach().clone()
-    f = pkg.SirenFitter(spec, flat, gt, precision="bf16", hist_cap=4096)
+    f = pkg.SirenFitter(spec, flat, gt, precision="fp16", hist_cap=4096)
     f.step(200)
     p_before = f.params.clone()
     r0 = f.rounding_noise_ratio()
@@ -315,13 +315,13 @@ def test_set_precision_and_step_auto(pkg, golden):
     ls = f.losses()
     # (full-batch Adam at lr 1e-3 spikes by 30-50x around steps 200-300 in the reference's own runs too: compare minima)
     assert len(ls) == 300 and np.all(np.isfinite(ls)) and ls[200:].min() < 2.0 * ls[:200].min()
-    f.set_precision("bf16")
+    f.set_precision("fp16")
     f.step(10)
     assert f.opt_state().step == 310
     # threshold 0 forces the switch at the first check; a huge threshold never switches
-    f2 = pkg.SirenFitter(spec, flat, gt, precision="bf16", hist_cap=4096)
+    f2 = pkg.SirenFitter(spec, flat, gt, precision="fp16", hist_cap=4096)
     assert f2.step_auto(300, check_every=100, threshold=0.0) == 100 and f2.precision == "fp32"
-    f3 = pkg.SirenFitter(spec, flat, gt, precision="bf16", hist_cap=4096)
-    assert f3.step_auto(300, check_every=100, threshold=1e9) is None and f3.precision == "bf16"
-    np.testing.assert_allclose(f2.losses()[:3], f3.losses()[:3], rtol=1e-3)   # same bf16 start (later steps: split-K atomics)
+    f3 = pkg.SirenFitter(spec, flat, gt, precision="fp16", hist_cap=4096)
+    assert f3.step_auto(300, check_every=100, threshold=1e9) is None and f3.precision == "fp16"
+    np.testing.assert_allclose(f2.losses()[:3], f3.losses()[:3], rtol=1e-3)   # same fp16 start (later steps: split-K atomics)
     assert len(f2.losses()) == len(f3.losses()) == 300

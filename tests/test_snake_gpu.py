@@ -135,9 +135,9 @@ def test_ragged_sizes_against_oracle(pkg):
                                                       (512, 1, 1, 0, True, 2500, False),
                                                       # first_linear: layer 0 = nn.Linear + Snake (models.py:343-347)
                                                       (128, 1, 1, 0, True, 3001, True), (256, 2, 0, 1, True, 5000, True)])
-def test_bf16_mode_snake_tanh_against_oracle(pkg, H, ns, nk, nt, last_lin, n, fl):
+def test_fp16_mode_snake_tanh_against_oracle(pkg, H, ns, nk, nt, last_lin, n, fl):
     """Snake / Tanh hidden layers in the tcgen05 mode (CTA-pair layer kernel, MODE_FWD_SNAKE / MODE_FWD_TANH /
-    MODE_BWD_SNAKE): loss within 1e-3 relative, gradients (incl. the Snake `a` gradients) within bf16 rounding noise
+    MODE_BWD_SNAKE): loss within 1e-3 relative, gradients (incl. the Snake `a` gradients) within fp16 rounding noise
     of the fp32 oracle."""
     from oracle import inr_oracle as O
     ospec = O.SirenSpec(1, H, ns, 1, last_lin, 30.0, 30.0, num_snake=nk, num_tanh=nt, first_linear=fl, a_initial=0.5)
@@ -148,7 +148,7 @@ def test_bf16_mode_snake_tanh_against_oracle(pkg, H, ns, nk, nt, last_lin, n, fl
     gt = torch.from_numpy(pkg.utils.synth_waveform(max(n, 2), seed=3)[:n].copy())
     coords = O.get_coord(n, 1).view(-1, 1)
     loss_o, _, grads_o, out_o = O.siren_loss_and_grads(ospec, ps, coords, gt.view(-1, 1))
-    f = pkg.SirenFitter(spec, flat, gt.to(dev()), precision="bf16", use_graph=False)
+    f = pkg.SirenFitter(spec, flat, gt.to(dev()), precision="fp16", use_graph=False)
     loss, grads, out = f.loss_and_grads()
     assert abs(loss - float(loss_o)) <= 1e-3 * abs(float(loss_o)) + 1e-9, (loss, float(loss_o))
     assert float(np.abs(out.cpu().numpy() - out_o.numpy().ravel()).max()) <= 3e-2
@@ -165,23 +165,23 @@ def test_bf16_mode_snake_tanh_against_oracle(pkg, H, ns, nk, nt, last_lin, n, fl
             ga, gr = gn[offs[pi]:offs[pi + 1]], go[offs[pi]:offs[pi + 1]]
             aerr = max(aerr, float(np.linalg.norm(ga - gr) / (np.linalg.norm(gr) + 1e-30)))
             pi += 1
-    print("bf16 snake/tanh H=%d %d/%d/%d n=%d: loss rel err %.2e, grad rel err %.2e, a-grad rel err %.2e" % (
+    print("fp16 snake/tanh H=%d %d/%d/%d n=%d: loss rel err %.2e, grad rel err %.2e, a-grad rel err %.2e" % (
         H, ns, nk, nt, n, abs(loss - float(loss_o)) / float(loss_o), gerr, aerr))
     assert gerr <= 5e-2 and aerr <= 5e-2
-    f2 = pkg.SirenFitter(spec, flat, gt.to(dev()), precision="bf16")
+    f2 = pkg.SirenFitter(spec, flat, gt.to(dev()), precision="fp16")
     f2.step(5)
     ls = f2.losses()
     assert np.all(np.isfinite(ls)) and ls.min() < 2 * ls[0]      # full-batch Adam at lr 1e-3 is not monotone
     np.testing.assert_allclose(f2.forward().cpu().numpy(), f2.forward().cpu().numpy())
 
 
-def test_bf16_mode_rejects_wide_inputs(pkg):
-    """the bf16 mode pads an encoded coordinate to H columns: in_features > H is refused loudly (fp32 mode takes it)"""
+def test_fp16_mode_rejects_wide_inputs(pkg):
+    """the fp16 mode pads an encoded coordinate to H columns: in_features > H is refused loudly (fp32 mode takes it)"""
     from inr_for_audio_b200 import _lib as L
     spec = pkg.SirenSpec(200, 128, 1, 1, True, 30.0, 30.0)
     with pytest.raises(L.InrLibraryError):
         pkg.SirenFitter(spec, torch.zeros(spec.num_params()), torch.zeros(256, device=dev()),
-                        torch.zeros(256, 200, device=dev()), precision="bf16")
+                        torch.zeros(256, 200, device=dev()), precision="fp16")
 
 
 def test_train_dropin_default_architecture(pkg, tmp_path):

@@ -1,4 +1,4 @@
-"""tcgen05 kernels (bf16 path) against matmul references, each case in a subprocess (a kernel trap would poison
+"""tcgen05 kernels (fp16 path) against matmul references, each case in a subprocess (a kernel trap would poison
 the CUDA context of the whole pytest process)."""
 import os
 import subprocess

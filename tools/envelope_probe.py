@@ -1,4 +1,4 @@
-"""bf16 convergence-envelope probe (the tests/test_siren_gpu.py case) under the current INR_TC_* switches."""
+"""fp16 convergence-envelope probe (the tests/test_siren_gpu.py case) under the current INR_TC_* switches."""
 import os, sys
 import numpy as np, torch
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
@@ -9,7 +9,7 @@ sr, data = wavfile.read(os.path.join(ROOT, "data", "gt_bach.wav"))
 data = data.astype(np.float32)[44100:44100 + 8192]
 gtn = data / np.max(np.abs(data))
 sig = float(np.mean(gtn.astype(np.float64) ** 2))
-prec = sys.argv[1] if len(sys.argv) > 1 else "bf16"
+prec = sys.argv[1] if len(sys.argv) > 1 else "fp16"
 for rep in range(int(sys.argv[2]) if len(sys.argv) > 2 else 3):
     torch.manual_seed(0)
     model = P.Siren(1, 128, 2, 1, True)

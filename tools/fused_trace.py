@@ -9,7 +9,7 @@ T = int(sys.argv[1]) if len(sys.argv) > 1 else 264600
 torch.manual_seed(0)
 m = P.Siren(1, 256, 3, 1, True)
 gt = torch.from_numpy(P.utils.synth_waveform(T, seed=0)).cuda()
-f = P.SirenFitter(m.spec, m.flat_parameters(), gt, precision="bf16", use_graph=False)
+f = P.SirenFitter(m.spec, m.flat_parameters(), gt, precision="fp16", use_graph=False)
 f.step(3)
 L.check(L.lib().inr_dbg_fused_trace_enable(1))
 f.step(1)

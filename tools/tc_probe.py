@@ -13,7 +13,8 @@ from inr_for_audio_b200 import _lib as L  # noqa: E402
 
 
 def bf(x):
-    return x.to(torch.bfloat16).to(torch.float32)
+    """round to the operand format of the SIREN tensor-core path (IEEE fp16)"""
+    return x.to(torch.float16).to(torch.float32)
 
 
 def run_layer(H, mode, variant, rows):
@@ -36,12 +37,12 @@ def run_layer(H, mode, variant, rows):
         t = omega * z + (omega * bias).double()
         e0 = (out0.double() - torch.sin(t)).abs().max().item()
         e1 = (out1.double() - torch.cos(t)).abs().max().item()
-        err, tol = max(e0, e1), 1.2e-2
+        err, tol = max(e0, e1), 2e-3
     else:
         z = bf(A).double() @ bf(W).double()
         ref = z * omega * bf(Cin).double()
         err = ((out0.double() - ref).abs() / (ref.abs() + 0.05)).max().item()
-        tol = 1.2e-2
+        tol = 2e-3
     return err, tol
 
 
@@ -57,7 +58,7 @@ def run_dw(H, variant, rows):
     torch.cuda.synchronize()
     ref = bf(dZ).double().t() @ bf(S).double()
     err = (gW.double() - ref).abs().max().item() / (rows ** 0.5)
-    return err, 1e-3
+    return err, 2e-4
 
 
 if __name__ == "__main__":
