@@ -35,7 +35,11 @@ extern "C" {
                            SIREN descriptors are refused: 8-bit significands floor a SIREN fit at ~24 dB      */
 #define INR_PREC_FP16 2 /* tcgen05 kind::f16, IEEE fp16 operands (11-bit significands) with a power-of-two loss
                            scale on dZ, fp32 TMEM accumulation; first layer, sin/cos arguments, loss, reductions
-                           and Adam master weights in fp32: the SIREN tensor-core mode                         */
+                           and Adam master weights in fp32: the fast SIREN tensor-core mode (fit floor ~31 dB
+                           on gt_bach: profiles/r02_c1_noise_*.jsonl)                                          */
+#define INR_PREC_FP16S 3 /* INR_PREC_FP16 with the FORWARD operands S_l and W_l as fp16 hi + lo pairs (22-bit
+                           significands) and three MMAs per K step (hi*hi + lo*hi + hi*lo): fp32-grade forward,
+                           fp16 backward -- the parity-grade tensor-core mode                                  */
 
 /* time-domain loss, run.py:124-125,161-169 */
 #define INR_LOSS_MSE 0

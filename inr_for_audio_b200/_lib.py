@@ -11,9 +11,9 @@ HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.path.join(HERE, "libinr_b200.so")
 
 INR_OK, INR_E_BADARG, INR_E_UNSUPPORTED, INR_E_CUDA, INR_E_WORKSPACE = 0, -1, -2, -3, -4
-PREC_FP32, PREC_BF16, PREC_FP16 = 0, 1, 2
+PREC_FP32, PREC_BF16, PREC_FP16, PREC_FP16S = 0, 1, 2, 3
 LOSS_MSE, LOSS_MAE = 0, 1
-PRECISIONS = {"fp32": PREC_FP32, "bf16": PREC_BF16, "fp16": PREC_FP16}
+PRECISIONS = {"fp32": PREC_FP32, "bf16": PREC_BF16, "fp16": PREC_FP16, "fp16s": PREC_FP16S}
 
 
 class SirenDesc(C.Structure):

@@ -80,9 +80,9 @@ static int check_desc(const inr_siren_desc* d) {
   INR_REQUIRE(d->first_linear == 0 || d->first_linear == 1, INR_E_BADARG, "first_linear must be 0 or 1");
   INR_REQUIRE(d->precision != INR_PREC_BF16, INR_E_UNSUPPORTED,
               "SIREN has no bf16 mode (bf16 operands floor the fit at ~24 dB): use INR_PREC_FP16 for the tcgen05 path");
-  INR_REQUIRE(d->precision == INR_PREC_FP32 || d->precision == INR_PREC_FP16, INR_E_BADARG, "unknown precision %d",
+  INR_REQUIRE(d->precision == INR_PREC_FP32 || d->precision == INR_PREC_FP16 || d->precision == INR_PREC_FP16S, INR_E_BADARG, "unknown precision %d",
               d->precision);
-  if (d->precision == INR_PREC_FP16)
+  if (d->precision == INR_PREC_FP16 || d->precision == INR_PREC_FP16S)
     INR_REQUIRE(siren_tc_supported(d), INR_E_UNSUPPORTED,
                 "fp16 tcgen05 path needs in_features <= hidden_features, hidden_features in {128,256,512} and >= 1 hidden layer "
                 "(got in=%d H=%d sine=%d snake=%d tanh=%d first_linear=%d); use INR_PREC_FP32",
@@ -169,7 +169,7 @@ int64_t inr_siren_num_params(const inr_siren_desc* d) {
 int64_t inr_siren_workspace_bytes(const inr_siren_desc* d, int64_t n_rows, int training) {
   if (check_desc(d) != INR_OK) return INR_E_BADARG;
   if (n_rows < 0) return INR_E_BADARG;
-  if (d->precision == INR_PREC_FP16) return siren_tc_workspace_bytes(d, n_rows, training);
+  if (d->precision == INR_PREC_FP16 || d->precision == INR_PREC_FP16S) return siren_tc_workspace_bytes(d, n_rows, training);
   // fp32 path: whole-problem activations up to a cap; the host code loops over row chunks beyond it
   const int64_t per_row = siren_fp32_workspace_per_row(d, training);
   const int64_t cap = (int64_t)64 << 30;   // of 180 GB
@@ -212,7 +212,7 @@ int inr_siren_forward(const inr_siren_desc* d, const float* params, const float*
               (long long)i0, (long long)(i0 + n), (long long)T_total);
   if (n == 0) return INR_OK;
   INR_REQUIRE(workspace && workspace_bytes > 0, INR_E_WORKSPACE, "workspace missing");
-  if (d->precision == INR_PREC_FP16)
+  if (d->precision == INR_PREC_FP16 || d->precision == INR_PREC_FP16S)
     return siren_tc_forward(d, params, coords, n, i0, T_total, coord_scale, out, workspace, workspace_bytes,
                             (cudaStream_t)stream);
   return siren_fp32_forward(d, params, coords, n, i0, T_total, coord_scale, out, workspace, workspace_bytes,
@@ -233,7 +233,7 @@ int inr_siren_loss_backward(const inr_siren_desc* d, const float* params, const 
               (long long)i0, (long long)(i0 + n), (long long)T_total);
   if (n == 0) return INR_OK;
   INR_REQUIRE(workspace && workspace_bytes > 0, INR_E_WORKSPACE, "workspace missing");
-  if (d->precision == INR_PREC_FP16)
+  if (d->precision == INR_PREC_FP16 || d->precision == INR_PREC_FP16S)
     return siren_tc_loss_backward(d, params, coords, target, n, i0, T_total, coord_scale, loss_kind, grad_scale,
                                   extra_gout_or_null, grads, opt, out_or_null, workspace, workspace_bytes,
                                   (cudaStream_t)stream);
@@ -262,7 +262,7 @@ int inr_siren_train_forward(const inr_siren_desc* d, const float* params, const 
   if (rc) return rc;
   INR_REQUIRE(out, INR_E_BADARG, "train_forward: out is NULL");
   if (n == 0) return INR_OK;
-  if (d->precision == INR_PREC_FP16)
+  if (d->precision == INR_PREC_FP16 || d->precision == INR_PREC_FP16S)
     return siren_tc_train(d, params, coords, nullptr, n, i0, T_total, coord_scale, 0, 0.f, nullptr, nullptr, nullptr, out,
                           workspace, workspace_bytes, 1, (cudaStream_t)stream);
   return siren_fp32_train(d, params, coords, nullptr, n, i0, T_total, coord_scale, 0, 0.f, nullptr, nullptr, nullptr, out,
@@ -279,7 +279,7 @@ int inr_siren_train_backward(const inr_siren_desc* d, const float* params, const
   INR_REQUIRE(target || extra_gout_or_null, INR_E_BADARG, "need a target and/or an upstream gradient");
   INR_REQUIRE(loss_kind == INR_LOSS_MSE || loss_kind == INR_LOSS_MAE, INR_E_BADARG, "unknown loss kind %d", loss_kind);
   if (n == 0) return INR_OK;
-  if (d->precision == INR_PREC_FP16)
+  if (d->precision == INR_PREC_FP16 || d->precision == INR_PREC_FP16S)
     return siren_tc_train(d, params, coords, target, n, i0, T_total, coord_scale, loss_kind, grad_scale, extra_gout_or_null,
                           grads, opt, nullptr, workspace, workspace_bytes, 2, (cudaStream_t)stream);
   return siren_fp32_train(d, params, coords, target, n, i0, T_total, coord_scale, loss_kind, grad_scale, extra_gout_or_null,

@@ -18,20 +18,27 @@ namespace inr {
 using namespace tc;
 
 // ------------------------------------------------------------------------------------------------ pack
-__global__ void __launch_bounds__(256) k_tc_pack(const float* __restrict__ params, SirenLayout lay, int NS,
+// Forward operand slices are [slice][hi | lo (split)][K/8][NSF][8] (NSF columns per CTA: tc_ns_fwd); the dX operand is
+// never split: [slice][K/8][NSB][8].
+__global__ void __launch_bounds__(256) k_tc_pack(const float* __restrict__ params, SirenLayout lay, int NSF, int NSB, int split,
                                                  op16* __restrict__ Wf, op16* __restrict__ Wb) {
   const int H = lay.H;
   const int64_t per = (int64_t)H * H;
   const int64_t total = per * lay.L;
+  const int64_t fper = per * (split ? 2 : 1);         // forward-operand elements per layer
+  const int64_t fslice = (int64_t)H * NSF * (split ? 2 : 1);
   for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
     const int l = (int)(i / per);
     const int rem = (int)(i - (int64_t)l * per);
     const int o = rem / H, in = rem - o * H;
-    const op16 w = to_op(params[lay.w_off(l + 1) + rem]);
+    const float wv = params[lay.w_off(l + 1) + rem];
+    const op16 w = to_op(wv);
     // forward operand: B[n = out][k = in]
-    Wf[(int64_t)l * per + (int64_t)(o / NS) * ((int64_t)H * NS) + ((int64_t)(in >> 3) * NS + (o % NS)) * 8 + (in & 7)] = w;
+    const int64_t fo = (int64_t)l * fper + (int64_t)(o / NSF) * fslice + ((int64_t)(in >> 3) * NSF + (o % NSF)) * 8 + (in & 7);
+    Wf[fo] = w;
+    if (split) Wf[fo + (int64_t)H * NSF] = to_op(wv - __half2float(w));
     // dX operand: B[n = in][k = out]
-    Wb[(int64_t)l * per + (int64_t)(in / NS) * ((int64_t)H * NS) + ((int64_t)(o >> 3) * NS + (in % NS)) * 8 + (o & 7)] = w;
+    Wb[(int64_t)l * per + (int64_t)(in / NSB) * ((int64_t)H * NSB) + ((int64_t)(o >> 3) * NSB + (in % NSB)) * 8 + (o & 7)] = w;
   }
 }
 
@@ -39,19 +46,23 @@ __global__ void __launch_bounds__(256) k_tc_pack(const float* __restrict__ param
 // Encoded coordinates (in_features = 2*num_freq > 2, run.py:81-82,141-144) on the tcgen05 path: the input rows become one
 // more tile image X (fp16, zero-padded to H columns) and layer 0 one more H x H layer GEMM with W_0 zero-padded to H
 // input columns; its weight gradient is the dW GEMM against X, cut back to (H x in).  Needs in_features <= H.
-__global__ void __launch_bounds__(256) k_tc_pack0(const float* __restrict__ W0, int in, int H, int NS,
+__global__ void __launch_bounds__(256) k_tc_pack0(const float* __restrict__ W0, int in, int H, int NS, int split,
                                                   op16* __restrict__ Wf0) {
   const int total = H * H;
+  const int64_t fslice = (int64_t)H * NS * (split ? 2 : 1);
   for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < total; i += gridDim.x * blockDim.x) {
     const int o = i / H, k = i - o * H;
     const float v = k < in ? W0[(int64_t)o * in + k] : 0.f;
-    Wf0[(int64_t)(o / NS) * ((int64_t)H * NS) + ((int64_t)(k >> 3) * NS + (o % NS)) * 8 + (k & 7)] = to_op(v);
+    const op16 w = to_op(v);
+    const int64_t fo = (int64_t)(o / NS) * fslice + ((int64_t)(k >> 3) * NS + (o % NS)) * 8 + (k & 7);
+    Wf0[fo] = w;
+    if (split) Wf0[fo + (int64_t)H * NS] = to_op(v - __half2float(w));
   }
 }
 
 // X[tile][group][row][8] <- coords (rows x in) fp32, zero beyond `in` columns and `rows` rows
 __global__ void __launch_bounds__(256) k_tc_rows_to_image(const float* __restrict__ coords, int in, int H, int64_t rows,
-                                                          int64_t rows_pad, op16* __restrict__ X) {
+                                                          int64_t rows_pad, op16* __restrict__ X, op16* __restrict__ Xlo) {
   const int lg = 31 - __clz(H >> 3);
   const int64_t total = rows_pad << lg;
   for (int64_t idx = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; idx < total; idx += (int64_t)gridDim.x * blockDim.x) {
@@ -65,8 +76,11 @@ __global__ void __launch_bounds__(256) k_tc_rows_to_image(const float* __restric
       const int f = kg * 8 + j;
       v[j] = (row < rows && f < in) ? coords[row * in + f] : 0.f;
     }
-    *reinterpret_cast<uint4*>(X + idx * 8) = make_uint4(pack_op2(v[0], v[1]), pack_op2(v[2], v[3]),
-                                                        pack_op2(v[4], v[5]), pack_op2(v[6], v[7]));
+    uint32_t hi[4], lo[4];
+#pragma unroll
+    for (int h = 0; h < 4; ++h) pack_op2_split(v[2 * h], v[2 * h + 1], &hi[h], &lo[h]);
+    *reinterpret_cast<uint4*>(X + idx * 8) = make_uint4(hi[0], hi[1], hi[2], hi[3]);
+    if (Xlo) *reinterpret_cast<uint4*>(Xlo + idx * 8) = make_uint4(lo[0], lo[1], lo[2], lo[3]);
   }
 }
 
@@ -87,7 +101,7 @@ __global__ void __launch_bounds__(256) k_tc_first(const float* __restrict__ W, c
                                                   int64_t rows_pad, int64_t g0, int64_t T_total, float scale,
                                                   float omega, op16* __restrict__ S0,
                                                   op16* __restrict__ C0, const float* __restrict__ Aparam,
-                                                  op16* __restrict__ E0) {
+                                                  op16* __restrict__ E0, op16* __restrict__ S0lo) {
   // Aparam != NULL: first_linear (models.py:343-347), layer 0 = nn.Linear + Snake: S0 = y, C0 = dy/dz, E0 = dy/da
   const int lg = 31 - __clz(H >> 3);                      // H/8 feature groups: a power of two on this path
   const int64_t total = rows_pad << lg;
@@ -105,7 +119,7 @@ __global__ void __launch_bounds__(256) k_tc_first(const float* __restrict__ W, c
     } else {
       x0 = linspace_at(g0 + row, T_total, scale);
     }
-    uint32_t so[4], co[4], eo[4];
+    uint32_t so[4], co[4], eo[4], sl[4];
 #pragma unroll
     for (int h = 0; h < 4; ++h) {
       float s[2], c[2], e[2] = {0.f, 0.f};
@@ -125,12 +139,13 @@ __global__ void __launch_bounds__(256) k_tc_first(const float* __restrict__ W, c
           sincos_reduced(omega * z, &s[u], &c[u]);
         }
       }
-      so[h] = pack_op2(s[0], s[1]);
+      pack_op2_split(s[0], s[1], &so[h], &sl[h]);
       co[h] = pack_op2(c[0], c[1]);
       eo[h] = pack_op2(e[0], e[1]);
     }
     const int64_t off = idx * 8;   // == ((tile*groups + kg)*128 + r)*8
     *reinterpret_cast<uint4*>(S0 + off) = make_uint4(so[0], so[1], so[2], so[3]);
+    if (S0lo) *reinterpret_cast<uint4*>(S0lo + off) = make_uint4(sl[0], sl[1], sl[2], sl[3]);
     if (C0) *reinterpret_cast<uint4*>(C0 + off) = make_uint4(co[0], co[1], co[2], co[3]);
     if (Aparam && E0) *reinterpret_cast<uint4*>(E0 + off) = make_uint4(eo[0], eo[1], eo[2], eo[3]);
   }
@@ -174,7 +189,9 @@ __global__ void __launch_bounds__(512, 1) k_tc_last2(const op16* __restrict__ S,
                                                      float* __restrict__ gw, float* __restrict__ gb,
                                                      double* __restrict__ loss_acc, float* __restrict__ out, int training,
                                                      const op16* __restrict__ Eimg, float* __restrict__ ga,
-                                                     const float* __restrict__ gsc, unsigned* __restrict__ gmax_acc) {
+                                                     const float* __restrict__ gsc, unsigned* __restrict__ gmax_acc,
+                                                     const op16* __restrict__ Slo) {
+  // Slo != NULL (operand split): S_L = S + Slo, the head's dot product takes both (straight from global memory)
   using Cfg = Last2Cfg<H>;
   constexpr int KPW = Cfg::KPW;
   extern __shared__ __align__(128) uint8_t smem[];
@@ -228,6 +245,13 @@ __global__ void __launch_bounds__(512, 1) k_tc_last2(const op16* __restrict__ S,
       if (target) tgt = target[row];
       if (extra_g) eg = extra_g[row];
     }
+    uint4 lov[KPW];
+    if (Slo) {
+      const size_t tile_off0 = (size_t)tile * (TILE_ROWS * (size_t)H);
+#pragma unroll
+      for (int i = 0; i < KPW; ++i)
+        lov[i] = __ldg(reinterpret_cast<const uint4*>(Slo + tile_off0 + ((size_t)(warp + 16 * i) * TILE_ROWS + r) * 8));
+    }
     cp_async_wait<Cfg::NSTAGE - 2>();
     __syncthreads();   // this unit's slabs have landed for every thread; the stage refilled below is no longer read
     issue(unit + (Cfg::NSTAGE - 1) * gridDim.x, (it + Cfg::NSTAGE - 1) % Cfg::NSTAGE);
@@ -245,6 +269,15 @@ __global__ void __launch_bounds__(512, 1) k_tc_last2(const op16* __restrict__ S,
         const float2 f = unpack_op2(uw[h]);
         pd = __fmaf_rn(f.x, s_w[kg * 8 + 2 * h], pd);
         pd = __fmaf_rn(f.y, s_w[kg * 8 + 2 * h + 1], pd);
+      }
+      if (Slo) {
+        const uint32_t lw[4] = {lov[i].x, lov[i].y, lov[i].z, lov[i].w};
+#pragma unroll
+        for (int h = 0; h < 4; ++h) {
+          const float2 f = unpack_op2(lw[h]);
+          pd = __fmaf_rn(f.x, s_w[kg * 8 + 2 * h], pd);
+          pd = __fmaf_rn(f.y, s_w[kg * 8 + 2 * h + 1], pd);
+        }
       }
     }
     s_dot[warp * 32 + lane] = pd;
@@ -451,22 +484,35 @@ bool siren_tc_supported(const inr_siren_desc* d) {
 // columns of the packed weight slices ([slice][K/8][ns][8]): one slice per CTA of a pair
 int tc_ns(int H) { return H >= 256 ? 128 : H / 2; }
 static int ns_of(int H) { return tc_ns(H); }
+// INR_PREC_FP16S: forward GEMM operands as fp16 hi + lo pairs (k_tc_layer2<.., SPLIT>)
+static bool is_split(const inr_siren_desc* d) { return d->precision == INR_PREC_FP16S; }
+// columns per CTA of the FORWARD operand slices
+static int ns_fwd(int H, bool split) { return split ? (H >= 512 ? 64 : H / 2) : ns_of(H); }
 
 struct TcPlan {
-  int64_t pack_bytes, gvec_bytes, img_bytes_per_row, fixed_bytes;
+  int64_t pack_bytes, img_bytes_per_row, fixed_bytes;
   int n_images;
+  int x_image;     // wide inputs: index of the input image X, else -1
+  int lo_image;    // operand split: first of the two ping-pong lo images, else -1
+  int xlo_image;   // operand split + wide inputs: lo image of X, else -1
 };
 
 static TcPlan plan_of(const inr_siren_desc* d, int training) {
   TcPlan pl;
   const SirenLayout lay = layout_of(d);
   const int64_t H = lay.H, L = lay.L;
-  const bool wide = lay.in > 2;
-  pl.pack_bytes = 2 * L * H * H * 2 + (wide ? H * H * 2 + H * H * 4 : 0);   // + padded W_0 operand, padded gW_0 scratch
-  pl.n_images = (training ? 2 * (int)(L + 1) + lay.num_snake_layers() : 2) + (wide ? 1 : 0);   // + dy/da images, + X
+  const bool wide = lay.in > 2, split = is_split(d);
+  const int64_t fw = split ? 2 : 1;                    // forward operands: hi + lo
+  // forward + dX operands of the L layers, + padded W_0 operand and padded fp32 gW_0 scratch (wide inputs)
+  pl.pack_bytes = (fw + 1) * L * H * H * 2 + (wide ? fw * H * H * 2 + H * H * 4 : 0);
+  int n = training ? 2 * (int)(L + 1) + lay.num_snake_layers() : 2;   // S_l, C_l, dy/da images | two ping-pong images
+  pl.x_image = wide ? n++ : -1;
+  pl.lo_image = split ? n : -1;
+  if (split) n += 2;
+  pl.xlo_image = (split && wide) ? n++ : -1;
+  pl.n_images = n;
   pl.img_bytes_per_row = pl.n_images * H * 2;
   pl.fixed_bytes = round_up(pl.pack_bytes, 1024) + 4096;
-  pl.gvec_bytes = 0;
   return pl;
 }
 
@@ -495,35 +541,41 @@ static int launch_dw(const DwParams& p, cudaStream_t st) {
   return INR_OK;
 }
 
-template <int H, int MODE>
+template <int H, int MODE, bool SPLIT = false>
 static int launch_layer2(const LayerParams& p, cudaStream_t st) {
-  using Cfg = Layer2Cfg<H>;
+  using Cfg = Layer2Cfg<H, SPLIT>;
   static bool attr_set = false;
   if (!attr_set) {
-    INR_CUDA_CHECK(cudaFuncSetAttribute(k_tc_layer2<H, MODE>, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg::SMEM_BYTES));
+    INR_CUDA_CHECK(cudaFuncSetAttribute(k_tc_layer2<H, MODE, SPLIT>, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg::SMEM_BYTES));
     attr_set = true;
   }
   int pairs = (num_sms() / 2) / Cfg::NQ * Cfg::NQ;
   const int max_useful = ((p.num_tiles + 1) / 2) * Cfg::NQ;
   if (pairs > max_useful) pairs = max_useful;
   { LaunchScope ls(mode_is_fwd(MODE) ? "k_tc_layer_fwd" : "k_tc_layer_bwd", st);
-    k_tc_layer2<H, MODE><<<2 * pairs, Cfg::THREADS, Cfg::SMEM_BYTES, st>>>(p); }
+    k_tc_layer2<H, MODE, SPLIT><<<2 * pairs, Cfg::THREADS, Cfg::SMEM_BYTES, st>>>(p); }
   INR_LAUNCH_CHECK();
   return INR_OK;
 }
 
-template <int MODE>
+template <int MODE, bool SPLIT = false>
 static int launch_layer2_h(int H, const LayerParams& p, cudaStream_t st) {
   switch (H) {
-    case 128: return launch_layer2<128, MODE>(p, st);
-    case 256: return launch_layer2<256, MODE>(p, st);
-    case 512: return launch_layer2<512, MODE>(p, st);
+    case 128: return launch_layer2<128, MODE, SPLIT>(p, st);
+    case 256: return launch_layer2<256, MODE, SPLIT>(p, st);
+    case 512: return launch_layer2<512, MODE, SPLIT>(p, st);
   }
   set_error("tcgen05 layer kernel: unsupported H=%d", H);
   return INR_E_UNSUPPORTED;
 }
 
 int tc_layer(int H, int mode, const LayerParams& p, cudaStream_t st) {
+  if (p.A_lo) {   // operand split (forward modes): A = A + A_lo, Bpack = [hi | lo] slices, out0_lo written
+    INR_REQUIRE(mode_is_fwd(mode) && p.out0_lo, INR_E_BADARG, "operand split: forward layer modes with an out0_lo image only");
+    if (mode == MODE_FWD_SNAKE) return launch_layer2_h<MODE_FWD_SNAKE, true>(H, p, st);
+    if (mode == MODE_FWD_TANH) return launch_layer2_h<MODE_FWD_TANH, true>(H, p, st);
+    return launch_layer2_h<MODE_FWD, true>(H, p, st);
+  }
   if (mode == MODE_FWD_SNAKE) return launch_layer2_h<MODE_FWD_SNAKE>(H, p, st);
   if (mode == MODE_FWD_TANH) return launch_layer2_h<MODE_FWD_TANH>(H, p, st);
   if (mode == MODE_BWD_SNAKE) return launch_layer2_h<MODE_BWD_SNAKE>(H, p, st);
@@ -562,7 +614,8 @@ int tc_dw(int H, const DwParams& p, cudaStream_t st) {
 }
 
 static bool fused_ok(const inr_siren_desc* d) {
-  return (d->hidden_features == 128 || d->hidden_features == 256) &&
+  // the fused forward keeps single fp16 images on chip: two hi + lo slot pairs do not fit 227 KB at H = 256
+  return !is_split(d) && (d->hidden_features == 128 || d->hidden_features == 256) &&
          d->hidden_layers >= 1 && d->hidden_layers <= FUSED_MAX_L && d->num_snake == 0 && d->num_tanh == 0 &&
          d->first_linear == 0 && d->in_features <= 2;
 }
@@ -619,12 +672,12 @@ static int fused_forward(const inr_siren_desc* d, const float* params, const op1
 }
 
 static LayerParams layer_params(int H, const op16* A, const op16* Bp, const float* bias, float omega,
-                                op16* out0, op16* out1, const op16* Cin, int tiles) {
+                                op16* out0, op16* out1, const op16* Cin, int tiles, int ns = 0) {
   LayerParams p;
   p.A = A; p.Bpack = Bp; p.bias = bias; p.omega = omega; p.out0 = out0; p.out1 = out1; p.Cin = Cin; p.num_tiles = tiles;
   p.avec = nullptr; p.out2 = nullptr;
   p.a_lbo = TILE_ROWS * 16; p.a_sbo = 128;            // K-major, no swizzle: LBO = next 8-feature group, SBO = next 8 rows
-  p.b_lbo = (uint32_t)ns_of(H) * 16; p.b_sbo = 128;
+  p.b_lbo = (uint32_t)(ns ? ns : ns_of(H)) * 16; p.b_sbo = 128;
   return p;
 }
 
@@ -652,6 +705,8 @@ struct TcWorkspace {
   op16* Wf0;   // wide inputs: W_0 zero-padded to H x H (forward operand)
   float* gW0;           // wide inputs: H x H fp32 scratch of the padded first-layer weight gradient
   int x_image;          // wide inputs: index of the input image X, else -1
+  int lo_image, xlo_image;   // operand split: see TcPlan
+  bool split;
   float* gsc;           // {gs, 1/gs}: loss scale of the fp16 dZ images of this call (k_tc_gscale); [2] = max |extra_g| bits
   op16* img;
   int64_t chunk_rows;   // multiple of 128
@@ -663,11 +718,13 @@ static int carve(const inr_siren_desc* d, int training, int64_t n, void* ws, int
   const int64_t H = d->hidden_features, L = layout_of(d).L;
   uint8_t* base = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(ws) + 255) & ~(uintptr_t)255);
   const int64_t usable = ws_bytes - (base - reinterpret_cast<uint8_t*>(ws));
+  w->split = is_split(d);
+  const int64_t fw = w->split ? 2 : 1;
   w->Wf = reinterpret_cast<op16*>(base);
-  w->Wb = w->Wf + L * H * H;
+  w->Wb = w->Wf + fw * L * H * H;
   w->Wf0 = w->Wb + L * H * H;
-  w->gW0 = reinterpret_cast<float*>(w->Wf0 + H * H);
-  w->x_image = d->in_features > 2 ? pl.n_images - 1 : -1;
+  w->gW0 = reinterpret_cast<float*>(w->Wf0 + fw * H * H);
+  w->x_image = pl.x_image; w->lo_image = pl.lo_image; w->xlo_image = pl.xlo_image;
   int64_t avail = usable - pl.fixed_bytes;
   int64_t rows = avail / pl.img_bytes_per_row / TILE_ROWS * TILE_ROWS;
   INR_REQUIRE(rows >= TILE_ROWS, INR_E_WORKSPACE, "workspace of %lld bytes is too small for one 128-row tile", (long long)ws_bytes);
@@ -685,11 +742,12 @@ static int pack_weights(const inr_siren_desc* d, const float* params, const TcWo
   const int64_t total = (int64_t)lay.H * lay.H * lay.L;
   int blocks = (int)std::min<int64_t>(cdiv(total, 256), (int64_t)num_sms() * 8);
   { LaunchScope ls("k_tc_pack", st);
-    k_tc_pack<<<blocks, 256, 0, st>>>(params, lay, ns_of(lay.H), w.Wf, w.Wb); }
+    k_tc_pack<<<blocks, 256, 0, st>>>(params, lay, ns_fwd(lay.H, w.split), ns_of(lay.H), w.split ? 1 : 0, w.Wf, w.Wb); }
   INR_LAUNCH_CHECK();
   if (lay.in > 2) {
     LaunchScope ls("k_tc_pack", st);
-    k_tc_pack0<<<(lay.H * lay.H + 255) / 256, 256, 0, st>>>(params + lay.w_off(0), lay.in, lay.H, ns_of(lay.H), w.Wf0);
+    k_tc_pack0<<<(lay.H * lay.H + 255) / 256, 256, 0, st>>>(params + lay.w_off(0), lay.in, lay.H, ns_fwd(lay.H, w.split),
+                                                            w.split ? 1 : 0, w.Wf0);
     INR_LAUNCH_CHECK();
   }
   return INR_OK;
@@ -697,14 +755,14 @@ static int pack_weights(const inr_siren_desc* d, const float* params, const TcWo
 
 static int first_layer(const inr_siren_desc* d, const float* params, const float* coords, int64_t rows, int64_t rows_pad,
                        int64_t g0, int64_t T_total, float scale, op16* S0, op16* C0, cudaStream_t st,
-                       op16* E0 = nullptr) {
+                       op16* E0 = nullptr, op16* S0lo = nullptr) {
   SirenLayout lay = layout_of(d);
   const int64_t total = rows_pad * (lay.H / 8);
   int blocks = (int)std::min<int64_t>(cdiv(total, 256), (int64_t)num_sms() * 16);
   { LaunchScope ls("k_tc_first", st);
     k_tc_first<<<blocks, 256, 0, st>>>(params + lay.w_off(0), params + lay.b_off(0), coords, lay.in, lay.H, rows, rows_pad,
                                        g0, T_total, scale, d->first_omega_0, S0, C0,
-                                       lay.first_snake ? params + lay.a_off(0) : nullptr, E0); }
+                                       lay.first_snake ? params + lay.a_off(0) : nullptr, E0, S0lo); }
   INR_LAUNCH_CHECK();
   return INR_OK;
 }
@@ -713,7 +771,8 @@ template <int H, bool SNAKE>
 static int launch_last2(const op16* SL, op16* CL, const float* w, const float* b, const float* target,
                         const float* extra_g, int64_t rows, int tiles, float dfac, float omega_h, int outermost_linear,
                         int loss_kind, float grad_scale, float* gw, float* gb, double* loss_acc, float* out, int training,
-                        const op16* EL, float* ga, const float* gsc, unsigned* gmax_acc, cudaStream_t st) {
+                        const op16* EL, float* ga, const float* gsc, unsigned* gmax_acc, const op16* SLlo,
+                        cudaStream_t st) {
   using Cfg = Last2Cfg<H>;
   static bool attr_done = false;
   if (!attr_done) {
@@ -724,7 +783,7 @@ static int launch_last2(const op16* SL, op16* CL, const float* w, const float* b
   { LaunchScope ls("k_tc_last", st);
     k_tc_last2<H, SNAKE><<<blocks, 512, Cfg::SMEM_BYTES, st>>>(SL, CL, w, b, target, extra_g, rows, tiles, dfac, omega_h,
                                                                outermost_linear, loss_kind, grad_scale, gw, gb, loss_acc,
-                                                               out, training, EL, ga, gsc, gmax_acc); }
+                                                               out, training, EL, ga, gsc, gmax_acc, SLlo); }
   INR_LAUNCH_CHECK();
   return INR_OK;
 }
@@ -734,7 +793,7 @@ static int launch_last2(const op16* SL, op16* CL, const float* w, const float* b
 static int last_layer(const inr_siren_desc* d, const float* params, const op16* SL, op16* CL,
                       const float* target, const float* extra_g, int64_t rows, int tiles, int loss_kind, float grad_scale,
                       const float* gsc, float* grads, inr_opt_state* opt, float* out, int training, cudaStream_t st,
-                      op16* EL = nullptr) {
+                      op16* EL = nullptr, const op16* SLlo = nullptr) {
   SirenLayout lay = layout_of(d);
   const int last = lay.L + 1;
   const int H = lay.H;
@@ -751,10 +810,10 @@ static int last_layer(const inr_siren_desc* d, const float* params, const op16* 
 #define INR_LAST2(HH)                                                                                                   \
   return EL ? launch_last2<HH, true>(SL, CL, w, b, target, extra_g, rows, tiles, dfac, d->hidden_omega_0,              \
                                      d->outermost_linear, loss_kind, grad_scale, gw, gb, loss_acc, out, training, EL,   \
-                                     ga, gsc, gmax, st)                                                                 \
+                                     ga, gsc, gmax, SLlo, st)                                                           \
             : launch_last2<HH, false>(SL, CL, w, b, target, extra_g, rows, tiles, dfac, d->hidden_omega_0,             \
                                       d->outermost_linear, loss_kind, grad_scale, gw, gb, loss_acc, out, training,      \
-                                      nullptr, nullptr, gsc, gmax, st)
+                                      nullptr, nullptr, gsc, gmax, SLlo, st)
   if (H == 512) { INR_LAST2(512); }
   if (H == 256) { INR_LAST2(256); }
   INR_LAST2(128);
@@ -765,11 +824,13 @@ static int last_layer(const inr_siren_desc* d, const float* params, const op16* 
 // Eout = dy/da image (Snake layers)
 static int fwd_layer_tc(const inr_siren_desc* d, const SirenLayout& lay, const float* params, const TcWorkspace& w, int l,
                         const op16* Sin, op16* Sout, op16* Cout, op16* Eout, int tiles,
-                        cudaStream_t st) {
+                        cudaStream_t st, const op16* Sin_lo = nullptr, op16* Sout_lo = nullptr) {
   const int H = lay.H;
   const int kind = lay.kind(l);
-  LayerParams p = layer_params(H, Sin, w.Wf + (int64_t)(l - 1) * H * H, params + lay.b_off(l),
-                               kind == ACT_SINE ? d->hidden_omega_0 : 1.f, Sout, Cout, nullptr, tiles);
+  const int64_t fw = w.split ? 2 : 1;
+  LayerParams p = layer_params(H, Sin, w.Wf + (int64_t)(l - 1) * fw * H * H, params + lay.b_off(l),
+                               kind == ACT_SINE ? d->hidden_omega_0 : 1.f, Sout, Cout, nullptr, tiles, ns_fwd(H, w.split));
+  p.A_lo = Sin_lo; p.out0_lo = Sout_lo;
   if (kind == ACT_SNAKE) { p.avec = params + lay.a_off(l); p.out2 = Eout; }
   return tc_layer(H, kind == ACT_SINE ? MODE_FWD : (kind == ACT_SNAKE ? MODE_FWD_SNAKE : MODE_FWD_TANH), p, st);
 }
@@ -777,16 +838,17 @@ static int fwd_layer_tc(const inr_siren_desc* d, const SirenLayout& lay, const f
 // layer 0 on an encoded coordinate: X image from the rows, then the layer GEMM with the padded W_0
 static int first_layer_wide(const inr_siren_desc* d, const SirenLayout& lay, const float* params, const TcWorkspace& w,
                             const float* xc, int64_t rows, int64_t rows_pad, op16* X, op16* S0,
-                            op16* C0, op16* E0, int tiles, cudaStream_t st) {
+                            op16* C0, op16* E0, int tiles, cudaStream_t st, op16* Xlo = nullptr, op16* S0lo = nullptr) {
   const int H = lay.H;
   const int64_t total = rows_pad * (H / 8);
   const int blocks = (int)std::min<int64_t>(cdiv(total, 256), (int64_t)num_sms() * 16);
   { LaunchScope ls("k_tc_rows_to_image", st);
-    k_tc_rows_to_image<<<blocks, 256, 0, st>>>(xc, lay.in, H, rows, rows_pad, X); }
+    k_tc_rows_to_image<<<blocks, 256, 0, st>>>(xc, lay.in, H, rows, rows_pad, X, Xlo); }
   INR_LAUNCH_CHECK();
   const int kind = lay.kind(0);
   LayerParams p = layer_params(H, X, w.Wf0, params + lay.b_off(0), kind == ACT_SINE ? d->first_omega_0 : 1.f, S0, C0,
-                               nullptr, tiles);
+                               nullptr, tiles, ns_fwd(H, w.split));
+  p.A_lo = Xlo; p.out0_lo = S0lo;
   if (kind == ACT_SNAKE) { p.avec = params + lay.a_off(0); p.out2 = E0; }
   return tc_layer(H, kind == ACT_SINE ? MODE_FWD : MODE_FWD_SNAKE, p, st);
 }
@@ -804,6 +866,9 @@ int siren_tc_forward(const inr_siren_desc* d, const float* params, const float* 
     const int64_t rows_pad = round_up(rows, TILE_ROWS);
     const int tiles = (int)(rows_pad / TILE_ROWS);
     op16* S[2] = {w.img, w.img + w.img_elems};
+    op16* Slo[2] = {w.split ? w.img + (int64_t)w.lo_image * w.img_elems : nullptr,
+                    w.split ? w.img + (int64_t)(w.lo_image + 1) * w.img_elems : nullptr};
+    op16* Xlo = w.xlo_image >= 0 ? w.img + (int64_t)w.xlo_image * w.img_elems : nullptr;
     if (fused_ok(d)) {   // all layers in one kernel; only S_L goes to HBM, for the output dot below
       op16* Sl[FUSED_MAX_L + 1] = {nullptr};
       Sl[L] = S[0];
@@ -817,19 +882,20 @@ int siren_tc_forward(const inr_siren_desc* d, const float* params, const float* 
     }
     if (w.x_image >= 0) {
       rc = first_layer_wide(d, lay, params, w, coords + r0 * lay.in, rows, rows_pad, w.img + (int64_t)w.x_image * w.img_elems,
-                            S[0], nullptr, nullptr, tiles, st);
+                            S[0], nullptr, nullptr, tiles, st, Xlo, Slo[0]);
     } else {
       rc = first_layer(d, params, coords ? coords + r0 * lay.in : nullptr, rows, rows_pad, i0 + r0, T_total, scale, S[0],
-                       nullptr, st);
+                       nullptr, st, nullptr, Slo[0]);
     }
     if (rc) return rc;
     int cur = 0;
     for (int l = 1; l <= L; ++l) {
-      if ((rc = fwd_layer_tc(d, lay, params, w, l, S[cur], S[cur ^ 1], nullptr, nullptr, tiles, st))) return rc;
+      if ((rc = fwd_layer_tc(d, lay, params, w, l, S[cur], S[cur ^ 1], nullptr, nullptr, tiles, st, Slo[cur], Slo[cur ^ 1])))
+        return rc;
       cur ^= 1;
     }
     if ((rc = last_layer(d, params, S[cur], nullptr, nullptr, nullptr, rows, tiles, 0, 0.f, nullptr, nullptr, nullptr,
-                         out + r0, 0, st)))
+                         out + r0, 0, st, nullptr, Slo[cur])))
       return rc;
   }
   return INR_OK;
@@ -880,6 +946,9 @@ int siren_tc_train(const inr_siren_desc* d, const float* params, const float* co
     auto E = [&](int l) -> op16* {
       return lay.kind(l) == ACT_SNAKE ? w.img + (int64_t)(2 * (L + 1) + lay.snakes_before(l)) * w.img_elems : nullptr;
     };
+    // operand split: S_l's lo image is read by the forward of layer l+1 (and by the head for l = L) only: two ping-pong
+    auto Slo = [&](int l) -> op16* { return w.split ? w.img + (int64_t)(w.lo_image + (l & 1)) * w.img_elems : nullptr; };
+    op16* Xlo = w.xlo_image >= 0 ? w.img + (int64_t)w.xlo_image * w.img_elems : nullptr;
     const float* xc = coords ? coords + r0 * lay.in : nullptr;
     bool fused_tail = false;
     if (phase & 1) {
@@ -898,24 +967,24 @@ int siren_tc_train(const inr_siren_desc* d, const float* params, const float* co
       } else {
         if (w.x_image >= 0) {
           rc = first_layer_wide(d, lay, params, w, xc, rows, rows_pad, w.img + (int64_t)w.x_image * w.img_elems, S(0), C(0),
-                                E(0), tiles, st);
+                                E(0), tiles, st, Xlo, Slo(0));
         } else {
-          rc = first_layer(d, params, xc, rows, rows_pad, i0 + r0, T_total, scale, S(0), C(0), st, E(0));
+          rc = first_layer(d, params, xc, rows, rows_pad, i0 + r0, T_total, scale, S(0), C(0), st, E(0), Slo(0));
         }
         if (rc) return rc;
         for (int l = 1; l <= L; ++l)
-          if ((rc = fwd_layer_tc(d, lay, params, w, l, S(l - 1), S(l), C(l), E(l), tiles, st))) return rc;
+          if ((rc = fwd_layer_tc(d, lay, params, w, l, S(l - 1), S(l), C(l), E(l), tiles, st, Slo(l - 1), Slo(l)))) return rc;
       }
       if (phase == 1) {
         if ((rc = last_layer(d, params, S(L), nullptr, nullptr, nullptr, rows, tiles, 0, 0.f, nullptr, nullptr, nullptr,
-                             out + r0, 0, st)))
+                             out + r0, 0, st, nullptr, Slo(L))))
           return rc;
         continue;
       }
     }
     if (!fused_tail &&
         (rc = last_layer(d, params, S(L), C(L), target ? target + r0 : nullptr, extra_gout ? extra_gout + r0 : nullptr, rows,
-                         tiles, loss_kind, grad_scale, w.gsc, grads, opt, out ? out + r0 : nullptr, 1, st, E(L))))
+                         tiles, loss_kind, grad_scale, w.gsc, grads, opt, out ? out + r0 : nullptr, 1, st, E(L), Slo(L))))
       return rc;
     for (int l = L; l >= 1; --l) {
       DwParams dp;

@@ -216,6 +216,12 @@ __device__ __forceinline__ uint32_t pack_op2(float lo, float hi) {
   return r;
 }
 __device__ __forceinline__ float2 unpack_op2(uint32_t u) { return __half22float2(*reinterpret_cast<__half2*>(&u)); }
+// hi + lo split of two fp32 values: hi = fp16(x), lo = fp16(x - hi) (the subtraction is exact in fp32)
+__device__ __forceinline__ void pack_op2_split(float a, float b, uint32_t* hi, uint32_t* lo) {
+  *hi = pack_op2(a, b);
+  const float2 h = unpack_op2(*hi);
+  *lo = pack_op2(a - h.x, b - h.y);
+}
 __device__ __forceinline__ op16 to_op(float v) {
   uint16_t r;
   asm("cvt.rn.satfinite.f16.f32 %0, %1;" : "=h"(r) : "f"(v));

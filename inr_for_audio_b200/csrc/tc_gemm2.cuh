@@ -24,18 +24,25 @@
 namespace inr {
 namespace tc {
 
-template <int H>
+// SPLIT (INR_PREC_FP16S, forward modes only): both operands are fp16 hi + lo pairs (x = hi + lo, lo = fp16(x - hi):
+// 22 significant bits) and every K step issues THREE MMAs into the same accumulator, hi*hi + lo*hi + hi*lo -- fp32-grade
+// products (the lo*lo term is below 2^-22).  The weight slice keeps hi and lo resident, so a pair covers half as many
+// output features at H = 512; a ring stage carries the hi and the lo chunk of the A rows (two 16 KB copies issued by
+// two lanes: one thread sustains only ~1 bulk copy per 0.32 us).
+template <int H, bool SPLIT = false>
 struct Layer2Cfg {
-  static constexpr int NP = (H >= 256) ? 256 : H;   // output features per pair (MMA N)
+  static constexpr int NP = SPLIT ? ((H >= 512) ? 128 : H) : ((H >= 256) ? 256 : H);   // output features per pair (MMA N)
   static constexpr int NC = NP / 2;                 // B columns staged by each CTA
   static constexpr int NQ = H / NP;                 // N slices
   // One thread sustains ~1 cp.async.bulk per 0.32 us whatever its size (profiles/r01_bulk_probe_*.csv): 16 KB copies
   // cap a CTA at ~51 GB/s, below the ~60 GB/s the MMA consumes; 32 KB copies (128 K columns) lift the cap to ~100 GB/s.
-  static constexpr int KC = 128;                    // K columns per ring stage
+  static constexpr int KC = SPLIT ? 64 : 128;       // K columns per ring stage
   static constexpr int NCHUNK = H / KC;
-  static constexpr int B_BYTES = H * NC * 2;        // 128 KB (H=512), 64 KB (256), 16 KB (128)
-  static constexpr int A_STAGE_BYTES = (KC / 8) * TILE_ROWS * 16;  // 32 KB
-  static constexpr int STAGES = (H >= 512) ? 3 : 4; // 96 KB / 128 KB in flight
+  static constexpr int B_HALF = H * NC * 2;         // one (hi or lo) weight slice half
+  static constexpr int B_BYTES = B_HALF * (SPLIT ? 2 : 1);   // 128 KB (H=512; split H>=256), 64 KB (256), 16 KB (128)
+  static constexpr int A_HALF = (KC / 8) * TILE_ROWS * 16;   // one (hi or lo) A chunk: 32 KB, split 16 KB
+  static constexpr int A_STAGE_BYTES = A_HALF * (SPLIT ? 2 : 1);  // 32 KB
+  static constexpr int STAGES = (B_BYTES >= 131072) ? 3 : 4; // 96 KB / 128 KB in flight
   static constexpr int TMEM_COLS = 2 * NP;          // two accumulator buffers
   static constexpr int OFF_A = B_BYTES;
   static constexpr int OFF_BIAS = OFF_A + STAGES * A_STAGE_BYTES;
@@ -43,13 +50,15 @@ struct Layer2Cfg {
   static constexpr int OFF_BAR = OFF_AVEC + NP * 4;
   static constexpr int SMEM_BYTES = OFF_BAR + 256;
   static constexpr int THREADS = 320;
+  static constexpr int PF_DT = 3;                   // split: double tiles of L2 prefetch distance
   static_assert(H == 128 || H == 256 || H == 512, "hidden width");
   static_assert(SMEM_BYTES <= 232448, "shared-memory budget");
 };
 
-template <int H, int MODE>
-__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(Layer2Cfg<H>::THREADS, 1) k_tc_layer2(const LayerParams p) {
-  using Cfg = Layer2Cfg<H>;
+template <int H, int MODE, bool SPLIT = false>
+__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(Layer2Cfg<H, SPLIT>::THREADS, 1) k_tc_layer2(const LayerParams p) {
+  using Cfg = Layer2Cfg<H, SPLIT>;
+  static_assert(!SPLIT || mode_is_fwd(MODE), "operand split: forward modes only");
   constexpr int NP = Cfg::NP;
   constexpr int NC = Cfg::NC;
   extern __shared__ __align__(128) uint8_t smem[];
@@ -103,24 +112,34 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(Layer2Cfg<H>::THREAD
   if (warp == 0) {
     // ===================== producer: own half of the weight slice once, then own A rows through the ring =========
     if (lane == 0) {
+      // packed weights: [slice = q*2 + rank][hi | lo (split)][H/8][NC][8]
       mbar_arrive_expect_tx(bar_bfull, Cfg::B_BYTES);
       const uint8_t* bsrc = reinterpret_cast<const uint8_t*>(p.Bpack) + (size_t)(q * 2 + rank) * Cfg::B_BYTES;
       constexpr int BPIECE = Cfg::B_BYTES < 32768 ? Cfg::B_BYTES : 32768;
       for (int off = 0; off < Cfg::B_BYTES; off += BPIECE) bulk_g2s(sB + off, bsrc + off, BPIECE, bar_bfull);
+    }
+    if (lane < (SPLIT ? 2 : 1)) {                     // split: lane 0 copies the hi chunk, lane 1 the lo chunk
       int s = 0;
       uint32_t phase = 0;
+      const op16* abase = (SPLIT && lane == 1) ? p.A_lo : p.A;
       for (int dt = dt0; dt < num_dt; dt += dt_stride) {
         const int tile = 2 * dt + (int)rank;
         const bool valid = tile < p.num_tiles;
-        const uint8_t* asrc = reinterpret_cast<const uint8_t*>(p.A) + (size_t)tile * (TILE_ROWS * H * 2);
+        const uint8_t* asrc = reinterpret_cast<const uint8_t*>(abase) + (size_t)tile * (TILE_ROWS * H * 2);
+        // the NQ pairs that share this row tile pull it into L2 a few tiles ahead, a chunk each, so the ring's copies see
+        // L2-hit latency: 96 KB in flight per SM cannot cover DRAM latency at the rate three MMAs per K step consume
+        const int pf_tile = tile + 2 * Cfg::PF_DT * dt_stride;
+        const uint8_t* pfsrc = reinterpret_cast<const uint8_t*>(abase) + (size_t)pf_tile * (TILE_ROWS * H * 2);
         for (int c = 0; c < Cfg::NCHUNK; ++c) {
+          if (SPLIT && pf_tile < p.num_tiles && (c % Cfg::NQ) == q)
+            bulk_prefetch_l2(pfsrc + (size_t)c * Cfg::A_HALF, Cfg::A_HALF);
           mbar_wait(bar_empty(s), phase ^ 1);
-          if (valid) {
-            mbar_arrive_expect_tx(bar_full(s), Cfg::A_STAGE_BYTES);
-            bulk_g2s(sA + s * Cfg::A_STAGE_BYTES, asrc + (size_t)c * Cfg::A_STAGE_BYTES, Cfg::A_STAGE_BYTES, bar_full(s));
-          } else {
-            mbar_arrive(bar_full(s));                 // odd tile count: the MMA multiplies stale rows, nobody stores them
+          if (lane == 0) {
+            if (valid) mbar_arrive_expect_tx(bar_full(s), Cfg::A_STAGE_BYTES);
+            else mbar_arrive(bar_full(s));            // odd tile count: the MMA multiplies stale rows, nobody stores them
           }
+          if (valid)
+            bulk_g2s(sA + s * Cfg::A_STAGE_BYTES + lane * Cfg::A_HALF, asrc + (size_t)c * Cfg::A_HALF, Cfg::A_HALF, bar_full(s));
           if (++s == Cfg::STAGES) { s = 0; phase ^= 1; }
         }
       }
@@ -144,9 +163,19 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(Layer2Cfg<H>::THREAD
             tc_fence_after();
 #pragma unroll
             for (int kk = 0; kk < Cfg::KC / 16; ++kk) {
-              const uint64_t ad = make_smem_desc(sA + s * Cfg::A_STAGE_BYTES + kk * 2 * (TILE_ROWS * 16), p.a_lbo, p.a_sbo);
-              const uint64_t bd = make_smem_desc(sB + (c * (Cfg::KC / 8) + kk * 2) * (NC * 16), p.b_lbo, p.b_sbo);
-              umma2_f16(d_tmem, ad, bd, idesc, (c | kk) != 0 ? 1u : 0u);
+              const uint32_t a_addr = sA + s * Cfg::A_STAGE_BYTES + kk * 2 * (TILE_ROWS * 16);
+              const uint32_t b_addr = sB + (c * (Cfg::KC / 8) + kk * 2) * (NC * 16);
+              const uint64_t ad = make_smem_desc(a_addr, p.a_lbo, p.a_sbo);
+              const uint64_t bd = make_smem_desc(b_addr, p.b_lbo, p.b_sbo);
+              if (SPLIT) {   // small terms first: lo*hi + hi*lo, then hi*hi
+                const uint64_t adl = make_smem_desc(a_addr + Cfg::A_HALF, p.a_lbo, p.a_sbo);
+                const uint64_t bdl = make_smem_desc(b_addr + Cfg::B_HALF, p.b_lbo, p.b_sbo);
+                umma2_f16(d_tmem, adl, bd, idesc, (c | kk) != 0 ? 1u : 0u);
+                umma2_f16(d_tmem, ad, bdl, idesc, 1u);
+                umma2_f16(d_tmem, ad, bd, idesc, 1u);
+              } else {
+                umma2_f16(d_tmem, ad, bd, idesc, (c | kk) != 0 ? 1u : 0u);
+              }
             }
             umma2_commit_mc(bar_empty(s), 3);
             if (++s == Cfg::STAGES) { s = 0; phase ^= 1; }
@@ -205,7 +234,7 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(Layer2Cfg<H>::THREAD
           tmem_ld_wait();
 #pragma unroll
           for (int j = 0; j < 4; ++j) {
-            uint32_t o0[4], o1[4];
+            uint32_t o0[4], o1[4], ol[4];
             const size_t off = tile_off + ((size_t)(g0 + j) * TILE_ROWS + row) * 8;
             if (MODE == MODE_FWD_SNAKE || MODE == MODE_FWD_TANH) {
               uint32_t o2[4];
@@ -232,11 +261,13 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(Layer2Cfg<H>::THREAD
                     da[u] = 0.f;
                   }
                 }
-                o0[h] = pack_op2(y[0], y[1]);
+                if (SPLIT) pack_op2_split(y[0], y[1], &o0[h], &ol[h]);
+                else o0[h] = pack_op2(y[0], y[1]);
                 o1[h] = pack_op2(dz[0], dz[1]);
                 o2[h] = pack_op2(da[0], da[1]);
               }
               *reinterpret_cast<uint4*>(p.out0 + off) = make_uint4(o0[0], o0[1], o0[2], o0[3]);
+              if (SPLIT) *reinterpret_cast<uint4*>(p.out0_lo + off) = make_uint4(ol[0], ol[1], ol[2], ol[3]);
               if (p.out1) *reinterpret_cast<uint4*>(p.out1 + off) = make_uint4(o1[0], o1[1], o1[2], o1[3]);
               if (MODE == MODE_FWD_SNAKE && p.out2) *reinterpret_cast<uint4*>(p.out2 + off) = make_uint4(o2[0], o2[1], o2[2], o2[3]);
             } else if (MODE == MODE_FWD) {
@@ -248,10 +279,12 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(Layer2Cfg<H>::THREAD
                 float s0, c0, s1, c1;
                 __sincosf(t0, &s0, &c0);
                 __sincosf(t1, &s1, &c1);
-                o0[h] = pack_op2(s0, s1);
+                if (SPLIT) pack_op2_split(s0, s1, &o0[h], &ol[h]);
+                else o0[h] = pack_op2(s0, s1);
                 o1[h] = pack_op2(c0, c1);
               }
               *reinterpret_cast<uint4*>(p.out0 + off) = make_uint4(o0[0], o0[1], o0[2], o0[3]);
+              if (SPLIT) *reinterpret_cast<uint4*>(p.out0_lo + off) = make_uint4(ol[0], ol[1], ol[2], ol[3]);
               if (p.out1) *reinterpret_cast<uint4*>(p.out1 + off) = make_uint4(o1[0], o1[1], o1[2], o1[3]);
             } else {
               const uint32_t cw[4] = {cin[ci][j].x, cin[ci][j].y, cin[ci][j].z, cin[ci][j].w};

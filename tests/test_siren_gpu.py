@@ -235,10 +235,12 @@ def test_ragged_and_tiny_sizes(pkg, golden):
 
 
 # ------------------------------------------------------------------------------------------------ fp16 tcgen05 mode
-@pytest.mark.parametrize("H,Lh,n", [(128, 2, 4099), (256, 3, 20000), (512, 2, 3000), (128, 1, 1)])
-def test_fp16_mode_against_oracle(pkg, H, Lh, n):
+@pytest.mark.parametrize("prec", ["fp16", "fp16s"])
+@pytest.mark.parametrize("H,Lh,n", [(128, 2, 4099), (256, 3, 20000), (512, 2, 3000), (512, 5, 40000), (128, 1, 1)])
+def test_fp16_mode_against_oracle(pkg, H, Lh, n, prec):
     """fp16 operands / fp32 accumulation on the tensor cores: loss within 1e-3 relative (north star), gradients
-    within fp16 rounding noise of the fp32 oracle."""
+    within fp16 rounding noise of the fp32 oracle.  'fp16s' (forward operands as fp16 hi + lo pairs, three MMAs per K
+    step) has an fp32-grade forward: output and loss at the fp32 mode's own level; its backward is the fp16 one."""
     from oracle import inr_oracle as O
     spec = pkg.SirenSpec(1, H, Lh, 1, True)
     ospec = O.SirenSpec(1, H, Lh, 1, True)
@@ -247,14 +249,17 @@ def test_fp16_mode_against_oracle(pkg, H, Lh, n):
     gt = torch.from_numpy(pkg.utils.synth_waveform(max(n, 2), seed=3)[:n].copy())
     coords = O.get_coord(n, 1).view(-1, 1)
     loss_o, _, grads_o, out_o = O.siren_loss_and_grads(ospec, ps, coords, gt.view(-1, 1))
-    f = pkg.SirenFitter(spec, flat, gt.to(dev()), precision="fp16", use_graph=False)
+    f = pkg.SirenFitter(spec, flat, gt.to(dev()), precision=prec, use_graph=False)
     loss, grads, out = f.loss_and_grads()
-    assert abs(loss - float(loss_o)) <= 1e-3 * abs(float(loss_o)) + 1e-9, (loss, float(loss_o))
-    assert float(np.abs(out.cpu().numpy() - out_o.numpy().ravel()).max()) <= 2e-2
+    oerr = float(np.abs(out.cpu().numpy() - out_o.numpy().ravel()).max())
     go = torch.cat([x.reshape(-1) for x in grads_o]).numpy().astype(np.float64)
     gerr = np.linalg.norm(grads.cpu().numpy() - go) / np.linalg.norm(go)
-    print("fp16 H=%d L=%d n=%d: loss rel err %.2e, grad rel err %.2e" % (H, Lh, n, abs(loss - float(loss_o)) / float(loss_o), gerr))
-    assert gerr <= (5e-2 if n > 1 else 0.2)
+    print("%s H=%d L=%d n=%d: loss rel err %.2e, out max err %.2e, grad rel err %.2e" % (
+        prec, H, Lh, n, abs(loss - float(loss_o)) / float(loss_o), oerr, gerr))
+    ltol, otol = (1e-3, 2e-3) if prec == "fp16" else (2e-5, 2e-5)
+    assert abs(loss - float(loss_o)) <= ltol * abs(float(loss_o)) + 1e-9, (loss, float(loss_o))
+    assert oerr <= otol
+    assert gerr <= (5e-3 if n > 1 else 2e-2)
     assert torch.equal(f.forward(), f.forward())
     np.testing.assert_allclose(f.forward().cpu().numpy(), out.cpu().numpy(), atol=1e-6)
 
