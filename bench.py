@@ -1,13 +1,18 @@
 #!/usr/bin/env python
 """bench.py -- coord-samples/sec of the SIREN fit step (fwd + loss + bwd + Adam [+ allreduce]).
 
-    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference] [--workload c2|c1|c5clip]
-                    [--precision fp16|fp32]   (KAN: bf16|fp32)
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference] [--workload c2|c1|c3|c3stft|c4|c5|...]
+                    [--precision fp16s|fp16|fp32] [--extras auto|none] [--snr-steps 1000]
 
 N > 1 is launched by the driver under torch.distributed.run (one rank per GPU, NCCL); the coordinates of the ONE
 waveform are sharded by rank and every step has one sum-allreduce of [grads | loss]  => "scaling": "strong".
-Prints ONE JSON line (rank 0).  See the task contract for the keys; additions: roofline, cpu_baseline, e2e,
-gpu_launches, clocks, kernels (per-kernel ms/step from the event profiler of libinr_b200).
+Prints ONE JSON line (rank 0).  The headline (value, e2e, roofline) is BASELINE.json configs[1] (C2) in the
+parity-grade tensor-core mode (fp16s: fp16 hi+lo forward operands, fp32-grade forward; 36.8 dB at 20 000 C1 steps where
+the reference loop reaches 36.0).  Beside it, in the same line:
+  fast_mode   the same workload in the plain fp16 mode (one MMA per K step; fit floor ~31 dB on C1)
+  snr         SNR dB at fixed steps of this very fit (the metric's second half), with the oracle loop's figure
+  workloads   the other BASELINE.json configs: c1 (gt_bach.wav), c3 (MDCT loss), c3stft, c4 (KAN), c5 (clip-parallel)
+  roofline, hbm_stages, cpu_baseline, e2e, gpu_launches, clocks, kernels (per-kernel ms/step, library event profiler)
 """
 import argparse
 import json
@@ -27,9 +32,9 @@ WORKLOADS = {
     # BASELINE.json configs[1]: SIREN 5x512 on a synthetic 60 s 44.1 kHz waveform -- the config the metric is quoted on
     "c2": dict(kind="siren", T=2646000, H=512, L=5, seed=0,
                desc="SIREN 5x512, synthetic 60 s @ 44.1 kHz (T=2646000), mse, Adam lr 1e-3"),
-    # configs[0] model shape on a synthetic clip of gt_bach's length (parity case; not a bench line by default)
-    "c1": dict(kind="siren", T=264600, H=256, L=3, seed=0,
-               desc="SIREN 3x256, synthetic 6 s @ 44.1 kHz (T=264600), mse, Adam lr 1e-3"),
+    # configs[0]: the reference's own CPU-runnable case, on the real file
+    "c1": dict(kind="siren", T=264600, H=256, L=3, seed=0, wav="gt_bach.wav",
+               desc="SIREN 3x256 (omega 30) on data/gt_bach.wav, 6 s (T=264600), mse, Adam lr 1e-3"),
     # run.py:30's DEFAULT architecture (num_sine=2, num_snake=2, a_initial=0.5) on the C1-sized clip: Snake layers in
     # the tcgen05 mode (informational, not a BASELINE.json config)
     "c1snake": dict(kind="siren", T=264600, H=256, L=2, nk=2, seed=0,
@@ -63,6 +68,9 @@ def parse_args():
     ap.add_argument("--no-sm-partition", action="store_true", help="clip-parallel: every kernel sized for the whole GPU")
     ap.add_argument("--precision", default=os.environ.get("INR_BENCH_PRECISION", "auto"))
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--extras", default="auto", choices=["auto", "none"],
+                    help="auto: with the default workload also time fast_mode and the other BASELINE.json configs")
+    ap.add_argument("--snr-steps", type=int, default=1000, help="SNR of the headline fit after this many steps (0 = skip)")
     ap.add_argument("--cpu-budget-s", type=float, default=20.0)
     return ap.parse_args()
 
@@ -131,6 +139,20 @@ class ClockSampler:
                 "samples": len(sm), "reasons": sorted(reasons)}
 
 
+def load_target(wl):
+    """the workload's target signal (whole job, float32, peak-normalised as utils.py:146-147 does)"""
+    from inr_for_audio_b200.utils import synth_waveform, WaveformFitting
+    if wl.get("wav"):
+        return WaveformFitting(os.path.join(ROOT, "data", wl["wav"]), duration=6, verbose=False).normalised()[:wl["T"]]
+    return synth_waveform(wl["T"], seed=wl["seed"])
+
+
+def config_of(wl):
+    """identical in both arms: names the workload, nothing arm-specific"""
+    return {"workload": wl["desc"], "coordinates_per_step": int(wl["T"] * wl.get("clips", 1)),
+            "l2": "working set (activation workspace, GBs) >> 126 MB L2; no flush needed"}
+
+
 # ------------------------------------------------------------------------------------------------- reference arm
 def oracle_fit_rate(wl, rows, steps, warmup, threads):
     """The reference's own algorithm for the path on the host cores: oracle/inr_oracle.py (a line-for-line
@@ -141,7 +163,7 @@ def oracle_fit_rate(wl, rows, steps, warmup, threads):
     from oracle import inr_oracle as O
     from inr_for_audio_b200.utils import synth_waveform
     torch.set_num_threads(threads)
-    gt_full = synth_waveform(wl["T"], seed=wl["seed"])
+    gt_full = load_target(wl)
     coords = O.get_coord(wl["T"], 1)[:rows].view(1, -1, 1)
     gt = torch.from_numpy(gt_full[:rows]).view(1, -1, 1)
     if wl["kind"] == "kan":
@@ -202,7 +224,8 @@ def run_reference(args, wl):
     line = {"impl": "reference", "metric": METRIC, "value": rate, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
             "warmup": args.warmup, "ms_per_step": per * 1e3, "higher_is_better": True, "scaling": "strong",
             "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-            "config": {"workload": wl["desc"], "note": "CPU reference arm: oracle port of run.py's loop on host cores"},
+            "config": config_of(wl),
+            "note": "CPU reference arm: oracle port of run.py's loop (run.py:156-190, pinned against the reference) on host cores",
             "cpu_baseline": {"value": rate, "unit": UNIT, "cores": threads, "kind": "port", "sample": sample},
             "e2e": {"value": rate, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
     print(json.dumps(line), flush=True)
@@ -232,19 +255,22 @@ class Job:
             self.flat0 = torch.stack(flats)
             self.host_target = torch.from_numpy(gts).pin_memory()
             self.flops_per_coord = 6.0 * wl["L"] * wl["H"] ** 2
+            self.fwd_share = 1.0 / 3.0
         else:
             # contiguous shard per rank, rounded to the 128-row tile
             from inr_for_audio_b200.engine import shard_range
             self.i0, self.n_local, self.shard = shard_range(T, rank, world)
             self.units_total = T
-            gt_np = P.utils.synth_waveform(T, seed=wl["seed"])
-            self.host_target = torch.from_numpy(gt_np[self.i0:self.i0 + self.n_local]).pin_memory()
+            gt_np = load_target(wl)
+            self.gt_np = gt_np
+            self.host_target = torch.from_numpy(gt_np[self.i0:self.i0 + self.n_local].copy()).pin_memory()
             self.full_target = torch.from_numpy(gt_np).to(dev) if wl.get("spectral") else None
             torch.manual_seed(wl["seed"])
             if self.kind == "kan":
                 self.model = P.KAN(wl["widths"])
                 self.spec = self.model.spec
                 self.flops_per_coord = 3566592.0        # dense-equivalent fwd+bwd flops per coordinate
+                self.fwd_share = 1.0 / 3.0
             else:
                 if wl.get("nk") or wl.get("nt"):
                     self.model = P.SirenWithSnakeTanh(1, 1, wl["H"], wl["L"], wl.get("nk", 0), wl.get("nt", 0),
@@ -253,7 +279,12 @@ class Job:
                     self.model = P.Siren(1, wl["H"], wl["L"], 1, True)
                 self.spec = self.model.spec
                 self.flops_per_coord = 6.0 * self.spec.total_hidden * wl["H"] ** 2
+                self.fwd_share = 1.0 / 3.0
         self.target = self.host_target.to(dev, non_blocking=True)
+
+    def issued_factor(self):
+        """MMA flops issued per algorithmic flop: the fp16s mode runs three MMAs per K step in the forward GEMMs."""
+        return 1.0 + 2.0 * self.fwd_share if self.prec == "fp16s" else 1.0
 
     def make(self, use_graph):
         P, wl = self.P, self.wl
@@ -287,132 +318,154 @@ class Job:
             ls = ls.mean(axis=0)
         return [float(ls[0]), float(ls[-1])] if len(ls) else None
 
+    def snr_db(self, fit):
+        """utils.py:77-97 calculate_snr(target, model(coords)) over the WHOLE job (shards: power sums allreduced)."""
+        torch = self.torch
+        if self.kind == "clips":
+            return float(np.median(fit.snr_db(self.target)))
+        y = fit.forward().double()
+        t = fit.target.double()
+        sums = torch.stack([(t * t).sum(), ((y - t) ** 2).sum()])
+        if self.world > 1:
+            torch.distributed.all_reduce(sums, group=self.pg)
+        s = sums.cpu().numpy()
+        return float(10.0 * np.log10(s[0] / s[1]))
 
-def run_ours(args, wl):
-    import torch
-    import torch.distributed as dist
-    import inr_for_audio_b200 as P
-    from inr_for_audio_b200 import _lib as L
 
-    world = int(os.environ.get("WORLD_SIZE", "1"))
-    rank = int(os.environ.get("RANK", "0"))
-    local = int(os.environ.get("LOCAL_RANK", "0"))
-    assert torch.cuda.is_available(), "bench.py needs a CUDA device (no CPU fallback)"
-    torch.cuda.set_device(local)
-    dev = torch.device("cuda", local)
-    pg = None
-    if world > 1:
-        dist.init_process_group("nccl", device_id=dev)
-        pg = dist.group.WORLD
+class Ctx:
+    def __init__(self, args):
+        import torch
+        import torch.distributed as dist
+        self.torch, self.dist, self.args = torch, dist, args
+        self.world = int(os.environ.get("WORLD_SIZE", "1"))
+        self.rank = int(os.environ.get("RANK", "0"))
+        self.local = int(os.environ.get("LOCAL_RANK", "0"))
+        assert torch.cuda.is_available(), "bench.py needs a CUDA device (no CPU fallback)"
+        torch.cuda.set_device(self.local)
+        self.dev = torch.device("cuda", self.local)
+        self.pg = None
+        if self.world > 1:
+            dist.init_process_group("nccl", device_id=self.dev)
+            self.pg = dist.group.WORLD
 
-    prec = args.precision
-    if wl["kind"] == "kan":
-        prec = "bf16" if prec == "auto" else prec
-    elif prec == "auto":
-        try:
-            L.check(L.lib().inr_siren_workspace_bytes(P.SirenSpec(1, wl["H"], wl["L"], 1, True).desc("fp16"), 1024, 1))
-            prec = "fp16"
-        except L.InrLibraryError:
-            prec = "fp32"
-    job = Job(args, wl, rank, world, dev, pg, prec)
-    units = job.units_total                                   # coordinate-samples one whole-job step processes
+    def barrier(self):
+        if self.world > 1:
+            self.dist.barrier()
+        self.torch.cuda.synchronize(self.dev)
 
-    def barrier():
-        if world > 1:
-            dist.barrier()
-        torch.cuda.synchronize(dev)
+    def max_over_ranks(self, x):
+        t = self.torch.tensor([x], device=self.dev, dtype=self.torch.float64)
+        if self.world > 1:
+            self.dist.all_reduce(t, op=self.dist.ReduceOp.MAX)
+        return float(t.item())
 
-    def timed(fn, k):
-        barrier()
+    def timed_device(self, fn, k):
+        """K steps between two CUDA events on the launching stream, barrier + synchronize on both sides, max over ranks"""
+        torch = self.torch
+        self.barrier()
         e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         e0.record()
         fn(k)
         e1.record()
-        barrier()
-        ms = torch.tensor([e0.elapsed_time(e1)], device=dev, dtype=torch.float64)
-        if world > 1:
-            dist.all_reduce(ms, op=dist.ReduceOp.MAX)
-        return float(ms.item())
+        self.barrier()
+        return self.max_over_ranks(e0.elapsed_time(e1))
 
-    # ---- device-resident throughput ("value")
+
+def measure(cx, name, prec, steps, warmup, detail):
+    """One workload in one arithmetic mode: device-resident throughput, the end-to-end number through the public API
+    with host buffers, launches, and (detail) the per-kernel profile with the roofline records."""
+    import inr_for_audio_b200 as P
+    from inr_for_audio_b200 import _lib as L
+    torch, args = cx.torch, cx.args
+    wl = WORKLOADS[name]
+    job = Job(args, wl, cx.rank, cx.world, cx.dev, cx.pg, prec)
+    units = job.units_total
+    pk = peaks()
     fit = job.make(True)
-    fit.step(args.warmup)
-    sampler = ClockSampler(local)
-    if rank == 0:
+    fit.step(warmup)
+    sampler = ClockSampler(cx.local)
+    if cx.rank == 0:
         sampler.start()
-    ms = timed(fit.step, args.steps)
-    clocks = sampler.stop() if rank == 0 else None
-    value = units * args.steps / (ms * 1e-3)
-    first_last = job.first_last_loss(fit)
+    ms = cx.timed_device(fit.step, steps)
+    clocks = sampler.stop() if cx.rank == 0 else None
+    rec = {"workload": wl["desc"], "precision": prec, "value": units * steps / (ms * 1e-3), "unit": UNIT,
+           "ms_per_step": ms / steps, "steps": steps, "clocks": clocks, "cuda_graph": bool(fit._graph is not None)}
+    rec["loss_first_last"] = job.first_last_loss(fit)
+    lps = fit.launches_per_step
 
-    # ---- end to end through the public API with HOST buffers: H2D of the step's targets, D2H of its loss
+    # ---- end to end through the public API with HOST buffers: H2D of the step's targets, D2H of its loss -- timed right
+    #      after the device-resident block (same clocks), then the device-resident block once more as a drift check
     def e2e_steps(k):
         for _ in range(k):
             job.h2d(fit)
             fit.step(1)
             _ = job.d2h_loss(fit)
     e2e_steps(1)
-    barrier()
+    cx.barrier()
     t0 = time.perf_counter()
-    e2e_steps(args.steps)
-    barrier()
-    dt = torch.tensor([time.perf_counter() - t0], device=dev, dtype=torch.float64)
-    if world > 1:
-        dist.all_reduce(dt, op=dist.ReduceOp.MAX)
-    e2e = {"value": units * args.steps / float(dt.item()), "unit": UNIT,
-           "h2d_bytes_per_step": int(job.host_target.numel() * 4), "d2h_bytes_per_step": 4}
-    del fit
-    torch.cuda.empty_cache()
+    e2e_steps(steps)
+    cx.barrier()
+    dt = cx.max_over_ranks(time.perf_counter() - t0)
+    rec["e2e"] = {"value": units * steps / dt, "unit": UNIT, "h2d_bytes_per_step": int(job.host_target.numel() * 4),
+                  "d2h_bytes_per_step": 4}
+    ms2 = cx.timed_device(fit.step, steps)
+    rec["value_recheck"] = units * steps / (ms2 * 1e-3)
+    rec["launches_per_step"] = lps
+    useful = job.flops_per_coord * units / (ms / steps * 1e-3) / 1e12 / max(cx.world, 1)     # per GPU, whole step
+    rec["step_tflops_per_gpu"] = useful
+    rec["step_frac_of_peak"] = useful / pk["bf16_sus"]
+    rec["step_frac_issued"] = useful * job.issued_factor() / pk["bf16_sus"]
+    return rec, job, fit
 
-    # ---- launches per step and per-kernel device time (un-graphed pass: graph replays bypass the library's counter
-    #      and its event profiler); clip-parallel profiles a 8-clip subset on one stream and scales the launch count
+
+def kernel_profile(cx, job, prec, steps):
+    """Per-kernel device time of an UN-graphed pass (graph replays bypass the library's event profiler), the roofline of
+    the tensor-core kernels and the HBM-bound stages.  Clip-parallel profiles an 8-clip subset on one stream."""
+    import inr_for_audio_b200 as P
+    from inr_for_audio_b200 import _lib as L
+    torch, wl = cx.torch, job.wl
+    pk = peaks()
     if job.kind == "clips":
         sub = P.ClipBatchFitter(job.spec, job.flat0[:8], job.target[:8], precision=prec, n_streams=1, use_graph=False, hist_cap=16)
-        scale_launch = job.flat0.shape[0] / 8.0
         prof_units = 8 * wl["T"]
     else:
         sub = job.make(False)
-        scale_launch = 1.0
         prof_units = job.n_local
     sub.step(2)
-    torch.cuda.synchronize(dev)
-    lc0 = L.lib().inr_launch_count()
-    sub.step(1)
-    launches_per_step = int(round((L.lib().inr_launch_count() - lc0) * scale_launch))
-    prof_steps = max(1, min(args.steps, 5))
-    barrier()
+    prof_steps = max(1, min(steps, 5))
+    cx.barrier()
     L.profile_begin()
     sub.step(prof_steps)
     prof = L.profile_end()
     kern = {tag: {"launches_per_step": cnt / prof_steps, "ms_per_step": tot / prof_steps} for tag, (cnt, tot) in prof.items()}
-    gemm_tags = [t for t in kern if ("sgemm" in t or t.startswith("k_tc_") or t.startswith("k_kan_tc_") or t.startswith("k_kan_thin"))]
+    gemm_tags = [t for t in kern if t in ("k_tc_layer_fwd", "k_tc_layer_bwd", "k_tc_dw", "k_tc_fused_fwd", "k_sgemm") or
+                 "sgemm" in t or t.startswith("k_kan_tc_") or t.startswith("k_kan_thin")]
     gemm_ms = sum(kern[t]["ms_per_step"] for t in gemm_tags)
     gemm_launches = sum(kern[t]["launches_per_step"] for t in gemm_tags)
-    prof_total_ms = sum(v["ms_per_step"] for v in kern.values())
-    pk = peaks()
-    flops = job.flops_per_coord * prof_units              # dense contraction flops of the profiled rows, fwd + bwd
+    total_ms = sum(v["ms_per_step"] for v in kern.values())
+    flops = job.flops_per_coord * prof_units              # algorithmic dense-contraction flops of the profiled rows
     achieved = flops / (gemm_ms * 1e-3) / 1e12 if gemm_ms > 0 else 0.0
-    # DRAM bytes per launch (dram__bytes_read.sum + dram__bytes_write.sum) of the GEMM kernels from the committed
-    # `ncu --set full` capture of this workload (profiles/r01e_traffic.json <- tools/ncu_summary.py), averaged over the
-    # launches of one step; null for workloads without a capture.
-    traffic = None
-    if args.workload == "c2" and prec == "fp16" and world == 1:
+    traffic, tnote = None, None
+    tfile = os.path.join(ROOT, "profiles", "r02_traffic_%s_%s.json" % (cx.args.workload, prec))
+    if os.path.exists(tfile) and cx.world == 1:
         try:
-            with open(os.path.join(ROOT, "profiles", "r01e_traffic.json")) as f:
-                tj = json.load(f)
-            per_step = {"k_tc_layer2<512, 0>": wl["L"], "k_tc_layer2<512, 1>": wl["L"], "k_tc_dw2<512>": wl["L"]}
-            traffic = sum(tj[k]["dram_bytes_per_launch"] * n for k, n in per_step.items()) / sum(per_step.values())
+            tj = json.load(open(tfile))
+            traffic = tj["gemm_dram_bytes_per_launch_avg"]
+            tnote = tj.get("note")
         except Exception:
             traffic = None
+    tc = prec in ("fp16", "fp16s", "bf16")
     roofline = {"bound": "tensor", "achieved": achieved, "peak": pk["bf16_sus"], "unit": "TFLOP/s",
-                "frac": achieved / pk["bf16_sus"], "traffic": traffic,
-                "traffic_note": "avg DRAM bytes per launch of the three tcgen05 GEMM kernels (ncu, profiles/r01e_*); "
-                                "algorithmic: 8.13 GB layer FWD/BWD, 5.42 GB dW" if traffic else None,
+                "frac": achieved / pk["bf16_sus"],
+                "issued_achieved": achieved * job.issued_factor(), "issued_frac": achieved * job.issued_factor() / pk["bf16_sus"],
+                "traffic": traffic, "traffic_note": tnote,
                 "kernel": "+".join(sorted(gemm_tags)), "flops_per_launch": flops / max(gemm_launches, 1),
-                "avg_launch_ms": gemm_ms / max(gemm_launches, 1), "gemm_share_of_step": gemm_ms / max(prof_total_ms, 1e-9),
-                "peak_source": pk["src"] + ", sustained bf16 (kernel timed inside a long step)",
-                "mma_kind": "tcgen05 kind::f16 (%s operands)" % prec if prec in ("bf16", "fp16") else "none: fp32 FFMA on CUDA cores (parity mode)"}
-    # HBM-bound stages (north star: elementwise / spline / MDCT stages as achieved GB/s of the measured copy peak)
+                "avg_launch_ms": gemm_ms / max(gemm_launches, 1), "gemm_share_of_step": gemm_ms / max(total_ms, 1e-9),
+                "peak_source": pk["src"] + ", sustained dense bf16/fp16 kind::f16 rate (kernels timed inside a long step)",
+                "mma_kind": ("tcgen05 kind::f16, %s operands%s" % ("bf16" if prec == "bf16" else "fp16",
+                             "; forward GEMMs as hi*hi + lo*hi + hi*lo (3 MMAs per K step): `frac` counts the algorithmic"
+                             " flops once, `issued_frac` what the tensor pipe executed" if prec == "fp16s" else ""))
+                if tc else "none: fp32 FFMA on CUDA cores"}
     stages = {}
 
     def stage(tag, nbytes, what):
@@ -422,6 +475,13 @@ def run_ours(args, wl):
                            "algorithmic_bytes_per_step": int(nbytes), "what": what}
     nparams = job.spec.num_params() * (8 if job.kind == "clips" else 1)
     stage("k_adam", 32 * nparams, "28 B/param Adam + 4 B/param gradient re-zero")
+    H = wl.get("H", 0)
+    nloc = prof_units
+    if job.kind == "siren" and tc and "k_tc_first" in kern:
+        nimg = 3 if prec == "fp16s" else 2
+        stage("k_tc_first", nimg * 2 * H * nloc, "write S_0 (+ lo), C_0 images")
+        nimg = 4 if prec == "fp16s" else 3
+        stage("k_tc_last", nimg * 2 * H * nloc, "read S_L (+ lo), C_L; write dZ_L")
     if job.kind == "siren" and wl.get("spectral") == "mdct":
         T = wl["T"]
         stage("k_mdct_loss", 4 * T + 4 * (T // 1024) * 1024 + 8 * T, "read pred + target coefficients, read-modify-write d loss/d pred")
@@ -434,40 +494,113 @@ def run_ours(args, wl):
         n = job.n_local
         stage("k_kan_expand", 2 * (4 * n * (1 + 256 + 256) + 4 * n * 9 * (1 + 256 + 256)), "read layer inputs, write Phi (fwd + recompute in bwd)")
         stage("k_kan_dx", 4 * n * 256 * 11, "read x, dPhi (9/feature), write dx")
+    del sub
+    torch.cuda.empty_cache()
+    return kern, roofline, stages
+
+
+def default_precision(wl):
+    return "bf16" if wl["kind"] == "kan" else "fp16s"
+
+
+def run_ours(args):
+    cx = Ctx(args)
+    torch = cx.torch
+    name = args.workload
+    wl = WORKLOADS[name]
+    prec = default_precision(wl) if args.precision == "auto" else args.precision
+    head, job, fit = measure(cx, name, prec, args.steps, args.warmup, True)
+
+    # ---- the metric's second half: SNR dB at fixed steps, this very fit continued to --snr-steps
+    snr = None
+    if args.snr_steps and job.kind != "clips":
+        marks = sorted(set([m for m in (200, args.snr_steps) if m >= fit.steps_done and m <= args.snr_steps]))
+        snr = {"precision": prec, "db_at_step": {}, "how": "utils.py:77-97 calculate_snr(target, model(coords)) of this fit"}
+        for m in marks:
+            fit.step(m - fit.steps_done)
+            snr["db_at_step"][str(m)] = job.snr_db(fit)
+        ref_file = os.path.join(ROOT, "profiles", "r02_snr_reference.json")
+        if os.path.exists(ref_file):
+            try:
+                snr["reference"] = json.load(open(ref_file)).get(name)
+            except Exception:
+                pass
+    lps = head["launches_per_step"]
+    del fit
+    torch.cuda.empty_cache()
+    kern, roofline, stages = kernel_profile(cx, job, prec, args.steps)
+    if lps is None:
+        lps = int(round(sum(v["launches_per_step"] for v in kern.values())))
+    del job
+    torch.cuda.empty_cache()
+
+    extras, fast = {}, None
+    if args.extras == "auto" and name == "c2":
+        k = max(5, min(args.steps, 20))
+        if prec == "fp16s":
+            fast, j2, f2 = measure(cx, name, "fp16", k, 3, False)
+            del j2, f2
+            torch.cuda.empty_cache()
+        c5 = "c5" if cx.world >= 8 else "c5small"
+        for wname in ("c1", "c3", "c3stft", "c4", c5):
+            w = WORKLOADS[wname]
+            try:
+                r, j2, f2 = measure(cx, wname, default_precision(w), k, 3, False)
+                if w["kind"] != "clips":
+                    m = min(500, max(args.snr_steps, 0))
+                    if m > f2.steps_done:
+                        f2.step(m - f2.steps_done)
+                        r["snr_db"] = {str(m): j2.snr_db(f2)}
+                else:
+                    r["snr_db_median_over_clips"] = {str(f2.steps_done): j2.snr_db(f2)}
+                del f2
+                torch.cuda.empty_cache()
+                if wname in ("c3", "c3stft", "c4"):
+                    kk, rr, ss = kernel_profile(cx, j2, default_precision(w), 3)
+                    r["hbm_stages"] = ss
+                    r["roofline_frac_gemm_kernels"] = rr["frac"]
+                del j2
+                torch.cuda.empty_cache()
+                extras["c5" if wname.startswith("c5") else wname] = r
+            except Exception as ex:  # noqa: BLE001 -- an extra workload must not take the headline down
+                extras[wname] = {"error": repr(ex)[:300]}
 
     # ---- CPU baseline beside it (rank 0, N = 1 only)
     cpu = None
-    if rank == 0 and world == 1 and not args.no_cpu_baseline:
+    if cx.rank == 0 and cx.world == 1 and not args.no_cpu_baseline:
         threads = os.cpu_count() or 1
         rows = pick_rows(wl, args.cpu_budget_s, 4, threads)
         rate, per_s = oracle_fit_rate(wl, rows, 3, 1, threads)
         cpu = {"value": rate, "unit": UNIT, "cores": threads, "kind": "port",
                "sample": "oracle (torch-CPU fp32 restatement of run.py's loop) on the first %d of %d coordinates%s, "
-                         "3 timed steps after 1 warm-up, %.2f s/step" % (rows, wl["T"], " of one clip" if job.kind == "clips" else "", per_s)}
+                         "3 timed steps after 1 warm-up, %.2f s/step" % (rows, wl["T"], " of one clip" if wl["kind"] == "clips" else "", per_s)}
 
-    if rank == 0:
-        par = ("clip-parallel x%d (no collective)" % world) if job.kind == "clips" else ("coord-shard x%d" % world)
-        line = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps,
-                "warmup": args.warmup, "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": "strong",
-                "vs_baseline": None, "dtype": prec if prec in ("bf16", "fp16") else "f32", "data": "synthetic",
-                "config": {"workload": wl["desc"], "precision": prec, "parallelism": par,
-                           "units_per_rank": job.n_local, "l2": "working set (activation workspace, GBs) >> 126 MB L2; no flush needed",
-                           "cuda_graph": True},
-                "clocks": clocks, "e2e": e2e, "gpu_launches": launches_per_step * args.steps,
-                "roofline": roofline, "hbm_stages": stages, "cpu_baseline": cpu, "kernels": kern,
-                "loss_first_last": first_last}
+    if cx.rank == 0:
+        par = ("clip-parallel x%d (no collective)" % cx.world) if wl["kind"] == "clips" else ("coord-shard x%d" % cx.world)
+        line = {"metric": METRIC, "value": head["value"], "unit": UNIT, "n_gpus": cx.world, "steps": args.steps,
+                "warmup": args.warmup, "ms_per_step": head["ms_per_step"], "higher_is_better": True, "scaling": "strong",
+                "vs_baseline": None, "dtype": {"fp16s": "fp16 hi+lo (fwd) / fp16 (bwd), fp32 accumulate", "fp16": "fp16",
+                                               "bf16": "bf16", "fp32": "f32"}[prec],
+                "data": "data/gt_bach.wav" if wl.get("wav") else "synthetic",
+                "config": config_of(wl),
+                "mode": {"precision": prec, "parallelism": par, "cuda_graph": head["cuda_graph"],
+                         "exchange": "one NCCL sum-allreduce of [grads | loss] per step, inside the CUDA graph" if cx.world > 1 else None},
+                "clocks": head["clocks"], "e2e": head["e2e"], "value_recheck": head["value_recheck"],
+                "gpu_launches": int(lps) * args.steps, "launches_per_step": int(lps),
+                "roofline": roofline, "step_frac_of_peak": head["step_frac_of_peak"], "step_frac_issued": head["step_frac_issued"],
+                "hbm_stages": stages, "snr": snr, "fast_mode": fast, "workloads": extras,
+                "cpu_baseline": cpu, "kernels": kern, "loss_first_last": head["loss_first_last"]}
         print(json.dumps(line), flush=True)
-    if world > 1:
-        dist.destroy_process_group()
+    if cx.world > 1:
+        cx.dist.destroy_process_group()
 
 
 def main():
     args = parse_args()
-    wl = WORKLOADS[args.workload]
     if args.impl == "reference":
-        run_reference(args, wl)
+        run_reference(args, WORKLOADS[args.workload])
     else:
-        run_ours(args, wl)
+        run_ours(args)
 
 
 if __name__ == "__main__":

@@ -220,6 +220,13 @@ int inr_opt_init(inr_opt_state* opt_dev, float lr, float min_lr, int32_t hist_ca
 int inr_adam_step(float* params, float* grads, float* m, float* v, int64_t P, inr_opt_state* opt,
                   float loss_scale, float* loss_hist, void* stream);
 
+/* The exchange step of a coordinate-sharded fit as ONE collective: inr_opt_loss_to_f32 writes the two
+ * float64 loss accumulators as fp32 hi, hi, lo, lo into tail4 (the 4 floats right behind the P gradient floats), the
+ * caller sum-allreduces P + 4 floats, inr_opt_loss_from_f32 rebuilds the accumulators (spectral term * spectral_scale:
+ * 1/world when every rank evaluated the whole-output loss) and zeroes tail4. */
+int inr_opt_loss_to_f32(const inr_opt_state* opt, float* tail4, void* stream);
+int inr_opt_loss_from_f32(inr_opt_state* opt, float* tail4, float spectral_scale, void* stream);
+
 /* Fused single-GPU step = inr_siren_loss_backward + inr_adam_step (run.py:158-189), graph-capturable. */
 int inr_siren_fit_step(const inr_siren_desc* d, float* params, float* grads, float* m, float* v,
                        const float* coords, const float* target, int64_t n, int64_t i0, int64_t T_total,

@@ -69,6 +69,8 @@ SIGNATURES = {
     "inr_siren_train_forward": (_i, [C.POINTER(SirenDesc), _p, _p, _i64, _i64, _i64, _f, _p, _p, _i64, _p]),
     "inr_siren_train_backward": (_i, [C.POINTER(SirenDesc), _p, _p, _p, _i64, _i64, _i64, _f, _i, _f, _p, _p, _p, _p,
                                       _i64, _p]),
+    "inr_opt_loss_to_f32": (_i, [_p, _p, _p]),
+    "inr_opt_loss_from_f32": (_i, [_p, _p, _f, _p]),
     "inr_stmdct_num_frames": (_i64, [_i64, _i]),
     "inr_stmdct_forward": (_i, [_p, _i64, _i, _p, _p, _p]),
     "inr_istmdct": (_i, [_p, _i64, _i, _p, _p, _p]),

@@ -84,6 +84,22 @@ __global__ void k_opt_post(inr_opt_state* st, float loss_scale, float* loss_hist
   opt_prepare_next(st);
 }
 
+// One-collective exchange of a sharded step: the two float64 loss accumulators as fp32 hi + lo pairs behind the gradient
+// block (engine.allreduce_fused), and back after the sum-allreduce (the spectral term, evaluated identically on every
+// rank, is scaled by 1 / world).
+__global__ void k_loss_to_f32(const inr_opt_state* st, float* tail) {
+  for (int i = 0; i < 2; ++i) {
+    const float hi = (float)st->loss_acc[i];
+    tail[i] = hi;
+    tail[2 + i] = (float)(st->loss_acc[i] - (double)hi);
+  }
+}
+__global__ void k_loss_from_f32(inr_opt_state* st, float* tail, float spectral_scale) {
+  st->loss_acc[0] = (double)tail[0] + (double)tail[2];
+  st->loss_acc[1] = ((double)tail[1] + (double)tail[3]) * (double)spectral_scale;
+  for (int i = 0; i < 4; ++i) tail[i] = 0.f;
+}
+
 int opt_init(inr_opt_state* st, float lr, float min_lr, int hist_cap, cudaStream_t s) {
   { LaunchScope ls("k_opt_init", s);
   k_opt_init<<<1, 1, 0, s>>>(st, lr, min_lr, hist_cap); }
@@ -105,3 +121,20 @@ int adam_step(float* params, float* grads, float* m, float* v, int64_t P, inr_op
 }
 
 }  // namespace inr
+
+extern "C" int inr_opt_loss_to_f32(const inr_opt_state* opt, float* tail4, void* stream) {
+  using namespace inr;
+  INR_REQUIRE(opt && tail4, INR_E_BADARG, "inr_opt_loss_to_f32: null argument");
+  { LaunchScope ls("k_loss_xchg", (cudaStream_t)stream);
+    k_loss_to_f32<<<1, 1, 0, (cudaStream_t)stream>>>(opt, tail4); }
+  INR_LAUNCH_CHECK();
+  return INR_OK;
+}
+extern "C" int inr_opt_loss_from_f32(inr_opt_state* opt, float* tail4, float spectral_scale, void* stream) {
+  using namespace inr;
+  INR_REQUIRE(opt && tail4, INR_E_BADARG, "inr_opt_loss_from_f32: null argument");
+  { LaunchScope ls("k_loss_xchg", (cudaStream_t)stream);
+    k_loss_from_f32<<<1, 1, 0, (cudaStream_t)stream>>>(opt, tail4, spectral_scale); }
+  INR_LAUNCH_CHECK();
+  return INR_OK;
+}

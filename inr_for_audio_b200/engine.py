@@ -98,6 +98,24 @@ def allreduce_step_state(grads: torch.Tensor, loss_acc: torch.Tensor, pg, world:
         loss_acc[1:2].div_(world)
 
 
+def allreduce_fused(gbuf: torch.Tensor, P: int, loss_acc: torch.Tensor, pg, world: int, whole_output_loss: bool):
+    """The same exchange as ONE collective (a single fused buffer, capturable in a CUDA graph): the
+    two float64 loss accumulators ride behind the P gradient floats of `gbuf` (fp32, at least P + 4 long) as fp32
+    hi + lo pairs (the reduced sum is fp32-grade, ~1e-7 relative: the loss the scheduler sees is a float32) -- so a step issues one sum-allreduce
+    of P + 4 floats.  The result is bitwise identical on every rank, which keeps the replicas in lock-step."""
+    if world <= 1:
+        return
+    tail = gbuf[P:P + 4]
+    hi = loss_acc[0:2].to(torch.float32)
+    tail[0:2].copy_(hi)
+    tail[2:4].copy_((loss_acc[0:2] - hi.to(torch.float64)).to(torch.float32))
+    torch.distributed.all_reduce(gbuf[:P + 4], group=pg)
+    loss_acc[0:2].copy_(tail[0:2].to(torch.float64) + tail[2:4].to(torch.float64))
+    tail.zero_()
+    if whole_output_loss:
+        loss_acc[1:2].div_(world)
+
+
 def _require_cuda(t: torch.Tensor, what: str):
     if not t.is_cuda:
         raise L.InrLibraryError("%s must live on a CUDA device: the INR hot path has no CPU fallback" % what)
@@ -185,7 +203,7 @@ class SirenFitter:
                 self._shard = shard_range(self.full_T, 0, self.world)[2]
         dev = self.device
         # one arena: [params | grads | m | v], each padded to 64 floats so every block is 256-byte aligned
-        self.Ppad = (self.P + 63) // 64 * 64
+        self.Ppad = (self.P + 4 + 63) // 64 * 64        # + 4: the loss accumulators ride behind the gradients (allreduce_fused)
         self.arena = torch.zeros(4 * self.Ppad, dtype=torch.float32, device=dev)
         self.params = self.arena[0:self.P]
         self.grads = self.arena[self.Ppad:self.Ppad + self.P]
@@ -200,7 +218,10 @@ class SirenFitter:
         self.ws = workspace if workspace is not None else Workspace(dev)
         self.ws.get(self.desc, self.n, True)
         self.steps_done = 0
-        self.use_graph = bool(use_graph) and self.world == 1
+        # sharded fits are captured too: the one NCCL allreduce of a step is a graph node like the kernels around it
+        self.use_graph = bool(use_graph)
+        if self.world > 1:
+            self._allreduce()                         # communicator set-up outside any capture (all-zero buffers)
         self._graph = None
         self.launches_per_step = None
 
@@ -263,7 +284,16 @@ class SirenFitter:
         self.out_full.copy_(gathered[:self.full_T])
 
     def _allreduce(self):
-        allreduce_step_state(self.grads, self.loss_acc, self.pg, self.world, self.split)
+        """the one exchange of a sharded step: [grads | loss hi, lo] in a single NCCL sum-allreduce (allreduce_fused
+        is the same arithmetic on torch tensors, used where there is no device: tests/test_sharding_cpu.py)"""
+        if self.world <= 1:
+            return
+        gbuf = self.arena[self.Ppad:self.Ppad + self.P + 4]
+        tail = gbuf[self.P:]
+        L.check(L.lib().inr_opt_loss_to_f32(L.ptr(self.opt), L.ptr(tail), L.stream_ptr()))
+        torch.distributed.all_reduce(gbuf, group=self.pg)
+        L.check(L.lib().inr_opt_loss_from_f32(L.ptr(self.opt), L.ptr(tail), 1.0 / self.world if self.split else 1.0,
+                                              L.stream_ptr()))
 
     def _enqueue_step(self):
         if self.split:
@@ -281,8 +311,11 @@ class SirenFitter:
             s.wait_stream(torch.cuda.current_stream(self.device))
             with torch.cuda.stream(s):
                 g = torch.cuda.CUDAGraph()
+                lc0 = L.lib().inr_launch_count()
                 with torch.cuda.graph(g, stream=s):
                     self._enqueue_step()
+                # kernels of this library per replay (the capture ran the same host code once)
+                self.launches_per_step = int(L.lib().inr_launch_count() - lc0)
             torch.cuda.current_stream(self.device).wait_stream(s)
             self._graph = g
         for _ in range(n_steps):
@@ -432,6 +465,7 @@ class ClipBatchFitter:
         self.use_graph = bool(use_graph)
         self._graph = None
         self.steps_done = 0
+        self.launches_per_step = None
 
     @staticmethod
     def clip_range(num_clips: int, rank: int, world: int):
@@ -463,8 +497,10 @@ class ClipBatchFitter:
             cap.wait_stream(cur)
             with torch.cuda.stream(cap):
                 g = torch.cuda.CUDAGraph()
+                lc0 = L.lib().inr_launch_count()
                 with torch.cuda.graph(g, stream=cap):
                     self._enqueue_batch_step(cap)
+                self.launches_per_step = int(L.lib().inr_launch_count() - lc0)
             cur.wait_stream(cap)
             self._graph = g
         for _ in range(n_steps):

@@ -57,7 +57,16 @@ def _worker(rank, world, port, T, P, out_q):
     loss_acc[1] = 0.125                      # whole-output (spectral) loss: evaluated identically on every rank
     loss_acc[2] = 7.0                        # scratch slots are rank-local and must not be reduced
     allreduce_step_state(grads, loss_acc, dist.group.WORLD, world, True)
-    out_q.put((rank, grads.numpy(), loss_acc.numpy()))
+    # the same exchange as ONE collective over [grads | loss hi, lo] in fp32 (what the device path issues)
+    from inr_for_audio_b200.engine import allreduce_fused
+    gbuf = torch.zeros(P + 4, dtype=torch.float32)
+    gbuf[:P] = torch.from_numpy(rows[i0:i0 + n].sum(axis=0)).float()
+    acc2 = torch.zeros(4, dtype=torch.float64)
+    acc2[0] = float((err[i0:i0 + n] ** 2).sum())
+    acc2[1] = 0.125
+    acc2[2] = 7.0
+    allreduce_fused(gbuf, P, acc2, dist.group.WORLD, world, True)
+    out_q.put((rank, grads.numpy(), loss_acc.numpy(), gbuf.numpy(), acc2.numpy()))
     dist.barrier()
     dist.destroy_process_group()
 
@@ -77,8 +86,13 @@ def test_sharded_allreduce_equals_single_process():
     rng = np.random.default_rng(0)
     rows = rng.standard_normal((T, P))
     err = rng.standard_normal(T)
-    for rank, g, acc in res:
+    for rank, g, acc, gb, acc2 in res:
         np.testing.assert_allclose(g, rows.sum(axis=0), rtol=1e-12, atol=1e-12)
         assert abs(acc[0] - (err ** 2).sum()) < 1e-9
         assert acc[1] == 0.125 and acc[2] == 7.0
+        np.testing.assert_allclose(gb[:P], rows.sum(axis=0), rtol=1e-5, atol=1e-5)
+        assert np.all(gb[P:] == 0.0)                                      # the tail is handed back clean
+        assert abs(acc2[0] - (err ** 2).sum()) < 2e-7 * (err ** 2).sum()  # fp32-grade: the loss the scheduler sees is a float32
+        assert abs(acc2[1] - 0.125) < 1e-12 and acc2[2] == 7.0
     assert np.array_equal(res[0][1], res[1][1]) and np.array_equal(res[0][2], res[1][2])   # replicas stay in lock-step
+    assert np.array_equal(res[0][3], res[1][3]) and np.array_equal(res[0][4], res[1][4])
