@@ -26,9 +26,11 @@ namespace tc {
 
 // SPLIT (INR_PREC_FP16S, forward modes only): both operands are fp16 hi + lo pairs (x = hi + lo, lo = fp16(x - hi):
 // 22 significant bits) and every K step issues THREE MMAs into the same accumulator, hi*hi + lo*hi + hi*lo -- fp32-grade
-// products (the lo*lo term is below 2^-22).  The weight slice keeps hi and lo resident, so a pair covers half as many
-// output features at H = 512; a ring stage carries the hi and the lo chunk of the A rows (two 16 KB copies issued by
-// two lanes: one thread sustains only ~1 bulk copy per 0.32 us).
+// products (the lo*lo term is below 2^-22).  Only the hi half of the weight slice stays resident (a pair covers half as
+// many output features at H = 512); a ring stage carries the hi and the lo chunk of the A rows AND the matching K chunk of
+// the lo weights (L2-resident, re-streamed per tile: +25 % fabric bytes) -- three copies issued by three lanes (one
+// thread sustains only ~1 bulk copy per 0.32 us).  That leaves 160 KB (H = 512) instead of 96 KB for bytes in flight:
+// with both weight halves resident the kernel sat at 58 % tensor-pipe activity, waiting on the ring (profiles/r02_notes.md).
 template <int H, bool SPLIT = false>
 struct Layer2Cfg {
   static constexpr int NP = SPLIT ? ((H >= 512) ? 128 : H) : ((H >= 256) ? 256 : H);   // output features per pair (MMA N)
@@ -39,10 +41,13 @@ struct Layer2Cfg {
   static constexpr int KC = SPLIT ? 64 : 128;       // K columns per ring stage
   static constexpr int NCHUNK = H / KC;
   static constexpr int B_HALF = H * NC * 2;         // one (hi or lo) weight slice half
-  static constexpr int B_BYTES = B_HALF * (SPLIT ? 2 : 1);   // 128 KB (H=512; split H>=256), 64 KB (256), 16 KB (128)
+  static constexpr int B_SLICE = B_HALF * (SPLIT ? 2 : 1);   // bytes of one packed slice in global memory: [hi | lo]
+  static constexpr int B_BYTES = B_HALF;            // resident: 128 KB (H=512), 64 KB (256; split 512), 16 KB (128)
   static constexpr int A_HALF = (KC / 8) * TILE_ROWS * 16;   // one (hi or lo) A chunk: 32 KB, split 16 KB
-  static constexpr int A_STAGE_BYTES = A_HALF * (SPLIT ? 2 : 1);  // 32 KB
-  static constexpr int STAGES = (B_BYTES >= 131072) ? 3 : 4; // 96 KB / 128 KB in flight
+  static constexpr int WLO_CHUNK = SPLIT ? (KC / 8) * NC * 16 : 0;   // split: K chunk of the lo weights, 8 / 16 KB
+  static constexpr int A_STAGE_BYTES = A_HALF * (SPLIT ? 2 : 1) + WLO_CHUNK;  // 32 KB; split 40 / 48 KB
+  static constexpr int STAGES_FIT = (232448 - B_BYTES - 2 * NP * 4 - 256) / A_STAGE_BYTES;
+  static constexpr int STAGES = STAGES_FIT > 4 ? 4 : STAGES_FIT;   // 96 .. 160 KB in flight
   static constexpr int TMEM_COLS = 2 * NP;          // two accumulator buffers
   static constexpr int OFF_A = B_BYTES;
   static constexpr int OFF_BIAS = OFF_A + STAGES * A_STAGE_BYTES;
@@ -50,7 +55,6 @@ struct Layer2Cfg {
   static constexpr int OFF_BAR = OFF_AVEC + NP * 4;
   static constexpr int SMEM_BYTES = OFF_BAR + 256;
   static constexpr int THREADS = 320;
-  static constexpr int PF_DT = 3;                   // split: double tiles of L2 prefetch distance
   static_assert(H == 128 || H == 256 || H == 512, "hidden width");
   static_assert(SMEM_BYTES <= 232448, "shared-memory budget");
 };
@@ -114,32 +118,39 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(Layer2Cfg<H, SPLIT>:
     if (lane == 0) {
       // packed weights: [slice = q*2 + rank][hi | lo (split)][H/8][NC][8]
       mbar_arrive_expect_tx(bar_bfull, Cfg::B_BYTES);
-      const uint8_t* bsrc = reinterpret_cast<const uint8_t*>(p.Bpack) + (size_t)(q * 2 + rank) * Cfg::B_BYTES;
+      const uint8_t* bsrc = reinterpret_cast<const uint8_t*>(p.Bpack) + (size_t)(q * 2 + rank) * Cfg::B_SLICE;
       constexpr int BPIECE = Cfg::B_BYTES < 32768 ? Cfg::B_BYTES : 32768;
       for (int off = 0; off < Cfg::B_BYTES; off += BPIECE) bulk_g2s(sB + off, bsrc + off, BPIECE, bar_bfull);
     }
-    if (lane < (SPLIT ? 2 : 1)) {                     // split: lane 0 copies the hi chunk, lane 1 the lo chunk
+    if (lane < (SPLIT ? 3 : 1)) {                     // split: lane 0 copies the hi chunk, lane 1 the lo chunk, lane 2 the lo weights
       int s = 0;
       uint32_t phase = 0;
       const op16* abase = (SPLIT && lane == 1) ? p.A_lo : p.A;
+      const uint8_t* wlo = reinterpret_cast<const uint8_t*>(p.Bpack) + (size_t)(q * 2 + rank) * Cfg::B_SLICE + Cfg::B_HALF;
       for (int dt = dt0; dt < num_dt; dt += dt_stride) {
         const int tile = 2 * dt + (int)rank;
         const bool valid = tile < p.num_tiles;
         const uint8_t* asrc = reinterpret_cast<const uint8_t*>(abase) + (size_t)tile * (TILE_ROWS * H * 2);
         // the NQ pairs that share this row tile pull it into L2 a few tiles ahead, a chunk each, so the ring's copies see
         // L2-hit latency: 96 KB in flight per SM cannot cover DRAM latency at the rate three MMAs per K step consume
-        const int pf_tile = tile + 2 * Cfg::PF_DT * dt_stride;
+        const int pf_tile = tile + 2 * p.pf_dt * dt_stride;
         const uint8_t* pfsrc = reinterpret_cast<const uint8_t*>(abase) + (size_t)pf_tile * (TILE_ROWS * H * 2);
         for (int c = 0; c < Cfg::NCHUNK; ++c) {
-          if (SPLIT && pf_tile < p.num_tiles && (c % Cfg::NQ) == q)
+          if (SPLIT && lane < 2 && p.pf_dt > 0 && pf_tile < p.num_tiles && (c % Cfg::NQ) == q)
             bulk_prefetch_l2(pfsrc + (size_t)c * Cfg::A_HALF, Cfg::A_HALF);
           mbar_wait(bar_empty(s), phase ^ 1);
           if (lane == 0) {
+            // odd tile count: the MMA multiplies stale A rows of this CTA, nobody stores them -- but this CTA's half of
+            // the lo weights feeds the PEER's rows too, so it is staged regardless
             if (valid) mbar_arrive_expect_tx(bar_full(s), Cfg::A_STAGE_BYTES);
-            else mbar_arrive(bar_full(s));            // odd tile count: the MMA multiplies stale rows, nobody stores them
+            else if (SPLIT) mbar_arrive_expect_tx(bar_full(s), Cfg::WLO_CHUNK);
+            else mbar_arrive(bar_full(s));
           }
-          if (valid)
+          if (SPLIT && lane == 2) {
+            bulk_g2s(sA + s * Cfg::A_STAGE_BYTES + 2 * Cfg::A_HALF, wlo + (size_t)c * Cfg::WLO_CHUNK, Cfg::WLO_CHUNK, bar_full(s));
+          } else if (valid) {
             bulk_g2s(sA + s * Cfg::A_STAGE_BYTES + lane * Cfg::A_HALF, asrc + (size_t)c * Cfg::A_HALF, Cfg::A_HALF, bar_full(s));
+          }
           if (++s == Cfg::STAGES) { s = 0; phase ^= 1; }
         }
       }
@@ -169,7 +180,7 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(Layer2Cfg<H, SPLIT>:
               const uint64_t bd = make_smem_desc(b_addr, p.b_lbo, p.b_sbo);
               if (SPLIT) {   // small terms first: lo*hi + hi*lo, then hi*hi
                 const uint64_t adl = make_smem_desc(a_addr + Cfg::A_HALF, p.a_lbo, p.a_sbo);
-                const uint64_t bdl = make_smem_desc(b_addr + Cfg::B_HALF, p.b_lbo, p.b_sbo);
+                const uint64_t bdl = make_smem_desc(sA + s * Cfg::A_STAGE_BYTES + 2 * Cfg::A_HALF + kk * 2 * (NC * 16), p.b_lbo, p.b_sbo);
                 umma2_f16(d_tmem, adl, bd, idesc, (c | kk) != 0 ? 1u : 0u);
                 umma2_f16(d_tmem, ad, bdl, idesc, 1u);
                 umma2_f16(d_tmem, ad, bd, idesc, 1u);

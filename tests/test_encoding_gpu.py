@@ -148,7 +148,8 @@ def test_module_route_and_fp16_refusal(pkg, golden):
 
 @pytest.mark.parametrize("K,H,ns,nk,fl,n", [(16, 128, 2, 0, False, 4099), (64, 256, 1, 1, False, 6000), (100, 128, 1, 0, True, 2000),
                                             (128, 128, 1, 0, False, 1000), (34, 512, 1, 0, False, 2500)])
-def test_fp16_mode_wide_inputs_against_oracle(pkg, K, H, ns, nk, fl, n):
+@pytest.mark.parametrize("prec", ["fp16", "fp16s"])
+def test_fp16_mode_wide_inputs_against_oracle(pkg, K, H, ns, nk, fl, n, prec):
     """Encoded coordinates in the tcgen05 mode: the rows become a zero-padded H-wide tile image, layer 0 one more layer GEMM,
     its weight gradient one more dW GEMM cut back to (H x in).  Loss within 1e-3 relative, gradients (and the first-layer
     weight gradient on its own) within fp16 rounding noise of the fp32 oracle."""
@@ -162,22 +163,24 @@ def test_fp16_mode_wide_inputs_against_oracle(pkg, K, H, ns, nk, fl, n):
     x = torch.rand(n, K) * 2 - 1
     gt = torch.sin(torch.linspace(0, 20, n))
     loss_o, _, grads_o, out_o = O.siren_loss_and_grads(ospec, ps, x, gt.view(-1, 1))
-    f = pkg.SirenFitter(spec, flat, gt.to(dev()), x.to(dev()), precision="fp16", use_graph=False)
+    f = pkg.SirenFitter(spec, flat, gt.to(dev()), x.to(dev()), precision=prec, use_graph=False)
     loss, grads, out = f.loss_and_grads()
-    assert abs(loss - float(loss_o)) <= 1e-3 * abs(float(loss_o)) + 1e-9, (loss, float(loss_o))
-    assert float(np.abs(out.cpu().numpy() - out_o.numpy().ravel()).max()) <= 3e-2
+    oerr = float(np.abs(out.cpu().numpy() - out_o.numpy().ravel()).max())
+    ltol, otol = (1e-3, 3e-2) if prec == "fp16" else (5e-5, 5e-4)     # fp16s: the input image X is split too
+    assert abs(loss - float(loss_o)) <= ltol * abs(float(loss_o)) + 1e-9, (loss, float(loss_o), oerr)
+    assert oerr <= otol, oerr
     go = torch.cat([t.reshape(-1) for t in grads_o]).numpy().astype(np.float64)
     gn = grads.cpu().numpy().astype(np.float64)
     gerr = np.linalg.norm(gn - go) / np.linalg.norm(go)
     n0 = H * K
     g0err = np.linalg.norm(gn[:n0] - go[:n0]) / np.linalg.norm(go[:n0])
     gb0err = np.linalg.norm(gn[n0:n0 + H] - go[n0:n0 + H]) / np.linalg.norm(go[n0:n0 + H])
-    print("fp16 wide K=%d H=%d: loss rel err %.2e, grad rel err %.2e, gW0 %.2e, gb0 %.2e" % (
-        K, H, abs(loss - float(loss_o)) / float(loss_o), gerr, g0err, gb0err))
-    assert gerr <= 5e-2 and g0err <= 5e-2 and gb0err <= 5e-2
+    print("%s wide K=%d H=%d: loss rel err %.2e, out max err %.2e, grad rel err %.2e, gW0 %.2e, gb0 %.2e" % (
+        prec, K, H, abs(loss - float(loss_o)) / float(loss_o), oerr, gerr, g0err, gb0err))
+    assert gerr <= 1e-2 and g0err <= 1e-2 and gb0err <= 1e-2
     # forward-only entry and the graph-captured step
     np.testing.assert_allclose(f.forward().cpu().numpy(), out.cpu().numpy(), atol=1e-6)
-    f2 = pkg.SirenFitter(spec, flat, gt.to(dev()), x.to(dev()), precision="fp16")
+    f2 = pkg.SirenFitter(spec, flat, gt.to(dev()), x.to(dev()), precision=prec)
     f2.step(5)
     ls = f2.losses()
     assert np.all(np.isfinite(ls)) and ls.min() < 2 * ls[0]

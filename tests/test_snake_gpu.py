@@ -135,7 +135,8 @@ def test_ragged_sizes_against_oracle(pkg):
                                                       (512, 1, 1, 0, True, 2500, False),
                                                       # first_linear: layer 0 = nn.Linear + Snake (models.py:343-347)
                                                       (128, 1, 1, 0, True, 3001, True), (256, 2, 0, 1, True, 5000, True)])
-def test_fp16_mode_snake_tanh_against_oracle(pkg, H, ns, nk, nt, last_lin, n, fl):
+@pytest.mark.parametrize("prec", ["fp16", "fp16s"])
+def test_fp16_mode_snake_tanh_against_oracle(pkg, H, ns, nk, nt, last_lin, n, fl, prec):
     """Snake / Tanh hidden layers in the tcgen05 mode (CTA-pair layer kernel, MODE_FWD_SNAKE / MODE_FWD_TANH /
     MODE_BWD_SNAKE): loss within 1e-3 relative, gradients (incl. the Snake `a` gradients) within fp16 rounding noise
     of the fp32 oracle."""
@@ -148,10 +149,12 @@ def test_fp16_mode_snake_tanh_against_oracle(pkg, H, ns, nk, nt, last_lin, n, fl
     gt = torch.from_numpy(pkg.utils.synth_waveform(max(n, 2), seed=3)[:n].copy())
     coords = O.get_coord(n, 1).view(-1, 1)
     loss_o, _, grads_o, out_o = O.siren_loss_and_grads(ospec, ps, coords, gt.view(-1, 1))
-    f = pkg.SirenFitter(spec, flat, gt.to(dev()), precision="fp16", use_graph=False)
+    f = pkg.SirenFitter(spec, flat, gt.to(dev()), precision=prec, use_graph=False)
     loss, grads, out = f.loss_and_grads()
-    assert abs(loss - float(loss_o)) <= 1e-3 * abs(float(loss_o)) + 1e-9, (loss, float(loss_o))
-    assert float(np.abs(out.cpu().numpy() - out_o.numpy().ravel()).max()) <= 3e-2
+    oerr = float(np.abs(out.cpu().numpy() - out_o.numpy().ravel()).max())
+    ltol, otol = (1e-3, 3e-2) if prec == "fp16" else (5e-5, 5e-4)     # fp16s: fp32-grade forward (Snake a = 0.5: z up to ~10)
+    assert abs(loss - float(loss_o)) <= ltol * abs(float(loss_o)) + 1e-9, (loss, float(loss_o), oerr)
+    assert oerr <= otol, oerr
     go = torch.cat([x.reshape(-1) for x in grads_o]).numpy().astype(np.float64)
     gn = grads.cpu().numpy().astype(np.float64)
     gerr = np.linalg.norm(gn - go) / np.linalg.norm(go)
@@ -165,10 +168,10 @@ def test_fp16_mode_snake_tanh_against_oracle(pkg, H, ns, nk, nt, last_lin, n, fl
             ga, gr = gn[offs[pi]:offs[pi + 1]], go[offs[pi]:offs[pi + 1]]
             aerr = max(aerr, float(np.linalg.norm(ga - gr) / (np.linalg.norm(gr) + 1e-30)))
             pi += 1
-    print("fp16 snake/tanh H=%d %d/%d/%d n=%d: loss rel err %.2e, grad rel err %.2e, a-grad rel err %.2e" % (
-        H, ns, nk, nt, n, abs(loss - float(loss_o)) / float(loss_o), gerr, aerr))
-    assert gerr <= 5e-2 and aerr <= 5e-2
-    f2 = pkg.SirenFitter(spec, flat, gt.to(dev()), precision="fp16")
+    print("%s snake/tanh H=%d %d/%d/%d n=%d: loss rel err %.2e, out max err %.2e, grad rel err %.2e, a-grad rel err %.2e" % (
+        prec, H, ns, nk, nt, n, abs(loss - float(loss_o)) / float(loss_o), oerr, gerr, aerr))
+    assert gerr <= 1e-2 and aerr <= 1e-2
+    f2 = pkg.SirenFitter(spec, flat, gt.to(dev()), precision=prec)
     f2.step(5)
     ls = f2.losses()
     assert np.all(np.isfinite(ls)) and ls.min() < 2 * ls[0]      # full-batch Adam at lr 1e-3 is not monotone
