@@ -26,7 +26,8 @@ def main():
     T = 50000
     gt = torch.from_numpy(P.utils.synth_waveform(T, seed=5)).to(dev)
     i0, n, _ = shard_range(T, rank, world)
-    cases = [("fp32", None, 0.0, 64, 2, 1e-5, 2e-4), ("fp16", None, 0.0, 128, 2, 1e-3, 2e-2), ("fp32", "mdct", 0.2, 64, 2, 1e-5, 2e-4),
+    cases = [("fp32", None, 0.0, 64, 2, 1e-5, 2e-4), ("fp16", None, 0.0, 128, 2, 1e-3, 5e-3), ("fp16s", None, 0.0, 128, 2, 1e-5, 5e-3),
+             ("fp16s", "mdct", 0.2, 256, 3, 1e-5, 5e-3), ("fp32", "mdct", 0.2, 64, 2, 1e-5, 2e-4),
              ("fp32", "stft", 0.1, 64, 1, 1e-5, 5e-4)]
     for prec, spectral, alpha, H, Lh, ltol, gtol in cases:
         torch.manual_seed(0)
@@ -35,13 +36,14 @@ def main():
         full = P.SirenFitter(model.spec, flat, gt, precision=prec, alpha=alpha, spectral=spectral, use_graph=False)
         l1, g1, _ = full.loss_and_grads()
         sh = P.SirenFitter(model.spec, flat, gt[i0:i0 + n], i0=i0, T_total=T, precision=prec, alpha=alpha, spectral=spectral,
-                           spectral_target=gt if spectral else None, process_group=pg, use_graph=False)
+                           spectral_target=gt if spectral else None, process_group=pg, use_graph=True)
         l2, g2, _ = sh.loss_and_grads()
         gerr = float((g1 - g2).norm() / g1.norm())
         assert abs(l1 - l2) <= ltol * abs(l1), (prec, spectral, l1, l2)
         assert gerr <= gtol, (prec, spectral, gerr)
         full.step(5)
-        sh.step(5)
+        sh.step(5)                                # captured: kernels + the one NCCL allreduce of [grads | loss] per replay
+        assert sh._graph is not None
         np.testing.assert_allclose(sh.losses(), full.losses(), rtol=5e-3 if prec == "fp32" else 5e-2)
         mine = sh.params.clone()
         ref = mine.clone()
@@ -79,6 +81,15 @@ def main():
     dist.barrier()
     if rank == 0:
         print("MULTI_GPU_OK world=%d" % world, flush=True)
+    # CUDA graphs that captured NCCL work must be gone before the communicator is torn down (a live graph made
+    # destroy_process_group hang in round 2's first 2-GPU run); the timer is a backstop, the checks above are done
+    import gc, threading
+    t = threading.Timer(30.0, lambda: os._exit(0))
+    t.daemon = True
+    t.start()
+    del full, sh, fk, sk, mine, allc
+    gc.collect()
+    torch.cuda.synchronize()
     dist.destroy_process_group()
 
 
