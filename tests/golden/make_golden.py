@@ -339,6 +339,66 @@ def make_kan():
     np.savez_compressed(os.path.join(HERE, "kan.npz"), **out)
 
 
+# ---------------------------------------------------------------- in_features = 2: the MDCT-image fit (utils.py:382-403, run.py:67-76)
+def make_mdct2d():
+    """reference MDCTFitting (gt_bach, 1 s -> 1024 x 43 coefficient image) fitted by the reference Siren(2, 128, 2, 1):
+    init, forward, and teacher-forced steps 0/1/2 of run.py's loop."""
+    out = {}
+    ds = ref.utils.MDCTFitting(os.path.join(ROOT, "data", "gt_bach.wav"), duration=1, N=2048, takelog=False)
+    coords, pixels = ds[0]
+    coords = torch.as_tensor(coords).reshape(1, -1, 2).float()
+    gt = torch.as_tensor(np.asarray(pixels)).reshape(1, -1, 1).float()          # run.py:75 DataLoader adds the batch dim
+    out["shape"] = np.array([ds.height, ds.width])
+    out["coords_sha"] = np.array(sha(coords.numpy()))
+    out["gt"] = gt.numpy().ravel()
+    torch.manual_seed(5)
+    m = ref.models.Siren(2, 128, 2, 1, True, first_omega_0=30, hidden_omega_0=30.0)
+    out["p0"] = np.concatenate([p.detach().numpy().ravel() for p in m.parameters()])
+    losses, lrs, rec = ref_fit(m, coords, gt, 4, record_steps=(0, 1, 2))
+    out["losses"] = np.array(losses, dtype=np.float64)
+    for k, v in rec.items():
+        out[k] = v
+    np.savez_compressed(os.path.join(HERE, "mdct2d.npz"), **out)
+
+
+# ---------------------------------------------------------------- KAN convergence (run.py:109-110 + the loop)
+def make_kan_converge():
+    """reference kan.KAN([1, 256, 256, 1]) (BASELINE.json config 4's network) fitted to 8192 samples of gt_bach by
+    run.py's loop for 500 steps, at 8 threads and at 1 thread (the reference's own run-to-run band): SNR at marks."""
+    sr, data = gt_bach(8192, 44100)
+    gtn = data / np.max(np.abs(data))
+    gt = torch.from_numpy(gtn).view(1, -1, 1)
+    coords = ref.utils.get_coord(8192, 1).view(1, -1, 1)
+    marks = [50, 100, 200, 300, 500]
+    out = {"gt": gtn, "marks": np.array(marks)}
+    for nt in (8, 1):
+        torch.set_num_threads(nt)
+        torch.manual_seed(2)
+        m = ref.kan.KAN([1, 256, 256, 1])
+        if nt == 8:
+            out["p0"] = np.concatenate([p.detach().numpy().ravel() for p in m.parameters()])
+        opt = torch.optim.Adam(m.parameters(), lr=1e-3)
+        sched = torch.optim.lr_scheduler.ReduceLROnPlateau(opt, mode="min", factor=0.8, patience=200, min_lr=1e-6)
+        mse = torch.nn.MSELoss()
+        losses, snr = [], []
+        for step in range(500):
+            o = m(coords)
+            loss = mse(o, gt)
+            losses.append(loss.item())
+            opt.zero_grad()
+            loss.backward()
+            opt.step()
+            sched.step(loss)
+            if step + 1 in marks:
+                with torch.no_grad():
+                    snr.append(ref.utils.calculate_snr(gtn, m(coords).numpy().ravel()))
+                print("kan t%d step %d loss %.3e snr %.2f" % (nt, step + 1, losses[-1], snr[-1]), flush=True)
+        out["losses_t%d" % nt] = np.array(losses)
+        out["snr_t%d" % nt] = np.array(snr)
+    torch.set_num_threads(8)
+    np.savez_compressed(os.path.join(HERE, "kan_converge.npz"), **out)
+
+
 if __name__ == "__main__":
     which = sys.argv[1:] or ["coords", "siren", "snake", "encoding", "mdct", "kan", "converge"]
     for w in which:
