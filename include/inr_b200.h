@@ -108,7 +108,8 @@ int64_t inr_launch_count(void);
 /* Grid-size limit for the persistent kernels: launches enqueued after this call occupy at most n_sms SMs (rounded down
  * to an even number, at least 8; 0 = all SMs).  Used by the clip-parallel batch fitter (BASELINE.json config 5: many independent
  * clips, engine.ClipBatchFitter) so that the per-clip steps it enqueues on several streams run concurrently on disjoint
- * SMs.  Process-global; returns the limit in effect (0 = none). */
+ * SMs.  Scoped to the calling host thread (thread-local): it applies to the launches that thread enqueues until it calls
+ * inr_set_sm_limit(0); returns the limit in effect (0 = none). */
 int inr_set_sm_limit(int n_sms);
 int inr_profile_begin(void);
 int64_t inr_profile_end(char* buf, int64_t cap);
@@ -268,18 +269,7 @@ int inr_kan_loss_backward(const inr_kan_desc* d, const float* params, const floa
                           float grad_scale, const float* extra_gout_or_null, float* grads, inr_opt_state* opt,
                           float* out_or_null, void* workspace, int64_t workspace_bytes, void* stream);
 
-/* ---- test hooks for the tcgen05 kernels (tests/test_tc_gpu.py): one layer GEMM / one dW GEMM on row-major fp32
- * inputs; `variant` bit 0 / bit 1 swap the LBO/SBO descriptor strides of operand A / B (convention probe). */
-int64_t inr_dbg_tc_scratch_bytes(int H, int64_t rows);
-int inr_dbg_tc_layer(int H, int mode, const float* A, const float* W, const float* bias, float omega,
-                     const float* Cin, float* out0, float* out1, int64_t rows, int variant, void* scratch,
-                     int64_t scratch_bytes, void* stream);
-int inr_dbg_tc_dw(int H, const float* dZ, const float* S, float* gW, int64_t rows, int variant, void* scratch,
-                  int64_t scratch_bytes, void* stream);
-
-/* debug: clock64 stamps of the slot hand-offs of the fused forward kernel (pair 0), 4 per job */
-int inr_dbg_fused_trace_enable(int on);
-int inr_dbg_fused_trace_read(long long* host_out, int n);
+/* Test hooks and diagnostics (inr_dbg_*) are declared in include/inr_b200_debug.h: they are not part of the product ABI. */
 
 #ifdef __cplusplus
 }

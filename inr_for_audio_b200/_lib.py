@@ -49,7 +49,7 @@ _i64 = C.c_int64
 _f = C.c_float
 _i = C.c_int
 
-# name -> (restype, argtypes); mirrors include/inr_b200.h one to one
+# name -> (restype, argtypes); mirrors include/inr_b200.h (+ the inr_dbg_* test hooks of inr_b200_debug.h) one to one
 SIGNATURES = {
     "inr_last_error": (C.c_char_p, []),
     "inr_version": (_i, []),
@@ -90,6 +90,7 @@ SIGNATURES = {
     "inr_kan_forward": (_i, [C.POINTER(KanDesc), _p, _p, _p, _i64, _i64, _i64, _f, _p, _p, _i64, _p]),
     "inr_kan_loss_backward": (_i, [C.POINTER(KanDesc), _p, _p, _p, _p, _i64, _i64, _i64, _f, _i, _f, _p, _p, _p, _p, _p,
                                    _i64, _p]),
+    "inr_dbg_set_split_prefetch": (_i, [_i]),
     "inr_dbg_fused_trace_enable": (_i, [_i]),
     "inr_dbg_fused_trace_read": (_i, [_p, _i]),
     "inr_dbg_tc_scratch_bytes": (_i64, [_i, _i64]),

@@ -28,7 +28,8 @@ def _stamp(src):
     h.update(" ".join(FLAGS).encode())
     for f in [src] + sorted(x for x in os.listdir(CSRC) if x.endswith((".cuh", ".h"))):
         h.update(open(os.path.join(CSRC, f), "rb").read())
-    h.update(open(os.path.join(HERE, "..", "include", "inr_b200.h"), "rb").read())
+    for hdr in ("inr_b200.h", "inr_b200_debug.h"):
+        h.update(open(os.path.join(HERE, "..", "include", hdr), "rb").read())
     return h.hexdigest()
 
 

@@ -25,7 +25,9 @@ void set_error(const char* fmt, ...) {
 // inr_set_sm_limit: the persistent kernels size their grids from num_sms(); a limit below the device's SM count makes
 // every launch occupy only that many SMs, so that independent fits enqueued on different streams (clip-parallel mode)
 // run side by side on disjoint SMs instead of one after the other with one short tile loop per CTA.
-static int g_sm_limit = 0;
+// Per HOST THREAD (thread_local): it scopes the launches the calling thread enqueues between set(n) and set(0), so two
+// threads driving two fitters do not see each other's limit.
+static thread_local int g_sm_limit = 0;
 
 int num_sms() {
   if (g_sm_limit > 0) return g_sm_limit;

@@ -7,6 +7,7 @@
 #include <algorithm>
 
 #include "../../include/inr_b200.h"
+#include "../../include/inr_b200_debug.h"
 
 namespace inr {
 

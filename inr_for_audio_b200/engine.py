@@ -226,10 +226,9 @@ class SirenFitter:
         self.launches_per_step = None
 
     def set_precision(self, precision: str):
-        """Continue the same fit (parameters, Adam moments, step count, plateau scheduler, loss history) in the other
-        arithmetic mode: 'fp16' (tcgen05 throughput mode) <-> 'fp32' (parity mode).  The 16-bit mode's operand rounding
-        puts a floor under the loss late in a fit (profiles/r01e_c1_snr.md); a fit that starts in fp16 and finishes in
-        fp32 keeps most of the speed and the fp32 floor."""
+        """Continue the same fit (parameters, Adam moments, step count, plateau scheduler, loss history) in another
+        arithmetic mode: 'fp16' (plain fp16 tcgen05 operands: fastest, fit floor ~31 dB on gt_bach), 'fp16s' (fp16 hi+lo
+        forward operands: fp32-grade forward, reaches the reference's converged SNR), 'fp32' (CUDA cores)."""
         if precision == self.precision:
             return
         self.desc = self.spec.desc(precision)
@@ -382,13 +381,14 @@ class SirenFitter:
                              self.coord_scale)
 
     def rounding_noise_ratio(self) -> float:
-        """How much of the current fit error is the 16-bit mode's own rounding: mean((out_fp16 - out_fp32)^2) /
-        mean((out_fp32 - target)^2) at the current parameters (two forward passes; summed over the ranks of a sharded
-        fit).  Far below 1 the fp16 gradients are as good as fp32 ones; near 1 the fit sits on the fp16 noise floor."""
+        """How much of the current fit error is the plain fp16 mode's own forward rounding: mean((out_fp16 - out_fp16s)^2)
+        / mean((out_fp16s - target)^2) at the current parameters (two forward passes; summed over the ranks of a sharded
+        fit).  Far below 1 the fp16 mode fits as well as the split mode; near 1 the fit sits on the fp16 noise floor
+        (profiles/r02_c1_noise_fp16.jsonl: forward noise -31 dB of the signal, W rounding -33 dB, S rounding -36 dB)."""
         buf0 = self.ws.buf
         o16 = siren_forward(self.spec.desc("fp16"), self.params, self.coords, self.n, self.ws, self.i0, self.T_total,
                             self.coord_scale)
-        o32 = siren_forward(self.spec.desc("fp32"), self.params, self.coords, self.n, self.ws, self.i0, self.T_total,
+        o32 = siren_forward(self.spec.desc("fp16s"), self.params, self.coords, self.n, self.ws, self.i0, self.T_total,
                             self.coord_scale)
         sums = torch.stack([((o16 - o32).double() ** 2).sum(), ((o32 - self.target).double() ** 2).sum()])
         if self.pg is not None and self.world > 1:
@@ -399,9 +399,9 @@ class SirenFitter:
         num, den = (float(x) for x in sums.cpu())
         return num / max(den, 1e-300)
 
-    def step_auto(self, n_steps: int, check_every: int = 250, threshold: float = 0.05):
-        """n_steps steps that start in the fp16 tcgen05 mode and move to the fp32 mode once the fp16 rounding noise is
-        more than `threshold` of the fit error (checked every `check_every` steps: two forward passes, one host
+    def step_auto(self, n_steps: int, check_every: int = 250, threshold: float = 0.05, to: str = "fp16s"):
+        """n_steps steps that start in the plain fp16 mode and move to the split mode `to` once the fp16 forward rounding
+        noise is more than `threshold` of the fit error (checked every `check_every` steps: two forward passes, one host
         sync).  Returns the step index at which the fit switched (None if it stayed in fp16)."""
         switched = None
         done = 0
@@ -410,7 +410,7 @@ class SirenFitter:
             self.step(k)
             done += k
             if self.precision == "fp16" and done < n_steps and self.rounding_noise_ratio() > threshold:
-                self.set_precision("fp32")
+                self.set_precision(to)
                 switched = self.steps_done
         return switched
 

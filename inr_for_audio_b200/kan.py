@@ -199,6 +199,12 @@ def _kan_apply(layers: List[KANLinear], x: torch.Tensor) -> torch.Tensor:
                    layers[0].spline_order)
     flat = torch.cat([p.reshape(-1) for p in ps])
     grids = torch.cat([l.grid.reshape(-1) for l in layers]).contiguous().float()
+    if x.requires_grad and torch.is_grad_enabled():
+        # the device path returns parameter gradients only (run.py never reads d out / d coords);
+        # a differentiable INPUT -- stacked KANLinear modules, update_grid=True inside a training step -- would silently lose
+        # the gradient to earlier layers, so it is refused instead
+        raise L.InrLibraryError("KAN device path: gradients with respect to the input are not computed (the reference's "
+                                "KANLinear is differentiable in x); call the whole KAN as one module, or detach() the input")
     x2d = x.detach().reshape(-1, spec.in_features).contiguous().float()
     ws = _WS.setdefault(flat.device, Workspace(flat.device))
     out = _KanFn.apply(flat, grids, x2d, spec, ws)

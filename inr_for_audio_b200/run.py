@@ -86,10 +86,13 @@ def train(experiment_path: str, tag: str, inst: str, duration: int, num_channels
           loss_mode='mse', mode=None, decimation=1, bwe=False, num_hidden_features=256, num_sine=2, num_snake=2,
           num_tanh=0, num_freq=None, omega=22000, first_linear=False, last_linear=True, hidden_omega=30,
           a_initial=0.5, total_steps=20000, learning_rate=1e-3, min_learning_rate=1e-6, alpha=0.0,
-          prev_ckpt_path=None, visualization=False, *, precision='fp32', data_dir='data', seed=None, verbose=True,
+          prev_ckpt_path=None, visualization=False, *, precision='auto', data_dir='data', seed=None, verbose=True,
           spectral='stft'):
-    """run.py:30.  Extra keyword-only arguments: precision ('fp32' CUDA-core parity mode | 'fp16' tcgen05 mode | 'auto' =
-    start in fp16 and continue in fp32 once the fp16 rounding noise shows in the fit error, SirenFitter.step_auto),
+    """run.py:30.  Extra keyword-only arguments: precision ('fp32' CUDA-core mode | 'fp16s' tcgen05 mode with fp16 hi+lo
+    forward operands: fp32-grade forward, the parity-grade tensor-core mode | 'fp16' plain fp16 operands, fastest, fit
+    floor ~31 dB | 'fp16+' = start in fp16 and continue in fp16s once the fp16 rounding noise shows in the fit error,
+    SirenFitter.step_auto | 'auto' (default) = 'fp16s' where the shape allows it -- hidden width 128/256/512, input width
+    <= hidden width, a SIREN -- else 'fp32'),
     data_dir (the reference hard-codes 'data/'), seed (torch.manual_seed before model construction), spectral (which
     windowed-transform loss `alpha` mixes in: 'stft' = auraloss STFTLoss as run.py:128,160 does, 'mdct' / 'mdct_mse' =
     the MDCT-domain loss of BASELINE.json config 3)."""
@@ -100,10 +103,15 @@ def train(experiment_path: str, tag: str, inst: str, duration: int, num_channels
         experiment_folder = f'{experiment_path}/{inst}-{method}-{tag}'
     os.makedirs(experiment_folder)
     decimation = int(decimation)
-    auto_precision = precision == 'auto'
+    if precision == 'auto':
+        in_w = 2 * int(num_freq) if num_freq is not None else (2 if method == 'mdct' else 1)
+        tc_ok = arch != 'kan' and int(num_hidden_features) in (128, 256, 512) and in_w <= int(num_hidden_features) and \
+            (int(num_sine) + int(num_snake) + int(num_tanh)) >= 1
+        precision = 'fp16s' if tc_ok else 'fp32'
+    auto_precision = precision == 'fp16+'
     if auto_precision:
         if arch == 'kan':
-            raise NotImplementedError("precision='auto' is a SIREN schedule (SirenFitter.step_auto)")
+            raise NotImplementedError("precision='fp16+' is a SIREN schedule (SirenFitter.step_auto)")
         precision = 'fp16'
     takelog = False
     if num_freq is not None and method != 'wave':
@@ -225,7 +233,7 @@ def train(experiment_path: str, tag: str, inst: str, duration: int, num_channels
                     a_initial=a_initial, total_steps=total_steps, learning_rate=learning_rate,
                     min_learning_rate=min_learning_rate, alpha=alpha, prev_ckpt_path=prev_ckpt_path,
                     curr_ckpt_path=ckpt_path, visualization=visualization,
-                    precision=('auto' if auto_precision else precision), switched_to_fp32_at_step=switched_at,
+                    precision=('fp16+' if auto_precision else precision), switched_to_fp16s_at_step=switched_at,
                     **{'parameter_size(KB)': param_size / 1024, 'total_model_size(KB)': model_size,
                        'total_trainig_time(min)': total_time, 'SNR': snr_final,
                        'final_loss_dB': losses[-1] if losses else None})

@@ -425,7 +425,7 @@ def stmdct_torch(x: torch.Tensor, N: int = 2048, basis: Optional[torch.Tensor] =
 
 def mdct_loss(out: torch.Tensor, gt: torch.Tensor, N: int = 2048, kind: str = "l1") -> torch.Tensor:
     """MDCT-domain loss (config 3): mean |STMDCT(out) - STMDCT(gt)| (or squared), see module header."""
-    basis = mdct_basis(N, out.dtype)
+    basis = mdct_basis(N, out.dtype).to(out.device)
     a = stmdct_torch(out.reshape(-1), N, basis)
     b = stmdct_torch(gt.reshape(-1), N, basis)
     d = a - b

@@ -36,7 +36,10 @@ def main():
     for arm in args:
         t0 = time.time()
         snr, snr32 = {}, {}
-        if arm == "eager":
+        if arm in ("eager", "eager_tf32"):
+            # the reference loop in torch eager; eager_tf32 lets cuBLAS use TF32 tensor cores for the fp32 matmuls
+            # (10 explicit mantissa bits: the "fp32 mode on tensor cores" DESIGN.md §3 weighs against fp16 hi+lo)
+            torch.backends.cuda.matmul.allow_tf32 = (arm == "eager_tf32")
             ps = [p.clone().to(dev) for p in p0]
             coords = O.get_coord(T, 1).view(1, -1, 1).to(dev)
             gt = torch.from_numpy(gtn).view(1, -1, 1).to(dev)

@@ -95,3 +95,40 @@ def test_train_dropin_mdct_method(pkg, tmp_path):
     assert sr == 44100 and rec.shape == (1024 * F,) and np.all(np.isfinite(rec))
     sd = torch.load(ck, map_location="cpu")["model_state_dict"]
     assert sd["net.0.linear.weight"].shape == (64, 2)   # in_features = 2 (frequency, frame) coordinates
+
+
+@pytest.mark.parametrize("precision", ["fp16s"])
+def test_clip_parallel_snr_distribution_against_oracle(pkg, precision):
+    """SURVEY.md §8(d) for BASELINE.json config 5: a 16-clip subset of the batch (synthetic 2 s clips, T = 88 200, each its
+    own Siren(1,256,3,1,True) seeded by the clip index) fitted clip-parallel for 200 steps; per-clip SNR (utils.py:77-97)
+    and loss against the oracle loop (run.py:156-190 restated, torch fp32 on the same GPU) run on every clip alone."""
+    from oracle import inr_oracle as O
+    K, T, H, Lh, steps = 16, 88200, 256, 3, 200
+    gts = np.stack([pkg.utils.synth_waveform(T, seed=c) for c in range(K)])
+    flats = []
+    for c in range(K):
+        torch.manual_seed(c)
+        flats.append(pkg.Siren(1, H, Lh, 1, True).flat_parameters().clone())
+    spec = pkg.SirenSpec(1, H, Lh, 1, True)
+    tg = torch.from_numpy(gts).to(dev())
+    batch = pkg.ClipBatchFitter(spec, torch.stack(flats), tg, precision=precision, n_streams=8, hist_cap=steps)
+    batch.step(steps)
+    ours_snr = batch.snr_db(tg)
+    ours_loss = batch.losses()[:, -1]
+    ospec = O.SirenSpec(1, H, Lh, 1, True)
+    coords = O.get_coord(T, 1).view(1, -1, 1).to(dev())
+    ref_snr, ref_loss = [], []
+    for c in range(K):
+        ps = [p.to(dev()) for p in O.siren_init(ospec, seed=c)]
+        gt = tg[c].view(1, -1, 1)
+        losses, _, _ = O.siren_fit(ospec, ps, coords, gt, steps)
+        ref_loss.append(losses[-1])
+        ref_snr.append(O.calculate_snr(gts[c], O.siren_forward(ospec, ps, coords).cpu().numpy().ravel()))
+    ref_snr, ref_loss = np.array(ref_snr), np.array(ref_loss)
+    d = ours_snr - ref_snr
+    print("clip-parallel %s vs oracle, %d clips x %d steps: SNR ours median %.4f dB [%.4f, %.4f], oracle median %.4f dB "
+          "[%.4f, %.4f]; per-clip difference max %.4f dB; last-loss relative difference max %.2e" % (
+              precision, K, steps, np.median(ours_snr), ours_snr.min(), ours_snr.max(), np.median(ref_snr), ref_snr.min(),
+              ref_snr.max(), np.abs(d).max(), np.abs(ours_loss / ref_loss - 1).max()))
+    assert np.abs(d).max() <= 0.1 and abs(np.median(ours_snr) - np.median(ref_snr)) <= 0.03
+    np.testing.assert_allclose(ours_loss, ref_loss, rtol=2e-2)

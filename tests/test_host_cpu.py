@@ -23,9 +23,13 @@ def built():
 
 
 def test_library_exports_every_declared_symbol(built):
-    hdr = open(os.path.join(ROOT, "include", "inr_b200.h")).read()
-    hdr = re.sub(r"/\*.*?\*/", "", hdr, flags=re.S)
-    names = set(re.findall(r"\b(inr_[a-z0-9_]+)\s*\(", hdr))
+    names = set()
+    for h in ("inr_b200.h", "inr_b200_debug.h"):          # product ABI + the test hooks
+        hdr = open(os.path.join(ROOT, "include", h)).read()
+        hdr = re.sub(r"/\*.*?\*/", "", hdr, flags=re.S)
+        found = set(re.findall(r"\b(inr_[a-z0-9_]+)\s*\(", hdr))
+        assert (h == "inr_b200.h") == (not any(n.startswith("inr_dbg_") for n in found)), h
+        names |= found
     assert len(names) >= 10
     lib = ctypes.CDLL(built)
     for n in sorted(names):

@@ -300,7 +300,7 @@ def test_fp16_convergence_envelope(pkg, golden):
 
 def test_set_precision_and_step_auto(pkg, golden):
     """A fit continued in the other arithmetic mode keeps its parameters, Adam moments, step count and loss history;
-    step_auto leaves the fp16 mode once its rounding noise shows in the fit error (profiles/r01e_c1_snr.md)."""
+    step_auto leaves the plain fp16 mode for the split mode once its rounding noise shows in the fit error."""
     from scipy.io import wavfile
     sr, data = wavfile.read(os.path.join(ROOT, "data", "gt_bach.wav"))
     data = data.astype(np.float32)[44100:44100 + 8192]
@@ -325,7 +325,7 @@ def test_set_precision_and_step_auto(pkg, golden):
     assert f.opt_state().step == 310
     # threshold 0 forces the switch at the first check; a huge threshold never switches
     f2 = pkg.SirenFitter(spec, flat, gt, precision="fp16", hist_cap=4096)
-    assert f2.step_auto(300, check_every=100, threshold=0.0) == 100 and f2.precision == "fp32"
+    assert f2.step_auto(300, check_every=100, threshold=0.0) == 100 and f2.precision == "fp16s"
     f3 = pkg.SirenFitter(spec, flat, gt, precision="fp16", hist_cap=4096)
     assert f3.step_auto(300, check_every=100, threshold=1e9) is None and f3.precision == "fp16"
     np.testing.assert_allclose(f2.losses()[:3], f3.losses()[:3], rtol=1e-3)   # same fp16 start (later steps: split-K atomics)

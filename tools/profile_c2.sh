@@ -1,14 +1,18 @@
 #!/bin/bash
-# ncu evidence for the C2 bench (run under gpurun; one GPU).  Outputs under gpurun_out/.
-#   1. launch list (gpu__time_duration.sum per launch) of a short bench run
-#   2. one --set full capture of the three GEMM kernels (layer FWD, layer BWD, dW) and the streaming kernels
+# ncu evidence for the C2 bench in one arithmetic mode (run under gpurun; one GPU).  Outputs under gpurun_out/.
+#   usage: tools/profile_c2.sh <tag> <precision>
+#   1. the plain bench line of the same command (no ncu)
+#   2. launch list (gpu__time_duration.sum per launch) of a short bench run
+#   3. one --set full capture of one step's kernels (un-graphed probe: tests/diag/c2_step_probe.py)
 set -u
 mkdir -p gpurun_out
-TAG=${1:-r01b}
-python bench.py --steps 2 --warmup 3 --no-cpu-baseline > gpurun_out/${TAG}_plain.json 2> gpurun_out/${TAG}_plain.err || exit 1
+TAG=${1:-r02}; PREC=${2:-fp16s}
+ARGS="--steps 2 --warmup 3 --no-cpu-baseline --extras none --snr-steps 0 --precision $PREC"
+python bench.py $ARGS > gpurun_out/${TAG}_plain.json 2> gpurun_out/${TAG}_plain.err || exit 1
 ncu --metrics gpu__time_duration.sum --clock-control none -c 400 --csv --log-file gpurun_out/${TAG}_launches_bench_c2.csv \
-    python bench.py --steps 2 --warmup 3 --no-cpu-baseline > gpurun_out/${TAG}_ncu_launch.log 2>&1
-ncu --set full --clock-control none --import-source on -k regex:'k_tc_layer2|k_tc_dw|k_tc_last|k_tc_first' -s 12 -c 8 \
-    -o gpurun_out/${TAG}_full -f python bench.py --steps 1 --warmup 3 --no-cpu-baseline > gpurun_out/${TAG}_ncu_full.log 2>&1
+    python bench.py $ARGS > gpurun_out/${TAG}_ncu_launch.log 2>&1
+# the probe runs 1 untimed + 1 profiled step without a CUDA graph: skip the first step's 24 launches, capture the second's
+ncu --set full --clock-control none --import-source on -k regex:'k_tc_|k_adam' -s 24 -c 24 \
+    -o gpurun_out/${TAG}_full -f python tests/diag/c2_step_probe.py $PREC 1 > gpurun_out/${TAG}_ncu_full.log 2>&1
 ncu -i gpurun_out/${TAG}_full.ncu-rep --page raw --csv > gpurun_out/${TAG}_full_raw.csv 2> /dev/null
-ls -la gpurun_out
+ls -la gpurun_out | grep ${TAG}
