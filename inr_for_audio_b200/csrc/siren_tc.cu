@@ -20,8 +20,11 @@ using namespace tc;
 // ------------------------------------------------------------------------------------------------ pack
 // Forward operand slices are [slice][hi | lo (split)][K/8][NSF][8] (NSF columns per CTA: tc_ns_fwd); the dX operand is
 // never split: [slice][K/8][NSB][8].
+// split: the forward operand carries W * wscale (a power of two, undone by the epilogue's acc_scale) so that the lo halves
+// |lo| <= 2^-12 |W wscale| stay in fp16's NORMAL range: trained SIREN weights are ~0.02, their unscaled lo halves ~5e-6 would
+// be subnormal (absolute spacing 6e-8 = only 18 bits of W, a -64 dB forward-noise floor at C1; with the scale < -75 dB).
 __global__ void __launch_bounds__(256) k_tc_pack(const float* __restrict__ params, SirenLayout lay, int NSF, int NSB, int split,
-                                                 op16* __restrict__ Wf, op16* __restrict__ Wb) {
+                                                 float wscale, op16* __restrict__ Wf, op16* __restrict__ Wb) {
   const int H = lay.H;
   const int64_t per = (int64_t)H * H;
   const int64_t total = per * lay.L;
@@ -35,8 +38,9 @@ __global__ void __launch_bounds__(256) k_tc_pack(const float* __restrict__ param
     const op16 w = to_op(wv);
     // forward operand: B[n = out][k = in]
     const int64_t fo = (int64_t)l * fper + (int64_t)(o / NSF) * fslice + ((int64_t)(in >> 3) * NSF + (o % NSF)) * 8 + (in & 7);
-    Wf[fo] = w;
-    if (split) Wf[fo + (int64_t)H * NSF] = to_op(wv - __half2float(w));
+    const op16 wf = to_op(wv * wscale);
+    Wf[fo] = wf;
+    if (split) Wf[fo + (int64_t)H * NSF] = to_op(wv * wscale - __half2float(wf));
     // dX operand: B[n = in][k = out]
     Wb[(int64_t)l * per + (int64_t)(in / NSB) * ((int64_t)H * NSB) + ((int64_t)(o >> 3) * NSB + (in % NSB)) * 8 + (o & 7)] = w;
   }
@@ -46,13 +50,13 @@ __global__ void __launch_bounds__(256) k_tc_pack(const float* __restrict__ param
 // Encoded coordinates (in_features = 2*num_freq > 2, run.py:81-82,141-144) on the tcgen05 path: the input rows become one
 // more tile image X (fp16, zero-padded to H columns) and layer 0 one more H x H layer GEMM with W_0 zero-padded to H
 // input columns; its weight gradient is the dW GEMM against X, cut back to (H x in).  Needs in_features <= H.
-__global__ void __launch_bounds__(256) k_tc_pack0(const float* __restrict__ W0, int in, int H, int NS, int split,
+__global__ void __launch_bounds__(256) k_tc_pack0(const float* __restrict__ W0, int in, int H, int NS, int split, float wscale,
                                                   op16* __restrict__ Wf0) {
   const int total = H * H;
   const int64_t fslice = (int64_t)H * NS * (split ? 2 : 1);
   for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < total; i += gridDim.x * blockDim.x) {
     const int o = i / H, k = i - o * H;
-    const float v = k < in ? W0[(int64_t)o * in + k] : 0.f;
+    const float v = (k < in ? W0[(int64_t)o * in + k] : 0.f) * wscale;
     const op16 w = to_op(v);
     const int64_t fo = (int64_t)(o / NS) * fslice + ((int64_t)(k >> 3) * NS + (o % NS)) * 8 + (k & 7);
     Wf0[fo] = w;
@@ -488,6 +492,8 @@ static int ns_of(int H) { return tc_ns(H); }
 static bool is_split(const inr_siren_desc* d) { return d->precision == INR_PREC_FP16S; }
 // columns per CTA of the FORWARD operand slices
 static int ns_fwd(int H, bool split) { return split ? (H >= 512 ? 64 : H / 2) : ns_of(H); }
+// power-of-two scale of the packed FORWARD weights (k_tc_pack): keeps the lo halves of the split mode out of fp16's subnormals
+static float wscale_fwd(bool split) { return split ? 64.f : 1.f; }
 
 struct TcPlan {
   int64_t pack_bytes, img_bytes_per_row, fixed_bytes;
@@ -743,12 +749,12 @@ static int pack_weights(const inr_siren_desc* d, const float* params, const TcWo
   const int64_t total = (int64_t)lay.H * lay.H * lay.L;
   int blocks = (int)std::min<int64_t>(cdiv(total, 256), (int64_t)num_sms() * 8);
   { LaunchScope ls("k_tc_pack", st);
-    k_tc_pack<<<blocks, 256, 0, st>>>(params, lay, ns_fwd(lay.H, w.split), ns_of(lay.H), w.split ? 1 : 0, w.Wf, w.Wb); }
+    k_tc_pack<<<blocks, 256, 0, st>>>(params, lay, ns_fwd(lay.H, w.split), ns_of(lay.H), w.split ? 1 : 0, wscale_fwd(w.split), w.Wf, w.Wb); }
   INR_LAUNCH_CHECK();
   if (lay.in > 2) {
     LaunchScope ls("k_tc_pack", st);
     k_tc_pack0<<<(lay.H * lay.H + 255) / 256, 256, 0, st>>>(params + lay.w_off(0), lay.in, lay.H, ns_fwd(lay.H, w.split),
-                                                            w.split ? 1 : 0, w.Wf0);
+                                                            w.split ? 1 : 0, wscale_fwd(w.split), w.Wf0);
     INR_LAUNCH_CHECK();
   }
   return INR_OK;
@@ -831,7 +837,7 @@ static int fwd_layer_tc(const inr_siren_desc* d, const SirenLayout& lay, const f
   const int64_t fw = w.split ? 2 : 1;
   LayerParams p = layer_params(H, Sin, w.Wf + (int64_t)(l - 1) * fw * H * H, params + lay.b_off(l),
                                kind == ACT_SINE ? d->hidden_omega_0 : 1.f, Sout, Cout, nullptr, tiles, ns_fwd(H, w.split));
-  p.A_lo = Sin_lo; p.out0_lo = Sout_lo;
+  p.A_lo = Sin_lo; p.out0_lo = Sout_lo; p.acc_scale = 1.f / wscale_fwd(w.split);
   if (kind == ACT_SNAKE) { p.avec = params + lay.a_off(l); p.out2 = Eout; }
   return tc_layer(H, kind == ACT_SINE ? MODE_FWD : (kind == ACT_SNAKE ? MODE_FWD_SNAKE : MODE_FWD_TANH), p, st);
 }
@@ -849,7 +855,7 @@ static int first_layer_wide(const inr_siren_desc* d, const SirenLayout& lay, con
   const int kind = lay.kind(0);
   LayerParams p = layer_params(H, X, w.Wf0, params + lay.b_off(0), kind == ACT_SINE ? d->first_omega_0 : 1.f, S0, C0,
                                nullptr, tiles, ns_fwd(H, w.split));
-  p.A_lo = Xlo; p.out0_lo = S0lo;
+  p.A_lo = Xlo; p.out0_lo = S0lo; p.acc_scale = 1.f / wscale_fwd(w.split);
   if (kind == ACT_SNAKE) { p.avec = params + lay.a_off(0); p.out2 = E0; }
   return tc_layer(H, kind == ACT_SINE ? MODE_FWD : MODE_FWD_SNAKE, p, st);
 }

@@ -214,6 +214,7 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(Layer2Cfg<H, SPLIT>:
     const int quad = warp & 3;
     const int half = e >> 2;
     const int row = quad * 32 + lane;
+    const float om_acc = p.omega * p.acc_scale;          // forward: the packed weights carry 1 / acc_scale (a power of two)
     constexpr int NCH = NP / 64;                          // 32-column chunks per warp
     uint4 cin[NCH][4];
     auto cin_ptr = [&](int tile, int ci, int j) {
@@ -255,7 +256,7 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(Layer2Cfg<H, SPLIT>:
                 float y[2], dz[2], da[2];
 #pragma unroll
                 for (int u = 0; u < 2; ++u) {
-                  const float z = v[cc + u] + s_bias[c * 32 + cc + u];
+                  const float z = __fmaf_rn(v[cc + u], p.acc_scale, s_bias[c * 32 + cc + u]);
                   if (MODE == MODE_FWD_SNAKE) {
                     const float a = s_a[c * 32 + cc + u], ia = __fdividef(1.0f, a);
                     float sn, cs;
@@ -285,8 +286,8 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(Layer2Cfg<H, SPLIT>:
 #pragma unroll
               for (int h = 0; h < 4; ++h) {
                 const int cc = j * 8 + h * 2;
-                const float t0 = __fmaf_rn(v[cc], p.omega, s_bias[c * 32 + cc]);
-                const float t1 = __fmaf_rn(v[cc + 1], p.omega, s_bias[c * 32 + cc + 1]);
+                const float t0 = __fmaf_rn(v[cc], om_acc, s_bias[c * 32 + cc]);
+                const float t1 = __fmaf_rn(v[cc + 1], om_acc, s_bias[c * 32 + cc + 1]);
                 float s0, c0, s1, c1;
                 __sincosf(t0, &s0, &c0);
                 __sincosf(t1, &s1, &c1);

@@ -22,7 +22,8 @@ MARKS = [500, 2000, 20000]
 
 
 def main():
-    args = [a for a in sys.argv[1:] if not a.startswith("--")] or ["fp32", "fp16", "eager"]
+    known = ("fp32", "fp16", "fp16s", "eager", "eager_tf32")
+    args = [a for a in sys.argv[1:] if a in known] or ["fp32", "fp16s", "eager"]
     total = int(sys.argv[sys.argv.index("--steps") + 1]) if "--steps" in sys.argv else 20000
     seed = int(sys.argv[sys.argv.index("--seed") + 1]) if "--seed" in sys.argv else 0
     marks = [m for m in MARKS if m <= total]
