@@ -26,7 +26,7 @@ def _sources():
 def _stamp(src):
     h = hashlib.sha256()
     h.update(" ".join(FLAGS).encode())
-    for f in [src] + sorted(x for x in os.listdir(CSRC) if x.endswith((".cuh", ".h"))):
+    for f in [src] + sorted(x for x in os.listdir(CSRC) if x.endswith((".cuh", ".h", ".inc"))):
         h.update(open(os.path.join(CSRC, f), "rb").read())
     for hdr in ("inr_b200.h", "inr_b200_debug.h"):
         h.update(open(os.path.join(HERE, "..", "include", hdr), "rb").read())

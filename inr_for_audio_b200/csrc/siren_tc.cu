@@ -13,6 +13,7 @@
 
 #include "tc_gemm2.cuh"
 #include "tc_fused.cuh"
+#include "tc_fused_split.cuh"
 
 namespace inr {
 using namespace tc;
@@ -620,8 +621,8 @@ int tc_dw(int H, const DwParams& p, cudaStream_t st) {
 }
 
 static bool fused_ok(const inr_siren_desc* d) {
-  // the fused forward keeps single fp16 images on chip: two hi + lo slot pairs do not fit 227 KB at H = 256
-  return !is_split(d) && (d->hidden_features == 128 || d->hidden_features == 256) &&
+  // fp16: k_tc_fused_fwd (two ping-pong slots); fp16s: k_tc_fused_fwd_s (one hi + lo slot, layers pipelined by K chunk)
+  return (d->hidden_features == 128 || d->hidden_features == 256) &&
          d->hidden_layers >= 1 && d->hidden_layers <= FUSED_MAX_L && d->num_snake == 0 && d->num_tanh == 0 &&
          d->first_linear == 0 && d->in_features <= 2;
 }
@@ -654,9 +655,26 @@ struct FusedLast {   // arguments of the fused head + loss + dZ_L epilogue (Fuse
   const float* gsc; unsigned* gmax_acc;
 };
 
+template <int H>
+static int launch_fused_s(const FusedSParams& p, cudaStream_t st) {
+  using Cfg = FusedSCfg<H>;
+  static bool attr_set = false;
+  if (!attr_set) {
+    INR_CUDA_CHECK(cudaFuncSetAttribute(k_tc_fused_fwd_s<H>, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg::SMEM_BYTES));
+    attr_set = true;
+  }
+  int pairs = num_sms() / 2;
+  const int num_dt = (p.f.num_tiles + 1) / 2;
+  if (pairs > num_dt) pairs = num_dt;
+  { LaunchScope ls("k_tc_fused_fwd", st);
+    k_tc_fused_fwd_s<H><<<2 * pairs, Cfg::THREADS, Cfg::SMEM_BYTES, st>>>(p); }
+  INR_LAUNCH_CHECK();
+  return INR_OK;
+}
+
 static int fused_forward(const inr_siren_desc* d, const float* params, const op16* Wf, const float* coords,
                          int64_t rows, int tiles, int64_t g0, int64_t T_total, float scale, op16* const* S,
-                         op16* const* C, const FusedLast* fl, cudaStream_t st) {
+                         op16* const* C, const FusedLast* fl, cudaStream_t st, op16* S_lo_last = nullptr) {
   SirenLayout lay = layout_of(d);
   FusedParams p;
   p.Wf = Wf; p.W0 = params + lay.w_off(0); p.B0 = params + lay.b_off(0);
@@ -674,6 +692,13 @@ static int fused_forward(const inr_siren_desc* d, const float* params, const op1
   p.gsc = fl ? fl->gsc : nullptr; p.gmax_acc = fl ? fl->gmax_acc : nullptr;
   p.dbg = 0;
   p.trace = g_fused_trace; p.trace_jobs = g_fused_trace ? kFusedTraceJobs : 0;
+  if (is_split(d)) {
+    FusedSParams ps;
+    ps.f = p; ps.f.trace = nullptr; ps.f.trace_jobs = 0;
+    ps.S_lo_last = fl ? nullptr : S_lo_last;
+    ps.acc_scale = 1.f / wscale_fwd(true);
+    return lay.H == 256 ? launch_fused_s<256>(ps, st) : launch_fused_s<128>(ps, st);
+  }
   return lay.H == 256 ? launch_fused<256, 16>(p, st) : launch_fused<128, 16>(p, st);
 }
 
@@ -880,10 +905,10 @@ int siren_tc_forward(const inr_siren_desc* d, const float* params, const float* 
       op16* Sl[FUSED_MAX_L + 1] = {nullptr};
       Sl[L] = S[0];
       if ((rc = fused_forward(d, params, w.Wf, coords ? coords + r0 * lay.in : nullptr, rows, tiles, i0 + r0, T_total, scale,
-                              Sl, nullptr, nullptr, st)))
+                              Sl, nullptr, nullptr, st, Slo[0])))
         return rc;
       if ((rc = last_layer(d, params, S[0], nullptr, nullptr, nullptr, rows, tiles, 0, 0.f, nullptr, nullptr, nullptr,
-                           out + r0, 0, st)))
+                           out + r0, 0, st, nullptr, Slo[0])))
         return rc;
       continue;
     }
@@ -969,7 +994,8 @@ int siren_tc_train(const inr_siren_desc* d, const float* params, const float* co
                         opt ? &opt->loss_acc[0] : nullptr, out ? out + r0 : nullptr, w.gsc,
                         opt ? reinterpret_cast<unsigned*>(&opt->gmax_acc) : nullptr};
         if (fused_tail) Sl[L] = nullptr;
-        if ((rc = fused_forward(d, params, w.Wf, xc, rows, tiles, i0 + r0, T_total, scale, Sl, Cl, fused_tail ? &fl : nullptr, st)))
+        if ((rc = fused_forward(d, params, w.Wf, xc, rows, tiles, i0 + r0, T_total, scale, Sl, Cl, fused_tail ? &fl : nullptr, st,
+                                Slo(L))))
           return rc;
       } else {
         if (w.x_image >= 0) {
