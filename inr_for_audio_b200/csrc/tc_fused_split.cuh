@@ -7,8 +7,8 @@
 //
 //   * two TMEM accumulators alternate between consecutive layers of the tile;
 //   * the epilogue of layer l (omega*acc/wscale + omega*b -> sincos -> hi, lo) overwrites the slot IN PLACE, 64 input
-//     columns (one K chunk of layer l+1) at a time -- layer l's MMAs have all completed by then, so the old columns are
-//     dead -- and signals a per-chunk barrier;
+//     columns (one K chunk of layer l+1) at a time, ALL 16 warps on the same chunk (32 rows x 16 columns each) -- layer l's
+//     MMAs have all completed by then, so the old columns are dead -- and signals a per-chunk barrier;
 //   * the MMA thread starts layer l+1 on K chunk c as soon as chunk c is in place, accumulating into the OTHER
 //     accumulator while the epilogue warps are still draining the first: the second half of epilogue(l) overlaps the
 //     first half of MMA(l+1).
@@ -19,7 +19,7 @@
 // Barriers (leader = cluster rank 0; s = ring stage, a = accumulator j & 1 of job j, c = 64-column input chunk):
 //   wfull[s]    leader 2 (own producer tx + peer relay), peer 1      wempty[s]  both 1 (multicast commit)
 //   accfull[a]  both 1 (multicast commit after the job's last MMA)   accfree[a] leader 2*EW (every epilogue warp of the pair)
-//   inready[c]  leader 2*EW/NCK*... see init: the warps of both CTAs that write chunk c
+//   inready[c]  leader 2*EW: every epilogue warp of the pair writes a 16-column strip of chunk c
 #pragma once
 #include "tc_fused.cuh"
 
@@ -95,10 +95,9 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(FusedSCfg<H>::THREAD
   const int n_k = pair < num_dt ? (num_dt - pair + npairs - 1) / npairs : 0;   // double tiles of this pair
   const int L = p.L;
   auto dt_of = [&](int k) { return pair + k * npairs; };
-  constexpr int NPART = EW / 4;                          // column parts (warps per TMEM lane quadrant): 4
-  constexpr int NCH = NP / (32 * NPART);                 // 32-column chunks per warp: 2 (H = 256), 1 (128)
-  // a 64-column input chunk is written by the warps of two column parts, four lane quadrants, both CTAs
-  constexpr int INREADY_COUNT = 2 * 4 * 2;
+  constexpr int NPART = EW / 4;                          // column parts (warps per TMEM lane quadrant): 4 x 16 columns = one chunk
+  // every epilogue warp of both CTAs writes its 32 rows x 16 columns of each 64-column input chunk
+  constexpr int INREADY_COUNT = 2 * EW;
 
   if (threadIdx.x == 0) {
     for (int s = 0; s < Cfg::STAGES; ++s) { mbar_init(bar_wfull(s), leader ? 2 : 1); mbar_init(bar_wempty(s), 1); }

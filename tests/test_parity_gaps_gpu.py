@@ -229,24 +229,26 @@ def test_resumed_fit_loss_history_is_its_own(pkg):
 def test_kan_snr_after_500_steps_against_the_reference_loop(pkg, golden, prec):
     """BASELINE.json configs[3]'s network, kan.KAN([1,256,256,1]) (run.py:109-110), fitted by run.py's loop to 8 192
     samples of gt_bach: SNR (utils.py:77-97) at steps 100 / 300 / 500 against the reference's own runs at 8 threads and
-    at 1 thread (tests/golden/make_golden.py kan_converge).  The fit is as chaotic as the SIREN one, so the bar is the
-    reference's own band widened by 1.5 dB (fp32) / 3 dB (bf16 operands)."""
+    at 1 thread (tests/golden/make_golden.py kan_converge): per-step losses and SNR.  (With grid_range [-1, 1] and a single
+    input the KAN barely moves in 500 steps -- 0.012 dB -- in the reference too; the check is that it moves the same way.)"""
     g = golden("kan_converge")
     marks = [int(m) for m in g["marks"]]
     gtn = g["gt"].astype(np.float32)
     torch.manual_seed(2)
     k = pkg.KAN([1, 256, 256, 1])
-    np.testing.assert_array_equal(np.concatenate([p.detach().numpy().ravel() for p in k.parameters()]), g["p0"])
-    f = pkg.KanFitter(k.spec, k.flat_parameters(), k.flat_grids(), torch.from_numpy(gtn).to(dev()), None, precision=prec)
+    # same seeded init (the lstsq inside kan.py:131-133 moves single ulps with the host thread count: 0.3 % of the entries)
+    np.testing.assert_allclose(np.concatenate([p.detach().numpy().ravel() for p in k.parameters()]), g["p0"], atol=1e-7)
+    f = pkg.KanFitter(k.spec, torch.from_numpy(g["p0"]), k.flat_grids(), torch.from_numpy(gtn).to(dev()), None, precision=prec,
+                      hist_cap=512)
     done, ours = 0, []
     for m in marks:
         f.step(m - done)
         done = m
         ours.append(float(pkg.calculate_snr(gtn, f.forward().cpu().numpy())))
-    print("KAN %s SNR at %s: ours %s | ref t8 %s | ref t1 %s" % (prec, marks, np.round(ours, 2), np.round(g["snr_t8"], 2), np.round(g["snr_t1"], 2)))
-    tol = 1.5 if prec == "fp32" else 3.0
-    for i, m in enumerate(marks):
-        if m < 100:
-            continue
-        lo, hi = min(g["snr_t8"][i], g["snr_t1"][i]), max(g["snr_t8"][i], g["snr_t1"][i])
-        assert lo - tol <= ours[i] <= hi + tol + 3.0, (m, ours[i], lo, hi)
+    ls = f.losses()
+    ref = g["losses_t8"]
+    print("KAN %s SNR at %s: ours %s | ref t8 %s | ref t1 %s; loss rel diff max %.2e" % (
+        prec, marks, np.round(ours, 4), np.round(g["snr_t8"], 4), np.round(g["snr_t1"], 4), np.abs(ls / ref - 1).max()))
+    # this fit is NOT chaotic over 500 steps (the reference at 1 and at 8 threads agrees to 8 digits): compare directly
+    np.testing.assert_allclose(ls, ref, rtol=2e-4 if prec == "fp32" else 5e-3)
+    np.testing.assert_allclose(ours, g["snr_t8"], atol=2e-3 if prec == "fp32" else 2e-2)
