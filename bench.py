@@ -499,6 +499,15 @@ def kernel_profile(cx, job, prec, steps):
     return kern, roofline, stages
 
 
+def snr_reference():
+    """SNR of the reference's own loop (torch eager fp32 on a B200) at the same marks, measured once and committed
+    (a C2 run takes 8 minutes: 482 ms/step)."""
+    try:
+        return json.load(open(os.path.join(ROOT, "profiles", "r02_snr_reference.json")))
+    except Exception:
+        return {}
+
+
 def default_precision(wl):
     return "bf16" if wl["kind"] == "kan" else "fp16s"
 
@@ -519,12 +528,7 @@ def run_ours(args):
         for m in marks:
             fit.step(m - fit.steps_done)
             snr["db_at_step"][str(m)] = job.snr_db(fit)
-        ref_file = os.path.join(ROOT, "profiles", "r02_snr_reference.json")
-        if os.path.exists(ref_file):
-            try:
-                snr["reference"] = json.load(open(ref_file)).get(name)
-            except Exception:
-                pass
+        snr["reference"] = snr_reference().get(name)
     lps = head["launches_per_step"]
     del fit
     torch.cuda.empty_cache()
@@ -547,10 +551,14 @@ def run_ours(args):
             try:
                 r, j2, f2 = measure(cx, wname, default_precision(w), k, 3, False)
                 if w["kind"] != "clips":
-                    m = min(500, max(args.snr_steps, 0))
-                    if m > f2.steps_done:
-                        f2.step(m - f2.steps_done)
-                        r["snr_db"] = {str(m): j2.snr_db(f2)}
+                    r["snr_db"] = {}
+                    for m in ((500, 2000) if wname == "c1" else (500,)):     # C1: SURVEY.md §8(d) marks (20 000: profiles/)
+                        if args.snr_steps and m > f2.steps_done:
+                            f2.step(m - f2.steps_done)
+                            r["snr_db"][str(m)] = j2.snr_db(f2)
+                    ref = snr_reference().get(wname)
+                    if ref:
+                        r["snr_reference"] = ref
                 else:
                     r["snr_db_median_over_clips"] = {str(f2.steps_done): j2.snr_db(f2)}
                 del f2

@@ -92,7 +92,7 @@ typedef struct {
   float gmax_prev;     /* ... of the previous step: sets the fp16 loss scale         */
   float omb1, omb2;    /* (float)(1.0 - beta1), (float)(1.0 - beta2) formed in float64, as torch passes them */
   int32_t hist_base;   /* Adam step at which loss_hist[0] was written (resume)      */
-  int32_t reserved0;
+  int32_t reserved0;   /* ticket counter of k_adam (the last block out runs the scheduler); zero between launches */
   double loss_acc[4];  /* [0] time-loss numerator sum, [1] spectral loss, [2..3] scratch; zeroed per step */
 } inr_opt_state;
 

@@ -2,14 +2,18 @@
 //
 // The reference syncs the host 3-4 times per step (loss.item() x3, scheduler.step(loss)); here the whole
 // optimiser state lives in an inr_opt_state in device memory, so a fit step never touches the host:
-//   k_adam      one pass over the flat params: 28 B/param (r g,p,m,v; w p,m,v) + 4 B to re-zero the gradient
-//   k_opt_post  1 thread: loss = acc*scale, plateau state machine, t += 1, next bias corrections in float64
+//   k_adam      one pass over the flat params: 28 B/param (r g,p,m,v; w p,m,v) + 4 B to re-zero the gradient; the LAST block to
+//               finish (atomic ticket) then runs the scheduler: loss = acc*scale, plateau state machine, t += 1, next bias
+//               corrections in float64 -- every block has read the step's scalars by then, so one launch does both
 #include "common.cuh"
 
 namespace inr {
 
+__device__ void opt_post(inr_opt_state* st, float loss_scale, float* loss_hist);
+
 __global__ void __launch_bounds__(256) k_adam(float* __restrict__ p, float* __restrict__ g, float* __restrict__ m,
-                                              float* __restrict__ v, int64_t P, const inr_opt_state* __restrict__ st) {
+                                              float* __restrict__ v, int64_t P, inr_opt_state* st, float loss_scale,
+                                              float* loss_hist) {
   const float b1 = st->beta1, b2 = st->beta2, eps = st->adam_eps;
   const float step_size = st->step_size, bc2_sqrt = st->bc2_sqrt;
   const float w1 = st->omb1, w2 = st->omb2;   // (float)(1.0 - beta) formed in float64, as torch's Python scalars are
@@ -42,6 +46,16 @@ __global__ void __launch_bounds__(256) k_adam(float* __restrict__ p, float* __re
       }
     }
   }
+  // ---- scheduler + next step's scalars, by the last block out
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    __threadfence();
+    const unsigned ticket = atomicAdd(reinterpret_cast<unsigned*>(&st->reserved0), 1u);
+    if (ticket == gridDim.x - 1) {
+      st->reserved0 = 0;
+      opt_post(st, loss_scale, loss_hist);
+    }
+  }
 }
 
 __device__ void opt_prepare_next(inr_opt_state* st) {
@@ -64,7 +78,7 @@ __global__ void k_opt_init(inr_opt_state* st, float lr, float min_lr, int hist_c
 }
 
 // torch/optim/lr_scheduler.py ReduceLROnPlateau.step (mode='min', threshold_mode='rel', cooldown=0)
-__global__ void k_opt_post(inr_opt_state* st, float loss_scale, float* loss_hist) {
+__device__ void opt_post(inr_opt_state* st, float loss_scale, float* loss_hist) {
   const float loss = (float)(st->loss_acc[0] * (double)loss_scale + st->loss_acc[1]);
   st->last_loss = loss;
   if (loss_hist && st->hist_cap > 0) loss_hist[(st->step - st->hist_base) % st->hist_cap] = loss;
@@ -112,10 +126,7 @@ int adam_step(float* params, float* grads, float* m, float* v, int64_t P, inr_op
   int blocks = (int)std::min<int64_t>(cdiv(P, 256 * 4), (int64_t)num_sms() * 8);
   if (blocks < 1) blocks = 1;
   { LaunchScope ls("k_adam", s);
-  k_adam<<<blocks, 256, 0, s>>>(params, grads, m, v, P, opt); }
-  INR_LAUNCH_CHECK();
-  { LaunchScope ls("k_opt_post", s);
-  k_opt_post<<<1, 1, 0, s>>>(opt, loss_scale, loss_hist); }
+  k_adam<<<blocks, 256, 0, s>>>(params, grads, m, v, P, opt, loss_scale, loss_hist); }
   INR_LAUNCH_CHECK();
   return INR_OK;
 }

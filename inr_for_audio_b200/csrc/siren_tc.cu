@@ -18,6 +18,25 @@
 namespace inr {
 using namespace tc;
 
+// ------------------------------------------------------------------------------------------------ loss scale
+// fp16 dZ images need a loss scale: g = d loss / d out is O(1/T).  gsc = {gs, 1/gs} with gs the power of two that puts
+// max |g| of the PREVIOUS step (opt->gmax_prev, measured by the last-layer kernels) at 2^10, so |dZ_L| = |g w omega C|
+// stays around 10^2 with two decades of head-room to 65504 (conversions saturate) and eight decades above the fp16
+// normal minimum.  Without history (first step, or no optimiser state: the autograd path) the estimate is
+// 4 * grad_scale (|2 diff| <= 4 for peak-normalised audio) plus max |extra_g|.  Consumers of dZ (dW, column sums)
+// multiply by 1/gs: exact, it is a power of two.
+__device__ __forceinline__ void gscale_compute(const inr_opt_state* opt, float extra_max, float grad_scale, int has_target,
+                                               float* gsc) {
+  float est = opt ? opt->gmax_prev : 0.f;
+  if (!(est > 0.f)) est = (has_target ? 4.f * grad_scale : 0.f) + extra_max;
+  est = fmaxf(est, extra_max);
+  int e = 0;
+  if (est > 0.f && est < 3e38f) e = 10 - (int)ceilf(log2f(est));
+  e = max(-100, min(100, e));
+  gsc[0] = exp2f((float)e);
+  gsc[1] = exp2f((float)-e);
+}
+
 // ------------------------------------------------------------------------------------------------ pack
 // Forward operand slices are [slice][hi | lo (split)][K/8][NSF][8] (NSF columns per CTA: tc_ns_fwd); the dX operand is
 // never split: [slice][K/8][NSB][8].
@@ -25,7 +44,11 @@ using namespace tc;
 // |lo| <= 2^-12 |W wscale| stay in fp16's NORMAL range: trained SIREN weights are ~0.02, their unscaled lo halves ~5e-6 would
 // be subnormal (absolute spacing 6e-8 = only 18 bits of W, a -64 dB forward-noise floor at C1; with the scale < -75 dB).
 __global__ void __launch_bounds__(256) k_tc_pack(const float* __restrict__ params, SirenLayout lay, int NSF, int NSB, int split,
-                                                 float wscale, op16* __restrict__ Wf, op16* __restrict__ Wb) {
+                                                 float wscale, op16* __restrict__ Wf, op16* __restrict__ Wb,
+                                                 const inr_opt_state* __restrict__ opt, float grad_scale, int has_target,
+                                                 float* __restrict__ gsc) {
+  // gsc != NULL: the fused step without an upstream gradient -- this launch also sets the step's loss scale
+  if (gsc && blockIdx.x == 0 && threadIdx.x == 0) gscale_compute(opt, 0.f, grad_scale, has_target, gsc);
   const int H = lay.H;
   const int64_t per = (int64_t)H * H;
   const int64_t total = per * lay.L;
@@ -373,13 +396,7 @@ __global__ void __launch_bounds__(512, 1) k_tc_last2(const op16* __restrict__ S,
   }
 }
 
-// ------------------------------------------------------------------------------------------------ loss scale
-// fp16 dZ images need a loss scale: g = d loss / d out is O(1/T).  gsc = {gs, 1/gs} with gs the power of two that puts
-// max |g| of the PREVIOUS step (opt->gmax_prev, measured by the last-layer kernels) at 2^10, so |dZ_L| = |g w omega C|
-// stays around 10^2 with two decades of head-room to 65504 (conversions saturate) and eight decades above the fp16
-// normal minimum.  Without history (first step, or no optimiser state: the autograd path) the estimate is
-// 4 * grad_scale (|2 diff| <= 4 for peak-normalised audio) plus max |extra_g|.  Consumers of dZ (dW, column sums)
-// multiply by 1/gs: exact, it is a power of two.
+// ------------------------------------------------------------------------------------------------ loss scale (stand-alone launches)
 __global__ void __launch_bounds__(256) k_tc_absmax(const float* __restrict__ x, int64_t n, unsigned* __restrict__ out) {
   float m = 0.f;
   for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x)
@@ -389,15 +406,7 @@ __global__ void __launch_bounds__(256) k_tc_absmax(const float* __restrict__ x, 
 }
 __global__ void k_tc_gscale(const inr_opt_state* __restrict__ opt, const unsigned* __restrict__ extra_max, float grad_scale,
                             int has_target, float* __restrict__ gsc) {
-  const float ex = extra_max ? __uint_as_float(*extra_max) : 0.f;
-  float est = opt ? opt->gmax_prev : 0.f;
-  if (!(est > 0.f)) est = (has_target ? 4.f * grad_scale : 0.f) + ex;
-  est = fmaxf(est, ex);
-  int e = 0;
-  if (est > 0.f && est < 3e38f) e = 10 - (int)ceilf(log2f(est));
-  e = max(-100, min(100, e));
-  gsc[0] = exp2f((float)e);
-  gsc[1] = exp2f((float)-e);
+  gscale_compute(opt, extra_max ? __uint_as_float(*extra_max) : 0.f, grad_scale, has_target, gsc);
 }
 
 // ------------------------------------------------------------------------------------------------ column sums
@@ -769,12 +778,17 @@ static int carve(const inr_siren_desc* d, int training, int64_t n, void* ws, int
   return INR_OK;
 }
 
-static int pack_weights(const inr_siren_desc* d, const float* params, const TcWorkspace& w, cudaStream_t st) {
+struct GscaleFold { const inr_opt_state* opt; float grad_scale; int has_target; };
+
+static int pack_weights(const inr_siren_desc* d, const float* params, const TcWorkspace& w, cudaStream_t st,
+                        const GscaleFold* gf = nullptr) {
   SirenLayout lay = layout_of(d);
   const int64_t total = (int64_t)lay.H * lay.H * lay.L;
   int blocks = (int)std::min<int64_t>(cdiv(total, 256), (int64_t)num_sms() * 8);
   { LaunchScope ls("k_tc_pack", st);
-    k_tc_pack<<<blocks, 256, 0, st>>>(params, lay, ns_fwd(lay.H, w.split), ns_of(lay.H), w.split ? 1 : 0, wscale_fwd(w.split), w.Wf, w.Wb); }
+    k_tc_pack<<<blocks, 256, 0, st>>>(params, lay, ns_fwd(lay.H, w.split), ns_of(lay.H), w.split ? 1 : 0, wscale_fwd(w.split), w.Wf, w.Wb,
+                                      gf ? gf->opt : nullptr, gf ? gf->grad_scale : 0.f, gf ? gf->has_target : 0,
+                                      gf ? w.gsc : nullptr); }
   INR_LAUNCH_CHECK();
   if (lay.in > 2) {
     LaunchScope ls("k_tc_pack", st);
@@ -966,8 +980,11 @@ int siren_tc_train(const inr_siren_desc* d, const float* params, const float* co
   INR_REQUIRE(phase == 3 || w.chunk_rows >= n, INR_E_WORKSPACE,
               "split forward/backward needs the whole row range in one workspace chunk (%lld rows > %lld)", (long long)n,
               (long long)w.chunk_rows);
-  if ((phase & 1) && (rc = pack_weights(d, params, w, st))) return rc;
-  if ((phase & 2) && (rc = set_gscale(w, opt, extra_gout, n, target, grad_scale, st))) return rc;
+  // the fused step without an upstream gradient sets its loss scale inside the pack launch
+  const bool fold_gs = phase == 3 && !extra_gout;
+  const GscaleFold gf = {opt, grad_scale, target != nullptr};
+  if ((phase & 1) && (rc = pack_weights(d, params, w, st, fold_gs ? &gf : nullptr))) return rc;
+  if ((phase & 2) && !fold_gs && (rc = set_gscale(w, opt, extra_gout, n, target, grad_scale, st))) return rc;
   for (int64_t r0 = 0; r0 < n; r0 += w.chunk_rows) {
     const int64_t rows = std::min(w.chunk_rows, n - r0);
     const int64_t rows_pad = round_up(rows, TILE_ROWS);
