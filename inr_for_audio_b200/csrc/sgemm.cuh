@@ -290,22 +290,12 @@ static inline void sgemm_launch(dim3 grid, cudaStream_t st, const float* A, int6
   auto al16 = [](const void* p) { return (reinterpret_cast<uintptr_t>(p) & 15) == 0; };
   const bool va = A_KC ? (sAk == 1 && sAm % 4 == 0 && K % 4 == 0) : (sAm == 1 && sAk % 4 == 0 && M % 4 == 0);
   const bool vb = B_KC ? (sBk == 1 && sBn % 4 == 0 && K % 4 == 0) : (sBn == 1 && sBk % 4 == 0 && N % 4 == 0);
-  // K-loop unroll factor of the main loop: 2 (default) keeps the loop body inside the instruction cache; the fully unrolled
-  // body (INR_SGEMM_KU=16, 17 KB) measured 10 % slower (fp32 C1 9.23 vs 8.32 ms/step; ncu: no_instruction stalls)
-  static int ku = -1;
-  if (ku < 0) { const char* e = getenv("INR_SGEMM_KU"); ku = e ? atoi(e) : 2; }
+  // Vector path: K loop unrolled by 2 (the body stays inside the instruction cache: the fully unrolled 17 KB body measured
+  // 10 % slower, fp32 C1 9.23 vs 8.32 ms/step, ncu no_instruction stalls) and the inner product on packed fma.rn.f32x2
+  // (fp32 C1 step 8.31 -> 7.89 ms); both A/Bs in profiles/r01e_sgemm_ncu_summary.md.
   if (va && vb && al16(A) && al16(B) && k_chunk % 4 == 0) {
-    static int f2 = -1;
-    if (f2 < 0) { const char* e = getenv("INR_SGEMM_F2"); f2 = e ? atoi(e) : 1; }   // default on: fp32 C1 step 8.31 -> 7.89 ms
-    if (f2)
-      k_sgemm<A_KC, B_KC, EPI, true, 2, true><<<grid, 256, 0, st>>>(A, sAm, sAk, B, sBn, sBk, M, N, K, k_chunk, bias, omega,
-                                                                    out0, out1, ldo, aux0, aux1);
-    else if (ku != 16)
-      k_sgemm<A_KC, B_KC, EPI, true, 2><<<grid, 256, 0, st>>>(A, sAm, sAk, B, sBn, sBk, M, N, K, k_chunk, bias, omega, out0,
-                                                              out1, ldo, aux0, aux1);
-    else
-      k_sgemm<A_KC, B_KC, EPI, true, 16><<<grid, 256, 0, st>>>(A, sAm, sAk, B, sBn, sBk, M, N, K, k_chunk, bias, omega, out0,
-                                                               out1, ldo, aux0, aux1);
+    k_sgemm<A_KC, B_KC, EPI, true, 2, true><<<grid, 256, 0, st>>>(A, sAm, sAk, B, sBn, sBk, M, N, K, k_chunk, bias, omega,
+                                                                  out0, out1, ldo, aux0, aux1);
   } else
     k_sgemm<A_KC, B_KC, EPI, false><<<grid, 256, 0, st>>>(A, sAm, sAk, B, sBn, sBk, M, N, K, k_chunk, bias, omega, out0,
                                                           out1, ldo, aux0, aux1);

@@ -1,14 +1,17 @@
 // siren_tc.cu -- the fp16 tensor-core SIREN fit path (INR_PREC_FP16): host orchestration + the streaming kernels
 // around the tcgen05 GEMMs of tc_gemm.cuh.  All activations live in HBM as fp16 "tile images" (tc_common.cuh).
 //
-//   per step and row chunk (DESIGN.md "fp16 path"):
-//     k_tc_pack        fp32 master weights -> fp16 UMMA operand images W_l (fwd) and W_l^T (dX)      once per call
-//     k_tc_first       S_0, C_0 = sincos(omega_0 (W_0 x + b_0))      fp32, accurate sincosf (models.py:114-115)
-//     k_tc_layer<FWD>  S_l, C_l = sincos(omega (S_{l-1} W_l^T + b_l))                               l = 1..L
-//     k_tc_last        out = S_L w + b; loss; g = dloss/dout; dZ_L = g w omega C_L (over C_L); g -> gvec
-//     k_tc_dw          gW_l += dZ_l^T S_{l-1}                                                       l = L..1
-//     k_tc_layer<BWD>  dZ_{l-1} = (dZ_l W_l) omega C_{l-1}  (over C_{l-1})                          l = L..1
-//     k_tc_colsum      gb_l += colsum(dZ_l); gw_out += gvec^T S_L; gW_0 += dZ_0^T x, gb_0 += colsum(dZ_0)
+//   per step and row chunk:
+//     k_tc_pack        fp32 master weights -> fp16 UMMA operand images W_l (fwd: [hi | lo] x wscale in the split mode) and
+//                      W_l^T (dX); sets the step's loss scale when there is no upstream gradient
+//     H <= 256, sine stacks:   k_tc_fused_fwd / k_tc_fused_fwd_s   first layer + all hidden layers + head + loss + dZ_L
+//     otherwise:
+//       k_tc_first       S_0 [+ lo], C_0 = sincos(omega_0 (W_0 x + b_0))      fp32 argument, Cody-Waite + MUFU (models.py:114-115)
+//       k_tc_layer2<FWD> S_l [+ lo], C_l = sincos(omega (S_{l-1} W_l^T + b_l))                          l = 1..L
+//       k_tc_last2       out = S_L w + b; loss; g = dloss/dout; dZ_L = gs g w omega C_L (over C_L); last-layer gradients
+//     k_tc_dw / dw2    gW_l += dZ_l^T S_{l-1} / gs, gb_l += colsum(dZ_l) / gs                            l = L..1
+//     k_tc_layer2<BWD> dZ_{l-1} = (dZ_l W_l) omega C_{l-1}  (over C_{l-1})                               l = L..1
+//     k_tc_colsum      gW_0 += dZ_0^T x / gs, gb_0 += colsum(dZ_0) / gs; `a` gradients of Snake layers
 #include <stdlib.h>
 
 #include "tc_gemm2.cuh"

@@ -55,11 +55,12 @@ __device__ __forceinline__ bool mbar_try_wait(uint32_t bar, uint32_t parity) {
       : "memory");
   return ok != 0;
 }
-// Bounded wait: a protocol bug must surface as a trapped kernel (an error the host sees), never as a hang.
+// Bounded wait: a protocol bug must surface as a trapped kernel (an error the host sees), never as a hang.  2^24 polls of a
+// try_wait (each suspends for the hardware's time limit) is seconds: far beyond any DRAM / L2 stall under contention.
 __device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
   uint32_t spins = 0;
   while (!mbar_try_wait(bar, parity)) {
-    if (++spins > (1u << 20)) {
+    if (++spins > (1u << 24)) {
       printf("inr: mbarrier wait timed out (block %d thread %d bar %u parity %u)\n", blockIdx.x, threadIdx.x, bar, parity);
       __trap();
     }

@@ -100,7 +100,7 @@ struct FusedParams {
   double* loss_acc;            // += sum (out - target)^2 or |out - target|
   const float* gsc;            // {gs, 1/gs}: power-of-two loss scale of the fp16 dZ images (siren_tc.cu k_tc_gscale)
   unsigned* gmax_acc;          // max |g| of this step (float bits, atomicMax) or NULL: the next step's scale
-  // timing ablations (INR_TC_FUSED_DBG bit mask, results are WRONG when set; profiles/r01c_notes.md):
+  // timing ablations (bit mask, always 0 in the product: results are WRONG when set; how profiles/r01c_notes.md was measured):
   // 1 = no stash stores to HBM, 2 = no sin/cos (raw accumulator values), 4 = head: dot + loss only (no dZ_L, no g_w)
   int dbg;
   // hand-off trace (inr_dbg_fused_trace): pair 0's leader CTA writes clock64() stamps, 4 per job in MMA order:

@@ -1,4 +1,4 @@
-"""fp16 convergence-envelope probe (the tests/test_siren_gpu.py case) under the current INR_TC_* switches."""
+"""fp16 convergence-envelope probe (the tests/test_siren_gpu.py case) for one arithmetic mode: python tools/envelope_probe.py [fp16s|fp16|fp32] [runs]."""
 import os, sys
 import numpy as np, torch
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
@@ -17,5 +17,4 @@ for rep in range(int(sys.argv[2]) if len(sys.argv) > 2 else 3):
     f.step(1500)
     losses = f.losses().astype(np.float64)
     env = 10 * np.log10(sig / np.minimum.accumulate(losses))
-    print(prec, os.environ.get("INR_TC_FUSED", "-"), os.environ.get("INR_TC_FUSED_LAST", "-"), os.environ.get("INR_TC_FUSED_BWD", "-"),
-          " ".join("%d:%.2f" % (i + 1, env[i]) for i in (9, 49, 99, 299, 599, 999, 1499)), "loss[:3]", losses[:3])
+    print(prec, " ".join("%d:%.2f" % (i + 1, env[i]) for i in (9, 49, 99, 299, 599, 999, 1499)), "loss[:3]", losses[:3])
