@@ -330,3 +330,35 @@ def test_set_precision_and_step_auto(pkg, golden):
     assert f3.step_auto(300, check_every=100, threshold=1e9) is None and f3.precision == "fp16"
     np.testing.assert_allclose(f2.losses()[:3], f3.losses()[:3], rtol=1e-3)   # same fp16 start (later steps: split-K atomics)
     assert len(f2.losses()) == len(f3.losses()) == 300
+
+
+@pytest.mark.parametrize("prec", ["fp16s", "fp16"])
+@pytest.mark.parametrize("gain", [1e3, 1e-4])
+def test_loss_scale_adapts_to_the_target_scale(pkg, prec, gain):
+    """The fp16 dZ images carry a power-of-two loss scale chosen from the PREVIOUS step's max |d loss / d out| (k_tc_gscale,
+    opt.gmax); the first step only has the guess 4 * grad_scale, made for peak-normalised audio.  A target 1000x larger
+    saturates some dZ entries on that first step (conversions are cvt.satfinite: clipped, never inf/nan), a target 1e-4x
+    smaller pushes them towards fp16 subnormals; from the second step on the scale follows the data and the gradient
+    is as accurate as for a normalised target."""
+    from oracle import inr_oracle as O
+    H, Lh, n = 128, 2, 6000
+    spec = pkg.SirenSpec(1, H, Lh, 1, True)
+    ospec = O.SirenSpec(1, H, Lh, 1, True)
+    ps = O.siren_init(ospec, seed=11)
+    flat = torch.cat([p.reshape(-1) for p in ps])
+    gt = torch.from_numpy(pkg.utils.synth_waveform(n, seed=4).copy()) * gain
+    f = pkg.SirenFitter(spec, flat, gt.to(dev()), precision=prec, use_graph=False, lr=1e-6)   # tiny lr: parameters ~ unchanged
+    f.step(2)
+    assert np.all(np.isfinite(f.losses())) and torch.isfinite(f.params).all()
+    st = f.opt_state()
+    assert st.gmax_prev > 0
+    cur = [p.clone() for p in torch.split(f.params.cpu(), spec.param_sizes())]
+    cur = [c.view_as(p) for c, p in zip(cur, ps)]
+    loss_o, _, grads_o, _ = O.siren_loss_and_grads(ospec, cur, O.get_coord(n, 1).view(-1, 1), gt.view(-1, 1))
+    loss, grads, _ = f.loss_and_grads()
+    go = torch.cat([x.reshape(-1) for x in grads_o]).numpy().astype(np.float64)
+    gerr = np.linalg.norm(grads.cpu().numpy() - go) / np.linalg.norm(go)
+    print("%s target x %g: gmax_prev %.3e, loss rel err %.2e, grad rel err %.2e" % (
+        prec, gain, st.gmax_prev, abs(loss - float(loss_o)) / float(loss_o), gerr))
+    assert abs(loss - float(loss_o)) <= 1e-3 * float(loss_o)
+    assert gerr <= 5e-3
