@@ -383,6 +383,12 @@ def measure(cx, name, prec, steps, warmup, detail):
     pk = peaks()
     fit = job.make(True)
     fit.step(warmup)
+    if not detail:
+        # the side workloads have steps of 0.3 .. 5 ms: a 20-step region is over before the SM clock has left idle (the job
+        # set-up before it is host work).  Warm up for ~40 ms of device time and time at least ~80 ms, same K on every rank.
+        est = max(cx.timed_device(fit.step, 3) / 3.0, 1e-3)
+        fit.step(int(min(400, max(0, 40.0 / est))))
+        steps = int(min(400, max(steps, 80.0 / est)))
     sampler = ClockSampler(cx.local)
     if cx.rank == 0:
         sampler.start()
