@@ -21,10 +21,6 @@ int inr_dbg_tc_dw(int H, const float* dZ, const float* S, float* gW, int64_t row
 int inr_dbg_fused_trace_enable(int on);
 int inr_dbg_fused_trace_read(long long* host_out, int n);
 
-/* A/B switch of the L2 prefetch in the operand-split layer kernel's producer (double tiles ahead; 0 = off, the default:
- * measured slower on B200, profiles/r02_notes.md) */
-int inr_dbg_set_split_prefetch(int double_tiles);
-
 #ifdef __cplusplus
 }
 #endif

@@ -90,7 +90,6 @@ SIGNATURES = {
     "inr_kan_forward": (_i, [C.POINTER(KanDesc), _p, _p, _p, _i64, _i64, _i64, _f, _p, _p, _i64, _p]),
     "inr_kan_loss_backward": (_i, [C.POINTER(KanDesc), _p, _p, _p, _p, _i64, _i64, _i64, _f, _i, _f, _p, _p, _p, _p, _p,
                                    _i64, _p]),
-    "inr_dbg_set_split_prefetch": (_i, [_i]),
     "inr_dbg_fused_trace_enable": (_i, [_i]),
     "inr_dbg_fused_trace_read": (_i, [_p, _i]),
     "inr_dbg_tc_scratch_bytes": (_i64, [_i, _i64]),

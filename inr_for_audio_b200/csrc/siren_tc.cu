@@ -702,7 +702,6 @@ static int fused_forward(const inr_siren_desc* d, const float* params, const op1
   p.g_wlast = fl ? fl->grads + lay.w_off(lay.L + 1) : nullptr; p.g_blast = fl ? fl->grads + lay.b_off(lay.L + 1) : nullptr;
   p.loss_acc = fl ? fl->loss_acc : nullptr;
   p.gsc = fl ? fl->gsc : nullptr; p.gmax_acc = fl ? fl->gmax_acc : nullptr;
-  p.dbg = 0;
   p.trace = g_fused_trace; p.trace_jobs = g_fused_trace ? kFusedTraceJobs : 0;
   if (is_split(d)) {
     FusedSParams ps;
@@ -714,12 +713,11 @@ static int fused_forward(const inr_siren_desc* d, const float* params, const op1
   return lay.H == 256 ? launch_fused<256, 16>(p, st) : launch_fused<128, 16>(p, st);
 }
 
-static int g_split_pf_dt = 0;   // inr_dbg_set_split_prefetch: A/B switch of the split producer's L2 prefetch (profiles/r02_notes.md)
 static LayerParams layer_params(int H, const op16* A, const op16* Bp, const float* bias, float omega,
                                 op16* out0, op16* out1, const op16* Cin, int tiles, int ns = 0) {
   LayerParams p;
   p.A = A; p.Bpack = Bp; p.bias = bias; p.omega = omega; p.out0 = out0; p.out1 = out1; p.Cin = Cin; p.num_tiles = tiles;
-  p.avec = nullptr; p.out2 = nullptr; p.pf_dt = g_split_pf_dt;
+  p.avec = nullptr; p.out2 = nullptr;
   p.a_lbo = TILE_ROWS * 16; p.a_sbo = 128;            // K-major, no swizzle: LBO = next 8-feature group, SBO = next 8 rows
   p.b_lbo = (uint32_t)(ns ? ns : ns_of(H)) * 16; p.b_sbo = 128;
   return p;
@@ -1091,7 +1089,6 @@ int siren_tc_loss_backward(const inr_siren_desc* d, const float* params, const f
 }  // namespace inr
 
 // ---- debug: clock64 stamps of the slot hand-offs in pair 0 of k_tc_fused_fwd (profiles/r01c_notes.md)
-extern "C" int inr_dbg_set_split_prefetch(int dt) { inr::g_split_pf_dt = dt; return INR_OK; }
 extern "C" int inr_dbg_fused_trace_enable(int on) {
   using namespace inr;
   if (on && !g_fused_trace) {

@@ -100,9 +100,6 @@ struct FusedParams {
   double* loss_acc;            // += sum (out - target)^2 or |out - target|
   const float* gsc;            // {gs, 1/gs}: power-of-two loss scale of the fp16 dZ images (siren_tc.cu k_tc_gscale)
   unsigned* gmax_acc;          // max |g| of this step (float bits, atomicMax) or NULL: the next step's scale
-  // timing ablations (bit mask, always 0 in the product: results are WRONG when set; how profiles/r01c_notes.md was measured):
-  // 1 = no stash stores to HBM, 2 = no sin/cos (raw accumulator values), 4 = head: dot + loss only (no dZ_L, no g_w)
-  int dbg;
   // hand-off trace (inr_dbg_fused_trace): pair 0's leader CTA writes clock64() stamps, 4 per job in MMA order:
   // [MMA thread passed aready, MMA thread committed tfull, epilogue warp 0 passed tfull, epilogue warp 0 signalled]
   long long* trace;
@@ -288,8 +285,8 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(64 + 32 * EW, 1) k_t
             }
             const size_t loc = ((size_t)(g0 + j) * TILE_ROWS + row) * 8;   // elements inside the tile image
             *reinterpret_cast<uint4*>(img + loc * 2) = make_uint4(so[0], so[1], so[2], so[3]);
-            if (p.S[0] && !(p.dbg & 1)) *reinterpret_cast<uint4*>(p.S[0] + tile_off + loc) = make_uint4(so[0], so[1], so[2], so[3]);
-            if (p.C[0] && !(p.dbg & 1)) *reinterpret_cast<uint4*>(p.C[0] + tile_off + loc) = make_uint4(co[0], co[1], co[2], co[3]);
+            if (p.S[0]) *reinterpret_cast<uint4*>(p.S[0] + tile_off + loc) = make_uint4(so[0], so[1], so[2], so[3]);
+            if (p.C[0]) *reinterpret_cast<uint4*>(p.C[0] + tile_off + loc) = make_uint4(co[0], co[1], co[2], co[3]);
           }
         }
       }
@@ -380,7 +377,7 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(64 + 32 * EW, 1) k_t
               if (half == 0) { gb_local += g; gmax_local = fmaxf(gmax_local, fabsf(g)); }
             }
             if (half == 0) s_g[row] = g;
-            if (valid && !(p.dbg & 4)) {
+            if (valid) {
               const float gw = g * gs * p.omega_h;
 #pragma unroll
               for (int ci = 0; ci < NCH; ++ci) {
@@ -406,7 +403,7 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(64 + 32 * EW, 1) k_t
               }
             }
             asm volatile("bar.sync 1, %0;" ::"n"(32 * EW) : "memory");      // S_L image and s_g complete
-            if (valid && !(p.dbg & 4)) {
+            if (valid) {
               constexpr int TPG = (32 * EW) / (H / 8);                 // threads per feature group: 8 (H = 256), 16 (H = 128)
               constexpr int RPT = TILE_ROWS / TPG;               // rows per thread
               const int et = threadIdx.x - 64;                   // 0..255 over the epilogue warps
@@ -447,15 +444,15 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(64 + 32 * EW, 1) k_t
                   const float t0 = __fmaf_rn(v[cc], p.omega_h, bias_l[c * 32 + cc]);
                   const float t1 = __fmaf_rn(v[cc + 1], p.omega_h, bias_l[c * 32 + cc + 1]);
                   float s0, c0, s1, c1;
-                  if (p.dbg & 2) { s0 = t0; c0 = t0; s1 = t1; c1 = t1; }
-                  else { __sincosf(t0, &s0, &c0); __sincosf(t1, &s1, &c1); }
+                  __sincosf(t0, &s0, &c0);
+                  __sincosf(t1, &s1, &c1);
                   o0[h] = pack_op2(s0, s1);
                   o1[h] = pack_op2(c0, c1);
                 }
                 const size_t loc = ((size_t)(g0 + j) * TILE_ROWS + row) * 8;
                 if (l < L) *reinterpret_cast<uint4*>(img + loc * 2) = make_uint4(o0[0], o0[1], o0[2], o0[3]);
-                if (Sl && !(p.dbg & 1)) *reinterpret_cast<uint4*>(Sl + tile_off + loc) = make_uint4(o0[0], o0[1], o0[2], o0[3]);
-                if (Cl && !(p.dbg & 1)) *reinterpret_cast<uint4*>(Cl + tile_off + loc) = make_uint4(o1[0], o1[1], o1[2], o1[3]);
+                if (Sl) *reinterpret_cast<uint4*>(Sl + tile_off + loc) = make_uint4(o0[0], o0[1], o0[2], o0[3]);
+                if (Cl) *reinterpret_cast<uint4*>(Cl + tile_off + loc) = make_uint4(o1[0], o1[1], o1[2], o1[3]);
               }
             }
           }

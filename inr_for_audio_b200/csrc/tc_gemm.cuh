@@ -41,7 +41,6 @@ struct LayerParams {
   const op16* A_lo = nullptr;  // operand split (k_tc_layer2<.., SPLIT>): lo image of A; Bpack then holds [hi | lo] per slice
   op16* out0_lo = nullptr;     // operand split: lo image of out0 (the next layer's A_lo)
   float acc_scale = 1.f;       // forward modes: multiplies the accumulator (1 / the power-of-two scale of the packed weights)
-  int pf_dt = 0;               // operand split: L2 prefetch distance in double tiles (0 = off)
   int num_tiles;
   uint32_t a_lbo, a_sbo, b_lbo, b_sbo;  // descriptor strides (bytes); passed in so a test can probe the convention
 };

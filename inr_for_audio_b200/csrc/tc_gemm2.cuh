@@ -131,13 +131,7 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(Layer2Cfg<H, SPLIT>:
         const int tile = 2 * dt + (int)rank;
         const bool valid = tile < p.num_tiles;
         const uint8_t* asrc = reinterpret_cast<const uint8_t*>(abase) + (size_t)tile * (TILE_ROWS * H * 2);
-        // the NQ pairs that share this row tile pull it into L2 a few tiles ahead, a chunk each, so the ring's copies see
-        // L2-hit latency: 96 KB in flight per SM cannot cover DRAM latency at the rate three MMAs per K step consume
-        const int pf_tile = tile + 2 * p.pf_dt * dt_stride;
-        const uint8_t* pfsrc = reinterpret_cast<const uint8_t*>(abase) + (size_t)pf_tile * (TILE_ROWS * H * 2);
         for (int c = 0; c < Cfg::NCHUNK; ++c) {
-          if (SPLIT && lane < 2 && p.pf_dt > 0 && pf_tile < p.num_tiles && (c % Cfg::NQ) == q)
-            bulk_prefetch_l2(pfsrc + (size_t)c * Cfg::A_HALF, Cfg::A_HALF);
           mbar_wait(bar_empty(s), phase ^ 1);
           if (lane == 0) {
             // odd tile count: the MMA multiplies stale A rows of this CTA, nobody stores them -- but this CTA's half of

@@ -1,5 +1,5 @@
 """Diagnostic: a few un-graphed C2 steps in one arithmetic mode, per-kernel event times printed (and the process ncu attaches to).
-    python tests/diag/c2_step_probe.py PREC [steps] [split_prefetch_dt] [T]"""
+    python tests/diag/c2_step_probe.py PREC [steps] [unused] [T]"""
 import ctypes as C, json, os, sys
 import torch
 ROOT = os.path.dirname(os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
@@ -11,9 +11,6 @@ steps = int(sys.argv[2]) if len(sys.argv) > 2 else 2
 pf = int(sys.argv[3]) if len(sys.argv) > 3 else 0
 T = int(sys.argv[4]) if len(sys.argv) > 4 else 2646000
 H, Lh = int(os.environ.get("PROBE_H", "512")), int(os.environ.get("PROBE_L", "5"))
-lib = L.lib()
-lib.inr_dbg_set_split_prefetch.restype = C.c_int
-lib.inr_dbg_set_split_prefetch(pf)
 dev = torch.device("cuda:0")
 gt = torch.from_numpy(P.utils.synth_waveform(T, seed=0)).to(dev)
 torch.manual_seed(0)
