@@ -151,6 +151,23 @@ int inr_siren_forward(const inr_siren_desc* d, const float* params, const float*
                       int64_t i0, int64_t T_total, float coord_scale, float* out, void* workspace,
                       int64_t workspace_bytes, void* stream);
 
+/* No counterpart in the reference (its tensors come from PyTorch's allocator): inr_siren_forward for callers that
+ * cannot allocate device memory -- a real-time audio render callback, where cudaMalloc/cudaFree (driver-wide locks,
+ * possible device synchronisation) are as forbidden as malloc; a process whose HBM is already owned by another pool so
+ * a late cudaMalloc fails; a plain-C or scripting host with no CUDA runtime binding of its own.  Same arguments and
+ * result as inr_siren_forward minus the workspace: the activations go through ONE array of INR_STATIC_SCRATCH_BYTES
+ * built into the library (every GPU that loads the library holds it until the process exits).
+ *   - the whole call must fit: inr_siren_workspace_bytes(d, n, 0) <= INR_STATIC_SCRATCH_BYTES, else INR_E_WORKSPACE
+ *     (about 16 000 rows at H = 256, 8 000 at H = 512 in INR_PREC_FP32); split the rows yourself beyond that;
+ *   - every call on a device shares the array, which keeps the previous call's bytes (the forward overwrites all it
+ *     reads): calls whose GPU work may overlap -- two streams, two threads -- race; keep them in one stream order;
+ *   - the first call on each device looks the array's device address up and loads the module there: make it a warm-up
+ *     call, outside the latency-critical part and before any stream capture is begun;
+ *   - calls no cudaMalloc/cudaFree or allocating library routine (unless the inr_profile_* event profiler is on). */
+#define INR_STATIC_SCRATCH_BYTES (32 * 1024 * 1024)
+int inr_siren_forward_static(const inr_siren_desc* d, const float* params, const float* coords, int64_t n, int64_t i0,
+                             int64_t T_total, float coord_scale, float* out, void* stream);
+
 /* run.py:158-169 + 185: forward, loss = weight * reduce(out, target), and backward to the flat gradient.
  *   grads (P floats)  += d loss / d params      (ACCUMULATES: zero it, or let inr_adam_step re-zero it)
  *   opt->loss_acc[0]  += sum_j (out-target)^2 or |out-target|   (caller divides by count)

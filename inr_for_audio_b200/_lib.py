@@ -13,6 +13,7 @@ LIB_PATH = os.path.join(HERE, "libinr_b200.so")
 INR_OK, INR_E_BADARG, INR_E_UNSUPPORTED, INR_E_CUDA, INR_E_WORKSPACE = 0, -1, -2, -3, -4
 PREC_FP32, PREC_BF16, PREC_FP16, PREC_FP16S = 0, 1, 2, 3
 LOSS_MSE, LOSS_MAE = 0, 1
+STATIC_SCRATCH_BYTES = 32 * 1024 * 1024   # INR_STATIC_SCRATCH_BYTES
 PRECISIONS = {"fp32": PREC_FP32, "bf16": PREC_BF16, "fp16": PREC_FP16, "fp16s": PREC_FP16S}
 
 
@@ -64,6 +65,7 @@ SIGNATURES = {
     "inr_encode_gaussian": (_i, [_p, _i, _i64, _i64, _i64, _f, _p, _i, _p, _p]),
     "inr_encode_nerf": (_i, [_p, _i, _i64, _i64, _i64, _f, _i, _f, _p, _p]),
     "inr_siren_forward": (_i, [C.POINTER(SirenDesc), _p, _p, _i64, _i64, _i64, _f, _p, _p, _i64, _p]),
+    "inr_siren_forward_static": (_i, [C.POINTER(SirenDesc), _p, _p, _i64, _i64, _i64, _f, _p, _p]),
     "inr_siren_loss_backward": (_i, [C.POINTER(SirenDesc), _p, _p, _p, _i64, _i64, _i64, _f, _i, _f, _p, _p, _p, _p,
                                      _p, _i64, _p]),
     "inr_siren_train_forward": (_i, [C.POINTER(SirenDesc), _p, _p, _i64, _i64, _i64, _f, _p, _p, _i64, _p]),
