@@ -7,8 +7,8 @@
 N > 1 is launched by the driver under torch.distributed.run (one rank per GPU, NCCL); the coordinates of the ONE
 waveform are sharded by rank and every step has one sum-allreduce of [grads | loss]  => "scaling": "strong".
 Prints ONE JSON line (rank 0).  The headline (value, e2e, roofline) is BASELINE.json configs[1] (C2) in the
-parity-grade tensor-core mode (fp16s: fp16 hi+lo forward operands, fp32-grade forward; 36.8 dB at 20 000 C1 steps where
-the reference loop reaches 36.0).  Beside it, in the same line:
+parity-grade tensor-core mode (fp16s: fp16 hi+lo forward operands, fp32-grade forward; median 36.08 dB over 19 C1 fits
+of 20 000 steps where the reference loop's 8 fits have median 35.93: profiles/r02_c1_seeds.md).  Beside it, in the same line:
   fast_mode   the same workload in the plain fp16 mode (one MMA per K step; fit floor ~31 dB on C1)
   snr         SNR dB at fixed steps of this very fit (the metric's second half), with the oracle loop's figure
   workloads   the other BASELINE.json configs: c1 (gt_bach.wav), c3 (MDCT loss), c3stft, c4 (KAN), c5 (clip-parallel)

@@ -30,7 +30,7 @@ extern "C" {
 #define INR_E_WORKSPACE (-4)
 
 /* arithmetic of the hidden HxH contractions */
-#define INR_PREC_FP32 0 /* CUDA-core fp32 FMA (the parity mode: matches the fp32 reference to ~1e-6)   */
+#define INR_PREC_FP32 0 /* CUDA-core fp32 FMA everywhere, like the reference: matches it to ~1e-6 per step  */
 #define INR_PREC_BF16 1 /* tcgen05 kind::f16, bf16 operands, fp32 TMEM accumulation: the KAN tensor-core mode.
                            SIREN descriptors are refused: 8-bit significands floor a SIREN fit at ~24 dB      */
 #define INR_PREC_FP16 2 /* tcgen05 kind::f16, IEEE fp16 operands (11-bit significands) with a power-of-two loss
@@ -54,8 +54,8 @@ extern "C" {
  *   num_tanh       x   nn.Linear(H->H) + nn.Tanh()
  *   last               nn.Linear(H->1) (outermost_linear)   or SineLayer(H->1)
  * flat params = state_dict order: W, b per layer, with a Snake layer's `a` (H floats) right after its bias.
- * Both modes (INR_PREC_FP32, INR_PREC_FP16) take every stack; INR_PREC_FP16 needs H in {128,256,512}, at least one
- * HxH layer and in_features <= H. */
+ * INR_PREC_FP32, INR_PREC_FP16 and INR_PREC_FP16S take every stack; the two tcgen05 modes need H in {128,256,512}, at
+ * least one HxH layer and in_features <= H.  INR_PREC_BF16 is refused for a SIREN descriptor. */
 typedef struct {
   int32_t in_features;     /* 1 (waveform), 2 (MDCT image), or the width of an encoded
                               coordinate (2*num_freq, run.py:81-82; fp16 mode: <= hidden_features) */
@@ -97,6 +97,11 @@ typedef struct {
 } inr_opt_state;
 
 const char* inr_last_error(void);
+/* ABI version of the library that was loaded; a binding compares it with the INR_ABI_VERSION it was written against and
+ * refuses a mismatch (struct layouts -- inr_opt_state grew in 101 -- and entry points change between versions).
+ *   100  round 1      101  inr_opt_state + gmax/omb/hist_base fields, INR_PREC_FP16S, SIREN bf16 refused
+ *   102  inr_siren_forward_static */
+#define INR_ABI_VERSION 102
 int inr_version(void);
 
 /* Launch accounting: number of kernels this library has launched in this process (bench.py gpu_launches),
@@ -262,7 +267,7 @@ typedef struct {
   int32_t widths[INR_KAN_MAX_LAYERS + 1];   /* layers_hidden                             */
   int32_t grid_size;                        /* G (5)                                     */
   int32_t spline_order;                     /* K (3)                                     */
-  int32_t precision;                        /* INR_PREC_FP32 (bf16 mode: see DESIGN.md)  */
+  int32_t precision;                        /* INR_PREC_FP32 or INR_PREC_BF16 */
 } inr_kan_desc;
 
 int64_t inr_kan_num_params(const inr_kan_desc* d);

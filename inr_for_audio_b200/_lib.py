@@ -13,6 +13,7 @@ LIB_PATH = os.path.join(HERE, "libinr_b200.so")
 INR_OK, INR_E_BADARG, INR_E_UNSUPPORTED, INR_E_CUDA, INR_E_WORKSPACE = 0, -1, -2, -3, -4
 PREC_FP32, PREC_BF16, PREC_FP16, PREC_FP16S = 0, 1, 2, 3
 LOSS_MSE, LOSS_MAE = 0, 1
+ABI_VERSION = 102                          # INR_ABI_VERSION of include/inr_b200.h
 STATIC_SCRATCH_BYTES = 32 * 1024 * 1024   # INR_STATIC_SCRATCH_BYTES
 PRECISIONS = {"fp32": PREC_FP32, "bf16": PREC_BF16, "fp16": PREC_FP16, "fp16s": PREC_FP16S}
 
@@ -119,6 +120,10 @@ def lib():
             fn = getattr(l, name)
             fn.restype = res
             fn.argtypes = args
+        got = l.inr_version()
+        if got != ABI_VERSION:
+            raise InrLibraryError("libinr_b200.so reports ABI version %d, this binding was written against %d: rebuild "
+                                  "with `python -m inr_for_audio_b200.build`" % (got, ABI_VERSION))
         _lib = l
     return _lib
 

@@ -113,7 +113,7 @@ using namespace inr;
 extern "C" {
 
 const char* inr_last_error(void) { return g_err; }
-int inr_version(void) { return 100; }
+int inr_version(void) { return INR_ABI_VERSION; }
 
 int64_t inr_launch_count(void) { return g_launches.load(); }
 

@@ -81,7 +81,12 @@ __global__ void k_opt_init(inr_opt_state* st, float lr, float min_lr, int hist_c
 __device__ void opt_post(inr_opt_state* st, float loss_scale, float* loss_hist) {
   const float loss = (float)(st->loss_acc[0] * (double)loss_scale + st->loss_acc[1]);
   st->last_loss = loss;
-  if (loss_hist && st->hist_cap > 0) loss_hist[(st->step - st->hist_base) % st->hist_cap] = loss;
+  if (loss_hist && st->hist_cap > 0) {
+    // non-negative ring index even when a caller rewound `step` below hist_base (teacher-forced tests, resume)
+    int idx = (st->step - st->hist_base) % st->hist_cap;
+    if (idx < 0) idx += st->hist_cap;
+    loss_hist[idx] = loss;
+  }
   st->gmax_prev = st->gmax_acc;
   st->gmax_acc = 0.f;
   // python: current < best * (1 - threshold), evaluated in float64 on a float32-valued loss

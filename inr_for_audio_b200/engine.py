@@ -225,6 +225,20 @@ class SirenFitter:
         self._graph = None
         self.launches_per_step = None
 
+    def close(self):
+        """Drop the captured CUDA graph and wait for the device.  A sharded fitter's graph holds the NCCL allreduce it
+        captured: release every fitter (close() or del) BEFORE torch.distributed.destroy_process_group(), otherwise the
+        communicator tear-down can hang on the live graph.  The fitter stays usable: the next step() re-captures."""
+        self._graph = None
+        if torch.cuda.is_available():
+            torch.cuda.synchronize(self.device)
+
+    def __del__(self):
+        try:
+            self._graph = None
+        except Exception:
+            pass
+
     def set_precision(self, precision: str):
         """Continue the same fit (parameters, Adam moments, step count, plateau scheduler, loss history) in another
         arithmetic mode: 'fp16' (plain fp16 tcgen05 operands: fastest, fit floor ~31 dB on gt_bach), 'fp16s' (fp16 hi+lo
@@ -331,6 +345,11 @@ class SirenFitter:
         st = self.opt_state()
         for k, v in fields.items():
             setattr(st, k, v)
+        if st.hist_base > st.step:          # the loss ring is indexed by step - hist_base: never let it go negative
+            st.hist_base = st.step
+        # (float)(1.0 - beta) formed in float64 as torch passes them to its kernels; k_adam reads these, not beta itself
+        st.omb1 = 1.0 - float(st.beta1)
+        st.omb2 = 1.0 - float(st.beta2)
         t = st.step + 1
         st.step_size = float(st.lr) / (1.0 - float(st.beta1) ** t)
         st.bc2_sqrt = math.sqrt(1.0 - float(st.beta2) ** t)
@@ -489,6 +508,12 @@ class ClipBatchFitter:
             L.check(L.lib().inr_set_sm_limit(0))
         for s in self.streams:
             main.wait_stream(s)
+
+    def close(self):
+        """Drop the captured graph (and the per-clip fitters' graphs) and wait for the device; see SirenFitter.close."""
+        self._graph = None
+        for f in self.fitters:
+            f.close()
 
     def step(self, n_steps: int = 1):
         cur = torch.cuda.current_stream(self.device)

@@ -91,8 +91,8 @@ def train(experiment_path: str, tag: str, inst: str, duration: int, num_channels
     """run.py:30.  Extra keyword-only arguments: precision ('fp32' CUDA-core mode | 'fp16s' tcgen05 mode with fp16 hi+lo
     forward operands: fp32-grade forward, the parity-grade tensor-core mode | 'fp16' plain fp16 operands, fastest, fit
     floor ~31 dB | 'fp16+' = start in fp16 and continue in fp16s once the fp16 rounding noise shows in the fit error,
-    SirenFitter.step_auto | 'auto' (default) = 'fp16s' where the shape allows it -- hidden width 128/256/512, input width
-    <= hidden width, a SIREN -- else 'fp32'),
+    SirenFitter.step_auto | 'auto' (default) = 'fp16s' for the one family whose converged SNR has been compared with the
+    reference loop -- sine-only stacks of width 128/256 on raw 1-D/2-D coordinates -- else 'fp32'),
     data_dir (the reference hard-codes 'data/'), seed (torch.manual_seed before model construction), spectral (which
     windowed-transform loss `alpha` mixes in: 'stft' = auraloss STFTLoss as run.py:128,160 does, 'mdct' / 'mdct_mse' =
     the MDCT-domain loss of BASELINE.json config 3)."""
@@ -105,8 +105,12 @@ def train(experiment_path: str, tag: str, inst: str, duration: int, num_channels
     decimation = int(decimation)
     if precision == 'auto':
         in_w = 2 * int(num_freq) if num_freq is not None else (2 if method == 'mdct' else 1)
-        tc_ok = arch != 'kan' and int(num_hidden_features) in (128, 256, 512) and in_w <= int(num_hidden_features) and \
-            (int(num_sine) + int(num_snake) + int(num_tanh)) >= 1
+        # fp16s only where a converged fit has been compared with the reference loop (profiles/r02_c1_seeds.md: the
+        # all-layer fused kernel, csrc/siren_tc.cu fused_ok): a sine-only stack of width 128/256 on raw coordinates.
+        # Everything else -- run.py's default Snake stack, H = 512, encoded inputs, KAN -- keeps the fp32 parity mode
+        # until it has converged-SNR evidence of its own; ask for precision='fp16s' explicitly to get the fast path.
+        tc_ok = arch != 'kan' and int(num_hidden_features) in (128, 256) and in_w <= 2 and \
+            1 <= int(num_sine) <= 8 and int(num_snake) == 0 and int(num_tanh) == 0 and not first_linear
         precision = 'fp16s' if tc_ok else 'fp32'
     auto_precision = precision == 'fp16+'
     if auto_precision:

@@ -36,7 +36,8 @@ def test_library_exports_every_declared_symbol(built):
         assert hasattr(lib, n), "missing export %s" % n
     from inr_for_audio_b200 import _lib as L
     assert set(L.SIGNATURES) == names, (set(L.SIGNATURES) ^ names)
-    assert L.lib().inr_version() >= 100
+    assert L.lib().inr_version() == L.ABI_VERSION
+    assert ("#define INR_ABI_VERSION %d" % L.ABI_VERSION) in open(os.path.join(ROOT, "include", "inr_b200.h")).read()
 
 
 def test_opt_state_struct_matches_header(built):

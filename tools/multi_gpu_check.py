@@ -84,9 +84,11 @@ def main():
     # CUDA graphs that captured NCCL work must be gone before the communicator is torn down (a live graph made
     # destroy_process_group hang in round 2's first 2-GPU run); the timer is a backstop, the checks above are done
     import gc, threading
-    t = threading.Timer(30.0, lambda: os._exit(0))
+    t = threading.Timer(30.0, lambda: os._exit(3))      # a tear-down hang is a FAILURE of the check, not a pass
     t.daemon = True
     t.start()
+    for f in (full, sh, fk, sk, mine, allc):
+        f.close()
     del full, sh, fk, sk, mine, allc
     gc.collect()
     torch.cuda.synchronize()
