@@ -392,10 +392,15 @@ def measure(cx, name, prec, steps, warmup, detail):
     sampler = ClockSampler(cx.local)
     if cx.rank == 0:
         sampler.start()
-    ms = cx.timed_device(fit.step, steps)
+    # N > 1: a 20-step region is ~0.1 s at N = 8 -- time `regions` consecutive K-step regions (each bracketed as the contract
+    # says: barrier + synchronize on both sides, CUDA events, max over ranks) and report the MEDIAN region; N = 1: one region
+    regions = 5 if (cx.world > 1 and detail) else 1
+    ms_all = [cx.timed_device(fit.step, steps) for _ in range(regions)]
+    ms = float(np.median(ms_all))
     clocks = sampler.stop() if cx.rank == 0 else None
     rec = {"workload": wl["desc"], "precision": prec, "value": units * steps / (ms * 1e-3), "unit": UNIT,
-           "ms_per_step": ms / steps, "steps": steps, "clocks": clocks, "cuda_graph": bool(fit._graph is not None)}
+           "ms_per_step": ms / steps, "steps": steps, "clocks": clocks, "cuda_graph": bool(fit._graph is not None),
+           "timed_regions_ms": [round(x, 4) for x in ms_all]}
     rec["loss_first_last"] = job.first_last_loss(fit)
     lps = fit.launches_per_step
 
@@ -419,6 +424,7 @@ def measure(cx, name, prec, steps, warmup, detail):
     rec["launches_per_step"] = lps
     useful = job.flops_per_coord * units / (ms / steps * 1e-3) / 1e12 / max(cx.world, 1)     # per GPU, whole step
     rec["step_tflops_per_gpu"] = useful
+    rec["flops_per_coord"] = job.flops_per_coord
     rec["step_frac_of_peak"] = useful / pk["bf16_sus"]
     rec["step_frac_issued"] = useful * job.issued_factor() / pk["bf16_sus"]
     return rec, job, fit
@@ -461,11 +467,31 @@ def kernel_profile(cx, job, prec, steps):
         except Exception:
             traffic = None
     tc = prec in ("fp16", "fp16s", "bf16")
-    roofline = {"bound": "tensor", "achieved": achieved, "peak": pk["bf16_sus"], "unit": "TFLOP/s",
-                "frac": achieved / pk["bf16_sus"],
-                "issued_achieved": achieved * job.issued_factor(), "issued_frac": achieved * job.issued_factor() / pk["bf16_sus"],
+    # per-kernel table (event profiler, un-graphed pass): algorithmic flops of each tensor-core kernel = 2 * rows * H^2 per
+    # HxH contraction it performs (fwd, dX, dW: one third of the step's 6*L*H^2 each); dominant kernel first
+    per_kernel = []
+    H_, nh = wl.get("H", 0), (job.spec.total_hidden if job.kind != "kan" else 0)
+    third = 2.0 * nh * H_ * H_ * prof_units
+    alg = {"k_tc_layer_fwd": third, "k_tc_layer_bwd": third, "k_tc_dw": third, "k_tc_fused_fwd": third}
+    for tag in sorted(kern, key=lambda t: -kern[t]["ms_per_step"]):
+        row = {"kernel": tag, "launches_per_step": kern[tag]["launches_per_step"], "ms_per_step": kern[tag]["ms_per_step"],
+               "share_of_kernel_time": kern[tag]["ms_per_step"] / max(total_ms, 1e-9)}
+        if job.kind == "siren" and tag in alg and tc and kern[tag]["ms_per_step"] > 0:
+            tf = alg[tag] / (kern[tag]["ms_per_step"] * 1e-3) / 1e12
+            issued = 3.0 if (prec == "fp16s" and tag in ("k_tc_layer_fwd", "k_tc_fused_fwd")) else 1.0
+            row.update({"bound": "tensor", "algorithmic_flops_per_step": alg[tag], "achieved": tf, "unit": "TFLOP/s",
+                        "frac": tf / pk["bf16_sus"], "issued_frac": tf * issued / pk["bf16_sus"]})
+        per_kernel.append(row)
+    roofline = {"bound": "tensor", "achieved": None, "peak": pk["bf16_sus"], "unit": "TFLOP/s",
+                "frac": None,                   # filled by run_ours with the WHOLE timed step (graph replay, CUDA events)
+                "kernel": "whole step (all launches of one fit step)",
+                "dominant_kernel": per_kernel[0] if per_kernel else None, "per_kernel": per_kernel,
+                "gemm_kernels": {"kernel": "+".join(sorted(gemm_tags)), "achieved": achieved, "frac": achieved / pk["bf16_sus"],
+                                 "issued_frac": achieved * job.issued_factor() / pk["bf16_sus"],
+                                 "note": "algorithmic flops of the step / summed event times of these kernels in the un-graphed "
+                                         "profiling pass (not the timed region)"},
                 "traffic": traffic, "traffic_note": tnote,
-                "kernel": "+".join(sorted(gemm_tags)), "flops_per_launch": flops / max(gemm_launches, 1),
+                "flops_per_launch": flops / max(gemm_launches, 1),
                 "avg_launch_ms": gemm_ms / max(gemm_launches, 1), "gemm_share_of_step": gemm_ms / max(total_ms, 1e-9),
                 "peak_source": pk["src"] + ", sustained dense bf16/fp16 kind::f16 rate (kernels timed inside a long step)",
                 "mma_kind": ("tcgen05 kind::f16, %s operands%s" % ("bf16" if prec == "bf16" else "fp16",
@@ -512,6 +538,52 @@ def snr_reference():
         return json.load(open(os.path.join(ROOT, "profiles", "r02_snr_reference.json")))
     except Exception:
         return {}
+
+
+def sharded_check(cx, prec, rows=65536):
+    """N > 1 correctness in the driver's own SCALE line: loss and flat gradient of one step on a 64 K-row slice of the C2
+    workload, coordinate-sharded over all ranks with the one allreduce, against every rank computing the slice alone."""
+    import inr_for_audio_b200 as P
+    from inr_for_audio_b200.engine import shard_range
+    torch = cx.torch
+    try:
+        wl = WORKLOADS["c2"]
+        gt = torch.from_numpy(P.utils.synth_waveform(rows, seed=7)).to(cx.dev)
+        torch.manual_seed(0)
+        model = P.Siren(1, wl["H"], wl["L"], 1, True)
+        flat = model.flat_parameters()
+        full = P.SirenFitter(model.spec, flat, gt, precision=prec, use_graph=False)
+        l1, g1, _ = full.loss_and_grads()
+        i0, n, _ = shard_range(rows, cx.rank, cx.world)
+        sh = P.SirenFitter(model.spec, flat, gt[i0:i0 + n], i0=i0, T_total=rows, precision=prec, process_group=cx.pg,
+                           use_graph=False)
+        l2, g2, _ = sh.loss_and_grads()
+        gerr = float((g1 - g2).norm() / g1.norm())
+        lerr = abs(l1 - l2) / abs(l1)
+        worst = cx.max_over_ranks(max(gerr, lerr))
+        full.close(); sh.close()
+        return {"rows": rows, "loss_single": l1, "loss_sharded": l2, "loss_rel_err": lerr, "grad_rel_err": gerr,
+                "worst_over_ranks": worst, "ok": bool(worst <= 5e-3), "tolerance": 5e-3, "precision": prec,
+                "what": "one step, SIREN 5x512, %d rows: sharded x%d + allreduce vs each rank alone" % (rows, cx.world)}
+    except Exception as ex:  # noqa: BLE001
+        return {"error": repr(ex)[:300], "ok": False}
+
+
+def c1_converged_snr(j2, f2, total=20000):
+    """BASELINE.json configs[0] run to run.py:426's default 20 000 steps in the timed mode, against the band of the
+    reference loop's own fits (8 seeds, torch eager fp32 on a B200: profiles/r02_snr_reference.json)."""
+    f2.step(total - f2.steps_done)
+    db = j2.snr_db(f2)
+    band = (snr_reference().get("c1") or {}).get("snr_db", {}).get(str(total))
+    f2.step(1)
+    out = {"snr_db": db, "steps": total, "final_lr": float(f2.last_lr()),
+           "dz_saturated": f2.dz_saturated()}      # fp16 gradient elements clipped at +-65504 in the step after the mark
+    if band:
+        sd = float(np.std(band, ddof=1))
+        lo, hi = min(band) - sd, max(band) + sd
+        out.update({"reference_fits_db": band, "reference_median_db": float(np.median(band)), "accept_lo": lo, "accept_hi": hi,
+                    "snr_ok": bool(lo <= db <= hi)})
+    return out
 
 
 def default_precision(wl):
@@ -565,6 +637,10 @@ def run_ours(args):
                     ref = snr_reference().get(wname)
                     if ref:
                         r["snr_reference"] = ref
+                    if wname == "c1" and args.snr_steps and cx.world == 1:
+                        r["converged"] = c1_converged_snr(j2, f2)
+                        r["snr_db"]["20000"] = r["converged"]["snr_db"]
+                        r["snr_ok"] = r["converged"].get("snr_ok")
                 else:
                     r["snr_db_median_over_clips"] = {str(f2.steps_done): j2.snr_db(f2)}
                 del f2
@@ -575,7 +651,16 @@ def run_ours(args):
                     r["roofline_frac_gemm_kernels"] = rr["frac"]
                 del j2
                 torch.cuda.empty_cache()
+                if wname == "c4":
+                    r["precision_note"] = ("bf16 tensor-core mode: per-step loss 2e-3 / gradient 3e-2 vs the oracle, OUTSIDE the "
+                                           "north star's 1e-3 tolerance; the parity-grade KAN figure is workloads.c4_fp32")
                 extras["c5" if wname.startswith("c5") else wname] = r
+                if wname == "c4":
+                    r32, j3, f3 = measure(cx, wname, "fp32", 5, 3, False)
+                    r32["precision_note"] = "fp32 CUDA-core mode: the KAN mode that meets the 1e-3 per-step tolerance"
+                    del j3, f3
+                    torch.cuda.empty_cache()
+                    extras["c4_fp32"] = r32
             except Exception as ex:  # noqa: BLE001 -- an extra workload must not take the headline down
                 extras[wname] = {"error": repr(ex)[:300]}
 
@@ -588,6 +673,13 @@ def run_ours(args):
         cpu = {"value": rate, "unit": UNIT, "cores": threads, "kind": "port",
                "sample": "oracle (torch-CPU fp32 restatement of run.py's loop) on the first %d of %d coordinates%s, "
                          "3 timed steps after 1 warm-up, %.2f s/step" % (rows, wl["T"], " of one clip" if wl["kind"] == "clips" else "", per_s)}
+
+    # the roofline of the line = the whole timed step: algorithmic flops of the step / its measured time, per GPU
+    roofline["achieved"] = head["step_tflops_per_gpu"]
+    roofline["frac"] = head["step_frac_of_peak"]
+    roofline["issued_frac"] = head["step_frac_issued"]
+    roofline["flops_per_coord"] = head["flops_per_coord"]
+    sharded = sharded_check(cx, prec) if (cx.world > 1 and wl["kind"] == "siren") else None
 
     if cx.rank == 0:
         par = ("clip-parallel x%d (no collective)" % cx.world) if wl["kind"] == "clips" else ("coord-shard x%d" % cx.world)
@@ -602,7 +694,8 @@ def run_ours(args):
                 "clocks": head["clocks"], "e2e": head["e2e"], "value_recheck": head["value_recheck"],
                 "gpu_launches": int(lps) * args.steps, "launches_per_step": int(lps),
                 "roofline": roofline, "step_frac_of_peak": head["step_frac_of_peak"], "step_frac_issued": head["step_frac_issued"],
-                "hbm_stages": stages, "snr": snr, "fast_mode": fast, "workloads": extras,
+                "hbm_stages": stages, "snr": snr, "fast_mode": fast, "workloads": extras, "sharded_check": sharded,
+                "timed_regions_ms": head["timed_regions_ms"],
                 "cpu_baseline": cpu, "kernels": kern, "loss_first_last": head["loss_first_last"]}
         print(json.dumps(line), flush=True)
     if cx.world > 1:

@@ -191,13 +191,19 @@ __global__ void __launch_bounds__(256) k_tc_first(const float* __restrict__ W, c
 //   phase A   warp w owns feature groups w, w+16, ..: partial dots of its 32 rows from the S slab (kept in registers)
 //   barrier   every warp sums the 16 partials (fixed order), forms g = dloss/dout redundantly; warp 0 writes out / loss
 //   phase C   dZ_L = g w omega C_L straight to global, acc_w[f] += g S[f] in registers (one butterfly at the very end)
-template <int H>
+// LO (operand split): the lo image of S_L rides the same ring as a third slab per stage.  (Round 2 fetched it with plain
+// loads at the top of each unit and consumed it at once: ~1 us of exposed latency per 5.5 us unit at H = 512, the kernel
+// ran at 0.53 of the HBM peak.)  At H = 512 three 32 KB slabs leave room for 2 stages = one unit in flight while one is
+// consumed; 96 KB in flight per SM is twice what the bandwidth-latency product asks for (6.5 TB/s x ~1 us / 148 SMs).
+template <int H, bool LO = false>
 struct Last2Cfg {
   static constexpr int G = H / 8;                  // feature groups
   static constexpr int KPW = G / 16;               // groups per warp
   static constexpr int SLAB = G * 32 * 16;         // bytes of a 32-row slab of one image
-  static constexpr int NSTAGE = (H >= 512) ? 3 : 4;
-  static constexpr int OFF_W = NSTAGE * 2 * SLAB;
+  static constexpr int NSLAB = LO ? 3 : 2;         // [S | C | S_lo]
+  static constexpr int NSTAGE = (H >= 512) ? (LO ? 2 : 3) : 4;
+  static constexpr int STAGE_BYTES = NSLAB * SLAB;
+  static constexpr int OFF_W = NSTAGE * STAGE_BYTES;
   static constexpr int OFF_DOT = OFF_W + H * 4;
   static constexpr int SMEM_BYTES = OFF_DOT + 16 * 32 * 4;
   static_assert(H == 128 || H == 256 || H == 512, "hidden width");
@@ -211,7 +217,7 @@ __device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commi
 template <int N>
 __device__ __forceinline__ void cp_async_wait() { asm volatile("cp.async.wait_group %0;" ::"n"(N) : "memory"); }
 
-template <int H, bool SNAKE>
+template <int H, bool SNAKE, bool LO>
 __global__ void __launch_bounds__(512, 1) k_tc_last2(const op16* __restrict__ S, op16* __restrict__ CdZ,
                                                      const float* __restrict__ w, const float* __restrict__ bptr,
                                                      const float* __restrict__ target, const float* __restrict__ extra_g,
@@ -222,8 +228,8 @@ __global__ void __launch_bounds__(512, 1) k_tc_last2(const op16* __restrict__ S,
                                                      const op16* __restrict__ Eimg, float* __restrict__ ga,
                                                      const float* __restrict__ gsc, unsigned* __restrict__ gmax_acc,
                                                      const op16* __restrict__ Slo) {
-  // Slo != NULL (operand split): S_L = S + Slo, the head's dot product takes both (straight from global memory)
-  using Cfg = Last2Cfg<H>;
+  // LO (operand split, Slo != NULL): S_L = S + Slo, the head's dot product takes both (third slab of the ring)
+  using Cfg = Last2Cfg<H, LO>;
   constexpr int KPW = Cfg::KPW;
   extern __shared__ __align__(128) uint8_t smem[];
   const uint32_t smem_base = smem_u32(smem);
@@ -241,13 +247,14 @@ __global__ void __launch_bounds__(512, 1) k_tc_last2(const op16* __restrict__ S,
     if (unit < num_units) {
       const int tile = unit >> 2, rb = unit & 3;
       const size_t tile_off = (size_t)tile * (TILE_ROWS * (size_t)H);
-      const uint32_t dstS = smem_base + stage * (2 * Cfg::SLAB);
+      const uint32_t dstS = smem_base + stage * Cfg::STAGE_BYTES;
 #pragma unroll
       for (int c = tid; c < Cfg::G * 32; c += 512) {
         const int kg = c >> 5, r = c & 31;
         const size_t off = tile_off + ((size_t)kg * TILE_ROWS + rb * 32 + r) * 8;
         cp_async16(dstS + c * 16, S + off);
         if (training) cp_async16(dstS + Cfg::SLAB + c * 16, CdZ + off);
+        if (LO) cp_async16(dstS + 2 * Cfg::SLAB + c * 16, Slo + off);
       }
     }
     cp_async_commit();
@@ -276,17 +283,10 @@ __global__ void __launch_bounds__(512, 1) k_tc_last2(const op16* __restrict__ S,
       if (target) tgt = target[row];
       if (extra_g) eg = extra_g[row];
     }
-    uint4 lov[KPW];
-    if (Slo) {
-      const size_t tile_off0 = (size_t)tile * (TILE_ROWS * (size_t)H);
-#pragma unroll
-      for (int i = 0; i < KPW; ++i)
-        lov[i] = __ldg(reinterpret_cast<const uint4*>(Slo + tile_off0 + ((size_t)(warp + 16 * i) * TILE_ROWS + r) * 8));
-    }
     cp_async_wait<Cfg::NSTAGE - 2>();
     __syncthreads();   // this unit's slabs have landed for every thread; the stage refilled below is no longer read
     issue(unit + (Cfg::NSTAGE - 1) * gridDim.x, (it + Cfg::NSTAGE - 1) % Cfg::NSTAGE);
-    const uint8_t* sS = smem + stage * (2 * Cfg::SLAB);
+    const uint8_t* sS = smem + stage * Cfg::STAGE_BYTES;
     const uint8_t* sC = sS + Cfg::SLAB;
     uint4 sv[KPW];
     float pd = 0.f;
@@ -301,8 +301,9 @@ __global__ void __launch_bounds__(512, 1) k_tc_last2(const op16* __restrict__ S,
         pd = __fmaf_rn(f.x, s_w[kg * 8 + 2 * h], pd);
         pd = __fmaf_rn(f.y, s_w[kg * 8 + 2 * h + 1], pd);
       }
-      if (Slo) {
-        const uint32_t lw[4] = {lov[i].x, lov[i].y, lov[i].z, lov[i].w};
+      if (LO) {
+        const uint4 lo4 = *reinterpret_cast<const uint4*>(sS + 2 * Cfg::SLAB + (kg * 32 + lane) * 16);
+        const uint32_t lw[4] = {lo4.x, lo4.y, lo4.z, lo4.w};
 #pragma unroll
         for (int h = 0; h < 4; ++h) {
           const float2 f = unpack_op2(lw[h]);
@@ -820,17 +821,30 @@ static int launch_last2(const op16* SL, op16* CL, const float* w, const float* b
                         int loss_kind, float grad_scale, float* gw, float* gb, double* loss_acc, float* out, int training,
                         const op16* EL, float* ga, const float* gsc, unsigned* gmax_acc, const op16* SLlo,
                         cudaStream_t st) {
-  using Cfg = Last2Cfg<H>;
-  static bool attr_done = false;
-  if (!attr_done) {
-    INR_CUDA_CHECK(cudaFuncSetAttribute(k_tc_last2<H, SNAKE>, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg::SMEM_BYTES));
-    attr_done = true;
-  }
   const int blocks = std::max(1, std::min(tiles * 4, num_sms()));
-  { LaunchScope ls("k_tc_last", st);
-    k_tc_last2<H, SNAKE><<<blocks, 512, Cfg::SMEM_BYTES, st>>>(SL, CL, w, b, target, extra_g, rows, tiles, dfac, omega_h,
-                                                               outermost_linear, loss_kind, grad_scale, gw, gb, loss_acc,
-                                                               out, training, EL, ga, gsc, gmax_acc, SLlo); }
+  if (SLlo) {
+    using Cfg = Last2Cfg<H, true>;
+    static bool attr_done = false;
+    if (!attr_done) {
+      INR_CUDA_CHECK(cudaFuncSetAttribute(k_tc_last2<H, SNAKE, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg::SMEM_BYTES));
+      attr_done = true;
+    }
+    LaunchScope ls("k_tc_last", st);
+    k_tc_last2<H, SNAKE, true><<<blocks, 512, Cfg::SMEM_BYTES, st>>>(SL, CL, w, b, target, extra_g, rows, tiles, dfac, omega_h,
+                                                                     outermost_linear, loss_kind, grad_scale, gw, gb, loss_acc,
+                                                                     out, training, EL, ga, gsc, gmax_acc, SLlo);
+  } else {
+    using Cfg = Last2Cfg<H, false>;
+    static bool attr_done = false;
+    if (!attr_done) {
+      INR_CUDA_CHECK(cudaFuncSetAttribute(k_tc_last2<H, SNAKE, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg::SMEM_BYTES));
+      attr_done = true;
+    }
+    LaunchScope ls("k_tc_last", st);
+    k_tc_last2<H, SNAKE, false><<<blocks, 512, Cfg::SMEM_BYTES, st>>>(SL, CL, w, b, target, extra_g, rows, tiles, dfac, omega_h,
+                                                                      outermost_linear, loss_kind, grad_scale, gw, gb, loss_acc,
+                                                                      out, training, EL, ga, gsc, gmax_acc, nullptr);
+  }
   INR_LAUNCH_CHECK();
   return INR_OK;
 }

@@ -132,8 +132,23 @@ class Workspace:
         fn = L.lib().inr_kan_workspace_bytes if isinstance(desc, L.KanDesc) else L.lib().inr_siren_workspace_bytes
         need = L.check(fn(C.byref(desc), n_rows, int(training)))
         if self.buf is None or self.buf.numel() < need:
-            self.buf = torch.empty(max(int(need), 256), dtype=torch.uint8, device=self.device)
+            # zero-filled once, so that dz_saturated() below never reads bytes no kernel wrote
+            self.buf = torch.zeros(max(int(need), 256), dtype=torch.uint8, device=self.device)
         return self.buf
+
+    def count_fp16_saturated(self, chunk_bytes: int = 1 << 28) -> int:
+        """Number of 16-bit words in the buffer that are +-65504, the value cvt.rn.satfinite clips an fp16 conversion to.
+        In the tcgen05 modes the buffer holds fp16 images of sin/cos values (|x| <= 1), packed weights and the loss-scaled
+        dZ_l, so after a training step any hit is a CLIPPED gradient element (csrc/tc_common.cuh pack_op2): the loss scale
+        of csrc/siren_tc.cu gscale_compute was too large for that layer.  Diagnostic; synchronises."""
+        if self.buf is None:
+            return 0
+        n = self.buf.numel() // 2 * 2
+        total = 0
+        for o in range(0, n, chunk_bytes):
+            v = self.buf[o:min(o + chunk_bytes, n)].view(torch.int16)
+            total += int(((v & 0x7FFF) == 0x7BFF).sum())
+        return total
 
 
 def siren_forward(desc: L.SirenDesc, params: torch.Tensor, coords: Optional[torch.Tensor], n: int, ws: Workspace,
@@ -224,6 +239,11 @@ class SirenFitter:
             self._allreduce()                         # communicator set-up outside any capture (all-zero buffers)
         self._graph = None
         self.launches_per_step = None
+
+    def dz_saturated(self) -> int:
+        """fp16 gradient-image elements the LAST step clipped at +-65504 (0 = the loss scale had head-room everywhere);
+        meaningful in the 'fp16' / 'fp16s' modes right after step() or loss_and_grads()."""
+        return self.ws.count_fp16_saturated()
 
     def close(self):
         """Drop the captured CUDA graph and wait for the device.  A sharded fitter's graph holds the NCCL allreduce it

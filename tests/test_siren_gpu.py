@@ -362,3 +362,10 @@ def test_loss_scale_adapts_to_the_target_scale(pkg, prec, gain):
         prec, gain, st.gmax_prev, abs(loss - float(loss_o)) / float(loss_o), gerr))
     assert abs(loss - float(loss_o)) <= 1e-3 * float(loss_o)
     assert gerr <= 5e-3
+    # the saturation detector (SirenFitter.dz_saturated: +-65504 words in the fp16 images): clean once the scale has adapted,
+    # and it does see the clipped first step of the 1000x target
+    assert f.dz_saturated() == 0
+    if gain > 1:
+        f1 = pkg.SirenFitter(spec, flat, gt.to(dev()), precision=prec, use_graph=False, lr=1e-6)
+        f1.step(1)
+        assert f1.dz_saturated() > 0
