@@ -23,9 +23,12 @@ using namespace tc;
 
 // ------------------------------------------------------------------------------------------------ loss scale
 // fp16 dZ images need a loss scale: g = d loss / d out is O(1/T).  gsc = {gs, 1/gs} with gs the power of two that puts
-// max |g| of the PREVIOUS step (opt->gmax_prev, measured by the last-layer kernels) at 2^10, so |dZ_L| = |g w omega C|
-// stays around 10^2 with two decades of head-room to 65504 (conversions saturate) and eight decades above the fp16
-// normal minimum.  Without history (first step, or no optimiser state: the autograd path) the estimate is
+// max |g| of the PREVIOUS step (opt->gmax_prev, measured by the last-layer kernels) at 2^6.  Round 2 aimed at 2^10, sized
+// for the INITIAL weights (|w_head| omega ~ 0.15): once the head weights have trained to O(1), |dZ_L| = |g w omega C| of
+// the largest-|g| rows passed 65504 and cvt.rn.satfinite clipped them silently -- SirenFitter.dz_saturated() counted
+// 1e4..1e5 clipped elements per step from step ~2000 on in the C1 and 5x512 fits (profiles/r03_notes.md).  2^6 leaves a
+// factor 1000 for |w| omega and the per-layer backward gains; typical dZ elements are then ~0.1..1, four decades above
+// the fp16 normal minimum (6e-5; subnormals degrade gracefully below it).  Without history (first step, or no optimiser state: the autograd path) the estimate is
 // 4 * grad_scale (|2 diff| <= 4 for peak-normalised audio) plus max |extra_g|.  Consumers of dZ (dW, column sums)
 // multiply by 1/gs: exact, it is a power of two.
 __device__ __forceinline__ void gscale_compute(const inr_opt_state* opt, float extra_max, float grad_scale, int has_target,
@@ -34,7 +37,7 @@ __device__ __forceinline__ void gscale_compute(const inr_opt_state* opt, float e
   if (!(est > 0.f)) est = (has_target ? 4.f * grad_scale : 0.f) + extra_max;
   est = fmaxf(est, extra_max);
   int e = 0;
-  if (est > 0.f && est < 3e38f) e = 10 - (int)ceilf(log2f(est));
+  if (est > 0.f && est < 3e38f) e = 6 - (int)ceilf(log2f(est));
   e = max(-100, min(100, e));
   gsc[0] = exp2f((float)e);
   gsc[1] = exp2f((float)-e);
