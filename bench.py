@@ -458,7 +458,9 @@ def kernel_profile(cx, job, prec, steps):
     flops = job.flops_per_coord * prof_units              # algorithmic dense-contraction flops of the profiled rows
     achieved = flops / (gemm_ms * 1e-3) / 1e12 if gemm_ms > 0 else 0.0
     traffic, tnote = None, None
-    tfile = os.path.join(ROOT, "profiles", "r02_traffic_%s_%s.json" % (cx.args.workload, prec))
+    tfile = os.path.join(ROOT, "profiles", "r03_traffic_%s_%s.json" % (cx.args.workload, prec))
+    if not os.path.exists(tfile):
+        tfile = os.path.join(ROOT, "profiles", "r02_traffic_%s_%s.json" % (cx.args.workload, prec))
     if os.path.exists(tfile) and cx.world == 1:
         try:
             tj = json.load(open(tfile))
